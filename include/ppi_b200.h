@@ -1,0 +1,212 @@
+/*
+ * ppi_b200.h -- C ABI of the B200-native posterior-policy-iteration (PPI) update path.
+ *
+ * The reference (JoeMWatson/monte-carlo-posterior-policy-iteration) is pure Python and has no
+ * FFI; its boundary is three duck-typed Python protocols (sampler / policy / optimizer).  This
+ * header declares what a ctypes binding under those protocols calls.  Every entry point cites the
+ * reference interface (file:line relative to the reference root) it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - matrices are dense row-major, fp32, unless typed otherwise;
+ *   - `stream` is a cudaStream_t passed as void*; all calls are asynchronous on it;
+ *   - the return value is 0 on success, a cudaError_t (>0) for CUDA failures or a negative
+ *     PPI_ERR_* code; ppi_last_error() returns a thread-local message;
+ *   - the library owns no device memory: workspaces are passed in, sizes come from the matching
+ *     *_workspace_bytes query;
+ *   - numerical failure (non positive-definite matrix, empty bracket) is reported through device
+ *     status words, never through the return value.
+ *   - There is NO CPU implementation behind any of these functions.
+ */
+#ifndef PPI_B200_H
+#define PPI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PPI_B200_VERSION 100
+
+#define PPI_ERR_INVALID (-1)     /* bad argument                                    */
+#define PPI_ERR_UNSUPPORTED (-2) /* shape outside what the kernels cover            */
+#define PPI_ERR_WORKSPACE (-3)   /* workspace too small                             */
+#define PPI_ERR_DRIVER (-4)      /* cuTensorMapEncodeTiled unavailable / failed     */
+
+int ppi_version(void);
+const char* ppi_last_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * a3  base normals: np.random.randn(n, d)                         ppi/samplers.py:18-20
+ * Philox4x32-10 + Box-Muller.  Element (r, c) of the (rows, cols) output is a pure function of
+ * (seed, draw_id, row_offset + r, c): K-sharded ranks reproduce the 1-GPU matrix bit for bit.
+ * ---------------------------------------------------------------------------------------- */
+int ppi_philox_normal(float* out, int64_t rows, int64_t cols, uint64_t seed, uint64_t draw_id,
+                      uint64_t row_offset, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * a22 kernel Gram matrix + Cholesky, one thread block, fp64 inside   ppi/policies.py:923-932,
+ * 935-974,1026-1037,1087-1091 (Gram) and :312,692-694 (np.linalg.cholesky).
+ * kind: 0 squared-exponential, 1 Matern12, 2 Matern32, 3 Matern52, 4 periodic, 5 white noise.
+ * t1 (n1), t2 (n2) are fp64 time stamps.  gram64/gram32 are (n1, n2).  If chol64/chol32 are
+ * non-NULL (needs n1 == n2 <= 256) the lower Cholesky factor is written too; *status = 0 when
+ * positive definite, else 1 + index of the failing pivot.
+ * ---------------------------------------------------------------------------------------- */
+enum { PPI_KERNEL_SE = 0, PPI_KERNEL_MATERN12 = 1, PPI_KERNEL_MATERN32 = 2,
+       PPI_KERNEL_MATERN52 = 3, PPI_KERNEL_PERIODIC = 4, PPI_KERNEL_WHITE = 5 };
+int ppi_kernel_gram_chol(const double* t1, int n1, const double* t2, int n2, int kind, double sigma,
+                         double lengthscale, double period, double* gram64, float* gram32,
+                         double* chol64, float* chol32, int* status, void* stream);
+
+/* np.linalg.cholesky of a small fp64 matrix (n <= 256), one thread block; a may alias l64.
+ * ppi/policies.py:312,321,481,819                                                          */
+int ppi_cholesky_small(const double* a, int n, double* l64, float* l32, int* status, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Sampling.  z == NULL selects on-device Philox normals (seed, draw_id, row_offset as above,
+ * the (K, rows*cols) base-normal matrix of ppi/policies.py:361-365); otherwise z holds injected
+ * standard normals with the same layout.  lower/upper (per output channel) may both be NULL
+ * (no Limiter, ppi/policies.py:65-75,284-285).
+ * ---------------------------------------------------------------------------------------- */
+
+/* a4+a5+a23  BaseKernel.__call__                                   ppi/policies.py:735-745
+ * x[b] = mean_fn + mean + l_in z[b] l_out^T, clipped.  z,x: (K,H,d); l_in (H,H); l_out (d,d).
+ * l_out_is_diag != 0 promises l_out is diagonal (design_moments, ppi/policies.py:40-50).    */
+int ppi_sample_matnorm(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
+                       int64_t K, int H, int d, const float* mean_fn, const float* mean,
+                       const float* l_in, const float* l_out, int l_out_is_diag,
+                       const float* lower, const float* upper, float* x, void* stream);
+
+/* a6  BaseFeatures.__call__                                        ppi/policies.py:404-421
+ * w[b] = mean + l_in z[b] l_out^T  (K,F,d);  y[b] = [mean_fn + feat w[b], dfeat w[b]] clipped,
+ * (K,T,d) or (K,T,2d) when dfeat != NULL.  feat, dfeat: (T,F).  lower/upper have dy entries. */
+int ppi_sample_features(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
+                        int64_t K, int F, int d, int T, const float* mean_fn, const float* mean,
+                        const float* l_in, const float* l_out, const float* feat,
+                        const float* dfeat, const float* lower, const float* upper, float* w,
+                        float* y, void* stream);
+
+/* a8  WhiteNoiseIid.__call__                                       ppi/policies.py:1166-1174 */
+int ppi_sample_iid(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset, int64_t K,
+                   int H, int d, const float* mean_fn, const float* mean, const float* std,
+                   const float* lower, const float* upper, float* x, void* stream);
+
+/* a7  GaussianPolicy.__call__ in Cholesky form  x = mu + z L^T      ppi/policies.py:247-249,
+ * ppi/samplers.py:38-39.  L (D,D) lower triangular.  D <= 128 runs an fp32 SIMT kernel; larger
+ * D runs the tcgen05 split-TF32 GEMM and needs the workspace.                               */
+size_t ppi_sample_gaussian_workspace_bytes(int64_t K, int64_t D);
+int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
+                        int64_t K, int64_t D, const float* mu, const float* L, float* x,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * a9  cost evaluation                                     optimization/functions.py:21-104
+ * fn: 0 Himmelblau, 1 Rosenbrock, 2 Styblinski, 3 Rastrigin, 4 NoisySphere (aux = A (D,D),
+ * noise = (K,) standard normals or NULL).  x (K,D) -> c (K,).
+ * ---------------------------------------------------------------------------------------- */
+enum { PPI_FN_HIMMELBLAU = 0, PPI_FN_ROSENBROCK = 1, PPI_FN_STYBLINSKI = 2, PPI_FN_RASTRIGIN = 3,
+       PPI_FN_NOISY_SPHERE = 4 };
+int ppi_cost_function(int fn, const float* x, int64_t K, int64_t D, const float* aux,
+                      const float* noise, float* c, void* stream);
+
+/* synthetic trajectory return = the Test env tracking cost     policy_search/envs.py:65-72,83-87
+ * c[b] = sum_{t, j<dt} (x[b,t,j] - target[t,j])^2 / (T*dt);  x (K,T,dy), dy >= dt.          */
+int ppi_cost_tracking(const float* x, int64_t K, int T, int dy, const float* target, int dt,
+                      float* c, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Weights.  All results of one update that the host reads come back in one struct.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct ppi_weight_stats {
+  double alpha;          /* inverse temperature used                                         */
+  double lse;            /* log sum_k exp(log_w_k)                                           */
+  double ess;            /* exp(-LSE(2 log nw))                 ppi/policies.py:87           */
+  double weighted_cost;  /* sum_k nw_k c_k on the normalised costs                           */
+  double weight_entropy; /* sum_k nw_k log nw_k                 ppi/algorithms.py:123,622    */
+  double cost_min, cost_max, cost_mean, cost_std; /* over non-NaN costs (:89-90, :184)       */
+  double objective;      /* value of the solved 1-D objective at alpha (dual / bound / |ess-N|) */
+  int64_t n_valid;       /* non-NaN costs; == K when all are NaN (all-NaN keeps everything)  */
+  int64_t argmax;        /* first index of the largest weight   ppi/policies.py:811          */
+  int32_t all_nan;       /* 1 when every cost was NaN           ppi/algorithms.py:62-64      */
+  int32_t iterations;    /* objective evaluations spent by the solver                        */
+  int32_t status;        /* 0 ok, 1 bracket hit a bound, 2 max iterations                    */
+  int32_t pad;
+} ppi_weight_stats;
+
+/* a2+a10..a14  NaN mask, normalisation, temperature solve, normalised weights.
+ * ppi/algorithms.py:57-68 (filter), :184,:510,:541,:597 (normalise), :472 (MPPI shift),
+ * :183-215 (REPS dual), :539-567 (LBPS), :596-615 (ESSPS), :509-511 (AIS).
+ * mode / hyper:
+ *   PPI_TEMP_FIXED_NORMALISED  hyper = alpha     log_w = -alpha (c-min)/(max-min)      (Ais)
+ *   PPI_TEMP_FIXED_SHIFTED     hyper = alpha     log_w = -alpha (c-min)                (Mppi)
+ *   PPI_TEMP_REPS_KL           hyper = epsilon   KL(nw || uniform) = epsilon, alpha in [1e-5,5e2]
+ *   PPI_TEMP_ESS_TARGET        hyper = n_elites  ESS(alpha) = n_elites
+ *   PPI_TEMP_LOWER_BOUND       hyper = delta     argmin_alpha E_nw[c] + sqrt((1-delta)/delta)/sqrt(ESS)
+ * NaN costs get weight 0 (the reference compacts them away); if all are NaN every cost is 0.
+ * nw (K) receives normalised weights, log_w (K, may be NULL) the unnormalised log-weights with
+ * -inf at NaN costs.  workspace: ppi_solve_temperature_workspace_bytes(K).                  */
+enum { PPI_TEMP_FIXED_NORMALISED = 0, PPI_TEMP_FIXED_SHIFTED = 1, PPI_TEMP_REPS_KL = 2,
+       PPI_TEMP_ESS_TARGET = 3, PPI_TEMP_LOWER_BOUND = 4 };
+size_t ppi_solve_temperature_workspace_bytes(int64_t K);
+int ppi_solve_temperature(const float* costs, int64_t K, int mode, double hyper, float* nw,
+                          float* log_w, ppi_weight_stats* stats, void* workspace,
+                          size_t workspace_bytes, void* stream);
+
+/* user-supplied log-weights -> normalised weights (m_projection head)  ppi/policies.py:84-87,
+ * argmax ppi/policies.py:811,1153.  costs may be NULL (then the cost_* fields are 0).       */
+int ppi_normalise_log_weights(const float* log_w, int64_t K, float* nw, ppi_weight_stats* stats,
+                              void* workspace, size_t workspace_bytes, void* stream);
+
+/* a15  CEM / iCEM elites                                         ppi/algorithms.py:117-120,149-154
+ * sorted_idx (K) = argsort by (cost, index), NaN last; nw = 1/k on the first k, 0 elsewhere
+ * (log_w in {0,-1e12} => exactly 1/k).  workspace: ppi_cem_workspace_bytes(K).              */
+size_t ppi_cem_workspace_bytes(int64_t K);
+int ppi_cem_weights(const float* costs, int64_t K, int64_t n_elites, int64_t* sorted_idx,
+                    float* nw, ppi_weight_stats* stats, void* workspace, size_t workspace_bytes,
+                    void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Moment matching.
+ * ---------------------------------------------------------------------------------------- */
+
+/* a16/a18/a21 first moment and element-wise second moment, HBM-bound float4 reduction.
+ * s1[i] += sum_k nw_k (x_ki - shift1_i);   s2[i] += sum_k nw_k (x_ki - shift2_i)^2  (s2 may be
+ * NULL; shifts may be NULL = 0).  x is (K,D) with D = H*d for trajectories.  fp64 accumulators
+ * must be zeroed by the caller (K-sharded ranks all-reduce them).
+ * ppi/policies.py:88 (mu), :122 (matrix-normal mean), :1158-1162 (iid mean / std).          */
+int ppi_wmoments_diag(const float* x, const float* nw, int64_t K, int64_t D, const float* shift1,
+                      const float* shift2, double* s1, double* s2, void* stream);
+
+/* a18  matrix-normal input covariance                               ppi/policies.py:129-132
+ * acc[i,l] += sum_b nw_b sum_j (x_bij - shift_ij)(x_blj - shift_lj) * inv_cov_out_j
+ * (caller divides by d).  x (K,H,d); shift (H,d); inv_cov_out (d) or NULL (= 1).  H <= 128.
+ * With d = 1 this is the small-D dense covariance of ppi/policies.py:91.                   */
+int ppi_wmoments_matnorm(const float* x, const float* nw, int64_t K, int H, int d,
+                         const float* shift, const float* inv_cov_out, double* acc, void* stream);
+
+/* a16  dense weighted covariance  sum_k nw_k (x_k - shift)(x_k - shift)^T   ppi/policies.py:89-92
+ * on tcgen05 tensor cores (split-TF32, 3 MMAs per tile step, chunked fp32 promotion), operands
+ * staged K-major by a transposing pre-pass and fed by TMA.  cov (D,D) receives the symmetrised
+ * result (+= when accumulate != 0).  Any D >= 1; D < 64 is cheaper through ppi_wmoments_matnorm.*/
+size_t ppi_wmoments_dense_workspace_bytes(int64_t K, int64_t D);
+int ppi_wmoments_dense(const float* x, const float* nw, int64_t K, int64_t D, const float* shift,
+                       float* cov, int accumulate, void* workspace, size_t workspace_bytes,
+                       void* stream);
+
+/* a17 tail: sigma = cov - delta delta^T (delta = new mean - shift), optional factorized() and
+ * symmetric()                                                        ppi/policies.py:53-62,92 */
+int ppi_finalize_gaussian(const double* s1, const float* cov_in, int64_t D, const float* shift,
+                          int diagonal_only, float* mu_out, float* sigma_out, void* stream);
+
+/* a19/a20 tail: mean = s1 (H,d); cov_in = sym(acc)/d - correction; fp64 Cholesky (one block).
+ * jitter is added to the diagonal before factorising (1e-12 for features, policies.py:480). */
+int ppi_finalize_matnorm(const double* s1, const double* acc, int H, int d, double jitter,
+                         double* mean64, float* mean32, double* cov64, float* cov32,
+                         double* chol64, float* chol32, int* status, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PPI_B200_H */

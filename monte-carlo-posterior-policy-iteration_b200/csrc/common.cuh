@@ -1,0 +1,172 @@
+// Shared device/host helpers for the PPI update-path kernels (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <math.h>
+
+#include "../../include/ppi_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "ppi_b200 kernels are written for sm_100a (B200) only"
+#endif
+
+namespace ppi {
+
+void set_error(const char* fmt, ...);
+
+inline int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return (int)e;
+  }
+  return 0;
+}
+
+#define PPI_CUDA_TRY(expr)                                                  \
+  do {                                                                      \
+    cudaError_t _e = (expr);                                                \
+    if (_e != cudaSuccess) {                                                \
+      ppi::set_error("%s: %s", #expr, cudaGetErrorString(_e));              \
+      return (int)_e;                                                       \
+    }                                                                       \
+  } while (0)
+
+#define PPI_REQUIRE(cond, code, ...)   \
+  do {                                 \
+    if (!(cond)) {                     \
+      ppi::set_error(__VA_ARGS__);     \
+      return (code);                   \
+    }                                  \
+  } while (0)
+
+constexpr int kNumSMs = 148;  // B200
+
+__host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al. 2011).  counter = (elem_quad lo, elem_quad hi, draw lo, draw hi),
+// key = seed.  One call -> four uint32 -> four standard normals (two Box-Muller pairs).
+// ---------------------------------------------------------------------------------------------
+struct Philox4 {
+  uint32_t x, y, z, w;
+};
+
+__device__ __forceinline__ Philox4 philox4x32_10(uint64_t ctr_lo, uint64_t ctr_hi, uint64_t seed) {
+  constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+  constexpr uint32_t W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+  uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32);
+  uint32_t c2 = (uint32_t)ctr_hi, c3 = (uint32_t)(ctr_hi >> 32);
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+    uint32_t hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += W0; k1 += W1;
+  }
+  return Philox4{c0, c1, c2, c3};
+}
+
+// (0,1] uniform from 32 random bits; never 0 so that log() is finite.
+__device__ __forceinline__ float u01(uint32_t r) {
+  return fmaf((float)r, 2.3283064365386963e-10f, 1.1641532182693481e-10f);
+}
+
+__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
+  float u = u01(a), v = u01(b);
+  float r = sqrtf(-2.0f * __logf(u));
+  float s, c;
+  __sincosf(6.283185307179586f * v, &s, &c);
+  z0 = r * c;
+  z1 = r * s;
+}
+
+// The four normals of element quad q (elements 4q..4q+3 of the row-major global (K_total, n)
+// base-normal matrix) for draw `draw_id`.
+__device__ __forceinline__ void philox_normal4(uint64_t seed, uint64_t draw_id, uint64_t quad,
+                                               float out[4]) {
+  Philox4 p = philox4x32_10(quad, draw_id, seed);
+  box_muller(p.x, p.y, out[0], out[1]);
+  box_muller(p.z, p.w, out[2], out[3]);
+}
+
+// Single element e of the global matrix (slow path for unaligned access).
+__device__ __forceinline__ float philox_normal1(uint64_t seed, uint64_t draw_id, uint64_t elem) {
+  float v[4];
+  philox_normal4(seed, draw_id, elem >> 2, v);
+  return v[elem & 3];
+}
+
+// ---------------------------------------------------------------------------------------------
+// warp / block reductions
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Sum over the block; result valid in every thread.  `scratch` holds >= 32 T.
+template <typename T>
+__device__ __forceinline__ T block_sum(T v, T* scratch) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) scratch[warp] = v;
+  __syncthreads();
+  T r = (lane < nw) ? scratch[lane] : T(0);
+  r = warp_sum(r);
+  return r;
+}
+
+__device__ __forceinline__ float clipf(float v, float lo, float hi) {
+  // np.clip(x, a_min, a_max) = minimum(maximum(x, a_min), a_max); NaN propagates.
+  return (v != v) ? v : fminf(fmaxf(v, lo), hi);
+}
+
+// In-place right-looking Cholesky of the n x n matrix in shared memory `a` (lower part used).
+// Returns through *fail the 1-based index of the first non-positive pivot (0 = success).
+__device__ inline void block_cholesky(double* a, int n, int* fail_smem) {
+  if (threadIdx.x == 0) *fail_smem = 0;
+  __syncthreads();
+  for (int j = 0; j < n; ++j) {
+    if (threadIdx.x == 0) {
+      const double p = a[j * n + j];
+      if (!(p > 0.0) || !isfinite(p)) {
+        if (*fail_smem == 0) *fail_smem = j + 1;
+        a[j * n + j] = nan("");
+      } else {
+        a[j * n + j] = sqrt(p);
+      }
+    }
+    __syncthreads();
+    if (*fail_smem) break;
+    const double dj = a[j * n + j];
+    for (int i = j + 1 + threadIdx.x; i < n; i += blockDim.x) a[i * n + j] /= dj;
+    __syncthreads();
+    const int m = n - j - 1;  // trailing size
+    for (int e = threadIdx.x; e < m * m; e += blockDim.x) {
+      const int i = j + 1 + e / m, k = j + 1 + e % m;
+      if (k <= i) a[i * n + k] -= a[i * n + j] * a[k * n + j];
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+}
+
+}  // namespace ppi

@@ -1,0 +1,549 @@
+// Action-prior sampling kernels.
+//   philox_normal            np.random.randn                      ppi/samplers.py:18-20
+//   gram_chol / chol_small   kernel Gram + np.linalg.cholesky     ppi/policies.py:312,923-1091
+//   sample_matnorm           BaseKernel.__call__                  ppi/policies.py:735-745
+//   sample_features          BaseFeatures.__call__                ppi/policies.py:404-421
+//   sample_iid               WhiteNoiseIid.__call__               ppi/policies.py:1166-1174
+//   sample_gaussian (small)  mu + z L^T                           ppi/samplers.py:38-39
+// The small matrix products (H, d, F <= ~128) run as fp32 SIMT with shared-memory operands;
+// the large dense Gaussian transform lives in tc_gemm.cu (tcgen05).
+#include "common.cuh"
+
+namespace ppi {
+
+// ------------------------------------------------------------------------------------------
+// Philox normals -> global memory
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) philox_normal_kernel(float* __restrict__ out, int64_t n_local,
+                                                            uint64_t elem_base, uint64_t seed,
+                                                            uint64_t draw) {
+  const uint64_t q0 = elem_base >> 2;
+  const uint64_t q1 = (elem_base + (uint64_t)n_local + 3) >> 2;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t q = q0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += stride) {
+    float v[4];
+    philox_normal4(seed, draw, q, v);
+    const int64_t local = (int64_t)(q * 4) - (int64_t)elem_base;
+    if (local >= 0 && local + 4 <= n_local &&
+        ((reinterpret_cast<uintptr_t>(out + local) & 15) == 0)) {
+      *reinterpret_cast<float4*>(out + local) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int64_t l = local + i;
+        if (l >= 0 && l < n_local) out[l] = v[i];
+      }
+    }
+  }
+}
+
+// Fill shared memory s[0..n) with base normals elem_base .. elem_base+n (Philox) or copy them
+// from the injected matrix z (global element index = elem_base - z_base).
+__device__ __forceinline__ void load_normals(float* s, int n, const float* __restrict__ z,
+                                             uint64_t z_local_base, uint64_t elem_base,
+                                             uint64_t seed, uint64_t draw) {
+  if (z != nullptr) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s[i] = z[z_local_base + i];
+  } else {
+    const uint64_t q0 = elem_base >> 2;
+    const int nq = (int)(((elem_base + n + 3) >> 2) - q0);
+    for (int qi = threadIdx.x; qi < nq; qi += blockDim.x) {
+      float v[4];
+      philox_normal4(seed, draw, q0 + qi, v);
+      const int64_t local = (int64_t)((q0 + qi) * 4) - (int64_t)elem_base;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int64_t l = local + i;
+        if (l >= 0 && l < n) s[l] = v[i];
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Matrix-normal sampler  x = bias + L_in (z L_out^T), S samples per block iteration.
+// Each thread owns one output column l and the row pair (p, H-1-p) for S samples, so every
+// L_in element read from shared memory feeds S FMAs and the triangular work is balanced.
+// ------------------------------------------------------------------------------------------
+template <int S>
+__global__ void __launch_bounds__(256)
+sample_matnorm_kernel(const float* __restrict__ z, uint64_t seed, uint64_t draw, uint64_t row_offset,
+                      int64_t K, int H, int d, const float* __restrict__ mean_fn,
+                      const float* __restrict__ mean, const float* __restrict__ l_in,
+                      const float* __restrict__ l_out, int l_out_diag,
+                      const float* __restrict__ lower, const float* __restrict__ upper,
+                      float* __restrict__ x) {
+  extern __shared__ float smem[];
+  const int HD = H * d;
+  float* sLin = smem;               // H*H
+  float* sLout = sLin + H * H;      // d*d
+  float* sBias = sLout + d * d;     // H*d
+  float* sZ = sBias + HD;           // S*H*d
+  float* sU = sZ + S * HD;          // S*H*d
+
+  for (int i = threadIdx.x; i < H * H; i += blockDim.x) sLin[i] = l_in[i];
+  for (int i = threadIdx.x; i < d * d; i += blockDim.x) sLout[i] = l_out[i];
+  for (int i = threadIdx.x; i < HD; i += blockDim.x) sBias[i] = mean_fn[i % d] + mean[i];
+  __syncthreads();
+
+  const int64_t n_groups = ceil_div(K, S);
+  const int half = (H + 1) / 2;
+  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+    const int64_t b0 = g * S;
+    const int ns = (int)min((int64_t)S, K - b0);
+    load_normals(sZ, ns * HD, z, (uint64_t)b0 * HD, (row_offset + (uint64_t)b0) * HD, seed, draw);
+    __syncthreads();
+    // U = Z L_out^T
+    for (int e = threadIdx.x; e < ns * HD; e += blockDim.x) {
+      const int l = e % d;
+      const float* zr = sZ + (e - l);
+      float u;
+      if (l_out_diag) {
+        u = zr[l] * sLout[l * d + l];
+      } else {
+        u = 0.f;
+        for (int j = 0; j < d; ++j) u = fmaf(zr[j], sLout[l * d + j], u);
+      }
+      sU[e] = u;
+    }
+    __syncthreads();
+    // X = bias + L_in U
+    for (int it = threadIdx.x; it < half * d; it += blockDim.x) {
+      const int l = it % d, p = it / d;
+      const int k1 = p, k2 = H - 1 - p;  // k1 <= k2
+      float a1[S], a2[S];
+#pragma unroll
+      for (int s = 0; s < S; ++s) a1[s] = a2[s] = 0.f;
+      const float* r1 = sLin + k1 * H;
+      const float* r2 = sLin + k2 * H;
+      for (int i = 0; i <= k1; ++i) {
+        const float w1 = r1[i], w2 = r2[i];
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+          const float u = sU[s * HD + i * d + l];
+          a1[s] = fmaf(w1, u, a1[s]);
+          a2[s] = fmaf(w2, u, a2[s]);
+        }
+      }
+      for (int i = k1 + 1; i <= k2; ++i) {
+        const float w2 = r2[i];
+#pragma unroll
+        for (int s = 0; s < S; ++s) a2[s] = fmaf(w2, sU[s * HD + i * d + l], a2[s]);
+      }
+      const float lo = lower ? lower[l] : -INFINITY, hi = upper ? upper[l] : INFINITY;
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        if (s < ns) {
+          float* xr = x + (b0 + s) * HD;
+          xr[k1 * d + l] = clipf(sBias[k1 * d + l] + a1[s], lo, hi);
+          if (k2 != k1) xr[k2 * d + l] = clipf(sBias[k2 * d + l] + a2[s], lo, hi);
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Feature sampler: w = mean + L_in z L_out^T (K,F,d); y = [mean_fn + Phi w, Phi' w] (K,T,dy).
+// grid.y tiles the time axis (TT steps); each block recomputes the tiny w for its samples.
+// ------------------------------------------------------------------------------------------
+constexpr int kFeatTT = 128;
+
+template <int S>
+__global__ void __launch_bounds__(256)
+sample_features_kernel(const float* __restrict__ z, uint64_t seed, uint64_t draw, uint64_t row_offset,
+                       int64_t K, int F, int d, int T, const float* __restrict__ mean_fn,
+                       const float* __restrict__ mean, const float* __restrict__ l_in,
+                       const float* __restrict__ l_out, const float* __restrict__ feat,
+                       const float* __restrict__ dfeat, const float* __restrict__ lower,
+                       const float* __restrict__ upper, float* __restrict__ w,
+                       float* __restrict__ y) {
+  extern __shared__ float smem[];
+  const int FD = F * d;
+  const int dy = dfeat ? 2 * d : d;
+  float* sPhi = smem;                       // F*TT (transposed tile)
+  float* sdPhi = sPhi + F * kFeatTT;        // F*TT
+  float* sLin = sdPhi + F * kFeatTT;        // F*F
+  float* sLout = sLin + F * F;              // d*d
+  float* sMean = sLout + d * d;             // F*d
+  float* sZ = sMean + FD;                   // S*F*d
+  float* sU = sZ + S * FD;                  // S*F*d
+  float* sW = sU + S * FD;                  // S*F*d
+
+  const int t0 = blockIdx.y * kFeatTT;
+  const int nt = min(kFeatTT, T - t0);
+  for (int i = threadIdx.x; i < F * kFeatTT; i += blockDim.x) {
+    const int f = i / kFeatTT, tl = i % kFeatTT;
+    const bool ok = tl < nt;
+    sPhi[i] = ok ? feat[(int64_t)(t0 + tl) * F + f] : 0.f;
+    sdPhi[i] = (ok && dfeat) ? dfeat[(int64_t)(t0 + tl) * F + f] : 0.f;
+  }
+  for (int i = threadIdx.x; i < F * F; i += blockDim.x) sLin[i] = l_in[i];
+  for (int i = threadIdx.x; i < d * d; i += blockDim.x) sLout[i] = l_out[i];
+  for (int i = threadIdx.x; i < FD; i += blockDim.x) sMean[i] = mean[i];
+  __syncthreads();
+
+  const int64_t n_groups = ceil_div(K, S);
+  const int tl = threadIdx.x % kFeatTT;
+  const int srow = threadIdx.x / kFeatTT, nsrow = blockDim.x / kFeatTT;
+  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+    const int64_t b0 = g * S;
+    const int ns = (int)min((int64_t)S, K - b0);
+    load_normals(sZ, ns * FD, z, (uint64_t)b0 * FD, (row_offset + (uint64_t)b0) * FD, seed, draw);
+    __syncthreads();
+    for (int e = threadIdx.x; e < ns * FD; e += blockDim.x) {
+      const int l = e % d;
+      const float* zr = sZ + (e - l);
+      float u = 0.f;
+      for (int j = 0; j < d; ++j) u = fmaf(zr[j], sLout[l * d + j], u);
+      sU[e] = u;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < ns * FD; e += blockDim.x) {
+      const int s = e / FD, r = e % FD, k = r / d, l = r % d;
+      float a = 0.f;
+      const float* row = sLin + k * F;
+      for (int i = 0; i <= k; ++i) a = fmaf(row[i], sU[s * FD + i * d + l], a);
+      a += sMean[r];
+      sW[e] = a;
+      if (blockIdx.y == 0) w[(b0 + s) * FD + r] = a;
+    }
+    __syncthreads();
+    if (tl < nt) {
+      for (int s = srow; s < ns; s += nsrow) {
+        float* yr = y + ((b0 + s) * (int64_t)T + (t0 + tl)) * dy;
+        for (int c0 = 0; c0 < d; c0 += 4) {
+          float ax[4] = {0.f, 0.f, 0.f, 0.f}, ad[4] = {0.f, 0.f, 0.f, 0.f};
+          const int nc = min(4, d - c0);
+          for (int f = 0; f < F; ++f) {
+            const float ph = sPhi[f * kFeatTT + tl], dph = sdPhi[f * kFeatTT + tl];
+            const float* wr = sW + s * FD + f * d + c0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (j < nc) {
+                ax[j] = fmaf(ph, wr[j], ax[j]);
+                ad[j] = fmaf(dph, wr[j], ad[j]);
+              }
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (j < nc) {
+              const int c = c0 + j;
+              const float lo = lower ? lower[c] : -INFINITY, hi = upper ? upper[c] : INFINITY;
+              yr[c] = clipf(mean_fn[c] + ax[j], lo, hi);
+              if (dfeat) {
+                const float lo2 = lower ? lower[d + c] : -INFINITY;
+                const float hi2 = upper ? upper[d + c] : INFINITY;
+                yr[d + c] = clipf(ad[j], lo2, hi2);
+              }
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// iid sampler: element-wise, one quad of the base-normal matrix per thread iteration.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+sample_iid_kernel(const float* __restrict__ z, uint64_t seed, uint64_t draw, uint64_t row_offset,
+                  int64_t K, int HD, int d, const float* __restrict__ mean_fn,
+                  const float* __restrict__ mean, const float* __restrict__ stdv,
+                  const float* __restrict__ lower, const float* __restrict__ upper,
+                  float* __restrict__ x) {
+  const int64_t n_local = K * HD;
+  const uint64_t elem_base = row_offset * (uint64_t)HD;
+  const uint64_t q0 = elem_base >> 2, q1 = (elem_base + n_local + 3) >> 2;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t q = q0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += stride) {
+    float v[4];
+    const int64_t local = (int64_t)(q * 4) - (int64_t)elem_base;
+    if (z == nullptr) philox_normal4(seed, draw, q, v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t l = local + i;
+      if (l >= 0 && l < n_local) {
+        const float zz = z ? z[l] : v[i];
+        const int e = (int)(l % HD), c = e % d;
+        const float lo = lower ? lower[c] : -INFINITY, hi = upper ? upper[c] : INFINITY;
+        x[l] = clipf(mean_fn[c] + mean[e] + stdv[e] * zz, lo, hi);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Small dense Gaussian transform x = mu + z L^T, D <= 128: L^T in shared memory.
+// ------------------------------------------------------------------------------------------
+template <int S>
+__global__ void __launch_bounds__(256)
+sample_gaussian_small_kernel(const float* __restrict__ z, uint64_t seed, uint64_t draw,
+                             uint64_t row_offset, int64_t K, int D, const float* __restrict__ mu,
+                             const float* __restrict__ L, float* __restrict__ x) {
+  extern __shared__ float smem[];
+  float* sLt = smem;            // D*D, sLt[j*D+i] = L[i][j]
+  float* sZ = sLt + D * D;      // S*D
+  for (int e = threadIdx.x; e < D * D; e += blockDim.x) {
+    const int i = e / D, j = e % D;
+    sLt[j * D + i] = L[e];
+  }
+  __syncthreads();
+  const int64_t n_groups = ceil_div(K, S);
+  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+    const int64_t b0 = g * S;
+    const int ns = (int)min((int64_t)S, K - b0);
+    load_normals(sZ, ns * D, z, (uint64_t)b0 * D, (row_offset + (uint64_t)b0) * D, seed, draw);
+    __syncthreads();
+    for (int e = threadIdx.x; e < ns * D; e += blockDim.x) {
+      const int s = e / D, i = e % D;
+      float a = 0.f;
+      const float* zr = sZ + s * D;
+      for (int j = 0; j <= i; ++j) a = fmaf(zr[j], sLt[j * D + i], a);
+      x[(b0 + s) * D + i] = mu[i] + a;
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Kernel Gram matrix + Cholesky, fp64, one block.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ double gram_entry(int kind, double a, double b, double sigma, double ls,
+                                             double period, bool square, bool on_diag) {
+  const double diff = a - b;
+  switch (kind) {
+    case PPI_KERNEL_SE: {
+      const double r = diff / ls;
+      double k = sigma * exp(-0.5 * r * r);
+      if (square && on_diag) k += 1e-3 * sigma;  // ppi/policies.py:929-931
+      return k;
+    }
+    case PPI_KERNEL_MATERN12: {
+      double ad = fabs(diff);
+      if (ad == 0.0) ad = 1e-8;  // ppi/policies.py:941
+      return sigma * exp(-ad / ls);
+    }
+    case PPI_KERNEL_MATERN32: {
+      double ad = fabs(diff);
+      if (ad == 0.0) ad = 1e-8;
+      const double dd = sqrt(3.0) * ad / ls;
+      return sigma * (1.0 + dd) * exp(-dd);
+    }
+    case PPI_KERNEL_MATERN52: {
+      double ad = fabs(diff);
+      if (ad == 0.0) ad = 1e-8;
+      const double dd = sqrt(5.0) * ad / ls;
+      return sigma * (1.0 + dd + dd * dd / 3.0) * exp(-dd);
+    }
+    case PPI_KERNEL_PERIODIC: {
+      double ad = fabs(diff == 0.0 ? -1e-8 : diff);  // ppi/policies.py:1031-1032
+      const double sn = sin(M_PI * ad / period);
+      double k = sigma * exp(-2.0 * sn * sn / ls);
+      if (square && on_diag) k += 1e-3 * sigma;
+      return k;
+    }
+    default:  // white noise, ppi/policies.py:1087-1091
+      return diff == 0.0 ? sigma : 0.0;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+gram_chol_kernel(const double* __restrict__ t1, int n1, const double* __restrict__ t2, int n2,
+                 int kind, double sigma, double ls, double period, double* __restrict__ gram64,
+                 float* __restrict__ gram32, double* __restrict__ chol64,
+                 float* __restrict__ chol32, int* __restrict__ status) {
+  extern __shared__ double sa[];
+  __shared__ int fail;
+  const bool square = (n1 == n2);
+  const bool do_chol = (chol64 != nullptr || chol32 != nullptr);
+  for (int e = threadIdx.x; e < n1 * n2; e += blockDim.x) {
+    const int i = e / n2, j = e % n2;
+    const double k = gram_entry(kind, t1[i], t2[j], sigma, ls, period, square, i == j);
+    if (gram64) gram64[e] = k;
+    if (gram32) gram32[e] = (float)k;
+    if (do_chol) sa[e] = k;
+  }
+  if (!do_chol) return;
+  __syncthreads();
+  block_cholesky(sa, n1, &fail);
+  for (int e = threadIdx.x; e < n1 * n1; e += blockDim.x) {
+    const int i = e / n1, j = e % n1;
+    const double v = (j <= i) ? sa[e] : 0.0;
+    if (chol64) chol64[e] = v;
+    if (chol32) chol32[e] = (float)v;
+  }
+  if (threadIdx.x == 0 && status) *status = fail;
+}
+
+__global__ void __launch_bounds__(256)
+chol_small_kernel(const double* __restrict__ a, int n, double* __restrict__ l64,
+                  float* __restrict__ l32, int* __restrict__ status) {
+  extern __shared__ double sa[];
+  __shared__ int fail;
+  for (int e = threadIdx.x; e < n * n; e += blockDim.x) sa[e] = a[e];
+  __syncthreads();
+  block_cholesky(sa, n, &fail);
+  for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+    const int i = e / n, j = e % n;
+    const double v = (j <= i) ? sa[e] : 0.0;
+    if (l64) l64[e] = v;
+    if (l32) l32[e] = (float)v;
+  }
+  if (threadIdx.x == 0 && status) *status = fail;
+}
+
+constexpr int kMaxSmemBytes = 200 * 1024;
+
+template <typename Kern>
+static int set_smem(Kern kern, size_t bytes) {
+  if (bytes > 48 * 1024) {
+    PPI_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  }
+  return 0;
+}
+
+static int grid_for(int64_t work_items, int per_sm) {
+  int64_t g = work_items < 1 ? 1 : work_items;
+  const int64_t cap = (int64_t)kNumSMs * per_sm;
+  return (int)(g < cap ? g : cap);
+}
+
+}  // namespace ppi
+
+using namespace ppi;
+
+extern "C" int ppi_philox_normal(float* out, int64_t rows, int64_t cols, uint64_t seed,
+                                 uint64_t draw_id, uint64_t row_offset, void* stream) {
+  PPI_REQUIRE(out && rows >= 0 && cols > 0, PPI_ERR_INVALID, "ppi_philox_normal: bad arguments");
+  if (rows == 0) return 0;
+  const int64_t n = rows * cols;
+  const int grid = grid_for(ceil_div(ceil_div(n, 4), 256 * 4), 8);
+  philox_normal_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(out, n, row_offset * (uint64_t)cols,
+                                                               seed, draw_id);
+  return check_launch("philox_normal_kernel");
+}
+
+extern "C" int ppi_kernel_gram_chol(const double* t1, int n1, const double* t2, int n2, int kind,
+                                    double sigma, double lengthscale, double period, double* gram64,
+                                    float* gram32, double* chol64, float* chol32, int* status,
+                                    void* stream) {
+  PPI_REQUIRE(t1 && t2 && n1 > 0 && n2 > 0, PPI_ERR_INVALID, "ppi_kernel_gram_chol: bad arguments");
+  PPI_REQUIRE(kind >= 0 && kind <= PPI_KERNEL_WHITE, PPI_ERR_INVALID, "unknown kernel kind %d", kind);
+  const bool do_chol = chol64 || chol32;
+  size_t smem = 0;
+  if (do_chol) {
+    PPI_REQUIRE(n1 == n2, PPI_ERR_INVALID, "Cholesky needs a square Gram matrix");
+    smem = (size_t)n1 * n1 * sizeof(double);
+    PPI_REQUIRE(smem <= (size_t)kMaxSmemBytes, PPI_ERR_UNSUPPORTED,
+                "single-block Cholesky supports n <= 160 (got %d)", n1);
+    if (int rc = set_smem(gram_chol_kernel, smem)) return rc;
+  }
+  gram_chol_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(t1, n1, t2, n2, kind, sigma, lengthscale,
+                                                           period, gram64, gram32, chol64, chol32,
+                                                           status);
+  return check_launch("gram_chol_kernel");
+}
+
+extern "C" int ppi_cholesky_small(const double* a, int n, double* l64, float* l32, int* status,
+                                  void* stream) {
+  PPI_REQUIRE(a && n > 0, PPI_ERR_INVALID, "ppi_cholesky_small: bad arguments");
+  const size_t smem = (size_t)n * n * sizeof(double);
+  PPI_REQUIRE(smem <= (size_t)kMaxSmemBytes, PPI_ERR_UNSUPPORTED,
+              "single-block Cholesky supports n <= 160 (got %d)", n);
+  if (int rc = set_smem(chol_small_kernel, smem)) return rc;
+  chol_small_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(a, n, l64, l32, status);
+  return check_launch("chol_small_kernel");
+}
+
+extern "C" int ppi_sample_matnorm(const float* z, uint64_t seed, uint64_t draw_id,
+                                  uint64_t row_offset, int64_t K, int H, int d,
+                                  const float* mean_fn, const float* mean, const float* l_in,
+                                  const float* l_out, int l_out_is_diag, const float* lower,
+                                  const float* upper, float* x, void* stream) {
+  PPI_REQUIRE(K >= 0 && H > 0 && d > 0 && mean_fn && mean && l_in && l_out && x, PPI_ERR_INVALID,
+              "ppi_sample_matnorm: bad arguments");
+  PPI_REQUIRE((lower == nullptr) == (upper == nullptr), PPI_ERR_INVALID,
+              "lower and upper must both be given or both be NULL");
+  if (K == 0) return 0;
+  const size_t fixed = ((size_t)H * H + (size_t)d * d + (size_t)H * d) * sizeof(float);
+  auto need = [&](int S) { return fixed + 2 * (size_t)S * H * d * sizeof(float); };
+  cudaStream_t st = (cudaStream_t)stream;
+#define PPI_LAUNCH_MATNORM(S)                                                                   \
+  do {                                                                                          \
+    if (int rc = set_smem(sample_matnorm_kernel<S>, need(S))) return rc;                        \
+    const int grid = grid_for(ceil_div(K, S), 4);                                               \
+    sample_matnorm_kernel<S><<<grid, 256, need(S), st>>>(z, seed, draw_id, row_offset, K, H, d, \
+                                                         mean_fn, mean, l_in, l_out,            \
+                                                         l_out_is_diag, lower, upper, x);       \
+  } while (0)
+  if (need(4) <= 48 * 1024) PPI_LAUNCH_MATNORM(4);
+  else if (need(2) <= 100 * 1024) PPI_LAUNCH_MATNORM(2);
+  else {
+    PPI_REQUIRE(need(1) <= (size_t)kMaxSmemBytes, PPI_ERR_UNSUPPORTED,
+                "ppi_sample_matnorm: H=%d d=%d does not fit shared memory", H, d);
+    PPI_LAUNCH_MATNORM(1);
+  }
+#undef PPI_LAUNCH_MATNORM
+  return check_launch("sample_matnorm_kernel");
+}
+
+extern "C" int ppi_sample_features(const float* z, uint64_t seed, uint64_t draw_id,
+                                   uint64_t row_offset, int64_t K, int F, int d, int T,
+                                   const float* mean_fn, const float* mean, const float* l_in,
+                                   const float* l_out, const float* feat, const float* dfeat,
+                                   const float* lower, const float* upper, float* w, float* y,
+                                   void* stream) {
+  PPI_REQUIRE(K >= 0 && F > 0 && d > 0 && T > 0 && mean_fn && mean && l_in && l_out && feat && w && y,
+              PPI_ERR_INVALID, "ppi_sample_features: bad arguments");
+  PPI_REQUIRE((lower == nullptr) == (upper == nullptr), PPI_ERR_INVALID,
+              "lower and upper must both be given or both be NULL");
+  if (K == 0) return 0;
+  constexpr int S = 4;
+  const size_t smem = (2 * (size_t)F * kFeatTT + (size_t)F * F + (size_t)d * d + (size_t)F * d +
+                       3 * (size_t)S * F * d) * sizeof(float);
+  PPI_REQUIRE(smem <= (size_t)kMaxSmemBytes, PPI_ERR_UNSUPPORTED,
+              "ppi_sample_features: F=%d d=%d does not fit shared memory", F, d);
+  if (int rc = set_smem(sample_features_kernel<S>, smem)) return rc;
+  const int ty = (int)ceil_div(T, kFeatTT);
+  int gx = grid_for(ceil_div(K, S), 4);
+  gx = (int)ceil_div(gx, ty);
+  if (gx < 1) gx = 1;
+  dim3 grid(gx, ty);
+  sample_features_kernel<S><<<grid, 256, smem, (cudaStream_t)stream>>>(
+      z, seed, draw_id, row_offset, K, F, d, T, mean_fn, mean, l_in, l_out, feat, dfeat, lower, upper,
+      w, y);
+  return check_launch("sample_features_kernel");
+}
+
+extern "C" int ppi_sample_iid(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
+                              int64_t K, int H, int d, const float* mean_fn, const float* mean,
+                              const float* stdv, const float* lower, const float* upper, float* x,
+                              void* stream) {
+  PPI_REQUIRE(K >= 0 && H > 0 && d > 0 && mean_fn && mean && stdv && x, PPI_ERR_INVALID,
+              "ppi_sample_iid: bad arguments");
+  PPI_REQUIRE((lower == nullptr) == (upper == nullptr), PPI_ERR_INVALID,
+              "lower and upper must both be given or both be NULL");
+  if (K == 0) return 0;
+  const int64_t n = K * H * d;
+  const int grid = grid_for(ceil_div(ceil_div(n, 4), 256 * 4), 8);
+  sample_iid_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(z, seed, draw_id, row_offset, K, H * d, d,
+                                                            mean_fn, mean, stdv, lower, upper, x);
+  return check_launch("sample_iid_kernel");
+}
+
+// Called from tc_gemm.cu's ppi_sample_gaussian for D <= 128.
+int ppi_sample_gaussian_small(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
+                              int64_t K, int D, const float* mu, const float* L, float* x,
+                              cudaStream_t st) {
+  constexpr int S = 8;
+  const size_t smem = ((size_t)D * D + (size_t)S * D) * sizeof(float);
+  if (int rc = set_smem(sample_gaussian_small_kernel<S>, smem)) return rc;
+  const int grid = grid_for(ceil_div(K, S), 2);
+  sample_gaussian_small_kernel<S><<<grid, 256, smem, st>>>(z, seed, draw_id, row_offset, K, D, mu, L, x);
+  return check_launch("sample_gaussian_small_kernel");
+}

@@ -1,0 +1,262 @@
+"""Tensor-level wrappers of the C ABI (include/ppi_b200.h): allocate outputs / workspaces with
+torch, pass raw device pointers + the current CUDA stream, check the status.  One function per
+entry point; the policy / optimizer classes and the parity tests both go through these.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from .device import f32, f64, ptr, read_stats, require_cuda, stream_ptr, workspace
+
+_u64 = lambda v: C.c_uint64(int(v) & 0xFFFFFFFFFFFFFFFF)  # noqa: E731
+
+
+def _opt(t, dev):
+    return None if t is None else f32(t, dev)
+
+
+# ------------------------------------------------------------------ a3
+def philox_normal(rows, cols, seed, draw_id=0, row_offset=0):
+    dev = require_cuda()
+    out = torch.empty((rows, cols), dtype=torch.float32, device=dev)
+    _lib.call("ppi_philox_normal", ptr(out), rows, cols, _u64(seed), _u64(draw_id), _u64(row_offset),
+              stream_ptr())
+    return out
+
+
+# ------------------------------------------------------------------ a22
+def gram(kind, t1, t2, sigma, ls=1.0, period=1.0, chol=False):
+    """Kernel Gram matrix in fp64 (and its Cholesky factor + status when chol=True)."""
+    dev = require_cuda()
+    t1d, t2d = f64(np.asarray(t1).reshape(-1), dev), f64(np.asarray(t2).reshape(-1), dev)
+    n1, n2 = t1d.numel(), t2d.numel()
+    g = torch.empty((n1, n2), dtype=torch.float64, device=dev)
+    if not chol:
+        _lib.call("ppi_kernel_gram_chol", ptr(t1d), n1, ptr(t2d), n2, _lib.KERNEL_KINDS[kind],
+                  float(sigma), float(ls), float(period), ptr(g), None, None, None, None, stream_ptr())
+        return g
+    l = torch.empty((n1, n1), dtype=torch.float64, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    _lib.call("ppi_kernel_gram_chol", ptr(t1d), n1, ptr(t2d), n2, _lib.KERNEL_KINDS[kind],
+              float(sigma), float(ls), float(period), ptr(g), None, ptr(l), None, ptr(status),
+              stream_ptr())
+    return g, l, int(status.item())
+
+
+def cholesky_small(a):
+    """np.linalg.cholesky of a small fp64 matrix on the device; returns (L fp64, status)."""
+    dev = require_cuda()
+    a = f64(a, dev)
+    n = a.shape[0]
+    l = torch.empty_like(a)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    _lib.call("ppi_cholesky_small", ptr(a), n, ptr(l), None, ptr(status), stream_ptr())
+    return l, int(status.item())
+
+
+# ------------------------------------------------------------------ a4-a8
+def _is_diag(m):
+    m = np.asarray(m)
+    return bool(np.count_nonzero(m - np.diag(np.diag(m))) == 0)
+
+
+def sample_matnorm(K, mean_fn, mean, l_in, l_out, z=None, seed=0, draw_id=0, row_offset=0,
+                   lower=None, upper=None, l_out_is_diag=False):
+    dev = require_cuda()
+    mean = f32(mean, dev)
+    H, d = mean.shape
+    x = torch.empty((K, H, d), dtype=torch.float32, device=dev)
+    zt = None if z is None else f32(z, dev).reshape(K, H * d)
+    lo, hi = _opt(lower, dev), _opt(upper, dev)
+    _lib.call("ppi_sample_matnorm", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, H, d,
+              ptr(f32(mean_fn, dev)), ptr(mean), ptr(f32(l_in, dev)), ptr(f32(l_out, dev)),
+              int(bool(l_out_is_diag)), ptr(lo), ptr(hi), ptr(x), stream_ptr())
+    return x
+
+
+def sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat=None, z=None, seed=0, draw_id=0,
+                    row_offset=0, lower=None, upper=None):
+    dev = require_cuda()
+    mean = f32(mean, dev)
+    F, d = mean.shape
+    feat = f32(feat, dev)
+    T = feat.shape[0]
+    dy = 2 * d if dfeat is not None else d
+    w = torch.empty((K, F, d), dtype=torch.float32, device=dev)
+    y = torch.empty((K, T, dy), dtype=torch.float32, device=dev)
+    zt = None if z is None else f32(z, dev).reshape(K, F * d)
+    lo, hi = _opt(lower, dev), _opt(upper, dev)
+    _lib.call("ppi_sample_features", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, F, d, T,
+              ptr(f32(mean_fn, dev)), ptr(mean), ptr(f32(l_in, dev)), ptr(f32(l_out, dev)), ptr(feat),
+              ptr(_opt(dfeat, dev)), ptr(lo), ptr(hi), ptr(w), ptr(y), stream_ptr())
+    return y, w
+
+
+def sample_iid(K, mean_fn, mean, std, z=None, seed=0, draw_id=0, row_offset=0, lower=None,
+               upper=None):
+    dev = require_cuda()
+    mean = f32(mean, dev)
+    H, d = mean.shape
+    x = torch.empty((K, H, d), dtype=torch.float32, device=dev)
+    zt = None if z is None else f32(z, dev).reshape(K, H * d)
+    lo, hi = _opt(lower, dev), _opt(upper, dev)
+    _lib.call("ppi_sample_iid", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, H, d,
+              ptr(f32(mean_fn, dev)), ptr(mean), ptr(f32(std, dev)), ptr(lo), ptr(hi), ptr(x),
+              stream_ptr())
+    return x
+
+
+def sample_gaussian(K, mu, L, z=None, seed=0, draw_id=0, row_offset=0, out=None):
+    """x = mu + z L^T with L lower triangular (Cholesky form, ppi/samplers.py:38-39)."""
+    dev = require_cuda()
+    mu = f32(mu, dev)
+    D = mu.numel()
+    x = out if out is not None else torch.empty((K, D), dtype=torch.float32, device=dev)
+    zt = None if z is None else f32(z, dev).reshape(K, D)
+    nbytes = _lib.query("ppi_sample_gaussian_workspace_bytes", K, D)
+    ws = workspace("sample_gaussian", nbytes) if nbytes else None
+    _lib.call("ppi_sample_gaussian", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, D,
+              ptr(mu), ptr(f32(L, dev)), ptr(x), ptr(ws), nbytes, stream_ptr())
+    return x
+
+
+# ------------------------------------------------------------------ a9
+def cost_function(name, x, A=None, noise=None):
+    dev = require_cuda()
+    x = f32(x, dev)
+    K, D = x.shape
+    c = torch.empty((K,), dtype=torch.float32, device=dev)
+    _lib.call("ppi_cost_function", _lib.FN_IDS[name], ptr(x), K, D, ptr(_opt(A, dev)),
+              ptr(_opt(noise, dev)), ptr(c), stream_ptr())
+    return c
+
+
+def cost_tracking(x, target):
+    dev = require_cuda()
+    x = f32(x, dev)
+    K, T, dy = x.shape
+    target = f32(target, dev)
+    dt = target.shape[1]
+    c = torch.empty((K,), dtype=torch.float32, device=dev)
+    _lib.call("ppi_cost_tracking", ptr(x), K, T, dy, ptr(target), dt, ptr(c), stream_ptr())
+    return c
+
+
+# ------------------------------------------------------------------ a2, a10-a15
+def _stats_tensor(dev):
+    return torch.zeros(_lib.STATS_BYTES, dtype=torch.uint8, device=dev)
+
+
+def solve_temperature(costs, mode, hyper, want_log_w=True, sync=True):
+    """-> (nw, log_w, stats).  stats is a _lib.WeightStats (host) when sync else the device bytes."""
+    dev = require_cuda()
+    c = f32(costs, dev).reshape(-1)
+    K = c.numel()
+    nw = torch.empty_like(c)
+    lw = torch.empty_like(c) if want_log_w else None
+    st = _stats_tensor(dev)
+    nbytes = _lib.query("ppi_solve_temperature_workspace_bytes", K)
+    ws = workspace("solve", nbytes)
+    _lib.call("ppi_solve_temperature", ptr(c), K, int(mode), float(hyper), ptr(nw), ptr(lw), ptr(st),
+              ptr(ws), nbytes, stream_ptr())
+    return nw, lw, (read_stats(st) if sync else st)
+
+
+def normalise_log_weights(log_w, sync=True):
+    dev = require_cuda()
+    lw = f32(log_w, dev).reshape(-1)
+    K = lw.numel()
+    nw = torch.empty_like(lw)
+    st = _stats_tensor(dev)
+    nbytes = _lib.query("ppi_solve_temperature_workspace_bytes", K)
+    ws = workspace("solve", nbytes)
+    _lib.call("ppi_normalise_log_weights", ptr(lw), K, ptr(nw), ptr(st), ptr(ws), nbytes, stream_ptr())
+    return nw, (read_stats(st) if sync else st)
+
+
+def cem_weights(costs, n_elites, sync=True):
+    dev = require_cuda()
+    c = f32(costs, dev).reshape(-1)
+    K = c.numel()
+    nw = torch.empty_like(c)
+    idx = torch.empty((K,), dtype=torch.int64, device=dev)
+    st = _stats_tensor(dev)
+    nbytes = _lib.query("ppi_cem_workspace_bytes", K)
+    ws = workspace("cem", nbytes)
+    _lib.call("ppi_cem_weights", ptr(c), K, int(n_elites), ptr(idx), ptr(nw), ptr(st), ptr(ws), nbytes,
+              stream_ptr())
+    return idx, nw, (read_stats(st) if sync else st)
+
+
+# ------------------------------------------------------------------ a16-a21
+def wmoments_diag(x, nw, shift1=None, shift2=None, second=False, s1=None, s2=None):
+    """fp64 accumulators: s1 = sum nw (x - shift1), s2 = sum nw (x - shift2)^2 over rows of x (K, D)."""
+    dev = require_cuda()
+    x = f32(x, dev)
+    K = x.shape[0]
+    x2 = x.reshape(K, -1)
+    D = x2.shape[1]
+    s1 = torch.zeros(D, dtype=torch.float64, device=dev) if s1 is None else s1
+    if second and s2 is None:
+        s2 = torch.zeros(D, dtype=torch.float64, device=dev)
+    _lib.call("ppi_wmoments_diag", ptr(x2), ptr(f32(nw, dev)), K, D, ptr(_opt(shift1, dev)),
+              ptr(_opt(shift2, dev)), ptr(s1), ptr(s2 if second else None), stream_ptr())
+    return (s1, s2) if second else s1
+
+
+def wmoments_matnorm(x, nw, shift=None, inv_cov_out=None, acc=None):
+    dev = require_cuda()
+    x = f32(x, dev)
+    K, H, d = x.shape
+    acc = torch.zeros((H, H), dtype=torch.float64, device=dev) if acc is None else acc
+    _lib.call("ppi_wmoments_matnorm", ptr(x), ptr(f32(nw, dev)), K, H, d, ptr(_opt(shift, dev)),
+              ptr(_opt(inv_cov_out, dev)), ptr(acc), stream_ptr())
+    return acc
+
+
+def wmoments_dense(x, nw, shift=None, cov=None, accumulate=False):
+    dev = require_cuda()
+    x = f32(x, dev)
+    K, D = x.shape
+    cov = torch.empty((D, D), dtype=torch.float32, device=dev) if cov is None else cov
+    nbytes = _lib.query("ppi_wmoments_dense_workspace_bytes", K, D)
+    ws = workspace("wmoments_dense", nbytes)
+    _lib.call("ppi_wmoments_dense", ptr(x), ptr(f32(nw, dev)), K, D, ptr(_opt(shift, dev)), ptr(cov),
+              int(bool(accumulate)), ptr(ws), nbytes, stream_ptr())
+    return cov
+
+
+def finalize_gaussian(s1=None, cov=None, shift=None, diagonal_only=False, want_mu=True,
+                      want_sigma=True):
+    dev = require_cuda()
+    D = (s1.numel() if s1 is not None else cov.shape[0])
+    mu = torch.empty(D, dtype=torch.float32, device=dev) if want_mu else None
+    sigma = torch.empty((D, D), dtype=torch.float32, device=dev) if want_sigma else None
+    _lib.call("ppi_finalize_gaussian", ptr(s1), ptr(cov), D, ptr(_opt(shift, dev)),
+              int(bool(diagonal_only)), ptr(mu), ptr(sigma), stream_ptr())
+    return mu, sigma
+
+
+def finalize_matnorm(s1, acc, H, d, jitter=0.0):
+    """-> dict(mean64, mean32, cov64, cov32, chol64, chol32, status) (status is a device int32)."""
+    dev = require_cuda()
+    out = dict(
+        mean64=torch.empty((H, d), dtype=torch.float64, device=dev),
+        mean32=torch.empty((H, d), dtype=torch.float32, device=dev),
+    )
+    if acc is not None:
+        out.update(
+            cov64=torch.empty((H, H), dtype=torch.float64, device=dev),
+            cov32=torch.empty((H, H), dtype=torch.float32, device=dev),
+            chol64=torch.empty((H, H), dtype=torch.float64, device=dev),
+            chol32=torch.empty((H, H), dtype=torch.float32, device=dev),
+            status=torch.zeros(1, dtype=torch.int32, device=dev),
+        )
+    _lib.call("ppi_finalize_matnorm", ptr(s1), ptr(acc), H, d, float(jitter), ptr(out["mean64"]),
+              ptr(out["mean32"]), ptr(out.get("cov64")), ptr(out.get("cov32")), ptr(out.get("chol64")),
+              ptr(out.get("chol32")), ptr(out.get("status")), stream_ptr())
+    return out

@@ -1,0 +1,969 @@
+"""Action priors with the reference's policy protocol (ppi/policies.py), computing on the B200.
+
+Drop-in surface: same class names, constructor keywords (superset tolerated),
+`policy(n) -> (actions, params)`, `weighted_update(log_weights, samples, update_covariance_in)
+-> (ess, kl)`, readable / writable NumPy attributes (`mu`, `sigma`; `mean`, `covariance_in`,
+`covariance_in_sqrt`, `covariance_out`, ...).  Sampling and moment matching run in
+libppi_b200.so; the host keeps fp64 mirrors of the small state (H x H, H x d) exactly like the
+reference keeps its attributes.  The host-side bookkeeping the reference does between updates
+(`update_timesteps`, `condition`, `predict`) stays NumPy on those mirrors.
+"""
+from __future__ import annotations
+
+import logging
+
+import numpy as np
+import torch
+
+from . import ops, samplers
+from .device import (DeviceArray, all_reduce_sum, broadcast_row, dist_info, f32, f64, require_cuda,
+                     shard_rows)
+
+__all__ = [
+    "RbfFeatures",
+    "RffFeatures",
+    "SquaredExponentialKernel",
+    "WhiteNoiseKernel",
+    "WhiteNoiseIid",
+    "ColouredNoise",
+    "SmoothActionNoise",
+    "SmoothExplorationNoise",
+    "Matern12Kernel",
+    "Matern32Kernel",
+    "Matern52Kernel",
+    "PeriodicKernel",
+    "LinearGaussianDynamicalSystemKernel",
+    "GaussianPolicy",
+    "Limiter",
+    "design_moments",
+]
+
+EPS = np.finfo(np.float64).tiny  # ppi/policies.py:36
+SIGMA_MIN = 1e-6                 # ppi/policies.py:37
+_LOG_EPS = float(np.log(EPS))
+_LOG_MAX = float(np.log(np.finfo(np.float64).max))
+
+
+# ------------------------------------------------------------------------------------------------
+# small host helpers (same contracts as ppi/policies.py:40-62,65-75,146-158,213-231)
+# ------------------------------------------------------------------------------------------------
+def design_moments(upper, lower, ratio):
+    """Matrix-normal moments that explore an actuator box (ppi/policies.py:40-50)."""
+    centre = 0.5 * (upper + lower)
+    var_out = 0.25 * np.square(upper - lower) / ratio
+    return centre, np.array([ratio]), np.diag(var_out)
+
+
+def symmetric(mat):
+    assert mat.ndim == 2
+    return 0.5 * (mat + mat.T)
+
+
+def factorized(mat):
+    assert mat.ndim == 2
+    return np.diag(np.diag(mat))
+
+
+class Limiter(object):
+    """Clip actions to the actuator range (ppi/policies.py:65-75).  The sampling kernels fuse the
+    clip into their epilogue; calling the object clips a host array."""
+
+    def __init__(self, upper, lower):
+        assert upper.shape == lower.shape
+        self.dim = upper.shape[0]
+        self.upper, self.lower = upper, lower
+
+    def __call__(self, x):
+        assert x.shape[-1] == self.dim, f"{x.shape}, {self.dim}"
+        return np.clip(x, a_max=self.upper, a_min=self.lower).reshape(x.shape)
+
+
+def null_limiter(action_sequence):
+    return action_sequence
+
+
+def _limits(limiter):
+    """(lower, upper) arrays for the kernel epilogue, or (None, None)."""
+    if limiter is None or limiter is null_limiter:
+        return None, None
+    lo, hi = getattr(limiter, "lower", None), getattr(limiter, "upper", None)
+    if lo is None or hi is None:
+        raise TypeError("ppi_b200 policies need a Limiter with .lower/.upper (or null_limiter)")
+    return np.asarray(lo, np.float64), np.asarray(hi, np.float64)
+
+
+def _clamped_logdet(logdet, positive=True):
+    """log(max(EPS, det)) of ppi/policies.py:153-154,214 evaluated from a log-determinant: keeps
+    the reference's clamp at EPS and its overflow to +inf without forming the determinant."""
+    if not positive or logdet < _LOG_EPS:
+        return _LOG_EPS
+    if logdet > _LOG_MAX:
+        return float("inf")
+    return float(logdet)
+
+
+def multivariate_gaussian_entropy(sigma, d):
+    sign, logdet = np.linalg.slogdet(sigma)
+    return 0.5 * _clamped_logdet(logdet, sign > 0) + (d / 2) * (1 + np.log(2 * np.pi))
+
+
+def multivariate_gaussian_kl(mu_1, sigma_1, mu_2, sigma_2):
+    """KL(N1 || N2), ppi/policies.py:146-158 (host version for small D)."""
+    d = sigma_1.shape[0]
+    diff = mu_2 - mu_1
+    s1, l1 = np.linalg.slogdet(sigma_1)
+    s2, l2 = np.linalg.slogdet(sigma_2)
+    return 0.5 * (_clamped_logdet(l2, s2 > 0) - _clamped_logdet(l1, s1 > 0)
+                  + np.trace(np.linalg.solve(sigma_2, sigma_1)) + diff @ np.linalg.solve(sigma_2, diff)
+                  - d)
+
+
+def matrix_normal_entropy(covariance_in, covariance_out, d_in, d_out):
+    """ppi/policies.py:219-231."""
+    sf = d_out / np.trace(covariance_out)
+    s_i, l_i = np.linalg.slogdet(covariance_in / sf)
+    s_o, l_o = np.linalg.slogdet(sf * covariance_out)
+    logdet_in = d_out * _clamped_logdet(l_i, s_i > 0)
+    logdet_out = d_in * _clamped_logdet(l_o, s_o > 0)
+    return 0.5 * (logdet_in + logdet_out) + (d_in * d_out / 2) * (1 + np.log(2 * np.pi))
+
+
+# ------------------------------------------------------------------------------------------------
+# weights handed from the optimizers to weighted_update
+# ------------------------------------------------------------------------------------------------
+class DeviceWeights:
+    """Normalised weights of all K (global) samples on the device + the solver statistics.
+    np.asarray(obj) yields the unnormalised log-weights, so foreign policies still work."""
+
+    def __init__(self, nw, log_w, stats):
+        self.nw, self.log_w, self.stats = nw, log_w, stats
+
+    @property
+    def shape(self):
+        return tuple(self.nw.shape)
+
+    def __len__(self):
+        return self.nw.shape[0]
+
+    def __array__(self, dtype=None, copy=None):
+        src = self.log_w if self.log_w is not None else torch.log(self.nw)
+        a = src.detach().cpu().numpy().astype(np.float64)
+        return a if dtype is None else a.astype(dtype, copy=False)
+
+    def max(self):
+        return float(np.asarray(self).max())
+
+    def min(self):
+        return float(np.asarray(self).min())
+
+
+def _weights(log_weights):
+    """Anything the reference accepts as log_weights -> DeviceWeights."""
+    if isinstance(log_weights, DeviceWeights):
+        return log_weights
+    lw = log_weights.tensor if isinstance(log_weights, DeviceArray) else log_weights
+    nw, stats = ops.normalise_log_weights(lw)
+    return DeviceWeights(nw, f32(lw).reshape(-1), stats)
+
+
+def _samples(samples):
+    """Samples handle or host array -> (local tensor, row_offset, global_rows, replicated)."""
+    if isinstance(samples, DeviceArray):
+        return samples.tensor, samples.row_offset, samples.global_rows, False
+    t = f32(samples)
+    return t, 0, t.shape[0], True  # host arrays are complete on every rank
+
+
+def _local(nw, row_offset, n_local):
+    return nw[row_offset:row_offset + n_local] if nw.shape[0] != n_local else nw
+
+
+def _row(samples_t, row_offset, n_total, replicated, index):
+    """samples[index] as a host fp64 array; under K-sharding the owner broadcasts the row."""
+    if replicated or dist_info()[1] == 1:
+        return samples_t[index - row_offset].detach().cpu().numpy().astype(np.float64)
+    return broadcast_row(samples_t, index, n_total).cpu().numpy().astype(np.float64)
+
+
+def _draw(sampler, n_total, d):
+    """Base normals for this rank's rows: (z_local or None, seed, draw_id, row_offset, n_local)."""
+    begin, end = shard_rows(n_total)
+    if hasattr(sampler, "device_normals"):
+        z, seed, draw = sampler.device_normals(n_total, d)
+    else:  # foreign sampler obeying only the reference protocol
+        z = f32(np.asarray(sampler(np.zeros((d,)), np.eye(1), n_total, standard_gaussian=True)))
+        seed = draw = 0
+    if z is not None:
+        n_total = z.shape[0]
+        begin, end = shard_rows(n_total)
+        z = z.reshape(n_total, d)[begin:end].contiguous()
+    return z, seed, draw, begin, end - begin, n_total
+
+
+# ------------------------------------------------------------------------------------------------
+# Gaussian policy (optimisation experiments)                               ppi/policies.py:234-281
+# ------------------------------------------------------------------------------------------------
+class GaussianPolicy(object):
+
+    name = "Gaussian"
+    small_dim = 128  # at or below: SIMT kernels + host fp64 tail; above: tcgen05 + device tail
+
+    def __init__(self, mu, sigma, sampler, diagonal=False):
+        self.sigma_init = np.array(sigma, dtype=np.float64)
+        self.sampler = sampler
+        self.diagonal = diagonal  # factorized covariance
+        self._set(np.array(mu, dtype=np.float64), np.array(sigma, dtype=np.float64))
+
+    # -- state: device fp32 copies used by the kernels, host fp64 mirrors read by callers --------
+    def _set(self, mu, sigma, chol64=None, logdet=None):
+        self._mu_host, self._sigma_host = mu, sigma
+        self._mu_dev = self._sigma_dev = self._chol_dev = None
+        self._chol64_dev, self._logdet = chol64, logdet
+
+    @property
+    def mu(self):
+        if self._mu_host is None:
+            self._mu_host = self._mu_dev.double().cpu().numpy()
+        return self._mu_host
+
+    @mu.setter
+    def mu(self, value):
+        self._mu_host, self._mu_dev = np.asarray(value, np.float64), None
+
+    @property
+    def sigma(self):
+        if self._sigma_host is None:
+            self._sigma_host = self._sigma_dev.double().cpu().numpy()
+        return self._sigma_host
+
+    @sigma.setter
+    def sigma(self, value):
+        self._sigma_host, self._sigma_dev = np.asarray(value, np.float64), None
+        self._chol_dev = self._chol64_dev = self._logdet = None
+
+    def _mu_d(self):
+        if self._mu_dev is None:
+            self._mu_dev = f32(self._mu_host)
+        return self._mu_dev
+
+    def _sigma64_d(self):
+        if self._sigma_dev is not None:
+            return self._sigma_dev.double()
+        return f64(self._sigma_host)
+
+    def _factor(self):
+        """Lower Cholesky factor of sigma on the device (fp64 factorisation, fp32 copy for the
+        sampling kernels) + log-determinant; cached until sigma changes."""
+        if self._chol_dev is None:
+            if self._chol64_dev is None:
+                s64 = self._sigma64_d()
+                if s64.shape[0] <= 160:
+                    l64, status = ops.cholesky_small(s64)
+                    if status != 0:
+                        raise np.linalg.LinAlgError("sigma is not positive definite")
+                else:
+                    l64 = torch.linalg.cholesky(s64)
+                self._chol64_dev = l64
+            self._chol_dev = self._chol64_dev.float().contiguous()
+            self._logdet = float(2.0 * torch.log(torch.diagonal(self._chol64_dev)).sum().item())
+        return self._chol_dev
+
+    @property
+    def entropy(self):
+        d = self.sigma_init.shape[0]
+        if d <= self.small_dim:
+            return multivariate_gaussian_entropy(self.sigma, d)
+        self._factor()
+        return 0.5 * _clamped_logdet(self._logdet) + (d / 2) * (1 + np.log(2 * np.pi))
+
+    def __call__(self, n_samples):
+        d = self.sigma_init.shape[0]
+        if not hasattr(self.sampler, "device_normals"):
+            # foreign sampler: it owns the transform (ppi/policies.py:248)
+            x = np.asarray(self.sampler(self.mu, self.sigma, n_samples, standard_gaussian=False))
+            begin, end = shard_rows(x.shape[0])
+            handle = DeviceArray(f32(x[begin:end]), begin, x.shape[0])
+            return handle, handle
+        z, seed, draw, begin, n_local, n_total = _draw(self.sampler, n_samples, d)
+        x = ops.sample_gaussian(n_local, self._mu_d(), self._factor(), z=z, seed=seed, draw_id=draw,
+                                row_offset=begin)
+        handle = DeviceArray(x, begin, n_total)
+        return handle, handle
+
+    def weighted_update(self, log_weights, samples, update_covariance_in=True):
+        w = _weights(log_weights)
+        x, row_offset, n_total, replicated = _samples(samples)
+        nw = _local(w.nw, row_offset, x.shape[0])
+        d = x.shape[1]
+        mu_old, sigma_old = self.mu.copy(), self.sigma.copy()
+        old_chol64, old_logdet = None, None
+        if d > self.small_dim:
+            self._factor()
+            old_chol64, old_logdet = self._chol64_dev, self._logdet
+
+        # pass 1: weighted mean, centred on the old mean for fp32 accuracy (policies.py:88)
+        shift_old = self._mu_d()
+        s1 = ops.wmoments_diag(x, nw, shift1=shift_old)
+        if not replicated:
+            all_reduce_sum(s1)
+        mu_new_dev, _ = ops.finalize_gaussian(s1=s1, shift=shift_old, want_sigma=False)
+        mu_new = mu_old + s1.cpu().numpy()
+
+        # pass 2: covariance centred on the new mean (policies.py:89-92)
+        sigma_new_host = sigma_new_dev = chol64 = None
+        pd = True
+        if not update_covariance_in:
+            pass
+        elif self.diagonal:
+            _, s2 = ops.wmoments_diag(x, nw, shift2=mu_new_dev, second=True)
+            if not replicated:
+                all_reduce_sum(s2)
+            var = s2.cpu().numpy()
+            sigma_new_host = np.diag(var)
+            pd = bool(np.all(var > 0.0) and np.all(np.isfinite(var)))
+            if pd:
+                chol64 = torch.diag(torch.sqrt(s2))
+        elif d <= self.small_dim:
+            acc = ops.wmoments_matnorm(x.reshape(x.shape[0], d, 1), nw, shift=mu_new_dev.reshape(d, 1))
+            if not replicated:
+                all_reduce_sum(acc)
+            fin = ops.finalize_matnorm(torch.zeros(d, dtype=torch.float64, device=x.device), acc, d, 1)
+            sigma_new_host = fin["cov64"].cpu().numpy()
+            pd = int(fin["status"].item()) == 0
+            chol64 = fin["chol64"]
+        else:
+            cov = ops.wmoments_dense(x, nw, shift=mu_new_dev)
+            if not replicated:
+                all_reduce_sum(cov)
+            sigma_new_dev = cov
+            chol64, info = torch.linalg.cholesky_ex(cov.double())
+            pd = int(info.item()) == 0
+
+        # accept / regularise exactly like ppi/policies.py:258-268
+        self._mu_host, self._mu_dev = mu_new, mu_new_dev
+        if update_covariance_in:
+            if pd:
+                self._sigma_host, self._sigma_dev = sigma_new_host, sigma_new_dev
+                self._chol64_dev, self._chol_dev, self._logdet = chol64, None, None
+            else:
+                logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
+                self.sigma = sigma_old + SIGMA_MIN * np.eye(d)
+        ess = float(w.stats.ess)
+        return ess, self._kl(mu_old, sigma_old, old_chol64, old_logdet)
+
+    def _kl(self, mu_old, sigma_old, old_chol64, old_logdet):
+        """KL(new || old), ppi/policies.py:146-158,269."""
+        d = mu_old.shape[0]
+        if d <= self.small_dim:
+            return float(multivariate_gaussian_kl(self.mu, self.sigma, mu_old, sigma_old))
+        self._factor()
+        l_new, logdet_new = self._chol64_dev, self._logdet
+        diff = f64(mu_old - self.mu)
+        # tr(S_old^-1 S_new) = |L_old^-1 L_new|_F^2 ; diff^T S_old^-1 diff = |L_old^-1 diff|^2
+        a = torch.linalg.solve_triangular(old_chol64, l_new, upper=False)
+        b = torch.linalg.solve_triangular(old_chol64, diff[:, None], upper=False)
+        tr = float((a * a).sum().item())
+        quad = float((b * b).sum().item())
+        return 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(logdet_new) + tr + quad - d)
+
+    @staticmethod
+    def smooth(x, y, alpha):
+        return alpha * x + (1 - alpha) * y
+
+    def smooth_update(self, mu, sigma, alpha):
+        self.mu = self.smooth(mu, self.mu, alpha)
+        self.sigma = self.smooth(sigma, self.sigma, alpha)
+
+    def reset_covariance(self):
+        self.sigma = self.sigma_init.copy()
+
+
+# ------------------------------------------------------------------------------------------------
+# Matrix-normal primitives                                                 ppi/policies.py:288-390
+# ------------------------------------------------------------------------------------------------
+class BasePrimitive(object):
+    """Kernel- and feature-based policies: matrix-normal over (dim_features, dim_out)."""
+
+    dim_features: int
+    dim_out: int
+    map_sequence: np.ndarray = None
+
+    def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out, sampler,
+                 limiter=null_limiter, use_derivatives=False):
+        self.t = time_sequence
+        self.mean = mean
+        self.dim_out = action_dimension
+        self.covariance_in_init = covariance_in.copy()
+        self.covariance_in = covariance_in
+        self.covariance_in_sqrt = self._chol(covariance_in)
+        self.covariance_out = covariance_out
+        self.cov_out_sqrt = self._chol(self.covariance_out)
+        self._sampler = sampler
+        self._sampler_cache = {}
+        self.limiter = limiter
+        self.use_derivatives = use_derivatives
+
+    @staticmethod
+    def _chol(a):
+        """np.linalg.cholesky semantics on the device (single-block fp64 kernel)."""
+        a = np.asarray(a, np.float64)
+        if a.shape[0] > 160:
+            return np.linalg.cholesky(a)  # beyond the single-block kernel; not on the update path
+        l, status = ops.cholesky_small(a)
+        if status != 0:
+            raise np.linalg.LinAlgError("Matrix is not positive definite")
+        return l.cpu().numpy()
+
+    def reset_covariance(self):
+        self.covariance_in = self.covariance_in_init.copy()
+        self.covariance_in_sqrt = self._chol(self.covariance_in)
+
+    @property
+    def sampler(self):
+        # the reference instantiates the class on every access (ppi/policies.py:323-325); the
+        # instance is cached here so that the Philox draw counter advances between calls
+        key = self.dim_sample
+        if key not in self._sampler_cache:
+            self._sampler_cache[key] = self._sampler(key)
+        return self._sampler_cache[key]
+
+    @property
+    def dim_sample(self):
+        return self.dim_features * self.dim_out
+
+    @property
+    def mu_z(self):
+        return np.zeros((self.dim_sample,))
+
+    @property
+    def sigma_z(self):
+        return np.eye(self.dim_sample)
+
+    def condition(self, t, action):
+        dim_t = t.shape[0]
+        assert action.shape == (dim_t, self.dim_out), f"{action.shape} ~= {dim_t, self.dim_out}"
+        self._condition(t, action)
+
+    def _condition(self, t, action):
+        raise NotImplementedError
+
+    def update(self, mean, covariance_in):
+        assert mean.shape == (self.dim_features, self.dim_out)
+        assert covariance_in.shape == (self.dim_features, self.dim_features)
+        self.mean = mean
+        self.covariance_in = covariance_in
+        self.covariance_in_sqrt = self._chol(covariance_in)
+
+    def base_sample(self, n_samples):
+        """(n, dim_features, dim_out) standard normals as a host array (ppi/policies.py:361-365)."""
+        z = self.sampler(self.mu_z, self.sigma_z, n_samples, standard_gaussian=True)
+        return np.asarray(z).reshape((-1, self.dim_features, self.dim_out))
+
+    @staticmethod
+    def smooth(x, y, alpha):
+        return alpha * x + (1 - alpha) * y
+
+    def smooth_update(self, mean, covariance_in, alpha):
+        self.mean = self.smooth(mean, self.mean, alpha)
+        self.covariance_in = self.smooth(covariance_in, self.covariance_in, alpha)
+
+    @property
+    def entropy(self):
+        return 0.0  # ppi/policies.py:379-384
+
+    def compute_prior(self, plan_time):
+        self.t = plan_time
+
+    # -- shared device pieces ---------------------------------------------------------------------
+    def _l_out_is_diag(self):
+        c = np.asarray(self.cov_out_sqrt)
+        return bool(np.count_nonzero(c - np.diag(np.diag(c))) == 0)
+
+    def _mavn_update(self, w, x, row_offset, replicated, shift1, jitter):
+        """m_projection_mavn (ppi/policies.py:96-143, iterations=1, update_out=False) on the
+        device: returns host fp64 (mean, cov_in, chol or None, pd)."""
+        K_local, H, d = x.shape
+        nw = _local(w.nw, row_offset, K_local)
+        s1 = ops.wmoments_diag(x, nw, shift1=shift1)
+        if not replicated:
+            all_reduce_sum(s1)
+        base = 0.0 if shift1 is None else f64(shift1).reshape(-1)
+        shift = (s1 + base).float().reshape(H, d)
+        inv_out = 1.0 / np.diag(np.asarray(self.covariance_out, np.float64))
+        acc = ops.wmoments_matnorm(x, nw, shift=shift, inv_cov_out=inv_out)
+        if not replicated:
+            all_reduce_sum(acc)
+        fin = ops.finalize_matnorm(s1, acc, H, d, jitter=jitter)
+        packed = torch.cat([fin["mean64"].reshape(-1), fin["cov64"].reshape(-1),
+                            fin["chol64"].reshape(-1), fin["status"].double()]).cpu().numpy()
+        mean = packed[:H * d].reshape(H, d)
+        cov = packed[H * d:H * d + H * H].reshape(H, H)
+        chol = packed[H * d + H * H:H * d + 2 * H * H].reshape(H, H)
+        return mean, cov, chol, packed[-1] == 0.0
+
+
+class BaseFeatures(BasePrimitive):
+    """Feature-based policies (ppi/policies.py:393-516)."""
+
+    def update_timesteps(self, t, anneal=1.0, eps=1e-5):
+        self.t = t
+        if anneal < 1.0:
+            self.covariance_in = anneal * self.covariance_in + (1 - anneal) * self.covariance_in_init
+            self.covariance_in_sqrt = self._chol(self.covariance_in)
+
+    def __call__(self, n_samples):
+        """-> (limited trajectories ys (K,T,d or 2d), feature weights ws (K,F,d))."""
+        feat_t = self.feat(self.t)
+        dfeat_t = self.dfeat(self.t) if self.use_derivatives else None
+        lo, hi = _limits(self.limiter) if self.limiter else (None, None)
+        z, seed, draw, begin, n_local, n_total = _draw(self.sampler, n_samples, self.dim_sample)
+        ys, ws = ops.sample_features(n_local, self.mean_fn, self.mean, self.covariance_in_sqrt,
+                                     self.cov_out_sqrt, feat_t, dfeat_t, z=z, seed=seed, draw_id=draw,
+                                     row_offset=begin, lower=lo, upper=hi)
+        return DeviceArray(ys, begin, n_total), DeviceArray(ws, begin, n_total)
+
+    def predict(self, only_mean=False):
+        feat_t = self.feat(self.t)
+        mu_y = self.limiter(self.mean_fn[None, :] + feat_t @ self.mean)
+        if only_mean:
+            return mu_y
+        sigma_y_in = feat_t @ self.covariance_in @ feat_t.T
+        sigma_y_out = self.covariance_out
+        std_y_out = np.sqrt(np.outer(np.diag(sigma_y_in), np.diag(sigma_y_out)))
+        return mu_y, sigma_y_in, sigma_y_out, std_y_out
+
+    def feat(self, t):
+        raise NotImplementedError
+
+    def dfeat(self, t):
+        raise NotImplementedError
+
+    def _condition(self, t, action):
+        """Bayesian linear-regression conditioning on (t, action), ppi/policies.py:449-459."""
+        phi = self.feat(t)
+        prior_precision = np.linalg.inv(self.covariance_in)
+        precision = phi.T @ phi + prior_precision
+        rhs = (action - self.mean_fn[None, :]).T @ phi + self.mean.T @ prior_precision
+        self.mean = np.linalg.solve(precision, rhs.T)
+        self.covariance_in = np.linalg.inv(precision)
+
+    def weighted_update(self, log_weights, samples, update_covariance_in=True):
+        """Importance-weighted ML fit of the feature weights (ppi/policies.py:461-516)."""
+        w = _weights(log_weights)
+        x, row_offset, n_total, replicated = _samples(samples)
+        mean_, cov_in_, chol_, pd = self._mavn_update(w, x, row_offset, replicated, None, 1e-12)
+        ess = float(w.stats.ess)
+        if pd:
+            self.mean = mean_
+            if update_covariance_in:
+                self.covariance_in, self.covariance_in_sqrt = cov_in_, chol_
+        else:
+            logging.warning(f"Update error, ESS={ess}")
+            logging.warning("Weighted update error, reverting")
+            ess = int(w.stats.n_valid)
+        return ess, 0.0
+
+
+class RbfFeatures(BaseFeatures):
+    """Radial basis function features (ppi/policies.py:519-590)."""
+
+    def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out, lengthscale,
+                 n_features, sampler, use_derivatives, limiter=null_limiter, add_bias=False, *args,
+                 **kwargs):
+        assert lengthscale > 0.0
+        assert mean.shape == (action_dimension,), f"{mean.shape} != {(action_dimension,)}"
+        assert covariance_in.shape == (1,)
+        self.add_bias = add_bias
+        self.ls = lengthscale / np.sqrt(2)
+        self.n_features = n_features
+        self.dim_features = n_features + (1 if add_bias else 0)
+        self.centres = np.linspace(time_sequence[0], time_sequence[-1], n_features)[:, None]
+        self.norm = 1 / np.sqrt(np.sqrt(np.pi) * n_features * self.ls)
+        self.mean_fn = mean
+        super().__init__(time_sequence, action_dimension, np.zeros((self.dim_features, action_dimension)),
+                         covariance_in.item() * np.eye(self.dim_features), covariance_out, sampler, limiter,
+                         use_derivatives)
+
+    def _bump(self, t):
+        u = (t[:, None] - self.centres.T) / self.ls
+        return u, self.norm * np.exp(-0.5 * u * u)
+
+    def feat(self, t):
+        cols = [self._bump(t)[1]]
+        if self.add_bias:
+            cols.append(np.ones((t.shape[0], 1)))
+        return np.concatenate(cols, axis=1)
+
+    def dfeat(self, t):
+        u, g = self._bump(t)
+        cols = [-(u / self.ls) * g]
+        if self.add_bias:
+            cols.append(np.zeros((t.shape[0], 1)))
+        return np.concatenate(cols, axis=1)
+
+
+class RffFeatures(BaseFeatures):
+    """Gauss-Hermite quadrature Fourier features (ppi/policies.py:593-663)."""
+
+    def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out, lengthscale,
+                 order, sampler, use_derivatives, add_bias=False, limiter=null_limiter, *args, **kwargs):
+        assert lengthscale > 0.0
+        assert mean.shape == (action_dimension,)
+        assert covariance_in.shape == (1,)
+        assert covariance_out.shape == (action_dimension, action_dimension)
+        self.add_bias = add_bias
+        self.ls = lengthscale
+        self.order = order
+        nodes, weights = np.polynomial.hermite.hermgauss(2 * order)
+        self.x = np.sqrt(2) * nodes[order:] / self.ls       # positive frequencies
+        self.w = 2 * weights[order:] / np.sqrt(np.pi)
+        self.dim_features = 2 * order + (1 if add_bias else 0)
+        self.mean_fn = mean
+        super().__init__(time_sequence, action_dimension, np.zeros((self.dim_features, action_dimension)),
+                         covariance_in.item() * np.eye(self.dim_features), covariance_out, sampler, limiter,
+                         use_derivatives)
+
+    def feat(self, t):
+        phase = np.outer(t, self.x)
+        amp = np.sqrt(self.w)[None, :]
+        cols = [np.cos(phase) * amp, np.sin(phase) * amp]
+        if self.add_bias:
+            cols.append(np.ones((t.shape[0], 1)))
+        return np.concatenate(cols, axis=1)
+
+    def dfeat(self, t):
+        phase = np.outer(t, self.x)
+        amp = (self.x * np.sqrt(self.w))[None, :]
+        cols = [-np.sin(phase) * amp, np.cos(phase) * amp]
+        if self.add_bias:
+            cols.append(np.zeros((t.shape[0], 1)))
+        return np.concatenate(cols, axis=1)
+
+
+class BaseKernel(BasePrimitive):
+    """Kernel (GP) policies (ppi/policies.py:666-860)."""
+
+    mean_fn: np.ndarray
+    covariance_in_prior: np.ndarray = None
+    covariance_in_prior_inv: np.ndarray = None
+    kernel_kind: str = None
+
+    def k(self, t1, t2):
+        raise NotImplementedError
+
+    def reset_covariance(self):
+        self.covariance_in = self.k(self.t, self.t)
+        self.covariance_in_sqrt = self._chol(self.covariance_in)
+
+    def __call__(self, n_samples):
+        lo, hi = _limits(self.limiter)
+        z, seed, draw, begin, n_local, n_total = _draw(self.sampler, n_samples, self.dim_sample)
+        xs = ops.sample_matnorm(n_local, self.mean_fn, self.mean, self.covariance_in_sqrt,
+                                self.cov_out_sqrt, z=z, seed=seed, draw_id=draw, row_offset=begin,
+                                lower=lo, upper=hi, l_out_is_diag=self._l_out_is_diag())
+        handle = DeviceArray(xs, begin, n_total)
+        return handle, handle  # the clipped samples are also the fitted "parameters" (:744-745)
+
+    def compute_prior(self, plan_time):
+        self.t = plan_time
+        self.covariance_in_prior = self.k(plan_time, plan_time)
+        self.covariance_in_prior_inv = np.linalg.inv(self.covariance_in_prior)
+
+    def timesteps_match(self, t):
+        return t.shape == self.t.shape and bool((t == self.t).all())
+
+    def update_timesteps(self, time_sequence, anneal=1.0, eps=1e-5):
+        """GP shift of mean / covariance onto a new time window (ppi/policies.py:761-791)."""
+        assert 0.0 <= anneal <= 1.0
+        if self.timesteps_match(time_sequence):
+            return
+        n_new = time_sequence.shape[0]
+        if n_new != self.covariance_in_prior.shape[0]:
+            self.covariance_in_prior = self.k(self.t, self.t)
+            self.covariance_in_prior_inv = np.linalg.inv(self.covariance_in_prior)
+        p_inv = self.covariance_in_prior_inv
+        gain = p_inv @ (self.covariance_in_prior - self.covariance_in) @ p_inv.T
+        cross = self.k(time_sequence, self.t)
+        shifted = self.limiter(cross @ p_inv @ self.mean + self.mean_fn[None, :]) - self.mean_fn[None, :]
+        cov_new = (self.k(time_sequence, time_sequence) - anneal * cross @ gain @ cross.T
+                   + eps * self.sigma * np.eye(n_new))
+        self.mean = shifted
+        self.covariance_in = cov_new
+        self.covariance_in_sqrt = self._chol(cov_new)
+        self.t = time_sequence
+        self.dim_features = n_new
+
+    def _condition(self, t, action):
+        cov_p = self.k(t, t)
+        cov_tp = self.k(self.t, t)
+        self.mean = cov_tp @ np.linalg.solve(cov_p, action - self.mean_fn[None, :])
+        self.covariance_in = self.covariance_in - cov_tp @ np.linalg.solve(cov_p, cov_tp.T)
+        self.covariance_in_sqrt = self._chol(self.covariance_in)
+
+    def weighted_update(self, log_weights, samples, update_covariance_in=True):
+        """ppi/policies.py:804-848."""
+        w = _weights(log_weights)
+        x, row_offset, n_total, replicated = _samples(samples)
+        H, d = x.shape[1], x.shape[2]
+        self.map_sequence = _row(x, row_offset, n_total, replicated, int(w.stats.argmax))
+        shift1 = np.broadcast_to(np.asarray(self.mean_fn, np.float64)[None, :], (H, d))
+        mean_, cov_in_, chol_, pd = self._mavn_update(w, x, row_offset, replicated,
+                                                      np.ascontiguousarray(shift1), 0.0)
+        self.mean = mean_
+        ess = float(w.stats.ess)
+        if update_covariance_in:
+            if pd:
+                self.covariance_in, self.covariance_in_sqrt = cov_in_, chol_
+            else:
+                logging.warning(f"Update error, ESS={ess}")
+                logging.warning("Weighted update error, reverting")
+                jitter = SIGMA_MIN * np.eye(self.dim_features)
+                self.covariance_in = self.covariance_in + jitter
+                self.covariance_in_sqrt = self.covariance_in_sqrt + jitter
+                ess = int(w.stats.n_valid)
+        return ess, 0.0
+
+    def predict(self, only_mean=False):
+        mu_y = self.mean_fn[None, :] + self.mean
+        if only_mean:
+            return mu_y
+        sigma_y = np.sqrt(np.outer(np.diag(self.covariance_in), np.diag(self.covariance_out)))
+        return mu_y, self.covariance_in, self.covariance_out, sigma_y
+
+
+def _gram_host(kind, t1, t2, sigma, ls=1.0, period=1.0):
+    return ops.gram(kind, t1, t2, sigma, ls, period).cpu().numpy()
+
+
+class StationaryKernel(BaseKernel):
+    """Squared exponential, Matern, periodic (ppi/policies.py:863-1037).  The Gram matrix and its
+    Cholesky factor come from the single-block fp64 device kernel."""
+
+    param_bounds = ((1e-5, None), (1e-3, 1e3))
+
+    def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out, lengthscale,
+                 sampler, limiter=null_limiter, *args, **kwargs):
+        self.dim_features = time_sequence.shape[0]
+        assert lengthscale > 0.0
+        assert mean.shape == (action_dimension,), f"{mean.shape} != (action_dimension,)"
+        assert covariance_in.shape == (1,)
+        assert covariance_out.shape == (action_dimension, action_dimension)
+        self.mean_fn = mean
+        self.ls = lengthscale
+        self.sigma = covariance_in.item()
+        super().__init__(time_sequence, action_dimension, np.zeros((self.dim_features, action_dimension)),
+                         self.k(time_sequence, time_sequence), covariance_out, sampler, limiter)
+
+    @property
+    def param(self):
+        return self.sigma, self.ls
+
+    @param.setter
+    def param(self, params):
+        self.sigma, self.ls = params
+
+    def k(self, t1, t2):
+        return self._k(t1, t2, sigma=self.sigma, ls=self.ls)
+
+
+class SquaredExponentialKernel(StationaryKernel):
+    can_optimize = True
+    param_bounds = ((1e-5, None), (1e-5, 1e3))
+
+    @staticmethod
+    def _k(t1, t2, sigma, ls, lib=np):
+        return _gram_host("se", t1, t2, sigma, ls)
+
+
+class Matern12Kernel(StationaryKernel):
+    @staticmethod
+    def _k(t1, t2, sigma, ls, eps=1e-8, lib=np):
+        return _gram_host("matern12", t1, t2, sigma, ls)
+
+
+class Matern32Kernel(StationaryKernel):
+    @staticmethod
+    def _k(t1, t2, sigma, ls, eps=1e-8, lib=np):
+        return _gram_host("matern32", t1, t2, sigma, ls)
+
+
+class Matern52Kernel(StationaryKernel):
+    @staticmethod
+    def _k(t1, t2, sigma, ls, eps=1e-8, lib=np):
+        return _gram_host("matern52", t1, t2, sigma, ls)
+
+
+class PeriodicKernel(StationaryKernel):
+    param_bounds = ((1e-3, None), (1e-4, 1e3), (1e-3, 1e3))
+
+    def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out, lengthscale,
+                 period, sampler, limiter=null_limiter, use_derivatives=False, *args, **kwargs):
+        self.period = period
+        super().__init__(time_sequence, action_dimension, mean, covariance_in, covariance_out, lengthscale,
+                         sampler, limiter)
+
+    @property
+    def param(self):
+        return self.sigma, self.ls, self.period
+
+    @param.setter
+    def param(self, params):
+        self.sigma, self.ls, self.period = params
+
+    def k(self, t1, t2):
+        return self._k(t1, t2, sigma=self.sigma, ls=self.ls, per=self.period)
+
+    @staticmethod
+    def _k(t1, t2, sigma, ls, per, eps=1e-8, lib=np):
+        return _gram_host("periodic", t1, t2, sigma, ls, per)
+
+
+class WhiteNoiseKernel(BaseKernel):
+    """ppi/policies.py:1040-1104."""
+
+    param_bounds = ((1e-5, None),)
+
+    def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out, sampler,
+                 use_derivatives=False, limiter=null_limiter, *args, **kwargs):
+        self.dim_features = time_sequence.shape[0]
+        assert mean.shape == (action_dimension,), f"{mean.shape} != (action_dimension,)"
+        assert covariance_in.shape == (1,)
+        assert covariance_out.shape == (action_dimension, action_dimension)
+        self.mean_fn = mean
+        self.sigma = covariance_in.item()
+        super().__init__(time_sequence, action_dimension, np.zeros((self.dim_features, action_dimension)),
+                         self.k(time_sequence, time_sequence), covariance_out, sampler, limiter,
+                         use_derivatives)
+
+    @property
+    def param(self):
+        return self.sigma
+
+    @param.setter
+    def param(self, params):
+        self.sigma = params[0]
+
+    def k(self, t1, t2):
+        return self._k(t1, t2, self.sigma)
+
+    @staticmethod
+    def _k(t1, t2, sigma, lib=np):
+        return _gram_host("white", t1, t2, sigma)
+
+    def update_timesteps(self, time_sequence, anneal=1.0, eps=1e-7):
+        if self.timesteps_match(time_sequence):
+            return
+        n_new = time_sequence.shape[0]
+        keep = 1.0 * (time_sequence.reshape(-1, 1) == self.t.reshape(1, -1))  # new x old selector
+        fresh = np.eye(n_new) - keep @ keep.T
+        self.mean = keep @ self.mean
+        self.covariance_in = keep @ self.covariance_in @ keep.T + fresh @ self.k(time_sequence, time_sequence)
+        self.covariance_in_sqrt = self._chol(self.covariance_in)
+        self.t = time_sequence
+        self.dim_features = n_new
+
+
+class WhiteNoiseIid(object):
+    """Independent Gaussian noise per (time step, actuator) (ppi/policies.py:1107-1195)."""
+
+    can_optimize = False
+    map_sequence: np.ndarray = None
+
+    def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out,
+                 use_derivatives=False, limiter=null_limiter, sampler=None, *args, **kwargs):
+        self.dim_features = time_sequence.shape[0]
+        self.dim_out = action_dimension
+        assert mean.shape == (action_dimension,), f"{mean.shape} != (action_dimension,)"
+        assert covariance_in.shape == (1,)
+        assert covariance_out.shape == (action_dimension, action_dimension)
+        self.t = time_sequence
+        self.sigma = np.sqrt(covariance_out * covariance_in.item())
+        self.mean_fn = mean
+        self.mean = np.zeros((self.dim_features, action_dimension))
+        self.std = np.ones((self.dim_features, action_dimension)) @ self.sigma
+        self.limiter = limiter
+        # the reference draws with np.random.randn directly (:1167); here a device Philox stream
+        self._rng = samplers.MonteCarlo(self.dim_features * action_dimension)
+        self.injected_normals = []  # parity harness: queue of (K, H, d) standard normals
+
+    def compute_prior(self, t):
+        pass
+
+    def reset_covariance(self):
+        self.std = np.ones((self.dim_features, self.dim_out)) @ self.sigma
+
+    @property
+    def covariance_out(self):
+        return np.diag(self.std.mean(axis=0) ** 2)
+
+    @property
+    def entropy(self):
+        # diagonal covariance: log det = sum log var, with the reference's clamp
+        d = self.dim_out * self.dim_features
+        logdet = float(np.sum(np.log(self.std.flatten() ** 2)))
+        return 0.5 * _clamped_logdet(logdet) + (d / 2) * (1 + np.log(2 * np.pi))
+
+    def __call__(self, n_samples):
+        lo, hi = _limits(self.limiter)
+        begin, end = shard_rows(n_samples)
+        if self.injected_normals:
+            z = f32(self.injected_normals.pop(0)).reshape(n_samples, -1)[begin:end].contiguous()
+            seed = draw = 0
+        else:
+            z, seed, draw = self._rng.device_normals(n_samples, self.dim_features * self.dim_out)
+        xs = ops.sample_iid(end - begin, self.mean_fn, self.mean, self.std, z=z, seed=seed, draw_id=draw,
+                            row_offset=begin, lower=lo, upper=hi)
+        handle = DeviceArray(xs, begin, n_samples)
+        return handle, handle
+
+    def weighted_update(self, log_weights, samples, update_covariance_in=True):
+        w = _weights(log_weights)
+        x, row_offset, n_total, replicated = _samples(samples)
+        K_local, H, d = x.shape
+        nw = _local(w.nw, row_offset, K_local)
+        self.map_sequence = _row(x, row_offset, n_total, replicated, int(w.stats.argmax))
+        base = np.ascontiguousarray(np.broadcast_to(np.asarray(self.mean_fn, np.float64)[None, :], (H, d)))
+        s1 = ops.wmoments_diag(x, nw, shift1=base)
+        if not replicated:
+            all_reduce_sum(s1)
+        if update_covariance_in:
+            centre = (s1 + f64(base).reshape(-1)).float()
+            _, s2 = ops.wmoments_diag(x, nw, shift2=centre, second=True)
+            if not replicated:
+                all_reduce_sum(s2)
+            self.std = np.sqrt(s2.cpu().numpy().reshape(H, d))
+        self.mean = s1.cpu().numpy().reshape(H, d)
+        return float(w.stats.ess), 0.0
+
+    def update_timesteps(self, time_sequence, anneal=1.0, eps=1e-7):
+        n_new = time_sequence.shape[0]
+        keep = 1.0 * (time_sequence.reshape(-1, 1) == self.t.reshape(1, -1))
+        std_new = np.ones((n_new, self.dim_out)) @ self.sigma
+        fresh = np.eye(n_new) - keep @ keep.T
+        self.mean = keep @ self.mean
+        std = np.sqrt(np.square(keep @ self.std) + np.square(fresh @ std_new))
+        self.std = anneal * std + (1 - anneal) * std_new
+        self.t = time_sequence
+        self.dim_features = n_new
+
+    def predict(self, only_mean=False):
+        mean = self.mean_fn[None, :] + self.mean
+        return mean if only_mean else (mean, self.std ** 2)
+
+
+def _next_row(name, where):
+    class _NotYet(object):
+        def __init__(self, *a, **k):
+            raise NotImplementedError(
+                f"{name} ({where}) is a 'next' row of the scope table (SURVEY 8(f) row 2) and is "
+                "not built yet")
+
+    _NotYet.__name__ = name
+    return _NotYet
+
+
+ColouredNoise = _next_row("ColouredNoise", "ppi/policies.py:1198-1254")
+SmoothExplorationNoise = _next_row("SmoothExplorationNoise", "ppi/policies.py:1257-1290")
+SmoothActionNoise = _next_row("SmoothActionNoise", "ppi/policies.py:1293-1326")
+LinearGaussianDynamicalSystemKernel = _next_row("LinearGaussianDynamicalSystemKernel",
+                                                "ppi/policies.py:1329-1410")

@@ -1,0 +1,170 @@
+"""Base-normal samplers with the reference's sampler protocol (ppi/samplers.py:9-22):
+`Sampler(dimension)`, `sampler(mu, sigma, n_samples, standard_gaussian=False) -> (n, d)`.
+
+On top of the protocol, native samplers expose `device_normals(n, d, row_offset)` which the
+ppi_b200 policies use to keep the draw on the GPU: MonteCarlo returns Philox parameters (the
+normals are generated inside the sampling kernel), InjectedNormals returns a device tensor.
+QuasiMonteCarlo / CubatureQuadrature are "next" rows; the reference's
+classes can be passed to the policies unchanged and are consumed through the protocol.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import ops
+from .device import f32, require_cuda
+
+__all__ = ["QuasiMonteCarlo", "MonteCarlo", "CubatureQuadrature", "Particles", "InjectedNormals"]
+
+
+class BaseSampler(object):
+    def __call__(self, mu, sigma, n_samples, standard_gaussian):
+        raise NotImplementedError
+
+
+class MonteCarlo(BaseSampler):
+    """np.random.randn / multivariate_normal replacement (ppi/samplers.py:14-22) backed by
+    on-device Philox4x32-10.  The Philox seed is taken from NumPy's global RNG at construction so
+    that `np.random.seed(s)` in the runners (optimization/run_opt.py:44) still fixes the run.
+    The non-standard path uses the Cholesky transform mu + z L^T (numpy's mvn factors by SVD: same
+    distribution, different draws -- SURVEY 7.3 item 7)."""
+
+    def __init__(self, dimension, seed=None):
+        self.d = dimension
+        self.seed = int(np.random.randint(0, 2 ** 31 - 1)) if seed is None else int(seed)
+        self.draw_id = 0
+
+    def device_normals(self, n_samples, d):
+        """-> (z or None, seed, draw_id): None means 'generate with Philox inside the kernel'."""
+        draw = self.draw_id
+        self.draw_id += 1
+        return None, self.seed, draw
+
+    def __call__(self, mu, sigma, n_samples, standard_gaussian=False):
+        _, seed, draw = self.device_normals(n_samples, self.d)
+        if standard_gaussian:
+            d = self.d if mu is None else np.asarray(mu).shape[0]
+            return ops.philox_normal(n_samples, d, seed, draw).cpu().numpy().astype(np.float64)
+        dev = require_cuda()
+        L = torch.linalg.cholesky(torch.as_tensor(np.asarray(sigma, np.float64), device=dev))
+        x = ops.sample_gaussian(n_samples, mu, L.float(), seed=seed, draw_id=draw)
+        return x.cpu().numpy().astype(np.float64)
+
+
+class InjectedNormals(BaseSampler):
+    """Replays pre-generated standard normals (the parity harness of SURVEY 8(c)).  The queue is
+    class-level because the reference re-instantiates the sampler class on every access
+    (ppi/policies.py:323-325)."""
+
+    queue = []
+
+    def __init__(self, dimension):
+        self.d = dimension
+
+    @classmethod
+    def push(cls, z):
+        cls.queue.append(np.asarray(z))
+
+    def device_normals(self, n_samples, d):
+        z = InjectedNormals.queue.pop(0)
+        assert z.shape[0] == n_samples and z.size == n_samples * d, (z.shape, n_samples, d)
+        return f32(z).reshape(n_samples, d), 0, 0
+
+    def __call__(self, mu, sigma, n_samples, standard_gaussian=False):
+        z = InjectedNormals.queue.pop(0)
+        if standard_gaussian:
+            return np.array(z, dtype=np.float64)
+        L = np.linalg.cholesky(sigma)
+        return mu[None, :] + np.asarray(z, np.float64) @ L.T
+
+
+class QuasiMonteCarlo(BaseSampler):
+    """Scrambled-Sobol + erfinv base normals (ppi/samplers.py:25-44).  "Next" row:
+    the low-discrepancy points still come from SciPy on the host and are uploaded as injected
+    normals; the transform / sampling kernels run on the device."""
+
+    def __init__(self, dimension):
+        from scipy.stats import qmc
+
+        self.d = dimension
+        self.sampler = qmc.Sobol(d=dimension, scramble=True)
+
+    def _base(self, n_samples, shrinkage=0.9999):
+        from scipy.special import erfinv
+
+        with np.errstate(invalid="ignore"):
+            n_b2 = 2 ** int(np.ceil(np.log(n_samples) / np.log(2)))
+            sobol = shrinkage * self.sampler.random(n_b2)[:n_samples]
+            return np.sqrt(2) * erfinv(2 * sobol - 1)
+
+    def device_normals(self, n_samples, d):
+        assert d == self.d
+        return f32(self._base(n_samples)), 0, 0
+
+    def __call__(self, mu, sigma, n_samples, shrinkage=0.9999, standard_gaussian=False):
+        base = self._base(n_samples, shrinkage)
+        if standard_gaussian:
+            return base
+        return mu[None, :] + base @ np.linalg.cholesky(sigma).T
+
+    @staticmethod
+    def covariance_scale(n):
+        return n - 1
+
+
+class CubatureQuadrature(BaseSampler):
+    """2d sigma points (ppi/samplers.py:47-64); ignores n_samples like the reference."""
+
+    def __init__(self, dimension):
+        self.d = dimension
+        self.base_points = np.sqrt(self.d) * np.concatenate((np.eye(dimension), -np.eye(dimension)))
+
+    def device_normals(self, n_samples, d):
+        return f32(self.base_points), 0, 0
+
+    def __call__(self, mu, sigma, n_samples, standard_gaussian=False):
+        if standard_gaussian:
+            return self.base_points
+        return mu[None, :] + self.base_points @ np.linalg.cholesky(sigma).T
+
+    @property
+    def n_samples(self):
+        return 2 * self.d
+
+
+class Particles(object):
+    """Sample re-use for iCEM (ppi/samplers.py:67-102).  Protocol-only implementation: the
+    reference's add_particles unpacks a 3-D shape from the 2-D base-normal matrix and therefore
+    raises as soon as particles exist; the same happens here."""
+
+    has_particles = False
+
+    def __init__(self, dimension):
+        self.d = dimension
+        self._particles = None
+        self._mc = MonteCarlo(dimension)
+
+    @property
+    def particles(self):
+        return self._particles
+
+    @particles.setter
+    def particles(self, particles):
+        self._particles = particles
+        self.has_particles = True
+
+    def __call__(self, mu, sigma, n_samples, standard_gaussian=False):
+        samples = self._mc(mu, sigma, n_samples, standard_gaussian)
+        return self.add_particles(samples)
+
+    def add_particles(self, samples):
+        if self._particles is not None:
+            d_n, d_t, _ = samples.shape
+            n = min(self._particles.shape[0], d_n)
+            samples[:n, ...] = np.asarray(self._particles)[:n, :d_t, :]
+        return samples
+
+    @staticmethod
+    def covariance_scale(n):
+        return n - 1

@@ -1,0 +1,462 @@
+"""GPU parity tests, kernel level: every C-ABI entry point (through ppi_b200.ops) against the CPU
+oracle (oracle/ppi_oracle.py, itself pinned to the reference) and the committed golden fixtures.
+
+Tolerances (BASELINE.json north_star): fp32 results within 1e-5 relative -- norm-wise
+(max|delta| / max|ref|) for vectors and matrices, element-wise for scalars -- and bit-exact
+integer indices.  The cost kernels are compared at 2e-6 norm-wise (fp32 row sums of up to 1024
+terms).  REPS alpha is checked by root / dual properties.
+"""
+import numpy as np
+import pytest
+from scipy.special import logsumexp
+
+from oracle import ppi_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+
+
+def nerr(a, ref):
+    a, ref = np.asarray(a, np.float64), np.asarray(ref, np.float64)
+    assert a.shape == ref.shape, (a.shape, ref.shape)
+    return np.max(np.abs(a - ref)) / max(np.max(np.abs(ref)), 1e-300)
+
+
+def host(t):
+    return t.detach().cpu().numpy().astype(np.float64)
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import torch
+
+    assert torch.cuda.is_available()
+    from ppi_b200 import ops as _ops
+
+    return _ops
+
+
+def f32r(x):
+    return np.asarray(x, np.float32).astype(np.float64)
+
+
+# ------------------------------------------------------------------ a3 Philox normals
+def test_philox_moments_and_determinism(ops):
+    z = host(ops.philox_normal(4096, 840, seed=7, draw_id=3))
+    assert abs(z.mean()) < 3e-3 and abs(z.std() - 1.0) < 3e-3
+    assert abs(np.mean(z ** 4) - 3.0) < 3e-2
+    assert np.isfinite(z).all() and np.abs(z).max() < 7.0
+    z2 = host(ops.philox_normal(4096, 840, seed=7, draw_id=3))
+    assert (z == z2).all()
+    assert not (z == host(ops.philox_normal(4096, 840, seed=7, draw_id=4))).all()
+    # columns are uncorrelated
+    c = np.corrcoef(z[:, :32].T)
+    assert np.abs(c - np.eye(32)).max() < 0.08
+
+
+@pytest.mark.parametrize("cols", [840, 42, 7, 1])
+def test_philox_sharding_invariance(ops, cols):
+    """Rows [a, b) drawn with row_offset = a equal rows a..b of the full matrix bit for bit."""
+    full = host(ops.philox_normal(1000, cols, seed=11, draw_id=2))
+    for a, b in [(0, 250), (250, 501), (501, 1000)]:
+        part = host(ops.philox_normal(b - a, cols, seed=11, draw_id=2, row_offset=a))
+        assert (part == full[a:b]).all()
+
+
+# ------------------------------------------------------------------ a22 Gram + Cholesky
+def test_gram_matrices(ops, golden):
+    g = golden
+    t = g["se0.05_t"]
+    for kind, key in [("matern12", "gram_matern12"), ("matern32", "gram_matern32"),
+                      ("matern52", "gram_matern52")]:
+        k = host(ops.gram(kind, t, t, 2.0, 0.03))
+        np.testing.assert_allclose(k, g[key], rtol=1e-12, atol=1e-14)
+        np.testing.assert_allclose(k, O.gram(kind, t, t, 2.0, 0.03), rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(host(ops.gram("periodic", t, t, 2.0, 0.5, 0.04)), g["gram_periodic"],
+                               rtol=1e-10, atol=1e-12)
+    np.testing.assert_allclose(host(ops.gram("white", t, t, 2.0)), g["gram_white"])
+    # rectangular cross-covariance gets no jitter, square ones do (ppi/policies.py:929-931)
+    np.testing.assert_allclose(host(ops.gram("se", t[:5], t, 2.0, 0.03)), g["gram_se_cross"],
+                               rtol=1e-12, atol=1e-14)
+    for ls in (0.05, 1.0):
+        k, l, status = ops.gram("se", t, t, 1000.0, ls, chol=True)
+        assert status == 0
+        np.testing.assert_allclose(host(k), g[f"se{ls}_gram"], rtol=1e-12)
+        assert nerr(host(l), g[f"se{ls}_lin"]) < 1e-9
+        assert np.allclose(np.diag(host(k)), 1.001 * 1000.0)
+
+
+def test_cholesky_small(ops):
+    rng = np.random.default_rng(0)
+    for n in (1, 3, 30, 64, 129, 160):
+        a = rng.standard_normal((n, n + 3))
+        a = a @ a.T + 1e-3 * np.eye(n)
+        l, status = ops.cholesky_small(a)
+        assert status == 0
+        assert nerr(host(l), np.linalg.cholesky(a)) < 1e-10
+    bad = np.array([[1.0, 2.0], [2.0, 1.0]])
+    assert ops.cholesky_small(bad)[1] == 2  # second pivot fails
+
+
+# ------------------------------------------------------------------ a4-a8 sampling with injected normals
+@pytest.mark.parametrize("ls", [0.05, 1.0])
+def test_sample_matnorm_golden(ops, golden, ls):
+    g, tag = golden, f"se{ls}"
+    K, H, d = 64, 8, 3
+    z = g[f"{tag}_z"]
+    xs = ops.sample_matnorm(K, np.zeros(d), np.zeros((H, d)), g[f"{tag}_lin"], g[f"{tag}_lout"], z=z,
+                            lower=-np.ones(d), upper=np.ones(d), l_out_is_diag=True)
+    assert nerr(host(xs), g[f"{tag}_xs"]) < TOL
+
+
+@pytest.mark.parametrize("K,H,d,diag,clip", [(37, 30, 28, True, True), (5, 30, 28, False, False),
+                                             (130, 7, 2, False, True), (64, 100, 28, True, False),
+                                             (9, 1, 1, True, False)])
+def test_sample_matnorm_oracle(ops, K, H, d, diag, clip):
+    rng = np.random.default_rng(K + H)
+    z = f32r(rng.standard_normal((K, H, d)))
+    a = rng.standard_normal((H, H + 2))
+    l_in = f32r(np.linalg.cholesky(a @ a.T / H + 0.1 * np.eye(H)))
+    if diag:
+        l_out = f32r(np.diag(0.1 + rng.random(d)))
+    else:
+        b = rng.standard_normal((d, d + 2))
+        l_out = f32r(np.linalg.cholesky(b @ b.T / d + 0.1 * np.eye(d)))
+    mean_fn, mean = f32r(rng.standard_normal(d)), f32r(rng.standard_normal((H, d)))
+    lo, hi = (f32r(-1.0 - rng.random(d)), f32r(1.0 + rng.random(d))) if clip else (None, None)
+    ref = O.sample_matnorm(z, mean_fn, mean, l_in, l_out, lo, hi, naive=False)
+    xs = ops.sample_matnorm(K, mean_fn, mean, l_in, l_out, z=z, lower=lo, upper=hi, l_out_is_diag=diag)
+    assert nerr(host(xs), ref) < TOL
+
+
+def test_sample_matnorm_philox_matches_injected(ops):
+    """Philox mode == injected mode fed with ppi_philox_normal of the same (seed, draw, offset)."""
+    K, H, d = 50, 30, 28
+    rng = np.random.default_rng(1)
+    l_in = f32r(np.tril(rng.standard_normal((H, H))))
+    l_out = f32r(np.diag(rng.random(d)))
+    mean_fn, mean = np.zeros(d), np.zeros((H, d))
+    z = ops.philox_normal(K, H * d, seed=5, draw_id=9, row_offset=100)
+    a = host(ops.sample_matnorm(K, mean_fn, mean, l_in, l_out, z=z, l_out_is_diag=True))
+    b = host(ops.sample_matnorm(K, mean_fn, mean, l_in, l_out, seed=5, draw_id=9, row_offset=100,
+                                l_out_is_diag=True))
+    assert (a == b).all()
+
+
+@pytest.mark.parametrize("tag", ["rff", "rbf"])
+def test_sample_features_golden(ops, golden, tag):
+    g = golden
+    K = 64
+    ys, ws = ops.sample_features(K, np.array([0.0, 1.5707]), g[f"{tag}_mean0"], g[f"{tag}_lin0"],
+                                 g[f"{tag}_lout"], g[f"{tag}_feat"], g[f"{tag}_dfeat"], z=g[f"{tag}_z"])
+    assert nerr(host(ws), g[f"{tag}_ws"]) < TOL
+    assert nerr(host(ys), g[f"{tag}_ys"]) < TOL
+    # the oracle's feature builders reproduce the reference's feature matrices
+    t = g[f"{tag}_t"]
+    if tag == "rff":
+        f, df = O.rff_features(t, np.sqrt(3e-2), 3, True)
+    else:
+        f, df = O.rbf_features(t, t[0], t[-1], np.sqrt(3e-2), 6, True)
+    np.testing.assert_allclose(f, g[f"{tag}_feat"], rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(df, g[f"{tag}_dfeat"], rtol=1e-12, atol=1e-14)
+
+
+@pytest.mark.parametrize("K,F,d,T,deriv,clip", [(33, 21, 2, 1000, True, True), (7, 21, 2, 300, False, False),
+                                                (20, 9, 5, 130, True, False)])
+def test_sample_features_oracle(ops, K, F, d, T, deriv, clip):
+    rng = np.random.default_rng(F + T)
+    z = f32r(rng.standard_normal((K, F, d)))
+    a = rng.standard_normal((F, F + 2))
+    l_in = f32r(np.linalg.cholesky(a @ a.T / F + 0.1 * np.eye(F)))
+    l_out = f32r(np.diag(0.03 + 0.01 * rng.random(d)))
+    mean_fn, mean = f32r(rng.standard_normal(d)), f32r(rng.standard_normal((F, d)))
+    feat, dfeat = f32r(rng.standard_normal((T, F))), f32r(rng.standard_normal((T, F)))
+    dy = 2 * d if deriv else d
+    lo, hi = (f32r(-2.0 - rng.random(dy)), f32r(2.0 + rng.random(dy))) if clip else (None, None)
+    ref_y, ref_w = O.sample_features(z, mean_fn, mean, l_in, l_out, feat, dfeat if deriv else None,
+                                     lo, hi, naive=False)
+    ys, ws = ops.sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat if deriv else None, z=z,
+                                 lower=lo, upper=hi)
+    assert nerr(host(ws), ref_w) < TOL
+    assert nerr(host(ys), ref_y) < TOL
+
+
+def test_sample_iid_golden(ops, golden):
+    g = golden
+    K, H, d = 64, 8, 3
+    xs = ops.sample_iid(K, np.zeros(d), np.zeros((H, d)), g["iid_std0"], z=g["iid_z"],
+                        lower=-np.ones(d), upper=np.ones(d))
+    assert nerr(host(xs), g["iid_xs"]) < TOL
+
+
+@pytest.mark.parametrize("K,D", [(100, 2), (257, 20), (64, 128), (3, 1)])
+def test_sample_gaussian_small(ops, K, D):
+    rng = np.random.default_rng(D)
+    z = f32r(rng.standard_normal((K, D)))
+    a = rng.standard_normal((D, D + 2))
+    sigma = a @ a.T / D + 0.1 * np.eye(D)
+    L = f32r(np.linalg.cholesky(sigma))
+    mu = f32r(rng.standard_normal(D))
+    ref = mu[None, :] + z @ L.T
+    x = ops.sample_gaussian(K, mu, L, z=z)
+    assert nerr(host(x), ref) < TOL
+
+
+# ------------------------------------------------------------------ a9 costs
+def test_cost_functions_golden(ops, golden):
+    g = golden
+    x = g["fn_x"]
+    for name in ["Himmelblau", "Rosenbrock", "Styblinski", "Rastrigin"]:
+        assert nerr(host(ops.cost_function(name, x)), g["fn_" + name]) < 2e-6, name
+    c = ops.cost_function("NoisySphere", x, A=g["fn_ns_A"], noise=g["fn_ns_noise"])
+    assert nerr(host(c), g["fn_NoisySphere"]) < 2e-6
+
+
+@pytest.mark.parametrize("K,D", [(100, 2), (33, 5), (64, 1024), (17, 1023), (8, 2048)])
+def test_cost_functions_oracle(ops, K, D):
+    rng = np.random.default_rng(K * D)
+    x = f32r(1.0 + 0.7 * rng.standard_normal((K, D)))
+    for name, fn in [("Rosenbrock", O.rosenbrock), ("Styblinski", O.styblinski),
+                     ("Rastrigin", O.rastrigin), ("Himmelblau", O.himmelblau)]:
+        assert nerr(host(ops.cost_function(name, x)), fn(x)) < 2e-6, name
+    # known optima: Rosenbrock at ones, Rastrigin at zeros, Styblinski at -2.903534
+    one = np.ones((1, D))
+    assert abs(host(ops.cost_function("Rosenbrock", one))[0]) < 1e-6
+    assert abs(host(ops.cost_function("Rastrigin", 0 * one))[0]) < 1e-3 * D
+    assert abs(host(ops.cost_function("Styblinski", -2.903534 * one))[0]) < 1e-4 * D
+
+
+def test_cost_tracking(ops):
+    rng = np.random.default_rng(3)
+    for K, T, dy, dt in [(50, 30, 28, 28), (20, 1000, 4, 2), (3, 7, 3, 1)]:
+        t = np.linspace(0, 2, T)
+        tgt = f32r(O.tracking_target(t, dt))
+        x = f32r(rng.standard_normal((K, T, dy)))
+        assert nerr(host(ops.cost_tracking(x, tgt)), O.synthetic_return(x, tgt)) < 2e-6
+
+
+# ------------------------------------------------------------------ a2, a10-a15 weights
+def _costs(K, seed, kind="rosen"):
+    rng = np.random.default_rng(seed)
+    if kind == "rosen":
+        x = 1.0 + 0.7 * rng.standard_normal((K, 4))
+        return f32r(O.rosenbrock(x))
+    return f32r(rng.random(K) ** 2 * 50.0 - 3.0)
+
+
+def _check_weights(nw, log_w, st, ref_log_w, costs, alpha_ref=None, alpha_tol=TOL):
+    ref_nw = np.exp(ref_log_w - logsumexp(ref_log_w))
+    assert nerr(host(nw), ref_nw) < TOL
+    assert abs(st.ess - O.ess_of(ref_log_w)) < TOL * O.ess_of(ref_log_w)
+    assert abs(st.lse - logsumexp(ref_log_w)) < TOL * max(1.0, abs(logsumexp(ref_log_w)))
+    assert abs(st.weight_entropy - O.weight_entropy(ref_log_w)) < TOL * max(1.0, abs(O.weight_entropy(ref_log_w)))
+    assert st.argmax == int(np.argmax(ref_log_w))
+    assert st.n_valid == len(costs) and st.all_nan == 0
+    assert abs(st.cost_mean - costs.mean()) <= 1e-9 * max(1.0, abs(costs.mean()))
+    assert abs(st.cost_std - costs.std()) <= 1e-7 * max(1.0, costs.std())
+    if alpha_ref is not None:
+        assert abs(st.alpha - alpha_ref) < alpha_tol * abs(alpha_ref), (st.alpha, alpha_ref)
+    if log_w is not None:
+        assert nerr(host(log_w), ref_log_w) < TOL
+
+
+@pytest.mark.parametrize("K", [100, 4096, 65536])
+@pytest.mark.parametrize("kind", ["rosen", "uniform"])
+def test_fixed_temperature(ops, K, kind):
+    from ppi_b200 import _lib
+
+    c = _costs(K, 1, kind)
+    ref, _ = O.ais_log_w(c, 0.9)
+    _check_weights(*ops.solve_temperature(c, _lib.TEMP_FIXED_NORMALISED, 0.9), ref, c, 0.9)
+    ref, _ = O.mppi_log_w(c, 0.01)
+    _check_weights(*ops.solve_temperature(c, _lib.TEMP_FIXED_SHIFTED, 0.01), ref, c, 0.01)
+
+
+@pytest.mark.parametrize("K,n_elites", [(100, 10), (4096, 64), (65536, 1024), (300000, 10)])
+def test_ess_target(ops, K, n_elites):
+    from ppi_b200 import _lib
+
+    c = _costs(K, 2)
+    ref, alpha = O.essps_log_w(c, n_elites)
+    nw, lw, st = ops.solve_temperature(c, _lib.TEMP_ESS_TARGET, n_elites)
+    assert abs(st.ess - n_elites) < TOL * n_elites          # root property
+    _check_weights(nw, lw, st, ref, c, alpha)
+    assert st.status == 0 and st.iterations < 100
+
+
+@pytest.mark.parametrize("K,delta", [(100, 0.5), (4096, 0.9), (65536, 0.5)])
+def test_lower_bound(ops, K, delta):
+    from ppi_b200 import _lib
+
+    c = _costs(K, 3)
+    ref, alpha = O.lbps_log_w(c, delta)
+    nw, lw, st = ops.solve_temperature(c, _lib.TEMP_LOWER_BOUND, delta)
+    cn = O.normalise(c)
+    # the device minimiser is at least as good as Brent's
+    assert O.lbps_objective(st.alpha, cn, delta) <= O.lbps_objective(alpha, cn, delta) + 1e-7
+    _check_weights(nw, lw, st, ref, c, alpha)
+
+
+@pytest.mark.parametrize("K,eps", [(100, 0.1), (4096, 2.0), (65536, 0.5)])
+def test_reps_root_properties(ops, K, eps):
+    from ppi_b200 import _lib
+
+    c = _costs(K, 4)
+    cn = O.normalise(c)
+    _, alpha_ref = O.reps_log_w(c, eps)
+    nw, lw, st = ops.solve_temperature(c, _lib.TEMP_REPS_KL, eps)
+    assert 1e-5 <= st.alpha <= 5e2
+    if st.status == 0:
+        assert abs(O.reps_kl(st.alpha, cn) - eps) < 1e-5                     # stationarity
+    assert O.reps_dual(st.alpha, cn, eps) <= O.reps_dual(float(alpha_ref[0]), cn, eps) + 1e-9
+    # weights at the device alpha match the oracle's formula at that alpha
+    _check_weights(nw, lw, st, -st.alpha * cn, c)
+
+
+def test_nan_filter_and_degenerate_costs(ops, golden):
+    from ppi_b200 import _lib
+
+    c = golden["nan_c"].copy()
+    good = ~np.isnan(c)
+    ref, alpha = O.essps_log_w(c[good], 4)
+    nw, lw, st = ops.solve_temperature(c, _lib.TEMP_ESS_TARGET, 4)
+    nwh = host(nw)
+    assert (nwh[~good] == 0).all() and np.isneginf(host(lw)[~good]).all()
+    assert nerr(nwh[good], np.exp(ref - logsumexp(ref))) < TOL
+    assert st.n_valid == good.sum() and st.all_nan == 0
+    assert abs(st.alpha - alpha) < TOL * alpha
+    assert abs(st.cost_mean - c[good].mean()) < 1e-9 and abs(st.cost_std - c[good].std()) < 1e-7
+    assert st.argmax == int(np.flatnonzero(good)[np.argmax(ref)])
+    # all NaN: costs := 0, nothing filtered (ppi/algorithms.py:62-64)
+    nw, lw, st = ops.solve_temperature(np.full(16, np.nan), _lib.TEMP_FIXED_NORMALISED, 0.9)
+    assert st.all_nan == 1 and st.n_valid == 16
+    assert np.allclose(host(nw), 1 / 16) and abs(st.ess - 16) < 1e-9
+    # all equal: (c - min) / (0 + EPS) = 0 -> uniform
+    nw, lw, st = ops.solve_temperature(np.full(100, 3.5), _lib.TEMP_FIXED_NORMALISED, 5.0)
+    assert np.allclose(host(nw), 0.01) and st.argmax == 0
+    nw, lw, st = ops.solve_temperature(np.full(100, 3.5), _lib.TEMP_LOWER_BOUND, 0.5)
+    assert np.allclose(host(nw), 0.01)
+    # a single sample
+    nw, lw, st = ops.solve_temperature(np.array([2.0]), _lib.TEMP_ESS_TARGET, 1)
+    assert host(nw)[0] == 1.0
+
+
+@pytest.mark.parametrize("K,k", [(100, 10), (2048, 1), (5000, 77), (65536, 1024), (300000, 4096)])
+def test_cem_elites_bit_exact(ops, K, k):
+    c = _costs(K, 5, "uniform")
+    c[::7] = np.nan if K > 1000 else c[::7]
+    good = ~np.isnan(c)
+    order = np.lexsort((np.arange(K), np.where(good, c, np.inf)))  # NaN last, ties by index
+    idx, nw, st = ops.cem_weights(c, k)
+    idx = idx.cpu().numpy()
+    n_good = int(good.sum())
+    assert (idx[:n_good] == order[:n_good]).all()                   # bit-exact argsort
+    assert sorted(idx[n_good:]) == sorted(np.flatnonzero(~good))
+    nwh = host(nw)
+    assert (nwh[order[:k]] == np.float32(1.0 / k)).all() and nwh.sum() == pytest.approx(1.0, abs=1e-6)
+    assert np.count_nonzero(nwh) == k
+    assert st.ess == k and st.argmax == order[0] and st.n_valid == n_good
+    assert abs(st.weight_entropy + np.log(k)) < 1e-12
+    assert abs(st.cost_mean - c[good].mean()) < 1e-9 * max(1, abs(c[good].mean()))
+
+
+def test_cem_ties_resolved_by_index(ops):
+    c = np.array([3.0, 1.0, 1.0, 2.0, 1.0, 0.5, 2.0, -0.0, 0.0], np.float32)
+    idx, nw, st = ops.cem_weights(c, 3)
+    assert idx.cpu().numpy().tolist() == [7, 8, 5, 1, 2, 4, 3, 6, 0]
+    assert st.argmax == 7
+
+
+@pytest.mark.parametrize("K", [128, 5000, 100000])
+def test_normalise_log_weights(ops, K):
+    rng = np.random.default_rng(K)
+    lw = f32r(-30.0 * rng.random(K) + 1000.0)  # needs the max shift
+    lw[3] = -np.inf
+    nw, st = ops.normalise_log_weights(lw)
+    ref = np.exp(lw - logsumexp(lw))
+    assert nerr(host(nw), ref) < TOL
+    assert abs(st.lse - logsumexp(lw)) < 1e-7 * abs(logsumexp(lw))
+    assert abs(st.ess - O.ess_of(lw)) < TOL * O.ess_of(lw)
+    assert st.argmax == int(np.argmax(lw))
+    fin = np.isfinite(lw)
+    we = (ref[fin] * (lw[fin] - logsumexp(lw))).sum()
+    assert abs(st.weight_entropy - we) < TOL * abs(we)
+    # CEM-style {0, -1e12} weights are exactly 1/k
+    lw = np.full(K, -1e12)
+    lw[5:15] = 0.0
+    nw, st = ops.normalise_log_weights(lw)
+    assert (host(nw)[5:15] == np.float32(0.1)).all() and abs(st.ess - 10) < 1e-9 and st.argmax == 5
+
+
+# ------------------------------------------------------------------ a16-a21 moments
+@pytest.mark.parametrize("K,D", [(100, 2), (1000, 840), (5000, 42), (4096, 1024), (333, 7), (70000, 64)])
+def test_wmoments_diag(ops, K, D):
+    rng = np.random.default_rng(K + D)
+    x = f32r(2.0 + rng.standard_normal((K, D)))
+    lw = f32r(-5 * rng.random(K))
+    nw = f32r(np.exp(lw - logsumexp(lw)))
+    nw[::11] = 0.0
+    x[::11] = np.nan  # zero-weight rows may be garbage
+    xs = np.nan_to_num(x)
+    a, b = f32r(rng.standard_normal(D)), f32r(2.0 + rng.standard_normal(D))
+    s1, s2 = ops.wmoments_diag(x, nw, shift1=a, shift2=b, second=True)
+    assert nerr(host(s1), nw @ (xs - a)) < 2e-6
+    assert nerr(host(s2), nw @ (xs - b) ** 2) < 2e-6
+    s1 = ops.wmoments_diag(x, nw)
+    assert nerr(host(s1), nw @ xs) < 2e-6
+
+
+def test_m_projection_mavn_golden(ops, golden):
+    g = golden
+    x, lw, cout = g["mv_x"], g["mv_lw"], g["mv_cout"]
+    K, H, d = x.shape
+    nw, st = ops.normalise_log_weights(lw)
+    s1 = ops.wmoments_diag(x, nw)
+    assert nerr(host(s1).reshape(H, d), g["mv_mu"]) < TOL
+    acc = ops.wmoments_matnorm(x, nw, shift=host(s1).reshape(H, d), inv_cov_out=1.0 / np.diag(cout))
+    fin = ops.finalize_matnorm(s1, acc, H, d)
+    assert nerr(host(fin["cov64"]), g["mv_cin"]) < TOL
+    assert nerr(host(fin["mean64"]), g["mv_mu"]) < TOL
+    assert int(fin["status"].item()) == 0
+    assert nerr(host(fin["chol64"]), np.linalg.cholesky(host(fin["cov64"]))) < 1e-9
+    assert abs(st.ess - g["mv_ess"]) < TOL * g["mv_ess"]
+
+
+@pytest.mark.parametrize("K,H,d", [(4096, 30, 28), (1000, 21, 2), (257, 128, 1), (300, 100, 3), (64, 2, 1),
+                                   (50, 65, 28)])
+def test_wmoments_matnorm_oracle(ops, K, H, d):
+    rng = np.random.default_rng(H * d)
+    x = f32r(rng.standard_normal((K, H, d)) * (0.5 + rng.random((1, H, d))))
+    lw = f32r(-6 * rng.random(K))
+    cout = np.diag(f32r(1e-3 * (1 + rng.random(d))))
+    mu, cin, _, ess = O.m_projection_mavn(lw, x, np.eye(H), cout, naive=False)
+    nw, st = ops.normalise_log_weights(lw)
+    s1 = ops.wmoments_diag(x, nw)
+    acc = ops.wmoments_matnorm(x, nw, shift=host(s1).reshape(H, d), inv_cov_out=1.0 / np.diag(cout))
+    fin = ops.finalize_matnorm(s1, acc, H, d)
+    assert nerr(host(fin["mean64"]), mu) < TOL
+    assert nerr(host(fin["cov64"]), cin) < TOL
+    # d = 1, cov_out = 1 reduces to m_projection
+    if d == 1:
+        mu2, sigma2, _ = O.m_projection(lw, x[:, :, 0], naive=False)
+        acc = ops.wmoments_matnorm(x, nw, shift=host(s1).reshape(H, 1))
+        assert nerr(host(ops.finalize_matnorm(s1, acc, H, 1)["cov64"]), sigma2) < TOL
+
+
+def test_finalize_gaussian(ops):
+    import torch
+
+    rng = np.random.default_rng(0)
+    D = 50
+    cov = f32r(rng.standard_normal((D, D)))
+    s1 = rng.standard_normal(D)
+    shift = f32r(rng.standard_normal(D))
+    dev = torch.device("cuda")
+    s1d = torch.as_tensor(s1, device=dev)
+    covd = torch.as_tensor(cov, device=dev, dtype=torch.float32)
+    mu, sigma = ops.finalize_gaussian(s1=s1d, cov=covd, shift=shift)
+    assert nerr(host(mu), shift + s1) < 1e-6
+    assert nerr(host(sigma), 0.5 * (cov + cov.T)) < 1e-6
+    _, sigma = ops.finalize_gaussian(cov=covd, diagonal_only=True, want_mu=False)
+    assert nerr(host(sigma), np.diag(np.diag(cov))) < 1e-7

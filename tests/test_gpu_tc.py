@@ -1,0 +1,129 @@
+"""GPU parity tests for the tcgen05 kernels (tc_gemm.cu): dense weighted covariance and the dense
+Gaussian transform, against the oracle (BLAS restatement of ppi/policies.py:78-93 and
+ppi/samplers.py:38-39).  Tolerance 1e-5 norm-wise (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+from scipy.special import logsumexp
+
+from oracle import ppi_oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def nerr(a, ref):
+    a, ref = np.asarray(a, np.float64), np.asarray(ref, np.float64)
+    assert a.shape == ref.shape, (a.shape, ref.shape)
+    return np.max(np.abs(a - ref)) / max(np.max(np.abs(ref)), 1e-300)
+
+
+def host(t):
+    return t.detach().cpu().numpy().astype(np.float64)
+
+
+def f32r(x):
+    return np.asarray(x, np.float32).astype(np.float64)
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import torch
+
+    assert torch.cuda.is_available()
+    from ppi_b200 import ops as _ops
+
+    return _ops
+
+
+def _problem(K, D, seed, ess_frac=None):
+    rng = np.random.default_rng(seed)
+    scale = 0.2 + rng.random(D) * 3.0
+    x = f32r(1.0 + rng.standard_normal((K, D)) * scale[None, :])
+    lw = f32r(-8.0 * rng.random(K))
+    nw = f32r(np.exp(lw - logsumexp(lw)))
+    return x, lw, nw
+
+
+@pytest.mark.parametrize("K,D", [(512, 128), (4096, 256), (1000, 200), (3000, 384), (70000, 256),
+                                 (8192, 1024), (600, 130)])
+def test_wmoments_dense(ops, K, D):
+    x, lw, nw = _problem(K, D, K + D)
+    mu, sigma, ess = O.m_projection(lw, x, naive=False)
+    # reference weights in fp64 differ from the fp32 nw by rounding only; use the fp32 ones on both sides
+    mu32 = f32r(nw @ x)
+    ref = (nw[:, None] * (x - mu32)).T @ (x - mu32)
+    cov = host(ops.wmoments_dense(x, nw, shift=mu32))
+    assert nerr(cov, ref) < TOL
+    assert np.array_equal(cov, cov.T)                        # symmetric by construction
+    assert nerr(cov, sigma) < 5e-5                           # and close to the oracle's m_projection
+    # linearity: two half batches accumulate to the full one
+    h = K // 2
+    c2 = ops.wmoments_dense(x[:h], nw[:h], shift=mu32)
+    c2 = host(ops.wmoments_dense(x[h:], nw[h:], shift=mu32, cov=c2, accumulate=True))
+    assert nerr(c2, ref) < TOL
+
+
+def test_wmoments_dense_zero_weight_rows(ops):
+    K, D = 2048, 256
+    x, lw, nw = _problem(K, D, 5)
+    nw[::5] = 0.0
+    xb = x.copy()
+    xb[::5] = np.nan  # failed rollouts: NaN rows with zero weight must not leak
+    ref = (nw[:, None] * np.nan_to_num(xb)).T @ np.nan_to_num(xb)
+    cov = host(ops.wmoments_dense(xb, nw))
+    assert np.isfinite(cov).all() and nerr(cov, ref) < TOL
+
+
+@pytest.mark.parametrize("K,D", [(256, 256), (1000, 200), (5000, 384), (40000, 256), (2048, 1024),
+                                 (300, 129)])
+def test_sample_gaussian_dense(ops, K, D):
+    rng = np.random.default_rng(K * D)
+    z = f32r(rng.standard_normal((K, D)))
+    a = rng.standard_normal((D, D + 8))
+    sigma = a @ a.T / D + 0.2 * np.eye(D)
+    L = f32r(np.linalg.cholesky(sigma))
+    mu = f32r(rng.standard_normal(D))
+    ref = mu[None, :] + z @ L.T
+    x = host(ops.sample_gaussian(K, mu, L, z=z))
+    assert nerr(x, ref) < TOL
+    # Philox mode equals injected mode fed with ppi_philox_normal
+    zp = ops.philox_normal(K, D, seed=3, draw_id=1, row_offset=77)
+    xa = host(ops.sample_gaussian(K, mu, L, z=zp))
+    xb = host(ops.sample_gaussian(K, mu, L, seed=3, draw_id=1, row_offset=77))
+    assert np.array_equal(xa, xb)
+
+
+def test_gaussian_policy_dense_update(ops):
+    """Config C2 in small (D = 256, K = 8192): sample -> Rastrigin -> ESSPS -> moment match,
+    against the oracle on the same injected normals."""
+    from ppi_b200 import algorithms as alg, functions as fn, policies as pol, samplers as smp
+
+    K, D = 8192, 256
+    rng = np.random.default_rng(0)
+    z = np.asarray(rng.standard_normal((K, D)), np.float32)
+    smp.InjectedNormals.queue = [z.copy()]
+    policy = pol.GaussianPolicy(np.ones(D), 0.5 * np.eye(D), smp.InjectedNormals(D))
+    solver = alg.Essps(n_elites=K // 64)
+    solver.reset(policy)
+    samples, _ = policy(K)
+    x32 = np.asarray(samples)
+    assert nerr(x32, O.sample_gaussian(z.astype(np.float64), np.ones(D), 0.5 * np.eye(D))) < TOL
+    costs = fn.Rastrigin(D)(samples)
+    c32 = np.asarray(costs)
+    assert nerr(c32, O.rastrigin(x32)) < 2e-6
+    solver.update(costs, samples, policy)
+    log_w, alpha = O.essps_log_w(c32, K // 64)
+    mu, sigma, ess, kl = O.gaussian_weighted_update(np.ones(D), 0.5 * np.eye(D), log_w, x32)
+    # (the oracle's m_projection uses the naive einsum: fine at this size)
+    tr = solver.trace
+    assert abs(tr["alpha"][-1] - alpha) < TOL * alpha
+    assert abs(tr["ess"][-1] - ess) < TOL * ess
+    assert nerr(policy.mu, mu) < TOL
+    assert nerr(policy.sigma, sigma) < TOL
+    assert abs(tr["kl"][-1] - kl) < 1e-4 * max(1.0, abs(kl))
+    assert abs(tr["ent"][-1] - O.gaussian_entropy(sigma, D)) < 1e-4 * abs(O.gaussian_entropy(sigma, D))
+    # second iteration samples from the fitted full covariance
+    z2 = np.asarray(rng.standard_normal((K, D)), np.float32)
+    smp.InjectedNormals.queue = [z2.copy()]
+    x2 = np.asarray(policy(K)[0])
+    assert nerr(x2, O.sample_gaussian(z2.astype(np.float64), policy.mu, policy.sigma)) < 2e-5

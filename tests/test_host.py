@@ -1,0 +1,149 @@
+"""CPU-side tests (no GPU): the C-ABI library loads and exports every symbol the header declares,
+the ctypes table mirrors the header, host helpers and the K-sharding plumbing (gloo, 2 ranks)."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_functions():
+    text = open(os.path.join(ROOT, "include", "ppi_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(ppi_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    import __graft_entry__
+
+    __graft_entry__.build()
+    from ppi_b200 import _lib
+
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    names = _header_functions()
+    assert len(names) >= 23
+    for name in names:
+        assert hasattr(lib, name), f"{name} declared in include/ppi_b200.h but not exported"
+        assert name in _lib.SIGNATURES, f"{name} has no ctypes signature"
+    assert sorted(_lib.SIGNATURES) == names
+    assert _lib.load().ppi_version() == 100
+
+
+def test_ctypes_arity_matches_header():
+    from ppi_b200 import _lib
+
+    text = open(os.path.join(ROOT, "include", "ppi_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    for name, (_, argtypes) in _lib.SIGNATURES.items():
+        m = re.search(r"\b" + name + r"\s*\(([^;]*?)\)\s*;", text, flags=re.S)
+        assert m, name
+        args = m.group(1).strip()
+        n = 0 if args in ("", "void") else len(args.split(","))
+        assert n == len(argtypes), (name, n, len(argtypes))
+
+
+def test_weight_stats_layout():
+    from ppi_b200 import _lib
+
+    assert _lib.STATS_BYTES == 10 * 8 + 2 * 8 + 4 * 4
+    assert _lib.WeightStats.n_valid.offset == 80 and _lib.WeightStats.all_nan.offset == 96
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    from ppi_b200 import _lib, device
+
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(_lib.PpiError):
+        device.require_cuda()
+    from ppi_b200 import ops
+
+    with pytest.raises(_lib.PpiError):
+        ops.philox_normal(4, 4, 0)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "monte-carlo-posterior-policy-iteration_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src.replace("ppi_oracle", "oracle") or "import oracle" not in src
+                assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
+
+
+def test_shard_rows_partition():
+    from ppi_b200.device import shard_rows
+
+    for n in (0, 1, 7, 100, 4096, 2 ** 20 + 3):
+        for world in (1, 2, 3, 8):
+            spans = [shard_rows(n, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
+            sizes = [e - b for b, e in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_host_helpers_match_reference_formulas():
+    from ppi_b200 import policies as pol
+
+    mean, cin, cout = pol.design_moments(np.ones(3), -np.ones(3), 1000.0)
+    assert (mean == 0).all() and cin.tolist() == [1000.0] and np.allclose(np.diag(cout), 1e-3)
+    rng = np.random.default_rng(0)
+    a = rng.standard_normal((5, 5))
+    s1, s2 = a @ a.T + np.eye(5), 2.0 * np.eye(5)
+    m1, m2 = rng.standard_normal(5), rng.standard_normal(5)
+    from oracle import ppi_oracle as O
+
+    assert np.isclose(pol.multivariate_gaussian_kl(m1, s1, m2, s2), O.gaussian_kl(m1, s1, m2, s2))
+    assert np.isclose(pol.multivariate_gaussian_entropy(s1, 5), O.gaussian_entropy(s1, 5))
+    # the reference clamps det at EPS: 0.5^2048 underflows (ppi/policies.py:214)
+    big = 0.5 * np.eye(2048)
+    assert np.isclose(pol.multivariate_gaussian_entropy(big, 2048), O.gaussian_entropy(big, 2048))
+    lim = pol.Limiter(upper=np.ones(2), lower=-np.ones(2))
+    assert lim(np.array([[3.0, -3.0], [0.5, 0.2]])).tolist() == [[1.0, -1.0], [0.5, 0.2]]
+
+
+_DIST_SCRIPT = r"""
+import os, sys
+import numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, os.path.join(sys.argv[1], "monte-carlo-posterior-policy-iteration_b200"))
+from ppi_b200 import device
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:" + sys.argv[2], rank=int(sys.argv[3]), world_size=2)
+rank = dist.get_rank()
+n = 11
+full = torch.arange(n * 3, dtype=torch.float32).reshape(n, 3)
+b, e = device.shard_rows(n)
+got = device.all_gather_rows(full[b:e].clone(), n)
+assert torch.equal(got, full), got
+s = device.all_reduce_sum(torch.full((4,), float(rank + 1), dtype=torch.float64))
+assert torch.equal(s, torch.full((4,), 3.0, dtype=torch.float64))
+row = device.broadcast_row(full[b:e].clone(), 7, n)
+assert torch.equal(row, full[7])
+# K-sharded statistics: partial (sum w, sum w x, sum w x x^T) all-reduced == single-rank result
+rng = np.random.default_rng(0)
+x = rng.standard_normal((n, 3)); w = rng.random(n); w /= w.sum()
+part = torch.as_tensor(np.concatenate([[w[b:e].sum()], w[b:e] @ x[b:e], ((w[b:e, None] * x[b:e]).T @ x[b:e]).ravel()]))
+device.all_reduce_sum(part)
+ref = np.concatenate([[1.0], w @ x, ((w[:, None] * x).T @ x).ravel()])
+assert np.allclose(part.numpy(), ref, atol=1e-12)
+dist.destroy_process_group()
+print("rank", rank, "ok")
+"""
+
+
+def test_k_sharding_plumbing_gloo_two_ranks(tmp_path):
+    script = tmp_path / "dist_check.py"
+    script.write_text(_DIST_SCRIPT)
+    port = str(29500 + os.getpid() % 2000)
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT, port, str(r)], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT) for r in range(2)]
+    outs = [p.communicate(timeout=240)[0].decode() for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
