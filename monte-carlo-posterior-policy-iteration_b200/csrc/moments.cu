@@ -327,7 +327,7 @@ extern "C" int ppi_finalize_gaussian(const double* s1, const float* cov_in, int6
   PPI_REQUIRE(D > 0 && (mu_out || sigma_out), PPI_ERR_INVALID, "ppi_finalize_gaussian: bad arguments");
   PPI_REQUIRE(!mu_out || s1, PPI_ERR_INVALID, "mu_out needs s1");
   PPI_REQUIRE(!sigma_out || cov_in, PPI_ERR_INVALID, "sigma_out needs cov_in");
-  PPI_REQUIRE(cov_in != sigma_out || diagonal_only, PPI_ERR_INVALID,
+  PPI_REQUIRE(!sigma_out || cov_in != sigma_out || diagonal_only, PPI_ERR_INVALID,
               "in-place symmetrisation is not supported");
   const int64_t n = sigma_out ? D * D : D;
   const int grid = (int)(ceil_div(n, 256) < kNumSMs * 8 ? ceil_div(n, 256) : kNumSMs * 8);

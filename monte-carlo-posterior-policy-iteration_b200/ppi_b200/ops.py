@@ -19,6 +19,21 @@ def _opt(t, dev):
     return None if t is None else f32(t, dev)
 
 
+class _Keep:
+    """Converts host arrays to device tensors and keeps them referenced until the C call has been
+    enqueued (a temporary freed inside the argument list would hand its block to the next one)."""
+
+    def __init__(self, dev):
+        self.dev, self.alive = dev, []
+
+    def p(self, a):
+        if a is None:
+            return ptr(None)
+        t = f32(a, self.dev)
+        self.alive.append(t)
+        return ptr(t)
+
+
 # ------------------------------------------------------------------ a3
 def philox_normal(rows, cols, seed, draw_id=0, row_offset=0):
     dev = require_cuda()
@@ -67,13 +82,14 @@ def _is_diag(m):
 def sample_matnorm(K, mean_fn, mean, l_in, l_out, z=None, seed=0, draw_id=0, row_offset=0,
                    lower=None, upper=None, l_out_is_diag=False):
     dev = require_cuda()
+    kp = _Keep(dev)
     mean = f32(mean, dev)
     H, d = mean.shape
     x = torch.empty((K, H, d), dtype=torch.float32, device=dev)
     zt = None if z is None else f32(z, dev).reshape(K, H * d)
     lo, hi = _opt(lower, dev), _opt(upper, dev)
     _lib.call("ppi_sample_matnorm", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, H, d,
-              ptr(f32(mean_fn, dev)), ptr(mean), ptr(f32(l_in, dev)), ptr(f32(l_out, dev)),
+              kp.p(mean_fn), ptr(mean), kp.p(l_in), kp.p(l_out),
               int(bool(l_out_is_diag)), ptr(lo), ptr(hi), ptr(x), stream_ptr())
     return x
 
@@ -81,6 +97,7 @@ def sample_matnorm(K, mean_fn, mean, l_in, l_out, z=None, seed=0, draw_id=0, row
 def sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat=None, z=None, seed=0, draw_id=0,
                     row_offset=0, lower=None, upper=None):
     dev = require_cuda()
+    kp = _Keep(dev)
     mean = f32(mean, dev)
     F, d = mean.shape
     feat = f32(feat, dev)
@@ -91,21 +108,22 @@ def sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat=None, z=None, see
     zt = None if z is None else f32(z, dev).reshape(K, F * d)
     lo, hi = _opt(lower, dev), _opt(upper, dev)
     _lib.call("ppi_sample_features", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, F, d, T,
-              ptr(f32(mean_fn, dev)), ptr(mean), ptr(f32(l_in, dev)), ptr(f32(l_out, dev)), ptr(feat),
-              ptr(_opt(dfeat, dev)), ptr(lo), ptr(hi), ptr(w), ptr(y), stream_ptr())
+              kp.p(mean_fn), ptr(mean), kp.p(l_in), kp.p(l_out), ptr(feat),
+              kp.p(dfeat), ptr(lo), ptr(hi), ptr(w), ptr(y), stream_ptr())
     return y, w
 
 
 def sample_iid(K, mean_fn, mean, std, z=None, seed=0, draw_id=0, row_offset=0, lower=None,
                upper=None):
     dev = require_cuda()
+    kp = _Keep(dev)
     mean = f32(mean, dev)
     H, d = mean.shape
     x = torch.empty((K, H, d), dtype=torch.float32, device=dev)
     zt = None if z is None else f32(z, dev).reshape(K, H * d)
     lo, hi = _opt(lower, dev), _opt(upper, dev)
     _lib.call("ppi_sample_iid", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, H, d,
-              ptr(f32(mean_fn, dev)), ptr(mean), ptr(f32(std, dev)), ptr(lo), ptr(hi), ptr(x),
+              kp.p(mean_fn), ptr(mean), kp.p(std), ptr(lo), ptr(hi), ptr(x),
               stream_ptr())
     return x
 
@@ -113,6 +131,7 @@ def sample_iid(K, mean_fn, mean, std, z=None, seed=0, draw_id=0, row_offset=0, l
 def sample_gaussian(K, mu, L, z=None, seed=0, draw_id=0, row_offset=0, out=None):
     """x = mu + z L^T with L lower triangular (Cholesky form, ppi/samplers.py:38-39)."""
     dev = require_cuda()
+    kp = _Keep(dev)
     mu = f32(mu, dev)
     D = mu.numel()
     x = out if out is not None else torch.empty((K, D), dtype=torch.float32, device=dev)
@@ -120,18 +139,19 @@ def sample_gaussian(K, mu, L, z=None, seed=0, draw_id=0, row_offset=0, out=None)
     nbytes = _lib.query("ppi_sample_gaussian_workspace_bytes", K, D)
     ws = workspace("sample_gaussian", nbytes) if nbytes else None
     _lib.call("ppi_sample_gaussian", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, D,
-              ptr(mu), ptr(f32(L, dev)), ptr(x), ptr(ws), nbytes, stream_ptr())
+              ptr(mu), kp.p(L), ptr(x), ptr(ws), nbytes, stream_ptr())
     return x
 
 
 # ------------------------------------------------------------------ a9
 def cost_function(name, x, A=None, noise=None):
     dev = require_cuda()
+    kp = _Keep(dev)
     x = f32(x, dev)
     K, D = x.shape
     c = torch.empty((K,), dtype=torch.float32, device=dev)
-    _lib.call("ppi_cost_function", _lib.FN_IDS[name], ptr(x), K, D, ptr(_opt(A, dev)),
-              ptr(_opt(noise, dev)), ptr(c), stream_ptr())
+    _lib.call("ppi_cost_function", _lib.FN_IDS[name], ptr(x), K, D, kp.p(A),
+              kp.p(noise), ptr(c), stream_ptr())
     return c
 
 
@@ -196,6 +216,7 @@ def cem_weights(costs, n_elites, sync=True):
 def wmoments_diag(x, nw, shift1=None, shift2=None, second=False, s1=None, s2=None):
     """fp64 accumulators: s1 = sum nw (x - shift1), s2 = sum nw (x - shift2)^2 over rows of x (K, D)."""
     dev = require_cuda()
+    kp = _Keep(dev)
     x = f32(x, dev)
     K = x.shape[0]
     x2 = x.reshape(K, -1)
@@ -203,29 +224,31 @@ def wmoments_diag(x, nw, shift1=None, shift2=None, second=False, s1=None, s2=Non
     s1 = torch.zeros(D, dtype=torch.float64, device=dev) if s1 is None else s1
     if second and s2 is None:
         s2 = torch.zeros(D, dtype=torch.float64, device=dev)
-    _lib.call("ppi_wmoments_diag", ptr(x2), ptr(f32(nw, dev)), K, D, ptr(_opt(shift1, dev)),
-              ptr(_opt(shift2, dev)), ptr(s1), ptr(s2 if second else None), stream_ptr())
+    _lib.call("ppi_wmoments_diag", ptr(x2), kp.p(nw), K, D, kp.p(shift1),
+              kp.p(shift2), ptr(s1), ptr(s2 if second else None), stream_ptr())
     return (s1, s2) if second else s1
 
 
 def wmoments_matnorm(x, nw, shift=None, inv_cov_out=None, acc=None):
     dev = require_cuda()
+    kp = _Keep(dev)
     x = f32(x, dev)
     K, H, d = x.shape
     acc = torch.zeros((H, H), dtype=torch.float64, device=dev) if acc is None else acc
-    _lib.call("ppi_wmoments_matnorm", ptr(x), ptr(f32(nw, dev)), K, H, d, ptr(_opt(shift, dev)),
-              ptr(_opt(inv_cov_out, dev)), ptr(acc), stream_ptr())
+    _lib.call("ppi_wmoments_matnorm", ptr(x), kp.p(nw), K, H, d, kp.p(shift),
+              kp.p(inv_cov_out), ptr(acc), stream_ptr())
     return acc
 
 
 def wmoments_dense(x, nw, shift=None, cov=None, accumulate=False):
     dev = require_cuda()
+    kp = _Keep(dev)
     x = f32(x, dev)
     K, D = x.shape
     cov = torch.empty((D, D), dtype=torch.float32, device=dev) if cov is None else cov
     nbytes = _lib.query("ppi_wmoments_dense_workspace_bytes", K, D)
     ws = workspace("wmoments_dense", nbytes)
-    _lib.call("ppi_wmoments_dense", ptr(x), ptr(f32(nw, dev)), K, D, ptr(_opt(shift, dev)), ptr(cov),
+    _lib.call("ppi_wmoments_dense", ptr(x), kp.p(nw), K, D, kp.p(shift), ptr(cov),
               int(bool(accumulate)), ptr(ws), nbytes, stream_ptr())
     return cov
 
@@ -233,10 +256,11 @@ def wmoments_dense(x, nw, shift=None, cov=None, accumulate=False):
 def finalize_gaussian(s1=None, cov=None, shift=None, diagonal_only=False, want_mu=True,
                       want_sigma=True):
     dev = require_cuda()
+    kp = _Keep(dev)
     D = (s1.numel() if s1 is not None else cov.shape[0])
     mu = torch.empty(D, dtype=torch.float32, device=dev) if want_mu else None
     sigma = torch.empty((D, D), dtype=torch.float32, device=dev) if want_sigma else None
-    _lib.call("ppi_finalize_gaussian", ptr(s1), ptr(cov), D, ptr(_opt(shift, dev)),
+    _lib.call("ppi_finalize_gaussian", ptr(s1), ptr(cov), D, kp.p(shift),
               int(bool(diagonal_only)), ptr(mu), ptr(sigma), stream_ptr())
     return mu, sigma
 

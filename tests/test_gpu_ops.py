@@ -224,7 +224,8 @@ def test_cost_functions_oracle(ops, K, D):
     one = np.ones((1, D))
     assert abs(host(ops.cost_function("Rosenbrock", one))[0]) < 1e-6
     assert abs(host(ops.cost_function("Rastrigin", 0 * one))[0]) < 1e-3 * D
-    assert abs(host(ops.cost_function("Styblinski", -2.903534 * one))[0]) < 1e-4 * D
+    # (the reference's 6-digit constants leave f(x_opt) = -1.8e-4 per dimension)
+    assert abs(host(ops.cost_function("Styblinski", -2.903534 * one))[0]) < 3e-4 * D
 
 
 def test_cost_tracking(ops):
