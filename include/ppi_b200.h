@@ -51,7 +51,7 @@ int ppi_philox_normal(float* out, int64_t rows, int64_t cols, uint64_t seed, uin
  * 935-974,1026-1037,1087-1091 (Gram) and :312,692-694 (np.linalg.cholesky).
  * kind: 0 squared-exponential, 1 Matern12, 2 Matern32, 3 Matern52, 4 periodic, 5 white noise.
  * t1 (n1), t2 (n2) are fp64 time stamps.  gram64/gram32 are (n1, n2).  If chol64/chol32 are
- * non-NULL (needs n1 == n2 <= 256) the lower Cholesky factor is written too; *status = 0 when
+ * non-NULL (needs n1 == n2 <= 160) the lower Cholesky factor is written too; *status = 0 when
  * positive definite, else 1 + index of the failing pivot.
  * ---------------------------------------------------------------------------------------- */
 enum { PPI_KERNEL_SE = 0, PPI_KERNEL_MATERN12 = 1, PPI_KERNEL_MATERN32 = 2,
@@ -60,7 +60,7 @@ int ppi_kernel_gram_chol(const double* t1, int n1, const double* t2, int n2, int
                          double lengthscale, double period, double* gram64, float* gram32,
                          double* chol64, float* chol32, int* status, void* stream);
 
-/* np.linalg.cholesky of a small fp64 matrix (n <= 256), one thread block; a may alias l64.
+/* np.linalg.cholesky of a small fp64 matrix (n <= 160), one thread block; a may alias l64.
  * ppi/policies.py:312,321,481,819                                                          */
 int ppi_cholesky_small(const double* a, int n, double* l64, float* l32, int* status, void* stream);
 
@@ -205,6 +205,21 @@ int ppi_finalize_gaussian(const double* s1, const float* cov_in, int64_t D, cons
 int ppi_finalize_matnorm(const double* s1, const double* acc, int H, int d, double jitter,
                          double* mean64, float* mean32, double* cov64, float* cov32,
                          double* chol64, float* chol32, int* status, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Measurement hooks (new; the reference has no instrumentation beyond profile_mpc.py:96-108).
+ * ppi_launch_count: kernels this library has launched since load.  ppi_profile_enable(1) makes
+ * the library bracket its kernels with CUDA events on the launching stream; ppi_profile_read
+ * returns the number of bracketed scopes of a slot and their summed device time, then
+ * ppi_profile_enable(0/1) clears the records.
+ * ---------------------------------------------------------------------------------------- */
+enum { PPI_PROF_SYRK_GEMM = 0, PPI_PROF_SAMPLE_GEMM = 1, PPI_PROF_SYRK_OPERAND = 2,
+       PPI_PROF_SAMPLE_OPERAND = 3, PPI_PROF_WMOMENTS_DIAG = 4, PPI_PROF_COST = 5,
+       PPI_PROF_SOLVE = 6, PPI_PROF_SYRK_REDUCE = 7, PPI_PROF_SAMPLE_SMALL = 8,
+       PPI_PROF_WMOMENTS_MATNORM = 9, PPI_PROF_NUM_SLOTS = 10 };
+int64_t ppi_launch_count(void);
+int ppi_profile_enable(int on);
+int ppi_profile_read(int slot, int64_t* count, double* total_ms);
 
 #ifdef __cplusplus
 }

@@ -2,6 +2,10 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <atomic>
+#include <mutex>
+#include <vector>
+
 #include "common.cuh"
 
 namespace ppi {
@@ -14,6 +18,60 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 }  // namespace ppi
+
+namespace ppi {
+// ---- launch counter + optional per-kernel CUDA-event timing (bench.py's roofline leg) ----
+static std::atomic<int64_t> g_launches{0};
+static bool g_profile = false;
+struct EventPair { cudaEvent_t a, b; };
+static std::vector<EventPair> g_events[PPI_PROF_NUM_SLOTS];
+static std::mutex g_prof_mutex;
+
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+ProfileScope::ProfileScope(int slot, cudaStream_t stream) : slot_(slot), stream_(stream), on_(g_profile) {
+  if (!on_) return;
+  EventPair ev;
+  if (cudaEventCreate(&ev.a) != cudaSuccess || cudaEventCreate(&ev.b) != cudaSuccess) { on_ = false; return; }
+  cudaEventRecord(ev.a, stream_);
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
+  g_events[slot_].push_back(ev);
+  index_ = g_events[slot_].size() - 1;
+}
+ProfileScope::~ProfileScope() {
+  if (!on_) return;
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
+  cudaEventRecord(g_events[slot_][index_].b, stream_);
+}
+}  // namespace ppi
+
+extern "C" int64_t ppi_launch_count(void) { return ppi::g_launches.load(); }
+
+extern "C" int ppi_profile_enable(int on) {
+  std::lock_guard<std::mutex> lock(ppi::g_prof_mutex);
+  for (auto& v : ppi::g_events) {
+    for (auto& e : v) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    v.clear();
+  }
+  ppi::g_profile = on != 0;
+  return 0;
+}
+
+extern "C" int ppi_profile_read(int slot, int64_t* count, double* total_ms) {
+  PPI_REQUIRE(slot >= 0 && slot < PPI_PROF_NUM_SLOTS && count && total_ms, PPI_ERR_INVALID,
+              "ppi_profile_read: bad arguments");
+  std::lock_guard<std::mutex> lock(ppi::g_prof_mutex);
+  double ms = 0.0;
+  for (auto& e : ppi::g_events[slot]) {
+    PPI_CUDA_TRY(cudaEventSynchronize(e.b));
+    float t = 0.f;
+    PPI_CUDA_TRY(cudaEventElapsedTime(&t, e.a, e.b));
+    ms += t;
+  }
+  *count = (int64_t)ppi::g_events[slot].size();
+  *total_ms = ms;
+  return 0;
+}
 
 extern "C" int ppi_version(void) { return PPI_B200_VERSION; }
 extern "C" const char* ppi_last_error(void) { return ppi::g_error; }

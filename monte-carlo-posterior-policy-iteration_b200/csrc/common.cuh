@@ -16,7 +16,23 @@ namespace ppi {
 
 void set_error(const char* fmt, ...);
 
-inline int check_launch(const char* what) {
+void count_launch(int n);
+
+// Records a CUDA-event pair around the launches in its scope when ppi_profile_enable(1) is set.
+class ProfileScope {
+ public:
+  ProfileScope(int slot, cudaStream_t stream);
+  ~ProfileScope();
+ private:
+  int slot_;
+  cudaStream_t stream_;
+  bool on_;
+  size_t index_ = 0;
+};
+
+// `n` = kernels launched since the previous check
+inline int check_launch(const char* what, int n = 1) {
+  count_launch(n);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s: %s", what, cudaGetErrorString(e));

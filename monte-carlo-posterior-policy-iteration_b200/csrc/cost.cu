@@ -143,6 +143,7 @@ extern "C" int ppi_cost_function(int fn, const float* x, int64_t K, int64_t D, c
   const int64_t warps_needed = K;
   int grid = (int)(ceil_div(warps_needed, 8) < (int64_t)kNumSMs * 8 ? ceil_div(warps_needed, 8)
                                                                    : (int64_t)kNumSMs * 8);
+  ProfileScope prof(PPI_PROF_COST, st);
   switch (fn) {
     case PPI_FN_HIMMELBLAU:
       PPI_REQUIRE(D >= 2, PPI_ERR_INVALID, "Himmelblau needs D >= 2");
@@ -180,6 +181,7 @@ extern "C" int ppi_cost_tracking(const float* x, int64_t K, int T, int dy, const
               "ppi_cost_tracking: bad arguments");
   if (K == 0) return 0;
   const int grid = (int)(ceil_div(K, 8) < (int64_t)kNumSMs * 8 ? ceil_div(K, 8) : (int64_t)kNumSMs * 8);
+  ProfileScope prof(PPI_PROF_COST, (cudaStream_t)stream);
   cost_tracking_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, K, T, dy, target, dt, c);
   return check_launch("cost_tracking_kernel");
 }

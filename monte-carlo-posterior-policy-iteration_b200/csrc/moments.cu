@@ -270,6 +270,7 @@ extern "C" int ppi_wmoments_diag(const float* x, const float* nw, int64_t K, int
   if (gy > 65535) gy = 65535;
   const int64_t rpb = ceil_div(K, gy);
   dim3 grid((unsigned)gx, (unsigned)ceil_div(K, rpb));
+  ProfileScope prof(PPI_PROF_WMOMENTS_DIAG, st);
 #define PPI_LAUNCH_DIAG(V, SEC) \
   wmoments_diag_kernel<V, SEC><<<grid, 256, 0, st>>>(x, nw, K, D, shift1, shift2, s1, s2, cgb, rpb)
   if (vec) { if (s2) PPI_LAUNCH_DIAG(4, true); else PPI_LAUNCH_DIAG(4, false); }
@@ -305,6 +306,7 @@ extern "C" int ppi_wmoments_matnorm(const float* x, const float* nw, int64_t K, 
   if (grid < 1) grid = 1;
   int64_t spb = ceil_div(ceil_div(K, grid), S) * S;
   grid = ceil_div(K, spb);
+  ProfileScope prof(PPI_PROF_WMOMENTS_MATNORM, st);
   if (nb <= 256) {
     if (smem > 48 * 1024)
       PPI_CUDA_TRY(cudaFuncSetAttribute(wmoments_matnorm_kernel<1>,

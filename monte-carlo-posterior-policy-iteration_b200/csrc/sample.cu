@@ -544,6 +544,7 @@ int ppi_sample_gaussian_small(const float* z, uint64_t seed, uint64_t draw_id, u
   const size_t smem = ((size_t)D * D + (size_t)S * D) * sizeof(float);
   if (int rc = set_smem(sample_gaussian_small_kernel<S>, smem)) return rc;
   const int grid = grid_for(ceil_div(K, S), 2);
+  ProfileScope prof(PPI_PROF_SAMPLE_SMALL, st);
   sample_gaussian_small_kernel<S><<<grid, 256, smem, st>>>(z, seed, draw_id, row_offset, K, D, mu, L, x);
   return check_launch("sample_gaussian_small_kernel");
 }

@@ -313,7 +313,8 @@ split_tf32_gemm_kernel(const __grid_constant__ CUtensorMap map_ah,
         }
       } else {
         float* dst = p.out + m * p.ld + n0;
-        const bool vec = (p.ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+        const bool vec = (p.ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0) &&
+                         ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           const int64_t n = n0 + 4 * j;
@@ -354,7 +355,8 @@ syrk_operand_kernel(const float* __restrict__ x, const float* __restrict__ nw,
   __shared__ float tile[32][129];
   const int64_t kt = (int64_t)blockIdx.x * 32;   // local sample offset in the chunk
   const int64_t it = (int64_t)blockIdx.y * 128;  // column offset
-  const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+  const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(shift) & 15) == 0);
   for (int e = threadIdx.x; e < 32 * 32; e += 256) {
     const int r = e / 32, c4 = (e % 32) * 4;
     const int64_t k = k0 + kt + r;
@@ -493,6 +495,7 @@ static int launch_gemm(const CUtensorMap& ah, const CUtensorMap& al, const CUten
                                       (int)kGemmSmemBytes));
     attr_set = true;
   }
+  ProfileScope prof(p.mode == GEMM_SYRK ? PPI_PROF_SYRK_GEMM : PPI_PROF_SAMPLE_GEMM, st);
   split_tf32_gemm_kernel<<<(unsigned)grid, kGemmThreads, kGemmSmemBytes, st>>>(ah, al, bh, bl, p);
   return check_launch("split_tf32_gemm_kernel");
 }
@@ -573,12 +576,16 @@ extern "C" int ppi_wmoments_dense(const float* x, const float* nw, int64_t K, in
   int pass = 0;
   for (int64_t k0 = 0; k0 < K; k0 += pl.Kc, ++pass) {
     dim3 og((unsigned)(pl.Kc / 32), (unsigned)ceil_div(pl.Dp, 128));
-    syrk_operand_kernel<<<og, 256, 0, st>>>(x, nw, shift, K, D, k0, pl.Kc, pl.Dp, at_hi, at_lo);
-    if (int rc = check_launch("syrk_operand_kernel")) return rc;
+    {
+      ProfileScope prof(PPI_PROF_SYRK_OPERAND, st);
+      syrk_operand_kernel<<<og, 256, 0, st>>>(x, nw, shift, K, D, k0, pl.Kc, pl.Dp, at_hi, at_lo);
+      if (int rc = check_launch("syrk_operand_kernel")) return rc;
+    }
     p.accumulate = pass > 0;
     if (int rc = launch_gemm(ah, al, bh, bl, p, pl.ntiles * pl.splits, st)) return rc;
   }
   const int grid = (int)(ceil_div(D * D, 256) < kNumSMs * 8 ? ceil_div(D * D, 256) : kNumSMs * 8);
+  ProfileScope prof(PPI_PROF_SYRK_REDUCE, st);
   syrk_reduce_kernel<<<grid, 256, 0, st>>>(partials, pl.splits, pl.Dp, pl.Dp * pl.Dp, D, cov,
                                            accumulate);
   return check_launch("syrk_reduce_kernel");
@@ -646,9 +653,12 @@ extern "C" int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_
     const int64_t total = rows_p * (Dk / 4);
     const int grid = (int)(ceil_div(total, 256) < kNumSMs * 16 ? ceil_div(total, 256) : kNumSMs * 16);
     // rows beyond `rows` are generated too (harmless, never stored)
-    split_rows_kernel<<<grid, 256, 0, st>>>(z ? z + k0 * D : nullptr, z ? rows : rows_p, D, Dk, seed,
-                                            draw_id, row_offset + (uint64_t)k0, 0, z_hi, z_lo);
-    if (int rc = check_launch("split_rows_kernel(z)")) return rc;
+    {
+      ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st);
+      split_rows_kernel<<<grid, 256, 0, st>>>(z ? z + k0 * D : nullptr, z ? rows : rows_p, D, Dk, seed,
+                                              draw_id, row_offset + (uint64_t)k0, 0, z_hi, z_lo);
+      if (int rc = check_launch("split_rows_kernel(z)")) return rc;
+    }
     p.tiles_m = (int)(rows_p / BM);
     p.M = rows;
     p.out = x + k0 * D;

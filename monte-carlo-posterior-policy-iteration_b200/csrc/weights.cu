@@ -524,8 +524,10 @@ static int launch_solve(const float* in, int64_t K, int mode, double hyper, floa
   if (g > kMaxSolveBlocks) g = kMaxSolveBlocks;
   void* args[] = {(void*)&in, (void*)&K, (void*)&mode, (void*)&hyper, (void*)&nw, (void*)&log_w,
                   (void*)&stats, (void*)&ws};
+  ProfileScope prof(PPI_PROF_SOLVE, st);
   PPI_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)solve_temperature_kernel, dim3((unsigned)g),
                                            dim3(kSolveThreads), args, 0, st));
+  count_launch(1);
   return 0;
 }
 
@@ -586,14 +588,17 @@ extern "C" int ppi_cem_weights(const float* costs, int64_t K, int64_t n_elites, 
   make_keys_kernel<<<gk, 256, 0, st>>>(costs, K, N, stats, keys);
   const int nchunks = (int)(N / kSortChunk);
   bitonic_local_sort_kernel<<<nchunks, kSortThreads, 0, st>>>(keys);
+  int launches = 2;
   for (int64_t k = 2 * kSortChunk; k <= N; k <<= 1) {
     for (int64_t j = k >> 1; j >= kSortChunk; j >>= 1) {
       const int gg = (int)(ceil_div(N / 2, 256) < kNumSMs * 8 ? ceil_div(N / 2, 256) : kNumSMs * 8);
       bitonic_global_step_kernel<<<gg, 256, 0, st>>>(keys, N, j, k);
+      ++launches;
     }
     bitonic_local_merge_kernel<<<nchunks, kSortThreads, 0, st>>>(keys, k);
+    ++launches;
   }
   const int gf = (int)(ceil_div(K, 256) < kNumSMs * 8 ? ceil_div(K, 256) : kNumSMs * 8);
   cem_finalize_kernel<<<gf, 256, 0, st>>>(keys, K, n_elites, sorted_idx, nw, stats);
-  return check_launch("cem kernels");
+  return check_launch("cem kernels", launches + 1);
 }

@@ -59,7 +59,25 @@ SIGNATURES = {
     "ppi_wmoments_dense": (_i, [_p, _p, _i64, _i64, _p, _p, _i, _p, _sz, _p]),
     "ppi_finalize_gaussian": (_i, [_p, _p, _i64, _p, _i, _p, _p, _p]),
     "ppi_finalize_matnorm": (_i, [_p, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "ppi_launch_count": (_i64, []),
+    "ppi_profile_enable": (_i, [_i]),
+    "ppi_profile_read": (_i, [_i, C.POINTER(_i64), C.POINTER(_d)]),
 }
+
+PROFILE_SLOTS = {"syrk_gemm": 0, "sample_gemm": 1, "syrk_operand": 2, "sample_operand": 3,
+                 "wmoments_diag": 4, "cost": 5, "solve": 6, "syrk_reduce": 7, "sample_small": 8,
+                 "wmoments_matnorm": 9}
+
+
+def profile_read():
+    """{slot name: (scopes, total device ms)} of the CUDA-event brackets since ppi_profile_enable(1)."""
+    out = {}
+    for name, slot in PROFILE_SLOTS.items():
+        n, ms = _i64(0), _d(0.0)
+        call("ppi_profile_read", slot, C.byref(n), C.byref(ms))
+        if n.value:
+            out[name] = (n.value, ms.value)
+    return out
 
 _lib = None
 
