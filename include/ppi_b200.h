@@ -42,6 +42,9 @@ const char* ppi_last_error(void);
  * a3  base normals: np.random.randn(n, d)                         ppi/samplers.py:18-20
  * Philox4x32-10 + Box-Muller.  Element (r, c) of the (rows, cols) output is a pure function of
  * (seed, draw_id, row_offset + r, c): K-sharded ranks reproduce the 1-GPU matrix bit for bit.
+ * The normals are emitted on the TF32 grid (11 significant bits, relative spacing 2^-11) so that
+ * they are exact tensor-core operands for ppi_sample_gaussian; every sampler below that draws
+ * on the device sees exactly these numbers.
  * ---------------------------------------------------------------------------------------- */
 int ppi_philox_normal(float* out, int64_t rows, int64_t cols, uint64_t seed, uint64_t draw_id,
                       uint64_t row_offset, void* stream);

@@ -51,6 +51,7 @@ struct GemmParams {
   int64_t split_stride;
   const float* bias; // SAMPLE: mu[n]
   int accumulate;    // SYRK: partial += acc
+  int a_exact;       // SAMPLE: A (the Philox normals) is exactly TF32: no A_lo operand, 2 MMAs per step
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -224,9 +225,9 @@ split_tf32_gemm_kernel(const __grid_constant__ CUtensorMap map_ah,
       for (int kb = kb_begin; kb < kb_end; ++kb) {
         mbar_wait(empty_bar(stage), phase ^ 1u);
         const uint32_t sb = base + stage * kStageBytes;
-        mbar_expect_tx(full_bar(stage), kStageBytes);
+        mbar_expect_tx(full_bar(stage), p.a_exact ? kStageBytes - kABytes : kStageBytes);
         tma_load_2d(sb, &map_ah, full_bar(stage), kb * BK, tm * BM);
-        tma_load_2d(sb + kABytes, &map_al, full_bar(stage), kb * BK, tm * BM);
+        if (!p.a_exact) tma_load_2d(sb + kABytes, &map_al, full_bar(stage), kb * BK, tm * BM);
         tma_load_2d(sb + 2 * kABytes, &map_bh, full_bar(stage), kb * BK, tn * BN);
         tma_load_2d(sb + 2 * kABytes + kBBytes, &map_bl, full_bar(stage), kb * BK, tn * BN);
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -258,7 +259,7 @@ split_tf32_gemm_kernel(const __grid_constant__ CUtensorMap map_ah,
             const uint64_t dbl = make_desc(sb + 2 * kABytes + kBBytes + koff);
             tc_mma_tf32(tmem_d, dah, dbh, kIdesc, accumulate);
             tc_mma_tf32(tmem_d, dah, dbl, kIdesc, 1u);
-            tc_mma_tf32(tmem_d, dal, dbh, kIdesc, 1u);
+            if (!p.a_exact) tc_mma_tf32(tmem_d, dal, dbh, kIdesc, 1u);
             accumulate = 1u;
           }
           tc_commit(empty_bar(stage));  // frees the smem stage once these MMAs retire
@@ -401,7 +402,7 @@ syrk_operand_kernel(const float* __restrict__ x, const float* __restrict__ nw,
 __global__ void __launch_bounds__(256)
 split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int64_t cols_p,
                   uint64_t seed, uint64_t draw, uint64_t row_offset, int lower_only,
-                  float* __restrict__ dst_hi, float* __restrict__ dst_lo) {
+                  float* __restrict__ dst_hi, float* __restrict__ dst_lo /* NULL: src is exact */) {
   const int64_t nq_row = cols_p / 4;
   const int64_t total = rows * nq_row;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -421,6 +422,10 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
         for (int u = 0; u < 4; ++u)
           if (c + u < cols) v[u] = philox_normal1(seed, draw, e0 + u);
       }
+    }
+    if (dst_lo == nullptr) {
+      *reinterpret_cast<float4*>(dst_hi + r * cols_p + c) = make_float4(v[0], v[1], v[2], v[3]);
+      continue;
     }
     float hi[4], lo[4];
 #pragma unroll
@@ -572,6 +577,7 @@ extern "C" int ppi_wmoments_dense(const float* x, const float* nw, int64_t K, in
   p.ld = pl.Dp;
   p.split_stride = pl.Dp * pl.Dp;
   p.bias = nullptr;
+  p.a_exact = 0;
 
   int pass = 0;
   for (int64_t k0 = 0; k0 < K; k0 += pl.Kc, ++pass) {
@@ -646,6 +652,7 @@ extern "C" int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_
   p.split_stride = 0;
   p.bias = mu;
   p.accumulate = 0;
+  p.a_exact = z ? 0 : 1;  // Philox normals sit on the TF32 grid (common.cuh box_muller)
 
   for (int64_t k0 = 0; k0 < K; k0 += Kc) {
     const int64_t rows = (K - k0) < Kc ? (K - k0) : Kc;
@@ -656,7 +663,8 @@ extern "C" int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_
     {
       ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st);
       split_rows_kernel<<<grid, 256, 0, st>>>(z ? z + k0 * D : nullptr, z ? rows : rows_p, D, Dk, seed,
-                                              draw_id, row_offset + (uint64_t)k0, 0, z_hi, z_lo);
+                                              draw_id, row_offset + (uint64_t)k0, 0, z_hi,
+                                              z ? z_lo : nullptr);
       if (int rc = check_launch("split_rows_kernel(z)")) return rc;
     }
     p.tiles_m = (int)(rows_p / BM);

@@ -17,7 +17,7 @@ import torch
 
 from . import ops, samplers
 from .device import (DeviceArray, all_reduce_sum, broadcast_row, dist_info, f32, f64, require_cuda,
-                     shard_rows)
+                     shard_rows, to_host64)
 
 __all__ = [
     "RbfFeatures",
@@ -223,7 +223,7 @@ class GaussianPolicy(object):
     @property
     def mu(self):
         if self._mu_host is None:
-            self._mu_host = self._mu_dev.double().cpu().numpy()
+            self._mu_host = to_host64(self._mu_dev)
         return self._mu_host
 
     @mu.setter
@@ -233,7 +233,7 @@ class GaussianPolicy(object):
     @property
     def sigma(self):
         if self._sigma_host is None:
-            self._sigma_host = self._sigma_dev.double().cpu().numpy()
+            self._sigma_host = to_host64(self._sigma_dev)
         return self._sigma_host
 
     @sigma.setter
@@ -295,11 +295,9 @@ class GaussianPolicy(object):
         x, row_offset, n_total, replicated = _samples(samples)
         nw = _local(w.nw, row_offset, x.shape[0])
         d = x.shape[1]
-        mu_old, sigma_old = self.mu.copy(), self.sigma.copy()
-        old_chol64, old_logdet = None, None
         if d > self.small_dim:
-            self._factor()
-            old_chol64, old_logdet = self._chol64_dev, self._logdet
+            return self._weighted_update_large(w, x, nw, replicated, update_covariance_in)
+        mu_old, sigma_old = self.mu.copy(), self.sigma.copy()
 
         # pass 1: weighted mean, centred on the old mean for fp32 accuracy (policies.py:88)
         shift_old = self._mu_d()
@@ -310,7 +308,7 @@ class GaussianPolicy(object):
         mu_new = mu_old + s1.cpu().numpy()
 
         # pass 2: covariance centred on the new mean (policies.py:89-92)
-        sigma_new_host = sigma_new_dev = chol64 = None
+        sigma_new_host = chol64 = None
         pd = True
         if not update_covariance_in:
             pass
@@ -323,7 +321,7 @@ class GaussianPolicy(object):
             pd = bool(np.all(var > 0.0) and np.all(np.isfinite(var)))
             if pd:
                 chol64 = torch.diag(torch.sqrt(s2))
-        elif d <= self.small_dim:
+        else:
             acc = ops.wmoments_matnorm(x.reshape(x.shape[0], d, 1), nw, shift=mu_new_dev.reshape(d, 1))
             if not replicated:
                 all_reduce_sum(acc)
@@ -331,40 +329,72 @@ class GaussianPolicy(object):
             sigma_new_host = fin["cov64"].cpu().numpy()
             pd = int(fin["status"].item()) == 0
             chol64 = fin["chol64"]
-        else:
-            cov = ops.wmoments_dense(x, nw, shift=mu_new_dev)
-            if not replicated:
-                all_reduce_sum(cov)
-            sigma_new_dev = cov
-            chol64, info = torch.linalg.cholesky_ex(cov.double())
-            pd = int(info.item()) == 0
 
         # accept / regularise exactly like ppi/policies.py:258-268
         self._mu_host, self._mu_dev = mu_new, mu_new_dev
         if update_covariance_in:
             if pd:
-                self._sigma_host, self._sigma_dev = sigma_new_host, sigma_new_dev
+                self._sigma_host, self._sigma_dev = sigma_new_host, None
                 self._chol64_dev, self._chol_dev, self._logdet = chol64, None, None
             else:
                 logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
                 self.sigma = sigma_old + SIGMA_MIN * np.eye(d)
         ess = float(w.stats.ess)
-        return ess, self._kl(mu_old, sigma_old, old_chol64, old_logdet)
+        return ess, float(multivariate_gaussian_kl(self.mu, self.sigma, mu_old, sigma_old))
 
-    def _kl(self, mu_old, sigma_old, old_chol64, old_logdet):
-        """KL(new || old), ppi/policies.py:146-158,269."""
-        d = mu_old.shape[0]
-        if d <= self.small_dim:
-            return float(multivariate_gaussian_kl(self.mu, self.sigma, mu_old, sigma_old))
+    def _weighted_update_large(self, w, x, nw, replicated, update_covariance_in):
+        """d > small_dim: every array stays in HBM (tcgen05 covariance, device fp64 Cholesky /
+        log-det / KL); the only device -> host traffic is the two scalars returned.  `mu` /
+        `sigma` are copied to the host lazily when a caller reads them."""
+        d = x.shape[1]
         self._factor()
-        l_new, logdet_new = self._chol64_dev, self._logdet
-        diff = f64(mu_old - self.mu)
+        mu_old_dev, old_chol64, old_logdet = self._mu_d(), self._chol64_dev, self._logdet
+        sigma_old_host, sigma_old_dev = self._sigma_host, self._sigma_dev
+
+        # pass 1: weighted mean, centred on the old mean for fp32 accuracy (policies.py:88)
+        s1 = ops.wmoments_diag(x, nw, shift1=mu_old_dev)
+        if not replicated:
+            all_reduce_sum(s1)
+        mu_new_dev, _ = ops.finalize_gaussian(s1=s1, shift=mu_old_dev, want_sigma=False)
+        self._mu_host, self._mu_dev = None, mu_new_dev
+
+        # pass 2: covariance centred on the new mean (policies.py:89-92)
+        if update_covariance_in:
+            if self.diagonal:
+                _, s2 = ops.wmoments_diag(x, nw, shift2=mu_new_dev, second=True)
+                if not replicated:
+                    all_reduce_sum(s2)
+                cov = torch.diag(s2).float()
+                chol64 = torch.diag(torch.sqrt(s2))
+                pd = bool((torch.isfinite(s2) & (s2 > 0)).all().item())
+            else:
+                cov = ops.wmoments_dense(x, nw, shift=mu_new_dev)
+                if not replicated:
+                    all_reduce_sum(cov)
+                chol64, info = torch.linalg.cholesky_ex(cov.double())
+                pd = int(info.item()) == 0
+            # accept / regularise exactly like ppi/policies.py:258-268
+            if pd:
+                self._sigma_host, self._sigma_dev = None, cov
+                self._chol64_dev, self._chol_dev = chol64, None
+                self._logdet = float(2.0 * torch.log(torch.diagonal(chol64)).sum().item())
+            else:
+                logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
+                if sigma_old_host is not None:
+                    self.sigma = sigma_old_host + SIGMA_MIN * np.eye(d)
+                else:
+                    self._sigma_host = None
+                    self._sigma_dev = sigma_old_dev + SIGMA_MIN * torch.eye(d, device=x.device)
+                    self._chol_dev = self._chol64_dev = self._logdet = None
+                self._factor()
+        # KL(new || old), ppi/policies.py:146-158,269, from the two Cholesky factors:
         # tr(S_old^-1 S_new) = |L_old^-1 L_new|_F^2 ; diff^T S_old^-1 diff = |L_old^-1 diff|^2
-        a = torch.linalg.solve_triangular(old_chol64, l_new, upper=False)
-        b = torch.linalg.solve_triangular(old_chol64, diff[:, None], upper=False)
-        tr = float((a * a).sum().item())
-        quad = float((b * b).sum().item())
-        return 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(logdet_new) + tr + quad - d)
+        l_new, logdet_new = self._chol64_dev, self._logdet
+        rhs = torch.cat([l_new, (mu_old_dev - mu_new_dev).double()[:, None]], dim=1)
+        sol = torch.linalg.solve_triangular(old_chol64, rhs, upper=False)
+        tr_quad = float((sol * sol).sum().item())
+        kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(logdet_new) + tr_quad - d)
+        return float(w.stats.ess), kl
 
     @staticmethod
     def smooth(x, y, alpha):
