@@ -38,13 +38,29 @@ extern "C" {
 int ppi_version(void);
 const char* ppi_last_error(void);
 
+/* Process-wide options (new; no reference counterpart).
+ * PPI_OPT_GEMM_SCHEME selects how the tcgen05 kernels (ppi_wmoments_dense, ppi_sample_gaussian)
+ * rebuild fp32-accurate products from exact tensor-core operands:
+ *   PPI_GEMM_FP16X2  v 2^e = h1 + h2, h1 = fp16(v 2^e), h2 = fp16(rest), one power-of-two scale per
+ *                    operand; h1 g1 + h1 g2 + h2 g1 as kind::f16 MMAs (error <= 3 2^-22 |a||b| for
+ *                    entries within 2^-28 of the operand's largest; 4 bytes per value).  Default.
+ *   PPI_GEMM_TF32X3  hi = tf32(v), lo = tf32(v - hi); hi hi + hi lo + lo hi as kind::tf32 MMAs
+ *                    (error ~2^-21 |a||b| at any magnitude; 8 bytes per value, twice the MMA time).
+ * PPI_OPT_GEMM_CHUNK = 32-deep k-blocks accumulated inside the tensor core before the partial sum is
+ * promoted to fp32 registers (tcgen05 accumulation truncates: ~3e-8 relative per MMA instruction).
+ * Even, default 4. */
+enum { PPI_OPT_GEMM_SCHEME = 0, PPI_OPT_GEMM_CHUNK = 1 };
+enum { PPI_GEMM_TF32X3 = 0, PPI_GEMM_FP16X2 = 1 };
+int ppi_set_option(int key, int value);
+int ppi_get_option(int key);
+
 /* ------------------------------------------------------------------------------------------
  * a3  base normals: np.random.randn(n, d)                         ppi/samplers.py:18-20
  * Philox4x32-10 + Box-Muller.  Element (r, c) of the (rows, cols) output is a pure function of
  * (seed, draw_id, row_offset + r, c): K-sharded ranks reproduce the 1-GPU matrix bit for bit.
- * The normals are emitted on the TF32 grid (11 significant bits, relative spacing 2^-11) so that
- * they are exact tensor-core operands for ppi_sample_gaussian; every sampler below that draws
- * on the device sees exactly these numbers.
+ * The normals are emitted as IEEE half-precision values held in fp32 (11 significant bits,
+ * relative spacing 2^-11) so that they are exact tensor-core operands for ppi_sample_gaussian;
+ * every sampler below that draws on the device sees exactly these numbers.
  * ---------------------------------------------------------------------------------------- */
 int ppi_philox_normal(float* out, int64_t rows, int64_t cols, uint64_t seed, uint64_t draw_id,
                       uint64_t row_offset, void* stream);
@@ -98,7 +114,7 @@ int ppi_sample_iid(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row
 
 /* a7  GaussianPolicy.__call__ in Cholesky form  x = mu + z L^T      ppi/policies.py:247-249,
  * ppi/samplers.py:38-39.  L (D,D) lower triangular.  D <= 128 runs an fp32 SIMT kernel; larger
- * D runs the tcgen05 split-TF32 GEMM and needs the workspace.                               */
+ * D runs the persistent tcgen05 split-product GEMM (PPI_OPT_GEMM_SCHEME) and needs the workspace. */
 size_t ppi_sample_gaussian_workspace_bytes(int64_t K, int64_t D);
 int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
                         int64_t K, int64_t D, const float* mu, const float* L, float* x,
@@ -190,13 +206,17 @@ int ppi_wmoments_matnorm(const float* x, const float* nw, int64_t K, int H, int 
                          const float* shift, const float* inv_cov_out, double* acc, void* stream);
 
 /* a16  dense weighted covariance  sum_k nw_k (x_k - shift)(x_k - shift)^T   ppi/policies.py:89-92
- * on tcgen05 tensor cores (split-TF32, 3 MMAs per tile step, chunked fp32 promotion), operands
- * staged K-major by a transposing pre-pass and fed by TMA.  cov (D,D) receives the symmetrised
- * result (+= when accumulate != 0).  Any D >= 1; D < 64 is cheaper through ppi_wmoments_matnorm.*/
+ * on tcgen05 tensor cores (split products per PPI_OPT_GEMM_SCHEME, chunked fp32 promotion),
+ * operands staged K-major by a transposing pre-pass and fed by TMA.  cov (D,D) receives the
+ * symmetrised result (+= when accumulate != 0).  Any D >= 1; D < 64 is cheaper through
+ * ppi_wmoments_matnorm.  dev_bound (device scalar, may be NULL): an upper bound of |x_ki - shift_i|
+ * over the rows with nw_k != 0, used by the FP16X2 scheme to pick its operand scale; any bound
+ * within ~2^10 of the true maximum is as good as the maximum itself.  NULL = measured with one
+ * extra pass over x.  ppi_wmoments_diag can produce it for free (absdev_max).               */
 size_t ppi_wmoments_dense_workspace_bytes(int64_t K, int64_t D);
 int ppi_wmoments_dense(const float* x, const float* nw, int64_t K, int64_t D, const float* shift,
-                       float* cov, int accumulate, void* workspace, size_t workspace_bytes,
-                       void* stream);
+                       const float* dev_bound, float* cov, int accumulate, void* workspace,
+                       size_t workspace_bytes, void* stream);
 
 /* a17 tail: sigma = cov - delta delta^T (delta = new mean - shift), optional factorized() and
  * symmetric()                                                        ppi/policies.py:53-62,92 */

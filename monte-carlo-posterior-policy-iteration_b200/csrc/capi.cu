@@ -45,6 +45,34 @@ ProfileScope::~ProfileScope() {
 }
 }  // namespace ppi
 
+namespace ppi {
+static std::atomic<int> g_gemm_scheme{PPI_GEMM_FP16X2};
+int gemm_scheme() { return g_gemm_scheme.load(std::memory_order_relaxed); }
+static std::atomic<int> g_gemm_chunk{4};
+int gemm_chunk() { return g_gemm_chunk.load(std::memory_order_relaxed); }
+}  // namespace ppi
+
+extern "C" int ppi_set_option(int key, int value) {
+  if (key == PPI_OPT_GEMM_SCHEME) {
+    PPI_REQUIRE(value == PPI_GEMM_TF32X3 || value == PPI_GEMM_FP16X2, PPI_ERR_INVALID,
+                "ppi_set_option: unknown GEMM scheme %d", value);
+    ppi::g_gemm_scheme.store(value);
+    return 0;
+  }
+  if (key == PPI_OPT_GEMM_CHUNK) {
+    PPI_REQUIRE(value >= 2 && value <= 4096 && value % 2 == 0, PPI_ERR_INVALID,
+                "ppi_set_option: GEMM chunk must be an even number of k-blocks in [2, 4096]");
+    ppi::g_gemm_chunk.store(value);
+    return 0;
+  }
+  PPI_REQUIRE(false, PPI_ERR_INVALID, "ppi_set_option: unknown key %d", key);
+}
+
+extern "C" int ppi_get_option(int key) {
+  return key == PPI_OPT_GEMM_SCHEME ? ppi::gemm_scheme()
+       : key == PPI_OPT_GEMM_CHUNK ? ppi::gemm_chunk() : -1;
+}
+
 extern "C" int64_t ppi_launch_count(void) { return ppi::g_launches.load(); }
 
 extern "C" int ppi_profile_enable(int on) {

@@ -1,6 +1,7 @@
 // Shared device/host helpers for the PPI update-path kernels (sm_100a only).
 #pragma once
 
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -92,25 +93,21 @@ __device__ __forceinline__ float u01(uint32_t r) {
   return fmaf((float)r, 2.3283064365386963e-10f, 1.1641532182693481e-10f);
 }
 
-// Round to nearest TF32 (10 explicit mantissa bits, low 13 bits of the fp32 pattern zero).
-__device__ __forceinline__ float round_tf32(float v) {
-  uint32_t u;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
-  return __uint_as_float(u);
-}
-
-// Box-Muller.  The base normals are emitted on the TF32 grid (relative spacing 2^-11, variance
-// inflation < 2^-22/12, far below the fast-math error of __logf / __sincosf): a Philox normal is
-// then an EXACT tensor-core operand, so the dense Gaussian transform z L^T needs no low-order
-// split of z (tc_gemm.cu).  Every consumer (ppi_philox_normal and the fused samplers) goes through
+// Box-Muller.  The base normals are emitted as IEEE half-precision VALUES (held in fp32): 11
+// significant bits, relative spacing 2^-11 (variance inflation < 2^-22/12, far below the error of
+// __logf / __sincosf), |z| <= 6.67 so nothing overflows.  A Philox normal is therefore an EXACT
+// tensor-core operand (fp16, and also tf32): the dense Gaussian transform z L^T needs no low-order
+// part of z (tc_gemm.cu).  Every consumer (ppi_philox_normal and the fused samplers) goes through
 // this function, so they all see the same numbers.
+__device__ __forceinline__ float round_half(float v) { return __half2float(__float2half_rn(v)); }
+
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
   float u = u01(a), v = u01(b);
   float r = sqrtf(-2.0f * __logf(u));
   float s, c;
   __sincosf(6.283185307179586f * v, &s, &c);
-  z0 = round_tf32(r * c);
-  z1 = round_tf32(r * s);
+  z0 = round_half(r * c);
+  z1 = round_half(r * s);
 }
 
 // The four normals of element quad q (elements 4q..4q+3 of the row-major global (K_total, n)

@@ -4,22 +4,41 @@
 //   ppi_sample_gaussian  x = mu + z L^T  (D > 128)                ppi/policies.py:247-249,
 //                                                                  ppi/samplers.py:38-39
 //
-// Both are the same tensor-core contraction  C[m,n] = sum_k A[m,k] B[n,k]  with both operands
-// stored K-major (contraction index contiguous), which is the canonical tcgen05 shared-memory
-// layout (128-byte swizzle, 8-row atoms).
+// Both are tensor-core contractions  C[m,n] = sum_k A[m,k] B[n,k]  with both operands stored
+// K-major (contraction index contiguous), the canonical tcgen05 shared-memory layout (128-byte
+// swizzle, 8-row atoms), staged by operand pre-passes and fed by TMA.
 //
-// Precision.  tcgen05 has no fp32-input MMA; kind::tf32 keeps 10 mantissa bits.  To meet the
-// 1e-5 parity bar every operand is split on the fly by a pre-pass into hi = tf32(v) and
-// lo = tf32(v - hi) and each k-step issues three MMAs (hi*hi + hi*lo + lo*hi), which leaves a
-// relative product error of ~2^-22.  The fp32 TMEM accumulator is drained into registers every
-// `chunk_kb` k-blocks (two 256-column TMEM buffers ping-pong), so no accumulation chain inside
-// the tensor core is longer than 3 * 4 * chunk_kb MMAs; across chunks the sum is carried in
-// fp32 registers with round-to-nearest adds.
+// Precision.  tcgen05 has no fp32-input MMA, and its fp32 accumulation TRUNCATES: measured here,
+// every MMA instruction that adds into a TMEM accumulator costs ~3e-8 relative (biased), so a
+// chain of n instructions drifts by ~3e-8 n.  Two consequences shape both kernels:
+//   (1) fp32 operand values are split by a pre-pass into exact tensor-core operands and the
+//       product is rebuilt from partial products (scheme chosen with ppi_set_option):
+//         PPI_GEMM_FP16X2  v 2^e = h1 + h2 + O(2^-22 |v 2^e|), h1 = fp16(v 2^e), h2 = fp16(rest); one
+//                          power-of-two scale 2^e per operand puts its largest entry in
+//                          [2^13, 2^14), so entries down to 2^-28 of the largest keep 22 bits.
+//                          h1 g1 + h1 g2 + h2 g1 as three kind::f16 MMAs: error <= 3 2^-22 |a||b|,
+//                          4 bytes per operand value, 6 MMA instructions per 32-deep k-block.
+//         PPI_GEMM_TF32X3  hi = tf32(v), lo = tf32(v - hi); hi hi + hi lo + lo hi as three
+//                          kind::tf32 MMAs: error ~2^-21 |a||b| at any magnitude, 8 bytes per
+//                          value, 12 MMA instructions per k-block.  Kept as the conservative path.
+//       Philox normals are exact single fp16 / tf32 operands (common.cuh box_muller).
+//   (2) the TMEM accumulator is drained into fp32 registers (round-to-nearest adds) every
+//       `chunk` k-blocks -- two 256-column TMEM buffers ping-pong, so draining overlaps the MMAs
+//       of the next chunk -- which bounds every in-tensor-core chain to a few dozen instructions.
+// Both kernels are fed faster by the tensor pipe than L2 can deliver operands (ncu: ~54 B/clk/SM
+// of TMA ingest), which is why the 4-byte operand form matters more than the MMA count.
 //
 // CTA = 10 warps: warp 0 TMA producer (one lane), warp 1 MMA issuer (one lane) + TMEM
 // allocation, warps 2..9 drain TMEM (each warp owns its hardware lane quarter and one 128-column
-// half).  One output tile of 128 x 256 per CTA.
+// half).  One 128 x 256 accumulator per TMEM buffer.
+//
+// Covariance: one upper-triangular 128 x 256 output tile x one K-split per CTA, 144 CTAs.
+// Sampling: transposed product  X^T[j, s] = sum_k L[j,k] z[s,k]  so that TMEM lanes are output
+// columns j and a warp's 32 lanes store 128 contiguous bytes of one sample row; persistent CTAs
+// walk (sample block, j-tile pair) work units -- pairs (i, T-1-i) have equal triangular cost --
+// and the epilogue of one tile overlaps the MMAs of the next through the two TMEM buffers.
 #include <cuda.h>
+#include <cuda_bf16.h>
 
 #include "common.cuh"
 
@@ -27,32 +46,13 @@ namespace ppi {
 
 constexpr int BM = 128;        // UMMA M (TMEM lanes)
 constexpr int BN = 256;        // UMMA N (TMEM columns per accumulator)
-constexpr int BK = 32;         // fp32 elements per k-block = 128 bytes = one swizzle row
-constexpr int UMMA_K = 8;      // tf32
-constexpr int kStages = 2;
+constexpr int BK = 32;         // contraction steps per k-block (one 128-byte row of fp32 or of an fp16 pair)
 constexpr int kGemmThreads = 320;
-constexpr uint32_t kABytes = BM * BK * 4;   // 16 KB
-constexpr uint32_t kBBytes = BN * BK * 4;   // 32 KB
-constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // Ah, Al, Bh, Bl = 96 KB
-constexpr uint32_t kGemmSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-
-enum { GEMM_SYRK = 0, GEMM_SAMPLE = 1 };
-
-struct GemmParams {
-  int mode;
-  int num_kb;        // total k-blocks of the contraction
-  int chunk_kb;      // k-blocks per TMEM accumulation chunk
-  int kb_per_split;  // SYRK: k-blocks handled by one CTA
-  int splits;        // SYRK: CTAs per output tile
-  int tiles_m, tiles_n;
-  int64_t M, N;      // valid output extent (rows, cols)
-  float* out;        // SYRK: partials [splits][ld][ld]; SAMPLE: x [M][ld]
-  int64_t ld;
-  int64_t split_stride;
-  const float* bias; // SAMPLE: mu[n]
-  int accumulate;    // SYRK: partial += acc
-  int a_exact;       // SAMPLE: A (the Philox normals) is exactly TF32: no A_lo operand, 2 MMAs per step
-};
+constexpr uint32_t kABytes = BM * 128;      // 16 KB: 128 rows x 128 B
+constexpr uint32_t kBBytes = BN * 128;      // 32 KB
+constexpr int kMaxStages = 4;
+constexpr uint32_t kPipeBytes = 192 * 1024; // every variant uses stages * stage_bytes = 192 KB
+constexpr uint32_t kGemmSmemBytes = kPipeBytes + 1024 /*align*/ + 256 /*barriers*/;
 
 // ---------------------------------------------------------------------------------------------
 // PTX wrappers
@@ -152,55 +152,82 @@ __device__ __forceinline__ void split_tf32(float v, float& hi, float& lo) {
   lo = __uint_as_float(tf32_rna(v - hi));
 }
 
-// ---------------------------------------------------------------------------------------------
-// The GEMM kernel
-// ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kGemmThreads, 1)
-split_tf32_gemm_kernel(const __grid_constant__ CUtensorMap map_ah,
-                       const __grid_constant__ CUtensorMap map_al,
-                       const __grid_constant__ CUtensorMap map_bh,
-                       const __grid_constant__ CUtensorMap map_bl, const GemmParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw = smem_u32(smem_raw);
-  const uint32_t base = (raw + 1023u) & ~1023u;
-  uint8_t* smem = smem_raw + (base - raw);
-  const uint32_t bar_base = base + kStages * kStageBytes;
-  // barriers: full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], then the TMEM pointer
-  auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
-  auto tfull_bar = [&](int b) { return bar_base + 8u * (2 * kStages + b); };
-  auto tempty_bar = [&](int b) { return bar_base + 8u * (2 * kStages + 2 + b); };
-  volatile uint32_t* tmem_ptr_smem =
-      reinterpret_cast<volatile uint32_t*>(smem + kStages * kStageBytes + 8 * (2 * kStages + 4));
+// kind::f16 with fp16 inputs, fp32 accumulate, A and B K-major.
+constexpr uint32_t kIdescF16 = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                           uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 
-  // ---- tile / k-range of this CTA ----
-  int tm, tn, kb_begin, kb_end, split = 0;
-  if (p.mode == GEMM_SYRK) {
-    int t = blockIdx.x / p.splits;
-    split = blockIdx.x % p.splits;
-    tm = 0;
-    for (;; ++tm) {  // upper-triangular tiles: tn >= tn_min(tm)
-      const int tn_min = (tm * BM) / BN;
-      const int cnt = p.tiles_n - tn_min;
-      if (t < cnt) { tn = tn_min + t; break; }
-      t -= cnt;
-    }
-    kb_begin = split * p.kb_per_split;
-    kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
-  } else {
-    tm = blockIdx.x / p.tiles_n;
-    tn = blockIdx.x % p.tiles_n;
-    kb_begin = 0;
-    kb_end = min(p.num_kb, ((tn + 1) * BN + BK - 1) / BK);  // L is lower triangular
+// ---- split products of one pipeline stage into the accumulator at tmem_d -------------------------
+// TF32X3 stage: A_hi | A_lo | B_hi | B_lo (fp32 rows of 32), 32 contraction steps.
+__device__ __forceinline__ void issue_tf32x3(uint32_t tmem_d, uint32_t sb, uint32_t& accumulate,
+                                             bool use_alo, bool use_blo) {
+  const uint32_t ah = sb, al = sb + kABytes, bh = sb + 2 * kABytes, bl = sb + 2 * kABytes + kBBytes;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t koff = (uint32_t)k * 32u;  // 8 tf32 = 32 bytes inside the 128-byte swizzle row
+    const uint64_t dah = make_desc(ah + koff), dbh = make_desc(bh + koff);
+    tc_mma_tf32(tmem_d, dah, dbh, kIdesc, accumulate);
+    accumulate = 1u;
+    if (use_blo) tc_mma_tf32(tmem_d, dah, make_desc(bl + koff), kIdesc, 1u);
+    if (use_alo) tc_mma_tf32(tmem_d, make_desc(al + koff), dbh, kIdesc, 1u);
   }
-  const int nkb = max(0, kb_end - kb_begin);
-  const int nchunks = (nkb + p.chunk_kb - 1) / p.chunk_kb;
+}
+// FP16X2 pair x pair: rows are [h1 x 32 | h2 x 32] fp16, 32 contraction steps, 2 k-steps of 16.
+__device__ __forceinline__ void issue_f16_pair_pair(uint32_t tmem_d, uint32_t a, uint32_t b,
+                                                    uint32_t& accumulate) {
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const uint32_t off = (uint32_t)k * 32u;  // 16 fp16 = 32 bytes
+    const uint64_t a1 = make_desc(a + off), b1 = make_desc(b + off);
+    tc_mma_f16(tmem_d, a1, b1, kIdescF16, accumulate);
+    accumulate = 1u;
+    tc_mma_f16(tmem_d, a1, make_desc(b + 64u + off), kIdescF16, 1u);
+    tc_mma_f16(tmem_d, make_desc(a + 64u + off), b1, kIdescF16, 1u);
+  }
+}
+// FP16X2 pair x single: A rows [h1 x 32 | h2 x 32], B rows hold 64 exact fp16 (two k-blocks);
+// `half` selects which 32 of them this A box multiplies.
+__device__ __forceinline__ void issue_f16_pair_single(uint32_t tmem_d, uint32_t a, uint32_t b, int half,
+                                                      uint32_t& accumulate) {
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const uint32_t off = (uint32_t)k * 32u;
+    const uint64_t bz = make_desc(b + (uint32_t)half * 64u + off);
+    tc_mma_f16(tmem_d, make_desc(a + off), bz, kIdescF16, accumulate);
+    accumulate = 1u;
+    tc_mma_f16(tmem_d, make_desc(a + 64u + off), bz, kIdescF16, 1u);
+  }
+}
 
+// ---- shared CTA prologue: barriers + TMEM allocation ----------------------------------------------
+struct GemmSmem {
+  uint32_t base;      // 1024-aligned shared address of stage 0
+  uint32_t bar_base;  // barriers: full[kMaxStages], empty[kMaxStages], tfull[2], tempty[2]
+  __device__ __forceinline__ uint32_t full_bar(int s) const { return bar_base + 8u * s; }
+  __device__ __forceinline__ uint32_t empty_bar(int s) const { return bar_base + 8u * (kMaxStages + s); }
+  __device__ __forceinline__ uint32_t tfull_bar(int b) const { return bar_base + 8u * (2 * kMaxStages + b); }
+  __device__ __forceinline__ uint32_t tempty_bar(int b) const { return bar_base + 8u * (2 * kMaxStages + 2 + b); }
+};
+
+__device__ __forceinline__ uint32_t gemm_prologue(uint8_t* smem_raw, GemmSmem& gs) {
+  const uint32_t raw = smem_u32(smem_raw);
+  gs.base = (raw + 1023u) & ~1023u;
+  gs.bar_base = gs.base + kPipeBytes;
+  uint8_t* smem = smem_raw + (gs.base - raw);
+  volatile uint32_t* tmem_ptr_smem =
+      reinterpret_cast<volatile uint32_t*>(smem + kPipeBytes + 8 * (2 * kMaxStages + 4));
+  const int warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 8); }
+    for (int s = 0; s < kMaxStages; ++s) { mbar_init(gs.full_bar(s), 1); mbar_init(gs.empty_bar(s), 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(gs.tfull_bar(b), 1); mbar_init(gs.tempty_bar(b), 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -211,25 +238,110 @@ split_tf32_gemm_kernel(const __grid_constant__ CUtensorMap map_ah,
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr_smem;
+  return *tmem_ptr_smem;
+}
+
+__device__ __forceinline__ void gemm_teardown(uint32_t tmem_base) {
+  tc_fence_before();
+  __syncthreads();
+  if ((threadIdx.x >> 5) == 1) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512)
+                 : "memory");
+  }
+}
+
+// acc[128] += the 128 columns [col0, col0+128) of this warp's TMEM lane quarter
+__device__ __forceinline__ void drain_add(uint32_t taddr, float (&acc)[128]) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint32_t v[32];
+    tc_ld32(taddr + j * 32, v);
+    tc_wait_ld();
+#pragma unroll
+    for (int i = 0; i < 32; ++i) acc[j * 32 + i] += __uint_as_float(v[i]);
+  }
+}
+
+// Device-side scalars of one GEMM call (filled by tiny kernels, never read by the host).
+struct GemmScalars {
+  unsigned int amax_a_bits;  // max |.| of operand A source (non-negative float bits, atomicMax)
+  unsigned int amax_b_bits;
+  float scale_a, scale_b;    // power-of-two operand scales (1 for TF32X3)
+  float inv_scale;           // 1 / (scale_a * scale_b)
+  float pad[3];
+};
+
+// ---------------------------------------------------------------------------------------------
+// Covariance kernel: partial[split][tile] (+)= A_tile A_tile'^T over this CTA's k-range
+// ---------------------------------------------------------------------------------------------
+struct SyrkParams {
+  int num_kb;        // k-blocks in the staged operand
+  int chunk_kb;      // k-blocks per TMEM accumulation chunk
+  int kb_per_split;  // k-blocks handled by one CTA
+  int splits;        // CTAs per output tile
+  int tiles_n;
+  float* out;        // partials [splits][ld][ld]
+  int64_t ld;
+  int64_t split_stride;
+  int accumulate;    // partial += acc
+};
+
+template <bool FP16>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+syrk_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_a2,
+                 const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_b2,
+                 const SyrkParams p) {
+  // FP16: stage = A pair (16 KB) | B pair (32 KB), 4 stages.  TF32X3: A_hi | A_lo | B_hi | B_lo, 2 stages.
+  constexpr int kStages = FP16 ? 4 : 2;
+  constexpr uint32_t kStageBytes = FP16 ? (kABytes + kBBytes) : 2 * (kABytes + kBBytes);
+  static_assert(kStages * kStageBytes == kPipeBytes, "pipeline must fill the smem budget");
+  constexpr int kx = FP16 ? 2 * BK : BK;  // elements per k-block in the operand array
+
+  extern __shared__ uint8_t smem_raw[];
+  GemmSmem gs;
+  const uint32_t tmem_base = gemm_prologue(smem_raw, gs);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // ---- tile / k-range of this CTA: upper-triangular tiles, tn >= tn_min(tm) ----
+  int t = blockIdx.x / p.splits;
+  const int split = blockIdx.x % p.splits;
+  int tm = 0, tn = 0;
+  for (;; ++tm) {
+    const int tn_min = (tm * BM) / BN;
+    const int cnt = p.tiles_n - tn_min;
+    if (t < cnt) { tn = tn_min + t; break; }
+    t -= cnt;
+  }
+  const int kb_begin = split * p.kb_per_split;
+  const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+  const int nkb = max(0, kb_end - kb_begin);
+  const int nchunks = (nkb + p.chunk_kb - 1) / p.chunk_kb;
 
   if (warp == 0) {
     if (lane == 0 && nkb > 0) {
       // ================= TMA producer =================
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_ah) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_al) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_bh) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_bl) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+      if (!FP16) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a2) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b2) : "memory");
+      }
       int stage = 0;
       uint32_t phase = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait(empty_bar(stage), phase ^ 1u);
-        const uint32_t sb = base + stage * kStageBytes;
-        mbar_expect_tx(full_bar(stage), p.a_exact ? kStageBytes - kABytes : kStageBytes);
-        tma_load_2d(sb, &map_ah, full_bar(stage), kb * BK, tm * BM);
-        if (!p.a_exact) tma_load_2d(sb + kABytes, &map_al, full_bar(stage), kb * BK, tm * BM);
-        tma_load_2d(sb + 2 * kABytes, &map_bh, full_bar(stage), kb * BK, tn * BN);
-        tma_load_2d(sb + 2 * kABytes + kBBytes, &map_bl, full_bar(stage), kb * BK, tn * BN);
+        mbar_wait(gs.empty_bar(stage), phase ^ 1u);
+        const uint32_t sb = gs.base + stage * kStageBytes;
+        mbar_expect_tx(gs.full_bar(stage), kStageBytes);
+        if (FP16) {
+          tma_load_2d(sb, &map_a, gs.full_bar(stage), kb * kx, tm * BM);
+          tma_load_2d(sb + kABytes, &map_b, gs.full_bar(stage), kb * kx, tn * BN);
+        } else {
+          tma_load_2d(sb, &map_a, gs.full_bar(stage), kb * kx, tm * BM);
+          tma_load_2d(sb + kABytes, &map_a2, gs.full_bar(stage), kb * kx, tm * BM);
+          tma_load_2d(sb + 2 * kABytes, &map_b, gs.full_bar(stage), kb * kx, tn * BN);
+          tma_load_2d(sb + 2 * kABytes + kBBytes, &map_b2, gs.full_bar(stage), kb * kx, tn * BN);
+        }
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
@@ -241,31 +353,21 @@ split_tf32_gemm_kernel(const __grid_constant__ CUtensorMap map_ah,
       int kb = 0;
       for (int c = 0; c < nchunks; ++c) {
         const int buf = c & 1;
-        mbar_wait(tempty_bar(buf), (((uint32_t)c >> 1) & 1u) ^ 1u);
+        mbar_wait(gs.tempty_bar(buf), (((uint32_t)c >> 1) & 1u) ^ 1u);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)buf * BN;
         const int kb_chunk_end = min(nkb, kb + p.chunk_kb);
         uint32_t accumulate = 0;
         for (; kb < kb_chunk_end; ++kb) {
-          mbar_wait(full_bar(stage), phase);
+          mbar_wait(gs.full_bar(stage), phase);
           tc_fence_after();
-          const uint32_t sb = base + stage * kStageBytes;
-#pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint32_t koff = (uint32_t)k * UMMA_K * 4;
-            const uint64_t dah = make_desc(sb + koff);
-            const uint64_t dal = make_desc(sb + kABytes + koff);
-            const uint64_t dbh = make_desc(sb + 2 * kABytes + koff);
-            const uint64_t dbl = make_desc(sb + 2 * kABytes + kBBytes + koff);
-            tc_mma_tf32(tmem_d, dah, dbh, kIdesc, accumulate);
-            tc_mma_tf32(tmem_d, dah, dbl, kIdesc, 1u);
-            if (!p.a_exact) tc_mma_tf32(tmem_d, dal, dbh, kIdesc, 1u);
-            accumulate = 1u;
-          }
-          tc_commit(empty_bar(stage));  // frees the smem stage once these MMAs retire
+          const uint32_t sb = gs.base + stage * kStageBytes;
+          if (FP16) issue_f16_pair_pair(tmem_d, sb, sb + kABytes, accumulate);
+          else issue_tf32x3(tmem_d, sb, accumulate, true, true);
+          tc_commit(gs.empty_bar(stage));  // frees the smem stage once these MMAs retire
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-        tc_commit(tfull_bar(buf));  // accumulator chunk complete
+        tc_commit(gs.tfull_bar(buf));  // accumulator chunk complete
       }
     }
   } else {
@@ -278,82 +380,318 @@ split_tf32_gemm_kernel(const __grid_constant__ CUtensorMap map_ah,
     for (int i = 0; i < 128; ++i) acc[i] = 0.f;
     for (int c = 0; c < nchunks; ++c) {
       const int buf = c & 1;
-      mbar_wait(tfull_bar(buf), ((uint32_t)c >> 1) & 1u);
+      mbar_wait(gs.tfull_bar(buf), ((uint32_t)c >> 1) & 1u);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN + h * 128);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uint32_t v[32];
-        tc_ld32(taddr + j * 32, v);
-        tc_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) acc[j * 32 + i] += __uint_as_float(v[i]);
-      }
+      drain_add(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN + h * 128), acc);
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(buf));
+      if (lane == 0) mbar_arrive(gs.tempty_bar(buf));
     }
-    // ---- write the tile ----
+    // ---- write the tile (ld is a multiple of 128; the partial buffer covers whole tiles) ----
     const int64_t m = (int64_t)tm * BM + q * 32 + lane;
     const int64_t n0 = (int64_t)tn * BN + h * 128;
-    if (m < p.M) {
-      if (p.mode == GEMM_SYRK) {
-        float* dst = p.out + (int64_t)split * p.split_stride + m * p.ld + n0;
-        // ld is a multiple of 128 and the partial buffer covers whole tiles of columns < ld
+    if (m < p.ld) {
+      float* dst = p.out + (int64_t)split * p.split_stride + m * p.ld + n0;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          if (n0 + 4 * j < p.ld) {
-            float4 v = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
-            float4* d4 = reinterpret_cast<float4*>(dst) + j;
-            if (p.accumulate) {
-              const float4 o = *d4;
-              v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+      for (int j = 0; j < 32; ++j) {
+        if (n0 + 4 * j < p.ld) {
+          float4 v = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
+          float4* d4 = reinterpret_cast<float4*>(dst) + j;
+          if (p.accumulate) {
+            const float4 o = *d4;
+            v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+          }
+          *d4 = v;
+        }
+      }
+    }
+  }
+  gemm_teardown(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sampling kernel (transposed, persistent):  x[s, j] = mu[j] + sum_{k<=j} L[j,k] z[s,k]
+//   A = L rows (UMMA M = 128 output columns j -> TMEM lanes), B = z rows (UMMA N = 256 samples
+//   -> TMEM columns).  Work unit = (sample block nb, pair p) -> j-tiles T-1-p then p.
+//   FP16, !ZPAIR  Philox z = one exact fp16 per value: stage = 64 steps: L pair x2 | z single, 3 stages
+//   FP16,  ZPAIR  injected z = fp16 pair:              stage = 32 steps: L pair | z pair,      4 stages
+//   !FP16         TF32X3:                               stage = 32 steps: L_hi|L_lo|z_hi|z_lo,  2 stages
+// ---------------------------------------------------------------------------------------------
+struct SampleParams {
+  int tiles_j;          // ceil(D / 128)
+  int units_per_block;  // ceil(tiles_j / 2)
+  int num_st;           // pipeline stages covering the padded contraction length
+  int chunk_st;         // stages per TMEM accumulation chunk
+  int64_t n_units;      // sample blocks * units_per_block
+  int64_t rows;         // valid samples in this pass
+  int64_t D;
+  float* x;             // [rows][D]
+  const float* mu;
+  const GemmScalars* scalars;  // inv_scale (FP16) or NULL
+  int z_exact;          // TF32X3 only: z is exactly tf32 (Philox), its low-order operand is skipped
+};
+
+template <bool FP16, bool ZPAIR>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_constant__ CUtensorMap map_l2,
+                   const __grid_constant__ CUtensorMap map_z, const __grid_constant__ CUtensorMap map_z2,
+                   const SampleParams p) {
+  constexpr bool kSingle = FP16 && !ZPAIR;
+  constexpr int KS = kSingle ? 64 : 32;  // contraction steps per stage
+  constexpr int kStages = kSingle ? 3 : (FP16 ? 4 : 2);
+  constexpr uint32_t kStageBytes = kSingle ? (2 * kABytes + kBBytes)
+                                           : (FP16 ? (kABytes + kBBytes) : 2 * (kABytes + kBBytes));
+  static_assert(kStages * kStageBytes == kPipeBytes, "pipeline must fill the smem budget");
+
+  extern __shared__ uint8_t smem_raw[];
+  GemmSmem gs;
+  const uint32_t tmem_base = gemm_prologue(smem_raw, gs);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool load_zlo = !FP16 && !p.z_exact;
+
+  // Every role walks the same tile sequence.
+  auto tile_j = [&](int pr, int tt) { return tt == 0 ? p.tiles_j - 1 - pr : pr; };
+  auto tiles_in_unit = [&](int pr) { return (p.tiles_j - 1 - pr != pr) ? 2 : 1; };
+  auto stages_of = [&](int tj) { return min(p.num_st, ((tj + 1) * BM + KS - 1) / KS); };  // L lower triangular
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ================= TMA producer =================
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_l) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_z) : "memory");
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int64_t u = blockIdx.x; u < p.n_units; u += gridDim.x) {
+        const int nb = (int)(u / p.units_per_block), pr = (int)(u % p.units_per_block);
+        for (int tt = 0; tt < tiles_in_unit(pr); ++tt) {
+          const int tj = tile_j(pr, tt), nst = stages_of(tj);
+          for (int s = 0; s < nst; ++s) {
+            mbar_wait(gs.empty_bar(stage), phase ^ 1u);
+            const uint32_t sb = gs.base + stage * kStageBytes;
+            const uint32_t fb = gs.full_bar(stage);
+            if (kSingle) {
+              mbar_expect_tx(fb, kStageBytes);
+              tma_load_2d(sb, &map_l, fb, (2 * s) * 64, tj * BM);            // L pair, k-block 2s
+              tma_load_2d(sb + kABytes, &map_l, fb, (2 * s + 1) * 64, tj * BM);  // k-block 2s+1
+              tma_load_2d(sb + 2 * kABytes, &map_z, fb, s * 64, nb * BN);    // 64 exact fp16 per row
+            } else if (FP16) {
+              mbar_expect_tx(fb, kStageBytes);
+              tma_load_2d(sb, &map_l, fb, s * 64, tj * BM);
+              tma_load_2d(sb + kABytes, &map_z, fb, s * 64, nb * BN);
+            } else {
+              mbar_expect_tx(fb, load_zlo ? kStageBytes : kStageBytes - kBBytes);
+              tma_load_2d(sb, &map_l, fb, s * BK, tj * BM);
+              tma_load_2d(sb + kABytes, &map_l2, fb, s * BK, tj * BM);
+              tma_load_2d(sb + 2 * kABytes, &map_z, fb, s * BK, nb * BN);
+              if (load_zlo) tma_load_2d(sb + 2 * kABytes + kBBytes, &map_z2, fb, s * BK, nb * BN);
             }
-            *d4 = v;
+            if (++stage == kStages) { stage = 0; phase ^= 1u; }
           }
         }
-      } else {
-        float* dst = p.out + m * p.ld + n0;
-        const bool vec = (p.ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0) &&
-                         ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ================= MMA issuer =================
+      int stage = 0;
+      uint32_t phase = 0, ccount = 0;  // ccount: chunks issued so far (selects the TMEM buffer)
+      for (int64_t u = blockIdx.x; u < p.n_units; u += gridDim.x) {
+        const int pr = (int)(u % p.units_per_block);
+        for (int tt = 0; tt < tiles_in_unit(pr); ++tt) {
+          const int nst = stages_of(tile_j(pr, tt));
+          for (int s0 = 0; s0 < nst; s0 += p.chunk_st, ++ccount) {
+            const uint32_t buf = ccount & 1u;
+            mbar_wait(gs.tempty_bar(buf), ((ccount >> 1) & 1u) ^ 1u);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + buf * BN;
+            uint32_t accumulate = 0;
+            const int s1 = min(nst, s0 + p.chunk_st);
+            for (int s = s0; s < s1; ++s) {
+              mbar_wait(gs.full_bar(stage), phase);
+              tc_fence_after();
+              const uint32_t sb = gs.base + stage * kStageBytes;
+              if (kSingle) {
+                issue_f16_pair_single(tmem_d, sb, sb + 2 * kABytes, 0, accumulate);
+                issue_f16_pair_single(tmem_d, sb + kABytes, sb + 2 * kABytes, 1, accumulate);
+              } else if (FP16) {
+                issue_f16_pair_pair(tmem_d, sb, sb + kABytes, accumulate);
+              } else {
+                issue_tf32x3(tmem_d, sb, accumulate, true, !p.z_exact);
+              }
+              tc_commit(gs.empty_bar(stage));
+              if (++stage == kStages) { stage = 0; phase ^= 1u; }
+            }
+            tc_commit(gs.tfull_bar(buf));
+          }
+        }
+      }
+    }
+  } else {
+    // ================= epilogue: TMEM -> registers -> global, 128 B per warp store =================
+    const int e = warp - 2;
+    const int q = warp & 3;   // TMEM lane quarter
+    const int h = e >> 2;     // sample (column) half
+    const float inv_scale = p.scalars ? p.scalars->inv_scale : 1.0f;
+    uint32_t ccount = 0;
+    for (int64_t u = blockIdx.x; u < p.n_units; u += gridDim.x) {
+      const int nb = (int)(u / p.units_per_block), pr = (int)(u % p.units_per_block);
+      for (int tt = 0; tt < tiles_in_unit(pr); ++tt) {
+        const int tj = tile_j(pr, tt), nst = stages_of(tj);
+        const int64_t j = (int64_t)tj * BM + q * 32 + lane;
+        const bool jok = j < p.D;
+        const float bias = jok ? __ldg(p.mu + j) : 0.f;
+        float acc[128];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int64_t n = n0 + 4 * j;
-          if (vec && n + 3 < p.N) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n));
-            *(reinterpret_cast<float4*>(dst) + j) =
-                make_float4(acc[4 * j] + b.x, acc[4 * j + 1] + b.y, acc[4 * j + 2] + b.z,
-                            acc[4 * j + 3] + b.w);
+        for (int i = 0; i < 128; ++i) acc[i] = 0.f;
+        for (int s0 = 0; s0 < nst; s0 += p.chunk_st, ++ccount) {
+          const uint32_t buf = ccount & 1u;
+          mbar_wait(gs.tfull_bar(buf), (ccount >> 1) & 1u);
+          tc_fence_after();
+          drain_add(tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + (uint32_t)(h * 128), acc);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(gs.tempty_bar(buf));
+        }
+        const int64_t s_first = (int64_t)nb * BN + h * 128;
+        const int64_t left = p.rows - s_first;
+        if (jok && left > 0) {
+          float* dst = p.x + s_first * p.D + j;
+          if (left >= 128) {
+#pragma unroll
+            for (int c = 0; c < 128; ++c) dst[(int64_t)c * p.D] = fmaf(acc[c], inv_scale, bias);
           } else {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-              if (n + i < p.N) dst[4 * j + i] = acc[4 * j + i] + __ldg(p.bias + n + i);
+            for (int c = 0; c < 128; ++c)
+              if (c < left) dst[(int64_t)c * p.D] = fmaf(acc[c], inv_scale, bias);
           }
         }
       }
     }
   }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    __syncwarp();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512)
-                 : "memory");
-  }
+  gemm_teardown(tmem_base);
 }
 
 // ---------------------------------------------------------------------------------------------
 // operand pre-passes
 // ---------------------------------------------------------------------------------------------
+enum { OP_TF32X3 = 0, OP_F16_PAIR = 1, OP_F16_SINGLE = 2 };
 
-// SYRK operand: At[i][k] = sqrt(nw_k) (x[k0+k][i] - shift_i), split into hi / lo, transposed so
-// that the sample index is contiguous.  Tile = 32 samples x 128 columns through shared memory.
+__device__ __forceinline__ uint32_t pack_half2(float a, float b) {
+  const __half2 t = __floats2half2_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&t);
+}
+
+// Store the split of 4 consecutive contraction elements (k .. k+3, k % 4 == 0) of operand row r;
+// v is already multiplied by the operand's power-of-two scale.  kp = padded contraction length.
+//   OP_TF32X3     op_a [rows][kp] fp32 hi = tf32(v);  op_b [rows][kp] fp32 lo = tf32(v - hi) (may be NULL)
+//   OP_F16_PAIR   op_a [rows][kp/32][ h1 x 32 | h2 x 32 ] fp16, h1 = fp16(v), h2 = fp16(v - h1)
+//   OP_F16_SINGLE op_a [rows][kp] fp16 (v is exactly representable: Philox normals)
+template <int MODE>
+__device__ __forceinline__ void store_split4(const float v[4], int64_t r, int64_t k, int64_t kp,
+                                             void* __restrict__ op_a, void* __restrict__ op_b) {
+  if (MODE == OP_TF32X3) {
+    float hi[4], lo[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) split_tf32(v[u], hi[u], lo[u]);
+    *reinterpret_cast<float4*>(reinterpret_cast<float*>(op_a) + r * kp + k) =
+        make_float4(hi[0], hi[1], hi[2], hi[3]);
+    if (op_b)
+      *reinterpret_cast<float4*>(reinterpret_cast<float*>(op_b) + r * kp + k) =
+          make_float4(lo[0], lo[1], lo[2], lo[3]);
+  } else if (MODE == OP_F16_PAIR) {
+    float r2[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r2[u] = v[u] - __half2float(__float2half_rn(v[u]));  // exact in fp32
+    uint16_t* base = reinterpret_cast<uint16_t*>(op_a) + r * (2 * kp) + (k >> 5) * 64 + (k & 31);
+    *reinterpret_cast<uint2*>(base) = make_uint2(pack_half2(v[0], v[1]), pack_half2(v[2], v[3]));
+    *reinterpret_cast<uint2*>(base + 32) = make_uint2(pack_half2(r2[0], r2[1]), pack_half2(r2[2], r2[3]));
+  } else {
+    uint16_t* base = reinterpret_cast<uint16_t*>(op_a) + r * kp + k;
+    *reinterpret_cast<uint2*>(base) = make_uint2(pack_half2(v[0], v[1]), pack_half2(v[2], v[3]));
+  }
+}
+
+// ---- power-of-two operand scales (FP16X2) -----------------------------------------------------------
+__device__ __forceinline__ void atomic_absmax(unsigned int* out, float m) {
+  m = warp_max(m);
+  if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out, __float_as_uint(m));  // non-negative floats order as uints
+}
+
+__global__ void __launch_bounds__(256) absmax_kernel(const float* __restrict__ a, int64_t n,
+                                                     unsigned int* __restrict__ out) {
+  float m = 0.f;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    m = fmaxf(m, fabsf(__ldg(a + i)));
+  atomic_absmax(out, m);
+}
+
+// max |x[k][i] - shift[i]| over rows with non-zero weight
+__global__ void __launch_bounds__(256)
+absmax_dev_kernel(const float* __restrict__ x, const float* __restrict__ nw,
+                  const float* __restrict__ shift, int64_t K, int64_t D, unsigned int* __restrict__ out) {
+  float m = 0.f;
+  const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(shift) & 15) == 0);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec) {
+    const int64_t nq = D / 4;
+    for (int64_t t = tid; t < K * nq; t += stride) {
+      const int64_t k = t / nq, i = (t % nq) * 4;
+      if (__ldg(nw + k) == 0.f) continue;
+      const float4 v = __ldg(reinterpret_cast<const float4*>(x + k * D + i));
+      const float4 s = shift ? __ldg(reinterpret_cast<const float4*>(shift + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x - s.x), fabsf(v.y - s.y))), fmaxf(fabsf(v.z - s.z), fabsf(v.w - s.w)));
+    }
+  } else {
+    for (int64_t t = tid; t < K * D; t += stride) {
+      const int64_t k = t / D, i = t % D;
+      if (__ldg(nw + k) == 0.f) continue;
+      m = fmaxf(m, fabsf(__ldg(x + t) - (shift ? __ldg(shift + i) : 0.f)));
+    }
+  }
+  atomic_absmax(out, m);
+}
+
+// 2^e with amax * 2^e in [2^13, 2^14): the largest entry sits two binades under the fp16 maximum.
+__device__ __forceinline__ float pow2_scale(float amax) {
+  if (!(amax > 0.f) || !isfinite(amax)) return 1.f;
+  int e;
+  frexpf(amax, &e);  // amax = m 2^e, m in [0.5, 1)
+  int s = 14 - e;
+  s = s < -60 ? -60 : (s > 60 ? 60 : s);
+  return ldexpf(1.f, s);
+}
+
+// covariance: operand a = sqrt(nw)(x - shift); |a| <= sqrt(max nw) * dev, dev = bound or measured
+__global__ void syrk_scale_kernel(GemmScalars* s, const float* __restrict__ dev_bound) {
+  const float wmax = __uint_as_float(s->amax_a_bits);
+  const float dev = dev_bound ? *dev_bound : __uint_as_float(s->amax_b_bits);
+  const float sc = pow2_scale(sqrtf(wmax) * dev);
+  s->scale_a = s->scale_b = sc;
+  s->inv_scale = (1.f / sc) * (1.f / sc);
+}
+
+// sampling: A = L, B = z (pair when injected; Philox normals are exact and unscaled)
+__global__ void sample_scale_kernel(GemmScalars* s, int z_pair) {
+  const float sa = pow2_scale(__uint_as_float(s->amax_a_bits));
+  const float sb = z_pair ? pow2_scale(__uint_as_float(s->amax_b_bits)) : 1.f;
+  s->scale_a = sa;
+  s->scale_b = sb;
+  s->inv_scale = (1.f / sa) * (1.f / sb);
+}
+
+// Covariance operand: At[i][k] = scale sqrt(nw_k) (x[k0+k][i] - shift_i), transposed so that the
+// sample index is contiguous, then split.  Tile = 32 samples x 128 columns through shared memory.
+template <int MODE>
 __global__ void __launch_bounds__(256)
 syrk_operand_kernel(const float* __restrict__ x, const float* __restrict__ nw,
                     const float* __restrict__ shift, int64_t K, int64_t D, int64_t k0, int64_t Kc,
-                    int64_t Dp, float* __restrict__ at_hi, float* __restrict__ at_lo) {
+                    int64_t Dp, const GemmScalars* __restrict__ scalars, void* __restrict__ op_a,
+                    void* __restrict__ op_b) {
   __shared__ float tile[32][129];
+  const float scale = scalars ? scalars->scale_a : 1.f;
   const int64_t kt = (int64_t)blockIdx.x * 32;   // local sample offset in the chunk
   const int64_t it = (int64_t)blockIdx.y * 128;  // column offset
   const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
@@ -381,28 +719,29 @@ syrk_operand_kernel(const float* __restrict__ x, const float* __restrict__ nw,
       }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) tile[r][c4 + u] = v[u];
+    for (int u = 0; u < 4; ++u) tile[r][c4 + u] = v[u] * scale;
   }
   __syncthreads();
   for (int e = threadIdx.x; e < 128 * 8; e += 256) {
     const int il = e / 8, k4 = (e % 8) * 4;
     const int64_t i = it + il;
     if (i >= Dp) continue;
-    float hi[4], lo[4];
+    float v[4];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) split_tf32(tile[k4 + u][il], hi[u], lo[u]);
-    const int64_t off = i * Kc + kt + k4;
-    *reinterpret_cast<float4*>(at_hi + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
-    *reinterpret_cast<float4*>(at_lo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+    for (int u = 0; u < 4; ++u) v[u] = tile[k4 + u][il];
+    store_split4<MODE>(v, i, kt + k4, Kc, op_a, op_b);
   }
 }
 
-// Generic row-major split: dst_hi/lo[r][c] (ld = cols_p, zero padded) from src[r][c] (ld = cols)
-// or, when src == NULL, from Philox normals of the global (.., cols) base-normal matrix.
+// Row-major operand (rows, cols) -> split rows of padded length cols_p (zero padded), from src
+// (pitch cols; lower_only keeps c <= r) scaled by *scale_ptr, or, when src == NULL, from Philox
+// normals of the global (.., cols) base-normal matrix (unscaled).
+template <int MODE>
 __global__ void __launch_bounds__(256)
 split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int64_t cols_p,
                   uint64_t seed, uint64_t draw, uint64_t row_offset, int lower_only,
-                  float* __restrict__ dst_hi, float* __restrict__ dst_lo /* NULL: src is exact */) {
+                  const float* __restrict__ scale_ptr, void* __restrict__ op_a, void* __restrict__ op_b) {
+  const float scale = (src && scale_ptr) ? *scale_ptr : 1.f;
   const int64_t nq_row = cols_p / 4;
   const int64_t total = rows * nq_row;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -412,7 +751,7 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
     if (src) {
 #pragma unroll
       for (int u = 0; u < 4; ++u)
-        if (c + u < cols && (!lower_only || c + u <= r)) v[u] = __ldg(src + r * cols + c + u);
+        if (c + u < cols && (!lower_only || c + u <= r)) v[u] = scale * __ldg(src + r * cols + c + u);
     } else {
       const uint64_t e0 = (row_offset + (uint64_t)r) * (uint64_t)cols + (uint64_t)c;
       if ((cols & 3) == 0) {
@@ -423,28 +762,22 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
           if (c + u < cols) v[u] = philox_normal1(seed, draw, e0 + u);
       }
     }
-    if (dst_lo == nullptr) {
-      *reinterpret_cast<float4*>(dst_hi + r * cols_p + c) = make_float4(v[0], v[1], v[2], v[3]);
-      continue;
-    }
-    float hi[4], lo[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) split_tf32(v[u], hi[u], lo[u]);
-    *reinterpret_cast<float4*>(dst_hi + r * cols_p + c) = make_float4(hi[0], hi[1], hi[2], hi[3]);
-    *reinterpret_cast<float4*>(dst_lo + r * cols_p + c) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+    store_split4<MODE>(v, r, c, cols_p, op_a, op_b);
   }
 }
 
-// cov[i][j] (+)= sum_s partial[s][min(i,j)][max(i,j)]
+// cov[i][j] (+)= inv_scale * sum_s partial[s][min(i,j)][max(i,j)]
 __global__ void syrk_reduce_kernel(const float* __restrict__ partials, int splits, int64_t Dp,
                                    int64_t split_stride, int64_t D, float* __restrict__ cov,
-                                   int accumulate) {
+                                   int accumulate, const GemmScalars* __restrict__ scalars) {
+  const float inv = scalars ? scalars->inv_scale : 1.f;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < D * D; e += stride) {
     const int64_t i = e / D, j = e % D;
     const int64_t a = i < j ? i : j, b = i < j ? j : i;
     float s = 0.f;
     for (int sp = 0; sp < splits; ++sp) s += partials[(int64_t)sp * split_stride + a * Dp + b];
+    s *= inv;
     cov[e] = accumulate ? cov[e] + s : s;
   }
 }
@@ -452,6 +785,9 @@ __global__ void syrk_reduce_kernel(const float* __restrict__ partials, int split
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
+int gemm_scheme();     // capi.cu: PPI_GEMM_TF32X3 / PPI_GEMM_FP16X2 (ppi_set_option)
+int gemm_chunk();      // capi.cu: pipeline stages per TMEM accumulation chunk
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -472,42 +808,45 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// 2-D fp32 tensor (rows, cols) row-major with row pitch `ld` floats; box = (box_rows, BK).
-static int make_map(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int64_t ld,
-                    int box_rows) {
+// 2-D K-major operand of `rows` rows; one box = box_rows x one 128-byte swizzle row.
+//   OP_TF32X3     fp32 [rows][kp]              box 32 elements  (32 contraction steps)
+//   OP_F16_PAIR   fp16 [rows][kp/32][h1|h2]    box 64 elements  (32 contraction steps)
+//   OP_F16_SINGLE fp16 [rows][kp]              box 64 elements  (64 contraction steps)
+static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t kp, int box_rows, int mode) {
   EncodeTiledFn fn = get_encode_fn();
   PPI_REQUIRE(fn != nullptr, PPI_ERR_DRIVER, "cuTensorMapEncodeTiled entry point not available");
-  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
-  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  const bool f16 = mode != OP_TF32X3;
+  const int64_t elems = mode == OP_F16_PAIR ? 2 * kp : kp;
+  cuuint64_t dims[2] = {(cuuint64_t)elems, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)elems * (f16 ? 2 : 4)};
+  cuuint32_t box[2] = {(cuuint32_t)(f16 ? 64 : 32), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)ptr, dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(map, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                  (void*)ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   PPI_REQUIRE(r == CUDA_SUCCESS, PPI_ERR_DRIVER, "cuTensorMapEncodeTiled failed with CUresult %d",
               (int)r);
   return 0;
 }
 
 static int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
-
-static int launch_gemm(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& bh,
-                       const CUtensorMap& bl, const GemmParams& p, int64_t grid, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    PPI_CUDA_TRY(cudaFuncSetAttribute(split_tf32_gemm_kernel,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)kGemmSmemBytes));
-    attr_set = true;
-  }
-  ProfileScope prof(p.mode == GEMM_SYRK ? PPI_PROF_SYRK_GEMM : PPI_PROF_SAMPLE_GEMM, st);
-  split_tf32_gemm_kernel<<<(unsigned)grid, kGemmThreads, kGemmSmemBytes, st>>>(ah, al, bh, bl, p);
-  return check_launch("split_tf32_gemm_kernel");
+static int grid_cap(int64_t work, int per_sm) {
+  const int64_t cap = (int64_t)kNumSMs * per_sm;
+  return (int)(work < 1 ? 1 : (work < cap ? work : cap));
 }
 
-constexpr int kChunkKb = 16;          // 16 k-blocks = 512 contraction steps per TMEM chunk
+template <typename Kern>
+static int set_gemm_smem(Kern kern) {
+  PPI_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kGemmSmemBytes));
+  return 0;
+}
+
 constexpr int64_t kSyrkKc = 65536;    // samples staged per pass
-constexpr int64_t kSampleKc = 32768;  // sample rows staged per pass
+constexpr int64_t kSampleKc = 65536;  // sample rows staged per pass
+constexpr int64_t kKcQuantum = 512;   // Kc granularity (covers every chunk / split rounding below)
+constexpr size_t kScalarBytes = 1024; // GemmScalars block at the head of the workspace
 
 struct SyrkPlan {
   int64_t Dp, Kc, tiles_m, tiles_n, ntiles;
@@ -518,13 +857,13 @@ struct SyrkPlan {
 static SyrkPlan syrk_plan(int64_t K, int64_t D) {
   SyrkPlan pl;
   pl.Dp = round_up(D, BM);
-  pl.Kc = round_up(K < kSyrkKc ? K : kSyrkKc, (int64_t)BK * kChunkKb);
+  pl.Kc = round_up(K < kSyrkKc ? K : kSyrkKc, kKcQuantum);
   pl.tiles_m = pl.Dp / BM;
   pl.tiles_n = (pl.Dp + BN - 1) / BN;
   pl.ntiles = 0;
   for (int64_t tm = 0; tm < pl.tiles_m; ++tm) pl.ntiles += pl.tiles_n - (tm * BM) / BN;
   int64_t s = kNumSMs / pl.ntiles;
-  const int64_t max_s = pl.Kc / ((int64_t)BK * kChunkKb);
+  const int64_t max_s = pl.Kc / kKcQuantum;
   if (s > max_s) s = max_s;
   if (s < 1) s = 1;
   pl.splits = (int)s;
@@ -540,61 +879,96 @@ using namespace ppi;
 extern "C" size_t ppi_wmoments_dense_workspace_bytes(int64_t K, int64_t D) {
   if (K <= 0 || D <= 0) return 0;
   const SyrkPlan pl = syrk_plan(K, D);
-  return 2 * pl.op_bytes + pl.partial_bytes + 1024;
+  return kScalarBytes + 2 * pl.op_bytes + pl.partial_bytes + 1024;
 }
 
-extern "C" int ppi_wmoments_dense(const float* x, const float* nw, int64_t K, int64_t D,
-                                  const float* shift, float* cov, int accumulate, void* workspace,
-                                  size_t workspace_bytes, void* stream) {
-  PPI_REQUIRE(x && nw && cov && K > 0 && D > 0 && workspace, PPI_ERR_INVALID,
-              "ppi_wmoments_dense: bad arguments");
-  PPI_REQUIRE(workspace_bytes >= ppi_wmoments_dense_workspace_bytes(K, D), PPI_ERR_WORKSPACE,
-              "ppi_wmoments_dense: workspace too small");
-  cudaStream_t st = (cudaStream_t)stream;
+template <bool FP16>
+static int wmoments_dense_impl(const float* x, const float* nw, int64_t K, int64_t D,
+                               const float* shift, const float* dev_bound, float* cov, int accumulate,
+                               void* workspace, cudaStream_t st) {
+  constexpr int MODE = FP16 ? OP_F16_PAIR : OP_TF32X3;
   const SyrkPlan pl = syrk_plan(K, D);
   char* wsp = (char*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
-  float* at_hi = (float*)wsp;
-  float* at_lo = (float*)(wsp + pl.op_bytes);
-  float* partials = (float*)(wsp + 2 * pl.op_bytes);
+  GemmScalars* scalars = FP16 ? (GemmScalars*)wsp : nullptr;
+  void* op_a = (void*)(wsp + kScalarBytes);
+  void* op_b = FP16 ? nullptr : (void*)(wsp + kScalarBytes + pl.op_bytes);
+  float* partials = (float*)(wsp + kScalarBytes + 2 * pl.op_bytes);
 
-  CUtensorMap ah, al, bh, bl;
-  if (int rc = make_map(&ah, at_hi, pl.Dp, pl.Kc, pl.Kc, BM)) return rc;
-  if (int rc = make_map(&al, at_lo, pl.Dp, pl.Kc, pl.Kc, BM)) return rc;
-  if (int rc = make_map(&bh, at_hi, pl.Dp, pl.Kc, pl.Kc, BN)) return rc;
-  if (int rc = make_map(&bl, at_lo, pl.Dp, pl.Kc, pl.Kc, BN)) return rc;
+  if (FP16) {
+    // operand scale: sqrt(max nw) * max |x - shift| (given as a bound, or measured with one more pass over x)
+    ProfileScope prof(PPI_PROF_SYRK_OPERAND, st);
+    PPI_CUDA_TRY(cudaMemsetAsync(scalars, 0, sizeof(GemmScalars), st));
+    absmax_kernel<<<grid_cap(ceil_div(K, 1024), 4), 256, 0, st>>>(nw, K, &scalars->amax_a_bits);
+    int n = 2;
+    if (!dev_bound) {
+      absmax_dev_kernel<<<grid_cap(ceil_div(K * D, 4096), 8), 256, 0, st>>>(x, nw, shift, K, D,
+                                                                              &scalars->amax_b_bits);
+      ++n;
+    }
+    syrk_scale_kernel<<<1, 1, 0, st>>>(scalars, dev_bound);
+    if (int rc = check_launch("syrk scale kernels", n)) return rc;
+  }
 
-  GemmParams p;
-  p.mode = GEMM_SYRK;
+  CUtensorMap a, a2, b, b2;
+  if (int rc = make_map(&a, op_a, pl.Dp, pl.Kc, BM, MODE)) return rc;
+  if (int rc = make_map(&b, op_a, pl.Dp, pl.Kc, BN, MODE)) return rc;
+  if (FP16) {
+    a2 = a;
+    b2 = b;
+  } else {
+    if (int rc = make_map(&a2, op_b, pl.Dp, pl.Kc, BM, MODE)) return rc;
+    if (int rc = make_map(&b2, op_b, pl.Dp, pl.Kc, BN, MODE)) return rc;
+  }
+
+  SyrkParams p;
   p.num_kb = (int)(pl.Kc / BK);
-  p.chunk_kb = kChunkKb;
-  p.kb_per_split = (int)round_up((p.num_kb + pl.splits - 1) / pl.splits, kChunkKb);
+  p.chunk_kb = gemm_chunk();
+  p.kb_per_split = (int)round_up((p.num_kb + pl.splits - 1) / pl.splits, p.chunk_kb);
   p.splits = pl.splits;
-  p.tiles_m = (int)pl.tiles_m;
   p.tiles_n = (int)pl.tiles_n;
-  p.M = pl.Dp;
-  p.N = pl.Dp;
   p.out = partials;
   p.ld = pl.Dp;
   p.split_stride = pl.Dp * pl.Dp;
-  p.bias = nullptr;
-  p.a_exact = 0;
 
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (int rc = set_gemm_smem(syrk_gemm_kernel<FP16>)) return rc;
+    attr_set = true;
+  }
   int pass = 0;
   for (int64_t k0 = 0; k0 < K; k0 += pl.Kc, ++pass) {
     dim3 og((unsigned)(pl.Kc / 32), (unsigned)ceil_div(pl.Dp, 128));
     {
       ProfileScope prof(PPI_PROF_SYRK_OPERAND, st);
-      syrk_operand_kernel<<<og, 256, 0, st>>>(x, nw, shift, K, D, k0, pl.Kc, pl.Dp, at_hi, at_lo);
+      syrk_operand_kernel<MODE><<<og, 256, 0, st>>>(x, nw, shift, K, D, k0, pl.Kc, pl.Dp, scalars, op_a, op_b);
       if (int rc = check_launch("syrk_operand_kernel")) return rc;
     }
     p.accumulate = pass > 0;
-    if (int rc = launch_gemm(ah, al, bh, bl, p, pl.ntiles * pl.splits, st)) return rc;
+    ProfileScope prof(PPI_PROF_SYRK_GEMM, st);
+    syrk_gemm_kernel<FP16><<<(unsigned)(pl.ntiles * pl.splits), kGemmThreads, kGemmSmemBytes, st>>>(
+        a, a2, b, b2, p);
+    if (int rc = check_launch("syrk_gemm_kernel")) return rc;
   }
-  const int grid = (int)(ceil_div(D * D, 256) < kNumSMs * 8 ? ceil_div(D * D, 256) : kNumSMs * 8);
   ProfileScope prof(PPI_PROF_SYRK_REDUCE, st);
-  syrk_reduce_kernel<<<grid, 256, 0, st>>>(partials, pl.splits, pl.Dp, pl.Dp * pl.Dp, D, cov,
-                                           accumulate);
+  syrk_reduce_kernel<<<grid_cap(ceil_div(D * D, 256), 8), 256, 0, st>>>(partials, pl.splits, pl.Dp,
+                                                                         pl.Dp * pl.Dp, D, cov, accumulate,
+                                                                         scalars);
   return check_launch("syrk_reduce_kernel");
+}
+
+extern "C" int ppi_wmoments_dense(const float* x, const float* nw, int64_t K, int64_t D,
+                                  const float* shift, const float* dev_bound, float* cov,
+                                  int accumulate, void* workspace, size_t workspace_bytes,
+                                  void* stream) {
+  PPI_REQUIRE(x && nw && cov && K > 0 && D > 0 && workspace, PPI_ERR_INVALID,
+              "ppi_wmoments_dense: bad arguments");
+  PPI_REQUIRE(workspace_bytes >= ppi_wmoments_dense_workspace_bytes(K, D), PPI_ERR_WORKSPACE,
+              "ppi_wmoments_dense: workspace too small");
+  if (gemm_scheme() == PPI_GEMM_FP16X2)
+    return wmoments_dense_impl<true>(x, nw, K, D, shift, dev_bound, cov, accumulate, workspace,
+                                     (cudaStream_t)stream);
+  return wmoments_dense_impl<false>(x, nw, K, D, shift, dev_bound, cov, accumulate, workspace,
+                                    (cudaStream_t)stream);
 }
 
 // sample.cu
@@ -602,11 +976,97 @@ int ppi_sample_gaussian_small(const float* z, uint64_t seed, uint64_t draw_id, u
                               int64_t K, int D, const float* mu, const float* L, float* x,
                               cudaStream_t st);
 
+static int64_t sample_kc(int64_t K) { return round_up(K < kSampleKc ? K : kSampleKc, BN); }
+
 extern "C" size_t ppi_sample_gaussian_workspace_bytes(int64_t K, int64_t D) {
   if (K <= 0 || D <= 128) return 0;
-  const int64_t Dk = round_up(D, BK);
-  const int64_t Kc = round_up(K < kSampleKc ? K : kSampleKc, BM);
-  return 2 * (size_t)D * Dk * sizeof(float) + 2 * (size_t)Kc * Dk * sizeof(float) + 1024;
+  const int64_t Dk = round_up(D, 64);
+  return kScalarBytes + 2 * (size_t)D * Dk * sizeof(float) +
+         2 * (size_t)sample_kc(K) * Dk * sizeof(float) + 1024;
+}
+
+// FP16: L -> fp16 pair; z -> one exact fp16 (Philox, ZPAIR = false) or an fp16 pair (injected).
+// !FP16: TF32X3 (ZPAIR ignored; the low-order z operand is skipped for Philox normals).
+template <bool FP16, bool ZPAIR>
+static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
+                                int64_t K, int64_t D, const float* mu, const float* L, float* x,
+                                void* workspace, cudaStream_t st) {
+  constexpr int LMODE = FP16 ? OP_F16_PAIR : OP_TF32X3;
+  constexpr int ZMODE = FP16 ? (ZPAIR ? OP_F16_PAIR : OP_F16_SINGLE) : OP_TF32X3;
+  constexpr int KS = (FP16 && !ZPAIR) ? 64 : 32;
+  const int64_t Dk = round_up(D, 64);
+  const int64_t Kc = sample_kc(K);
+  char* wsp = (char*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
+  const size_t l_bytes = (size_t)D * Dk * sizeof(float), z_bytes = (size_t)Kc * Dk * sizeof(float);
+  GemmScalars* scalars = FP16 ? (GemmScalars*)wsp : nullptr;
+  void* l_a = (void*)(wsp + kScalarBytes);
+  void* l_b = (void*)(wsp + kScalarBytes + l_bytes);
+  void* z_a = (void*)(wsp + kScalarBytes + 2 * l_bytes);
+  void* z_b = (void*)(wsp + kScalarBytes + 2 * l_bytes + z_bytes);
+  const bool z_exact = (z == nullptr);  // Philox normals sit on the TF32 grid (common.cuh box_muller)
+
+  if (FP16) {
+    PPI_CUDA_TRY(cudaMemsetAsync(scalars, 0, sizeof(GemmScalars), st));
+    absmax_kernel<<<grid_cap(ceil_div(D * D, 1024), 4), 256, 0, st>>>(L, D * D, &scalars->amax_a_bits);
+    int n = 2;
+    if (ZPAIR) {
+      absmax_kernel<<<grid_cap(ceil_div(K * D, 4096), 8), 256, 0, st>>>(z, K * D, &scalars->amax_b_bits);
+      ++n;
+    }
+    sample_scale_kernel<<<1, 1, 0, st>>>(scalars, ZPAIR ? 1 : 0);
+    if (int rc = check_launch("sample scale kernels", n)) return rc;
+  }
+  split_rows_kernel<LMODE><<<grid_cap(ceil_div(D * (Dk / 4), 256), 8), 256, 0, st>>>(
+      L, D, D, Dk, 0, 0, 0, 1, FP16 ? &scalars->scale_a : nullptr, l_a, l_b);
+  if (int rc = check_launch("split_rows_kernel(L)")) return rc;
+
+  CUtensorMap ml, ml2, mz, mz2;
+  if (int rc = make_map(&ml, l_a, D, Dk, BM, LMODE)) return rc;
+  if (int rc = make_map(&mz, z_a, Kc, Dk, BN, ZMODE)) return rc;
+  ml2 = ml;
+  mz2 = mz;
+  if (!FP16) {
+    if (int rc = make_map(&ml2, l_b, D, Dk, BM, LMODE)) return rc;
+    if (int rc = make_map(&mz2, z_b, Kc, Dk, BN, ZMODE)) return rc;
+  }
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (int rc = set_gemm_smem(sample_gemm_kernel<FP16, ZPAIR>)) return rc;
+    attr_set = true;
+  }
+  SampleParams p;
+  p.tiles_j = (int)ceil_div(D, BM);
+  p.units_per_block = (p.tiles_j + 1) / 2;
+  p.num_st = (int)(Dk / KS);
+  p.chunk_st = (FP16 && !ZPAIR) ? gemm_chunk() / 2 : gemm_chunk();  // same 32-step boundaries in every variant
+  p.D = D;
+  p.mu = mu;
+  p.scalars = scalars;
+  p.z_exact = z_exact ? 1 : 0;
+
+  for (int64_t k0 = 0; k0 < K; k0 += Kc) {
+    const int64_t rows = (K - k0) < Kc ? (K - k0) : Kc;
+    const int64_t rows_p = round_up(rows, BN);
+    // injected: rows beyond `rows` keep stale workspace values whose products are never stored;
+    // Philox: they are generated too (harmless)
+    {
+      ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st);
+      const int64_t nrows = z ? rows : rows_p;
+      split_rows_kernel<ZMODE><<<grid_cap(ceil_div(nrows * (Dk / 4), 256), 16), 256, 0, st>>>(
+          z ? z + k0 * D : nullptr, nrows, D, Dk, seed, draw_id, row_offset + (uint64_t)k0, 0,
+          FP16 ? &scalars->scale_b : nullptr, z_a, (!FP16 && !z_exact) ? z_b : nullptr);
+      if (int rc = check_launch("split_rows_kernel(z)")) return rc;
+    }
+    p.n_units = (rows_p / BN) * p.units_per_block;
+    p.rows = rows;
+    p.x = x + k0 * D;
+    const unsigned g = (unsigned)(p.n_units < kNumSMs ? p.n_units : kNumSMs);
+    ProfileScope prof(PPI_PROF_SAMPLE_GEMM, st);
+    sample_gemm_kernel<FP16, ZPAIR><<<g, kGemmThreads, kGemmSmemBytes, st>>>(ml, ml2, mz, mz2, p);
+    if (int rc = check_launch("sample_gemm_kernel")) return rc;
+  }
+  return 0;
 }
 
 extern "C" int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_id,
@@ -619,58 +1079,9 @@ extern "C" int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_
   if (D <= 128) return ppi_sample_gaussian_small(z, seed, draw_id, row_offset, K, (int)D, mu, L, x, st);
   PPI_REQUIRE(workspace && workspace_bytes >= ppi_sample_gaussian_workspace_bytes(K, D),
               PPI_ERR_WORKSPACE, "ppi_sample_gaussian: workspace too small");
-  const int64_t Dk = round_up(D, BK);
-  const int64_t Kc = round_up(K < kSampleKc ? K : kSampleKc, BM);
-  char* wsp = (char*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
-  const size_t l_bytes = (size_t)D * Dk * sizeof(float), z_bytes = (size_t)Kc * Dk * sizeof(float);
-  float* l_hi = (float*)wsp;
-  float* l_lo = (float*)(wsp + l_bytes);
-  float* z_hi = (float*)(wsp + 2 * l_bytes);
-  float* z_lo = (float*)(wsp + 2 * l_bytes + z_bytes);
-
-  {
-    const int64_t total = D * (Dk / 4);
-    const int grid = (int)(ceil_div(total, 256) < kNumSMs * 8 ? ceil_div(total, 256) : kNumSMs * 8);
-    split_rows_kernel<<<grid, 256, 0, st>>>(L, D, D, Dk, 0, 0, 0, 1, l_hi, l_lo);
-    if (int rc = check_launch("split_rows_kernel(L)")) return rc;
+  if (gemm_scheme() == PPI_GEMM_FP16X2) {
+    if (z) return sample_gaussian_impl<true, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, st);
+    return sample_gaussian_impl<true, false>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, st);
   }
-  CUtensorMap ah, al, bh, bl;
-  if (int rc = make_map(&ah, z_hi, Kc, Dk, Dk, BM)) return rc;
-  if (int rc = make_map(&al, z_lo, Kc, Dk, Dk, BM)) return rc;
-  if (int rc = make_map(&bh, l_hi, D, Dk, Dk, BN)) return rc;
-  if (int rc = make_map(&bl, l_lo, D, Dk, Dk, BN)) return rc;
-
-  GemmParams p;
-  p.mode = GEMM_SAMPLE;
-  p.num_kb = (int)(Dk / BK);
-  p.chunk_kb = 1 << 20;  // a single accumulation chunk: the contraction is only D long
-  p.kb_per_split = p.num_kb;
-  p.splits = 1;
-  p.tiles_n = (int)ceil_div(D, BN);
-  p.N = D;
-  p.ld = D;
-  p.split_stride = 0;
-  p.bias = mu;
-  p.accumulate = 0;
-  p.a_exact = z ? 0 : 1;  // Philox normals sit on the TF32 grid (common.cuh box_muller)
-
-  for (int64_t k0 = 0; k0 < K; k0 += Kc) {
-    const int64_t rows = (K - k0) < Kc ? (K - k0) : Kc;
-    const int64_t rows_p = round_up(rows, BM);
-    const int64_t total = rows_p * (Dk / 4);
-    const int grid = (int)(ceil_div(total, 256) < kNumSMs * 16 ? ceil_div(total, 256) : kNumSMs * 16);
-    // rows beyond `rows` are generated too (harmless, never stored)
-    {
-      ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st);
-      split_rows_kernel<<<grid, 256, 0, st>>>(z ? z + k0 * D : nullptr, z ? rows : rows_p, D, Dk, seed,
-                                              draw_id, row_offset + (uint64_t)k0, 0, z_hi,
-                                              z ? z_lo : nullptr);
-      if (int rc = check_launch("split_rows_kernel(z)")) return rc;
-    }
-    p.tiles_m = (int)(rows_p / BM);
-    p.M = rows;
-    p.out = x + k0 * D;
-    if (int rc = launch_gemm(ah, al, bh, bl, p, (int64_t)p.tiles_m * p.tiles_n, st)) return rc;
-  }
-  return 0;
+  return sample_gaussian_impl<false, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, st);
 }

@@ -13,6 +13,8 @@ LIB_PATH = os.path.join(_HERE, "libppi_b200.so")
 # enums of include/ppi_b200.h
 KERNEL_KINDS = {"se": 0, "matern12": 1, "matern32": 2, "matern52": 3, "periodic": 4, "white": 5}
 FN_IDS = {"Himmelblau": 0, "Rosenbrock": 1, "Styblinski": 2, "Rastrigin": 3, "NoisySphere": 4}
+OPT_GEMM_SCHEME, OPT_GEMM_CHUNK = 0, 1
+GEMM_TF32X3, GEMM_FP16X2 = 0, 1
 TEMP_FIXED_NORMALISED, TEMP_FIXED_SHIFTED, TEMP_REPS_KL, TEMP_ESS_TARGET, TEMP_LOWER_BOUND = range(5)
 
 
@@ -37,6 +39,8 @@ _p, _i, _i64, _u64, _d, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_do
 SIGNATURES = {
     "ppi_version": (_i, []),
     "ppi_last_error": (C.c_char_p, []),
+    "ppi_set_option": (_i, [_i, _i]),
+    "ppi_get_option": (_i, [_i]),
     "ppi_philox_normal": (_i, [_p, _i64, _i64, _u64, _u64, _u64, _p]),
     "ppi_kernel_gram_chol": (_i, [_p, _i, _p, _i, _i, _d, _d, _d, _p, _p, _p, _p, _p, _p]),
     "ppi_cholesky_small": (_i, [_p, _i, _p, _p, _p, _p]),
@@ -56,7 +60,7 @@ SIGNATURES = {
     "ppi_wmoments_diag": (_i, [_p, _p, _i64, _i64, _p, _p, _p, _p, _p]),
     "ppi_wmoments_matnorm": (_i, [_p, _p, _i64, _i, _i, _p, _p, _p, _p]),
     "ppi_wmoments_dense_workspace_bytes": (_sz, [_i64, _i64]),
-    "ppi_wmoments_dense": (_i, [_p, _p, _i64, _i64, _p, _p, _i, _p, _sz, _p]),
+    "ppi_wmoments_dense": (_i, [_p, _p, _i64, _i64, _p, _p, _p, _i, _p, _sz, _p]),
     "ppi_finalize_gaussian": (_i, [_p, _p, _i64, _p, _i, _p, _p, _p]),
     "ppi_finalize_matnorm": (_i, [_p, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p, _p]),
     "ppi_launch_count": (_i64, []),

@@ -240,7 +240,7 @@ def wmoments_matnorm(x, nw, shift=None, inv_cov_out=None, acc=None):
     return acc
 
 
-def wmoments_dense(x, nw, shift=None, cov=None, accumulate=False):
+def wmoments_dense(x, nw, shift=None, cov=None, accumulate=False, dev_bound=None):
     dev = require_cuda()
     kp = _Keep(dev)
     x = f32(x, dev)
@@ -248,7 +248,7 @@ def wmoments_dense(x, nw, shift=None, cov=None, accumulate=False):
     cov = torch.empty((D, D), dtype=torch.float32, device=dev) if cov is None else cov
     nbytes = _lib.query("ppi_wmoments_dense_workspace_bytes", K, D)
     ws = workspace("wmoments_dense", nbytes)
-    _lib.call("ppi_wmoments_dense", ptr(x), kp.p(nw), K, D, kp.p(shift), ptr(cov),
+    _lib.call("ppi_wmoments_dense", ptr(x), kp.p(nw), K, D, kp.p(shift), ptr(dev_bound), ptr(cov),
               int(bool(accumulate)), ptr(ws), nbytes, stream_ptr())
     return cov
 

@@ -25,14 +25,19 @@ def f32r(x):
     return np.asarray(x, np.float32).astype(np.float64)
 
 
-@pytest.fixture(scope="module")
-def ops():
+@pytest.fixture(scope="module", params=["tf32x3", "fp16x2"])
+def ops(request):
+    """Every test runs under both split-product schemes of the tcgen05 kernels (ppi_set_option)."""
     import torch
 
     assert torch.cuda.is_available()
-    from ppi_b200 import ops as _ops
+    from ppi_b200 import _lib, ops as _ops
 
-    return _ops
+    scheme = _lib.GEMM_TF32X3 if request.param == "tf32x3" else _lib.GEMM_FP16X2
+    _lib.call("ppi_set_option", _lib.OPT_GEMM_SCHEME, scheme)
+    assert _lib.query("ppi_get_option", _lib.OPT_GEMM_SCHEME) == scheme
+    yield _ops
+    _lib.call("ppi_set_option", _lib.OPT_GEMM_SCHEME, _lib.GEMM_FP16X2)
 
 
 def _problem(K, D, seed, ess_frac=None):
@@ -75,7 +80,7 @@ def test_wmoments_dense_zero_weight_rows(ops):
 
 
 @pytest.mark.parametrize("K,D", [(256, 256), (1000, 200), (5000, 384), (40000, 256), (2048, 1024),
-                                 (300, 129)])
+                                 (300, 129), (70001, 640), (513, 2048)])
 def test_sample_gaussian_dense(ops, K, D):
     rng = np.random.default_rng(K * D)
     z = f32r(rng.standard_normal((K, D)))
