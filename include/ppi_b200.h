@@ -48,8 +48,12 @@ const char* ppi_last_error(void);
  *                    (error ~2^-21 |a||b| at any magnitude; 8 bytes per value, twice the MMA time).
  * PPI_OPT_GEMM_CHUNK = 32-deep k-blocks accumulated inside the tensor core before the partial sum is
  * promoted to fp32 registers (tcgen05 accumulation truncates: ~3e-8 relative per MMA instruction).
- * Even, default 4. */
-enum { PPI_OPT_GEMM_SCHEME = 0, PPI_OPT_GEMM_CHUNK = 1 };
+ * Even, default 4.
+ * PPI_OPT_GEMM_OVERLAP != 0: the FP16X2 kernels stage the operands of pass p+1 on an internal side
+ * stream while pass p multiplies (two staging buffers, event-ordered against the caller's stream;
+ * the call stays asynchronous and stream-ordered for the caller).  Default 0: measured gain on
+ * B200 is ~1 % of a step because both kernels contend for L2 / HBM. */
+enum { PPI_OPT_GEMM_SCHEME = 0, PPI_OPT_GEMM_CHUNK = 1, PPI_OPT_GEMM_OVERLAP = 2 };
 enum { PPI_GEMM_TF32X3 = 0, PPI_GEMM_FP16X2 = 1 };
 int ppi_set_option(int key, int value);
 int ppi_get_option(int key);
@@ -193,10 +197,13 @@ int ppi_cem_weights(const float* costs, int64_t K, int64_t n_elites, int64_t* so
 /* a16/a18/a21 first moment and element-wise second moment, HBM-bound float4 reduction.
  * s1[i] += sum_k nw_k (x_ki - shift1_i);   s2[i] += sum_k nw_k (x_ki - shift2_i)^2  (s2 may be
  * NULL; shifts may be NULL = 0).  x is (K,D) with D = H*d for trajectories.  fp64 accumulators
- * must be zeroed by the caller (K-sharded ranks all-reduce them).
+ * must be zeroed by the caller (K-sharded ranks all-reduce them).  absdev_max (device scalar,
+ * may be NULL, zeroed by the caller) receives max |x_ki - shift1_i| over the rows with nw_k != 0
+ * (max-combined, so K-sharded ranks all-reduce it with MAX): twice this value bounds the
+ * deviation from the NEW mean and is what ppi_wmoments_dense takes as dev_bound.
  * ppi/policies.py:88 (mu), :122 (matrix-normal mean), :1158-1162 (iid mean / std).          */
 int ppi_wmoments_diag(const float* x, const float* nw, int64_t K, int64_t D, const float* shift1,
-                      const float* shift2, double* s1, double* s2, void* stream);
+                      const float* shift2, double* s1, double* s2, float* absdev_max, void* stream);
 
 /* a18  matrix-normal input covariance                               ppi/policies.py:129-132
  * acc[i,l] += sum_b nw_b sum_j (x_bij - shift_ij)(x_blj - shift_lj) * inv_cov_out_j

@@ -18,7 +18,8 @@ template <int VEC, bool SECOND>
 __global__ void __launch_bounds__(256)
 wmoments_diag_kernel(const float* __restrict__ x, const float* __restrict__ nw, int64_t K, int64_t D,
                      const float* __restrict__ shift1, const float* __restrict__ shift2,
-                     double* __restrict__ s1, double* __restrict__ s2, int cgb, int64_t rows_per_block) {
+                     double* __restrict__ s1, double* __restrict__ s2, unsigned int* __restrict__ absdev,
+                     int cgb, int64_t rows_per_block) {
   __shared__ double red[256 * VEC];
   const int64_t ncg = D / VEC;
   const int cg_local = threadIdx.x % cgb, rl = threadIdx.x / cgb, nrl = blockDim.x / cgb;
@@ -27,6 +28,7 @@ wmoments_diag_kernel(const float* __restrict__ x, const float* __restrict__ nw, 
   const int64_t r0 = (int64_t)blockIdx.y * rows_per_block;
   const int64_t r1 = min(K, r0 + rows_per_block);
   float a[VEC], b[VEC];
+  float dev = 0.f;  // max |x - shift1| over rows with non-zero weight (operand-scale bound for the dense pass)
   double d1[VEC], d2[VEC];
 #pragma unroll
   for (int v = 0; v < VEC; ++v) {
@@ -54,7 +56,9 @@ wmoments_diag_kernel(const float* __restrict__ x, const float* __restrict__ nw, 
         if (w != 0.f) {  // zero-weight rows (NaN rollouts) may hold non-finite samples
 #pragma unroll
           for (int v = 0; v < VEC; ++v) {
-            f1[v] = fmaf(w, xv[v] - a[v], f1[v]);
+            const float d0 = xv[v] - a[v];
+            dev = fmaxf(dev, fabsf(d0));
+            f1[v] = fmaf(w, d0, f1[v]);
             if (SECOND) {
               const float dv = xv[v] - b[v];
               f2[v] = fmaf(w * dv, dv, f2[v]);
@@ -68,6 +72,10 @@ wmoments_diag_kernel(const float* __restrict__ x, const float* __restrict__ nw, 
         if (SECOND) d2[v] += (double)f2[v];
       }
     }
+  }
+  if (absdev != nullptr) {
+    dev = warp_max(dev);
+    if ((threadIdx.x & 31) == 0 && dev > 0.f) atomicMax(absdev, __float_as_uint(dev));
   }
   // combine row lanes
   for (int pass = 0; pass < (SECOND ? 2 : 1); ++pass) {
@@ -253,7 +261,7 @@ using namespace ppi;
 
 extern "C" int ppi_wmoments_diag(const float* x, const float* nw, int64_t K, int64_t D,
                                  const float* shift1, const float* shift2, double* s1, double* s2,
-                                 void* stream) {
+                                 float* absdev_max, void* stream) {
   PPI_REQUIRE(x && nw && s1 && K >= 0 && D > 0, PPI_ERR_INVALID, "ppi_wmoments_diag: bad arguments");
   if (K == 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
@@ -272,7 +280,8 @@ extern "C" int ppi_wmoments_diag(const float* x, const float* nw, int64_t K, int
   dim3 grid((unsigned)gx, (unsigned)ceil_div(K, rpb));
   ProfileScope prof(PPI_PROF_WMOMENTS_DIAG, st);
 #define PPI_LAUNCH_DIAG(V, SEC) \
-  wmoments_diag_kernel<V, SEC><<<grid, 256, 0, st>>>(x, nw, K, D, shift1, shift2, s1, s2, cgb, rpb)
+  wmoments_diag_kernel<V, SEC><<<grid, 256, 0, st>>>(x, nw, K, D, shift1, shift2, s1, s2,     \
+                                                     reinterpret_cast<unsigned int*>(absdev_max), cgb, rpb)
   if (vec) { if (s2) PPI_LAUNCH_DIAG(4, true); else PPI_LAUNCH_DIAG(4, false); }
   else     { if (s2) PPI_LAUNCH_DIAG(1, true); else PPI_LAUNCH_DIAG(1, false); }
 #undef PPI_LAUNCH_DIAG

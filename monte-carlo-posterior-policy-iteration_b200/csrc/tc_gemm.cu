@@ -742,27 +742,33 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
                   uint64_t seed, uint64_t draw, uint64_t row_offset, int lower_only,
                   const float* __restrict__ scale_ptr, void* __restrict__ op_a, void* __restrict__ op_b) {
   const float scale = (src && scale_ptr) ? *scale_ptr : 1.f;
-  const int64_t nq_row = cols_p / 4;
-  const int64_t total = rows * nq_row;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
-    const int64_t r = t / nq_row, c = (t % nq_row) * 4;
-    float v[4] = {0.f, 0.f, 0.f, 0.f};
-    if (src) {
+  const int nq_row = (int)(cols_p / 4);
+  const bool quad_rng = (cols & 3) == 0;
+  // one row per block iteration; threads stride over the row's quads (no 64-bit divisions)
+  for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
+    const uint64_t e_row = (row_offset + (uint64_t)r) * (uint64_t)cols;
+    for (int q = threadIdx.x; q < nq_row; q += blockDim.x) {
+      const int64_t c = (int64_t)q * 4;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (src) {
+        if (quad_rng && !lower_only && c + 3 < cols &&
+            ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
+          const float4 t = __ldg(reinterpret_cast<const float4*>(src + r * cols + c));
+          v[0] = scale * t.x; v[1] = scale * t.y; v[2] = scale * t.z; v[3] = scale * t.w;
+        } else {
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
-        if (c + u < cols && (!lower_only || c + u <= r)) v[u] = scale * __ldg(src + r * cols + c + u);
-    } else {
-      const uint64_t e0 = (row_offset + (uint64_t)r) * (uint64_t)cols + (uint64_t)c;
-      if ((cols & 3) == 0) {
-        if (c < cols) philox_normal4(seed, draw, e0 >> 2, v);
+          for (int u = 0; u < 4; ++u)
+            if (c + u < cols && (!lower_only || c + u <= r)) v[u] = scale * __ldg(src + r * cols + c + u);
+        }
+      } else if (quad_rng) {
+        if (c < cols) philox_normal4(seed, draw, (e_row + (uint64_t)c) >> 2, v);
       } else {
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-          if (c + u < cols) v[u] = philox_normal1(seed, draw, e0 + u);
+          if (c + u < cols) v[u] = philox_normal1(seed, draw, e_row + (uint64_t)c + u);
       }
+      store_split4<MODE>(v, r, c, cols_p, op_a, op_b);
     }
-    store_split4<MODE>(v, r, c, cols_p, op_a, op_b);
   }
 }
 
@@ -843,6 +849,32 @@ static int set_gemm_smem(Kern kern) {
   return 0;
 }
 
+// Side stream for the operand pre-passes: staging pass p+1 (HBM-bound) overlaps the GEMM of pass p
+// (bound by operand delivery / the tensor pipe) through two operand buffers.  Ordered against the
+// caller's stream with events only; one set per device, created on first use.
+struct SideStream {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t fork = nullptr, op_done[2] = {nullptr, nullptr}, gemm_done[2] = {nullptr, nullptr};
+};
+static int side_stream(SideStream** out) {
+  static SideStream table[64];
+  int dev = 0;
+  PPI_CUDA_TRY(cudaGetDevice(&dev));
+  PPI_REQUIRE(dev >= 0 && dev < 64, PPI_ERR_UNSUPPORTED, "device ordinal %d out of range", dev);
+  SideStream& ss = table[dev];
+  if (ss.stream == nullptr) {
+    PPI_CUDA_TRY(cudaStreamCreateWithFlags(&ss.stream, cudaStreamNonBlocking));
+    PPI_CUDA_TRY(cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming));
+    for (int i = 0; i < 2; ++i) {
+      PPI_CUDA_TRY(cudaEventCreateWithFlags(&ss.op_done[i], cudaEventDisableTiming));
+      PPI_CUDA_TRY(cudaEventCreateWithFlags(&ss.gemm_done[i], cudaEventDisableTiming));
+    }
+  }
+  *out = &ss;
+  return 0;
+}
+int gemm_overlap();  // capi.cu: 1 = stage operands on the side stream
+
 constexpr int64_t kSyrkKc = 65536;    // samples staged per pass
 constexpr int64_t kSampleKc = 65536;  // sample rows staged per pass
 constexpr int64_t kKcQuantum = 512;   // Kc granularity (covers every chunk / split rounding below)
@@ -909,15 +941,20 @@ static int wmoments_dense_impl(const float* x, const float* nw, int64_t K, int64
     if (int rc = check_launch("syrk scale kernels", n)) return rc;
   }
 
-  CUtensorMap a, a2, b, b2;
-  if (int rc = make_map(&a, op_a, pl.Dp, pl.Kc, BM, MODE)) return rc;
-  if (int rc = make_map(&b, op_a, pl.Dp, pl.Kc, BN, MODE)) return rc;
-  if (FP16) {
-    a2 = a;
-    b2 = b;
-  } else {
-    if (int rc = make_map(&a2, op_b, pl.Dp, pl.Kc, BM, MODE)) return rc;
-    if (int rc = make_map(&b2, op_b, pl.Dp, pl.Kc, BN, MODE)) return rc;
+  // FP16: the second operand array is a second staging buffer (pass p+1 is staged while pass p
+  // multiplies); TF32X3 needs both arrays for one pass.
+  const bool overlap = FP16 && gemm_overlap() && K > pl.Kc;
+  void* bufs[2] = {op_a, FP16 ? (void*)(wsp + kScalarBytes + pl.op_bytes) : op_a};
+  CUtensorMap a[2], a2[2], b[2], b2[2];
+  for (int i = 0; i < (FP16 ? 2 : 1); ++i) {
+    if (int rc = make_map(&a[i], bufs[i], pl.Dp, pl.Kc, BM, MODE)) return rc;
+    if (int rc = make_map(&b[i], bufs[i], pl.Dp, pl.Kc, BN, MODE)) return rc;
+    a2[i] = a[i];
+    b2[i] = b[i];
+  }
+  if (!FP16) {
+    if (int rc = make_map(&a2[0], op_b, pl.Dp, pl.Kc, BM, MODE)) return rc;
+    if (int rc = make_map(&b2[0], op_b, pl.Dp, pl.Kc, BN, MODE)) return rc;
   }
 
   SyrkParams p;
@@ -935,19 +972,37 @@ static int wmoments_dense_impl(const float* x, const float* nw, int64_t K, int64
     if (int rc = set_gemm_smem(syrk_gemm_kernel<FP16>)) return rc;
     attr_set = true;
   }
+  SideStream* ss = nullptr;
+  cudaStream_t st_op = st;
+  if (overlap) {
+    if (int rc = side_stream(&ss)) return rc;
+    st_op = ss->stream;
+    PPI_CUDA_TRY(cudaEventRecord(ss->fork, st));
+    PPI_CUDA_TRY(cudaStreamWaitEvent(st_op, ss->fork, 0));
+  }
   int pass = 0;
   for (int64_t k0 = 0; k0 < K; k0 += pl.Kc, ++pass) {
+    const int bi = overlap ? (pass & 1) : 0;
     dim3 og((unsigned)(pl.Kc / 32), (unsigned)ceil_div(pl.Dp, 128));
     {
-      ProfileScope prof(PPI_PROF_SYRK_OPERAND, st);
-      syrk_operand_kernel<MODE><<<og, 256, 0, st>>>(x, nw, shift, K, D, k0, pl.Kc, pl.Dp, scalars, op_a, op_b);
+      if (overlap && pass >= 2) PPI_CUDA_TRY(cudaStreamWaitEvent(st_op, ss->gemm_done[bi], 0));
+      ProfileScope prof(PPI_PROF_SYRK_OPERAND, st_op);
+      syrk_operand_kernel<MODE><<<og, 256, 0, st_op>>>(x, nw, shift, K, D, k0, pl.Kc, pl.Dp, scalars,
+                                                       bufs[bi], op_b);
       if (int rc = check_launch("syrk_operand_kernel")) return rc;
     }
+    if (overlap) {
+      PPI_CUDA_TRY(cudaEventRecord(ss->op_done[bi], st_op));
+      PPI_CUDA_TRY(cudaStreamWaitEvent(st, ss->op_done[bi], 0));
+    }
     p.accumulate = pass > 0;
-    ProfileScope prof(PPI_PROF_SYRK_GEMM, st);
-    syrk_gemm_kernel<FP16><<<(unsigned)(pl.ntiles * pl.splits), kGemmThreads, kGemmSmemBytes, st>>>(
-        a, a2, b, b2, p);
-    if (int rc = check_launch("syrk_gemm_kernel")) return rc;
+    {
+      ProfileScope prof(PPI_PROF_SYRK_GEMM, st);
+      syrk_gemm_kernel<FP16><<<(unsigned)(pl.ntiles * pl.splits), kGemmThreads, kGemmSmemBytes, st>>>(
+          a[bi], a2[bi], b[bi], b2[bi], p);
+      if (int rc = check_launch("syrk_gemm_kernel")) return rc;
+    }
+    if (overlap) PPI_CUDA_TRY(cudaEventRecord(ss->gemm_done[bi], st));
   }
   ProfileScope prof(PPI_PROF_SYRK_REDUCE, st);
   syrk_reduce_kernel<<<grid_cap(ceil_div(D * D, 256), 8), 256, 0, st>>>(partials, pl.splits, pl.Dp,
@@ -1016,18 +1071,22 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
     sample_scale_kernel<<<1, 1, 0, st>>>(scalars, ZPAIR ? 1 : 0);
     if (int rc = check_launch("sample scale kernels", n)) return rc;
   }
-  split_rows_kernel<LMODE><<<grid_cap(ceil_div(D * (Dk / 4), 256), 8), 256, 0, st>>>(
+  split_rows_kernel<LMODE><<<grid_cap(D, 8), 256, 0, st>>>(
       L, D, D, Dk, 0, 0, 0, 1, FP16 ? &scalars->scale_a : nullptr, l_a, l_b);
   if (int rc = check_launch("split_rows_kernel(L)")) return rc;
 
-  CUtensorMap ml, ml2, mz, mz2;
+  const bool overlap = FP16 && gemm_overlap() && K > Kc;
+  void* zbufs[2] = {z_a, FP16 ? z_b : z_a};
+  CUtensorMap ml, ml2, mz[2], mz2[2];
   if (int rc = make_map(&ml, l_a, D, Dk, BM, LMODE)) return rc;
-  if (int rc = make_map(&mz, z_a, Kc, Dk, BN, ZMODE)) return rc;
   ml2 = ml;
-  mz2 = mz;
+  for (int i = 0; i < (FP16 ? 2 : 1); ++i) {
+    if (int rc = make_map(&mz[i], zbufs[i], Kc, Dk, BN, ZMODE)) return rc;
+    mz2[i] = mz[i];
+  }
   if (!FP16) {
     if (int rc = make_map(&ml2, l_b, D, Dk, BM, LMODE)) return rc;
-    if (int rc = make_map(&mz2, z_b, Kc, Dk, BN, ZMODE)) return rc;
+    if (int rc = make_map(&mz2[0], z_b, Kc, Dk, BN, ZMODE)) return rc;
   }
 
   static bool attr_set = false;
@@ -1045,26 +1104,44 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
   p.scalars = scalars;
   p.z_exact = z_exact ? 1 : 0;
 
-  for (int64_t k0 = 0; k0 < K; k0 += Kc) {
+  SideStream* ss = nullptr;
+  cudaStream_t st_op = st;
+  if (overlap) {
+    if (int rc = side_stream(&ss)) return rc;
+    st_op = ss->stream;
+    PPI_CUDA_TRY(cudaEventRecord(ss->fork, st));
+    PPI_CUDA_TRY(cudaStreamWaitEvent(st_op, ss->fork, 0));
+  }
+  int pass = 0;
+  for (int64_t k0 = 0; k0 < K; k0 += Kc, ++pass) {
+    const int bi = overlap ? (pass & 1) : 0;
     const int64_t rows = (K - k0) < Kc ? (K - k0) : Kc;
     const int64_t rows_p = round_up(rows, BN);
     // injected: rows beyond `rows` keep stale workspace values whose products are never stored;
     // Philox: they are generated too (harmless)
     {
-      ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st);
+      if (overlap && pass >= 2) PPI_CUDA_TRY(cudaStreamWaitEvent(st_op, ss->gemm_done[bi], 0));
+      ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st_op);
       const int64_t nrows = z ? rows : rows_p;
-      split_rows_kernel<ZMODE><<<grid_cap(ceil_div(nrows * (Dk / 4), 256), 16), 256, 0, st>>>(
+      split_rows_kernel<ZMODE><<<grid_cap(nrows, 8), 256, 0, st_op>>>(
           z ? z + k0 * D : nullptr, nrows, D, Dk, seed, draw_id, row_offset + (uint64_t)k0, 0,
-          FP16 ? &scalars->scale_b : nullptr, z_a, (!FP16 && !z_exact) ? z_b : nullptr);
+          FP16 ? &scalars->scale_b : nullptr, zbufs[bi], (!FP16 && !z_exact) ? z_b : nullptr);
       if (int rc = check_launch("split_rows_kernel(z)")) return rc;
+    }
+    if (overlap) {
+      PPI_CUDA_TRY(cudaEventRecord(ss->op_done[bi], st_op));
+      PPI_CUDA_TRY(cudaStreamWaitEvent(st, ss->op_done[bi], 0));
     }
     p.n_units = (rows_p / BN) * p.units_per_block;
     p.rows = rows;
     p.x = x + k0 * D;
     const unsigned g = (unsigned)(p.n_units < kNumSMs ? p.n_units : kNumSMs);
-    ProfileScope prof(PPI_PROF_SAMPLE_GEMM, st);
-    sample_gemm_kernel<FP16, ZPAIR><<<g, kGemmThreads, kGemmSmemBytes, st>>>(ml, ml2, mz, mz2, p);
-    if (int rc = check_launch("sample_gemm_kernel")) return rc;
+    {
+      ProfileScope prof(PPI_PROF_SAMPLE_GEMM, st);
+      sample_gemm_kernel<FP16, ZPAIR><<<g, kGemmThreads, kGemmSmemBytes, st>>>(ml, ml2, mz[bi], mz2[bi], p);
+      if (int rc = check_launch("sample_gemm_kernel")) return rc;
+    }
+    if (overlap) PPI_CUDA_TRY(cudaEventRecord(ss->gemm_done[bi], st));
   }
   return 0;
 }

@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libppi_b200.so")
 # enums of include/ppi_b200.h
 KERNEL_KINDS = {"se": 0, "matern12": 1, "matern32": 2, "matern52": 3, "periodic": 4, "white": 5}
 FN_IDS = {"Himmelblau": 0, "Rosenbrock": 1, "Styblinski": 2, "Rastrigin": 3, "NoisySphere": 4}
-OPT_GEMM_SCHEME, OPT_GEMM_CHUNK = 0, 1
+OPT_GEMM_SCHEME, OPT_GEMM_CHUNK, OPT_GEMM_OVERLAP = 0, 1, 2
 GEMM_TF32X3, GEMM_FP16X2 = 0, 1
 TEMP_FIXED_NORMALISED, TEMP_FIXED_SHIFTED, TEMP_REPS_KL, TEMP_ESS_TARGET, TEMP_LOWER_BOUND = range(5)
 
@@ -57,7 +57,7 @@ SIGNATURES = {
     "ppi_normalise_log_weights": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
     "ppi_cem_workspace_bytes": (_sz, [_i64]),
     "ppi_cem_weights": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _sz, _p]),
-    "ppi_wmoments_diag": (_i, [_p, _p, _i64, _i64, _p, _p, _p, _p, _p]),
+    "ppi_wmoments_diag": (_i, [_p, _p, _i64, _i64, _p, _p, _p, _p, _p, _p]),
     "ppi_wmoments_matnorm": (_i, [_p, _p, _i64, _i, _i, _p, _p, _p, _p]),
     "ppi_wmoments_dense_workspace_bytes": (_sz, [_i64, _i64]),
     "ppi_wmoments_dense": (_i, [_p, _p, _i64, _i64, _p, _p, _p, _i, _p, _sz, _p]),

@@ -184,6 +184,14 @@ def all_reduce_sum(t):
     return t
 
 
+def all_reduce_max(t):
+    import torch.distributed as dist
+
+    if dist_info()[1] > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t
+
+
 def broadcast_row(samples, global_index, n_total):
     """Row `global_index` of the K-sharded sample matrix, on every rank (owner broadcasts)."""
     import torch.distributed as dist

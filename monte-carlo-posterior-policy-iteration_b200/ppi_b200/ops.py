@@ -213,8 +213,9 @@ def cem_weights(costs, n_elites, sync=True):
 
 
 # ------------------------------------------------------------------ a16-a21
-def wmoments_diag(x, nw, shift1=None, shift2=None, second=False, s1=None, s2=None):
-    """fp64 accumulators: s1 = sum nw (x - shift1), s2 = sum nw (x - shift2)^2 over rows of x (K, D)."""
+def wmoments_diag(x, nw, shift1=None, shift2=None, second=False, s1=None, s2=None, absdev=None):
+    """fp64 accumulators: s1 = sum nw (x - shift1), s2 = sum nw (x - shift2)^2 over rows of x (K, D).
+    absdev: optional zeroed fp32 device scalar that receives max |x - shift1| over weighted rows."""
     dev = require_cuda()
     kp = _Keep(dev)
     x = f32(x, dev)
@@ -225,7 +226,7 @@ def wmoments_diag(x, nw, shift1=None, shift2=None, second=False, s1=None, s2=Non
     if second and s2 is None:
         s2 = torch.zeros(D, dtype=torch.float64, device=dev)
     _lib.call("ppi_wmoments_diag", ptr(x2), kp.p(nw), K, D, kp.p(shift1),
-              kp.p(shift2), ptr(s1), ptr(s2 if second else None), stream_ptr())
+              kp.p(shift2), ptr(s1), ptr(s2 if second else None), ptr(absdev), stream_ptr())
     return (s1, s2) if second else s1
 
 

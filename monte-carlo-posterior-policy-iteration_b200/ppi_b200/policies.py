@@ -16,7 +16,7 @@ import numpy as np
 import torch
 
 from . import ops, samplers
-from .device import (DeviceArray, all_reduce_sum, broadcast_row, dist_info, f32, f64, require_cuda,
+from .device import (DeviceArray, all_reduce_max, all_reduce_sum, broadcast_row, dist_info, f32, f64, require_cuda,
                      shard_rows, to_host64)
 
 __all__ = [
@@ -352,11 +352,15 @@ class GaussianPolicy(object):
         sigma_old_host, sigma_old_dev = self._sigma_host, self._sigma_dev
 
         # pass 1: weighted mean, centred on the old mean for fp32 accuracy (policies.py:88)
-        s1 = ops.wmoments_diag(x, nw, shift1=mu_old_dev)
+        absdev = torch.zeros(1, dtype=torch.float32, device=x.device)
+        s1 = ops.wmoments_diag(x, nw, shift1=mu_old_dev, absdev=absdev)
         if not replicated:
             all_reduce_sum(s1)
+            all_reduce_max(absdev)
         mu_new_dev, _ = ops.finalize_gaussian(s1=s1, shift=mu_old_dev, want_sigma=False)
         self._mu_host, self._mu_dev = None, mu_new_dev
+        # the new mean is a convex combination of the samples: |x - mu_new| <= 2 max |x - mu_old|
+        dev_bound = 2.0 * absdev
 
         # pass 2: covariance centred on the new mean (policies.py:89-92)
         if update_covariance_in:
@@ -368,7 +372,7 @@ class GaussianPolicy(object):
                 chol64 = torch.diag(torch.sqrt(s2))
                 pd = bool((torch.isfinite(s2) & (s2 > 0)).all().item())
             else:
-                cov = ops.wmoments_dense(x, nw, shift=mu_new_dev)
+                cov = ops.wmoments_dense(x, nw, shift=mu_new_dev, dev_bound=dev_bound)
                 if not replicated:
                     all_reduce_sum(cov)
                 chol64, info = torch.linalg.cholesky_ex(cov.double())

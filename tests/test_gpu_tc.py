@@ -132,3 +132,53 @@ def test_gaussian_policy_dense_update(ops):
     smp.InjectedNormals.queue = [z2.copy()]
     x2 = np.asarray(policy(K)[0])
     assert nerr(x2, O.sample_gaussian(z2.astype(np.float64), policy.mu, policy.sigma)) < 2e-5
+
+
+def test_wmoments_dense_dev_bound_and_overlap(ops):
+    """The operand-scale bound may come from the mean pass (ppi_wmoments_diag absdev_max) and may be
+    loose; staging on the side stream (several passes, K > 65536) changes nothing bit-wise."""
+    import torch
+
+    from ppi_b200 import _lib
+
+    K, D = 150000, 256
+    x, lw, nw = _problem(K, D, 3)
+    mu_old = f32r(np.ones(D))
+    xd, nwd = torch.as_tensor(x, dtype=torch.float32).cuda(), torch.as_tensor(nw, dtype=torch.float32).cuda()
+    absdev = torch.zeros(1, dtype=torch.float32, device="cuda")
+    s1 = ops.wmoments_diag(xd, nwd, shift1=mu_old, absdev=absdev)
+    assert abs(float(absdev.item()) - np.max(np.abs(x - mu_old))) < 1e-6 * np.max(np.abs(x))
+    mu32 = f32r(mu_old + host(s1))
+    ref = (nw[:, None] * (x - mu32)).T @ (x - mu32)
+    base = host(ops.wmoments_dense(xd, nwd, shift=mu32))
+    assert nerr(base, ref) < TOL
+    for factor in (2.0, 2000.0):
+        cov = host(ops.wmoments_dense(xd, nwd, shift=mu32, dev_bound=factor * absdev))
+        assert nerr(cov, ref) < TOL
+    _lib.call("ppi_set_option", _lib.OPT_GEMM_OVERLAP, 1)
+    try:
+        overlapped = host(ops.wmoments_dense(xd, nwd, shift=mu32))
+    finally:
+        _lib.call("ppi_set_option", _lib.OPT_GEMM_OVERLAP, 0)
+    assert np.array_equal(overlapped, base)
+
+
+def test_sample_gaussian_overlap_bitwise(ops):
+    import torch
+
+    from ppi_b200 import _lib
+
+    K, D = 140000, 256
+    rng = np.random.default_rng(1)
+    a = rng.standard_normal((D, D + 8))
+    L = f32r(np.linalg.cholesky(a @ a.T / D + 0.2 * np.eye(D)))
+    mu = f32r(rng.standard_normal(D))
+    xa = ops.sample_gaussian(K, mu, L, seed=9, draw_id=2)
+    _lib.call("ppi_set_option", _lib.OPT_GEMM_OVERLAP, 1)
+    try:
+        xb = ops.sample_gaussian(K, mu, L, seed=9, draw_id=2)
+    finally:
+        _lib.call("ppi_set_option", _lib.OPT_GEMM_OVERLAP, 0)
+    assert torch.equal(xa, xb)
+    zp = host(ops.philox_normal(K, D, seed=9, draw_id=2))
+    assert nerr(host(xa), mu[None, :] + zp @ L.T) < TOL
