@@ -47,6 +47,11 @@ WORKLOADS = {
 }
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+# `ncu --set full` capture under profiles/ (see profiles/README.md); keyed by (kernel, D).
+NCU_TRAFFIC = {}
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -348,13 +353,17 @@ def run_b200(args, wl):
         rows_per_launch = wl["K"] * args.steps / n        # samples contracted per launch
         algorithmic = 2.0 * rows_per_launch * D * D        # 2 D^2 useful flops per sample
         t = tot_ms / n * 1e-3
-        tf32_peak = pk["bf16"] / 2.0
+        scheme = lib.ppi_get_option(_lib.OPT_GEMM_SCHEME)
         roofline = {
-            "kernel": "split_tf32_gemm_kernel (SYRK mode, tcgen05 kind::tf32)",
-            "bound": "tensor", "achieved": algorithmic / t / 1e12, "peak": tf32_peak, "unit": "TFLOP/s",
-            "frac": algorithmic / t / 1e12 / tf32_peak, "traffic": None,
-            "peak_source": f"tf32 dense = bf16 sustained / 2, {pk['source']}",
+            "kernel": "syrk_gemm_kernel<FP16X2> (tcgen05 kind::f16, 3 partial products of fp16 pairs)"
+                      if scheme == _lib.GEMM_FP16X2 else "syrk_gemm_kernel<TF32X3> (tcgen05 kind::tf32)",
+            "bound": "tensor", "achieved": algorithmic / t / 1e12, "peak": pk["bf16"], "unit": "TFLOP/s",
+            "frac": algorithmic / t / 1e12 / pk["bf16"], "traffic": NCU_TRAFFIC.get(("syrk", wl["D"])),
+            "peak_source": f"dense 16-bit tensor peak, sustained, {pk['source']}",
+            "algorithmic_flops_per_launch": algorithmic,
             "executed_tflops": executed_syrk_flops(rows_per_launch, D) / t / 1e12,
+            "executed_note": "MMA flops actually issued: 3 partial products on the 72 upper-triangular "
+                             "128x256 tiles; executed / peak is the tensor-pipe utilisation",
             "launches": n, "avg_launch_ms": tot_ms / n,
             "share_of_step": tot_ms / (ms_per_step * args.steps),
         }
@@ -384,7 +393,9 @@ def run_b200(args, wl):
     line = {
         "metric": "PPI update samples/sec", "value": value, "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32 (split-tf32 tensor-core products, fp32/fp64 accumulation)",
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "dtype_note": "fp32 samples and results; dense products on tcgen05 as exact fp16-pair partial products "
+                      "with fp32 accumulation; fp64 scalars in the temperature solve and small-matrix tails",
         "data": "synthetic",
         "config": {"workload": wl["desc"], "samples_per_gpu": wl["K"], "samples_total": K_total,
                    "elements_per_s": value * (wl.get("D") or wl.get("H", 21) * wl["d"]),
