@@ -12,8 +12,8 @@ Rastrigin cost, ESSPS temperature with N = K/64, on-device Philox normals.
 value      whole-job samples/s with the policy state resident in HBM (CUDA events, max over ranks)
 e2e        same step through the public API with HOST buffers: a fresh policy is built from pinned
            host mu / sigma every step and the fitted mu / sigma are read back to the host
-roofline   the dominant kernel (split-TF32 tcgen05 SYRK): algorithmic flops per launch / its
-           CUDA-event time measured inside the timed region, against the measured tensor peak
+roofline   the dominant kernel (tcgen05 covariance GEMM): algorithmic flops per launch / its
+           CUDA-event time measured inside the timed region, against the measured 16-bit tensor peak
 cpu_baseline  the oracle port (NumPy restatement of the reference, its naive einsum) on a bounded
            sample of the same workload, timed on this box's host cores (rank 0, N = 1 only)
 --impl reference  times that CPU path alone (the reference is pure NumPy: there is no GPU arm)
@@ -49,7 +49,7 @@ WORKLOADS = {
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
 # `ncu --set full` capture under profiles/ (see profiles/README.md); keyed by (kernel, D).
-NCU_TRAFFIC = {}
+NCU_TRAFFIC = {("syrk", 2048): 541.2e6}  # profiles/r1_gemm_ncu_full_summary.csv (537.0 MB read + 4.2 MB written)
 
 
 def peaks():
