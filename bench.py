@@ -204,7 +204,7 @@ def run_reference(args, wl):
                                    "only the O(D^3) LAPACK tails use BLAS threads)"},
         "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -406,7 +406,7 @@ def run_b200(args, wl):
         "gpu_launches": int(launches), "kernels": kernels, "roofline": roofline, "cpu_baseline": cpu,
         "clocks": clocks,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -419,7 +419,26 @@ def executed_syrk_flops(rows, D):
     return 3 * 2.0 * rows * ntiles * 128 * 256
 
 
+def _claim_stdout():
+    """Keep stdout for the one JSON line: libraries (NCCL prints its version banner to fd 1) are
+    redirected to stderr; returns a file object on the original stdout."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
+def emit(line):
+    OUT.write(json.dumps(line) + "\n")
+    OUT.flush()
+
+
+OUT = sys.stdout
+
+
 def main():
+    global OUT
+    OUT = _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)

@@ -1,0 +1,200 @@
+// Warp-level tensor-core kernels for the small-matrix forms of the update path (H <= 32):
+//   wmoments_matnorm_mma   acc += sum_b nw_b A_b diag(1/cov_out) A_b^T        ppi/policies.py:129-132
+//   sample_matnorm_mma     x_b = clip(mean_fn + mean + L_in z_b diag(l_out))  ppi/policies.py:735-745
+//
+// These products are HBM-bound only if the H^2 d multiply-adds per sample cost (almost) nothing:
+// at C3 shapes (H = 30, d = 28) they need ~100 TFLOP/s at HBM speed, more than the fp32 SIMT
+// pipes deliver.  The matrices are far too small for a 128-row tcgen05 tile (a 30 x 30 output
+// would waste > 90 % of it), so they run on warp-level mma.sync.m16n8k16 (fp16 in, fp32
+// accumulate; measured 555 TFLOP/s on B200, tools/micro/mma_sync_rate.cu) with every operand in
+// registers: one warp owns a 32 x 32 output, fragments are loaded straight from global memory in
+// fragment order (every 32-byte sector fetched is fully used) and no shared-memory staging,
+// swizzle or TMEM is involved.
+//
+// fp32 accuracy from fp16 tensor cores = the FP16X2 scheme of tc_gemm.cu: v 2^e = h1 + h2, three
+// MMAs h1 g1 + h1 g2 + h2 g1, with the power-of-two scale chosen PER 32-COLUMN CHUNK by a warp max
+// (the accumulator of a chunk is promoted to fp32 registers with an exact 2^-2e factor right after
+// its 6 MMAs, so accumulation chains inside the tensor core stay 6 instructions long).
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+
+namespace ppi {
+
+__device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                         uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+      "{%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// (h1, h2) halves of two scaled values packed as half2 registers (low half = first value)
+__device__ __forceinline__ void split_pair(float v0, float v1, uint32_t& h1, uint32_t& h2) {
+  const __half2 a = __floats2half2_rn(v0, v1);
+  const float2 af = __half22float2(a);
+  const __half2 b = __floats2half2_rn(v0 - af.x, v1 - af.y);
+  h1 = *reinterpret_cast<const uint32_t*>(&a);
+  h2 = *reinterpret_cast<const uint32_t*>(&b);
+}
+
+// 2^e with amax 2^e in [2^13, 2^14)
+__device__ __forceinline__ float chunk_scale(float amax) {
+  if (!(amax > 0.f) || !isfinite(amax)) return 1.f;
+  int e = (int)((__float_as_uint(amax) >> 23) & 0xff) - 126;  // amax = m 2^e, m in [0.5, 1)
+  int s = 14 - e;
+  s = s < -60 ? -60 : (s > 60 ? 60 : s);
+  return __uint_as_float((uint32_t)(s + 127) << 23);
+}
+
+constexpr int kMmaWarps = 8;  // warps per block
+
+// ------------------------------------------------------------------------------------------
+// acc[i,l] += sum_{b,j} nw_b inv_j (x_bij - s_ij)(x_blj - s_lj),   i <= l,   H <= 32.
+// The contraction axis is the flattened (b, j) column index c = b d + j; a warp takes chunks of 32
+// consecutive columns (any d, ragged across samples).  Per chunk and thread: rows {g, g+8, g+16,
+// g+24} x columns {2t, 2t+1, 2t+8, 2t+9} (+16 for the second k-step), g = lane / 4, t = lane % 4:
+// exactly the A (and, transposed, B) fragments of the 6 upper-triangular 16 x 8 output tiles.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kMmaWarps * 32)
+wmoments_matnorm_mma_kernel(const float* __restrict__ x, const float* __restrict__ nw, int64_t K, int H,
+                            int d, const float* __restrict__ shift, const float* __restrict__ inv_cov,
+                            double* __restrict__ acc) {
+  extern __shared__ float smem[];
+  float* sShift = smem;            // H*d
+  float* sInv = sShift + H * d;    // d
+  float* sRed = sInv + d;          // 32*32 block reduction buffer
+  const int HD = H * d;
+  for (int i = threadIdx.x; i < HD; i += blockDim.x) sShift[i] = shift ? shift[i] : 0.f;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) sInv[i] = inv_cov ? inv_cov[i] : 1.f;
+  for (int i = threadIdx.x; i < 32 * 32; i += blockDim.x) sRed[i] = 0.f;
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int64_t ncols = K * (int64_t)d;
+  const int64_t nchunks = (ncols + 31) / 32;
+  const int64_t wid = (int64_t)blockIdx.x * kMmaWarps + warp, nwarps = (int64_t)gridDim.x * kMmaWarps;
+  const float inv_d = 1.0f / (float)d;
+
+  // row offsets (elements) of this thread's 4 row groups; rows >= H are masked
+  int roff[4];
+  bool rok[4];
+#pragma unroll
+  for (int rg = 0; rg < 4; ++rg) {
+    const int i = g + 8 * rg;
+    rok[rg] = i < H;
+    roff[rg] = (rok[rg] ? i : 0) * d;
+  }
+
+  // tiles: (r,s) = (0,0) (0,1) (0,2) (0,3) (1,2) (1,3)
+  float acc2[6][4];
+#pragma unroll
+  for (int q = 0; q < 6; ++q) acc2[q][0] = acc2[q][1] = acc2[q][2] = acc2[q][3] = 0.f;
+
+  for (int64_t ch = wid; ch < nchunks; ch += nwarps) {
+    const int64_t c0 = ch * 32;
+    const int64_t b0 = c0 / d;
+    const int rel0 = (int)(c0 - b0 * d);
+    // values v[step][rg][4 columns]
+    float v[2][4][4];
+    float amax = 0.f;
+#pragma unroll
+    for (int st = 0; st < 2; ++st) {
+#pragma unroll
+      for (int cp = 0; cp < 2; ++cp) {    // column pair: 2t (+8)
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int lc = 16 * st + 8 * cp + 2 * t + u;
+          const int rel = rel0 + lc;
+          const int bq = __float2int_rd(((float)rel + 0.5f) * inv_d);
+          const int j = rel - bq * d;
+          const int64_t b = b0 + bq;
+          const bool ok = (c0 + lc) < ncols;
+          float f = 0.f;
+          if (ok) {
+            const float w = __ldg(nw + b);
+            f = (w != 0.f) ? sqrtf(w * sInv[j]) : 0.f;
+          }
+          const float* px = x + b * HD + j;
+#pragma unroll
+          for (int rg = 0; rg < 4; ++rg) {
+            float val = 0.f;
+            if (f != 0.f && rok[rg]) val = (__ldg(px + roff[rg]) - sShift[roff[rg] + j]) * f;
+            v[st][rg][2 * cp + u] = val;
+            amax = fmaxf(amax, fabsf(val));
+          }
+        }
+      }
+    }
+    amax = warp_max(amax);
+    if (amax == 0.f) continue;  // warp-uniform: nothing but zero-weight samples / padding
+    const float sc = chunk_scale(amax);
+    const float isc2 = (1.f / sc) * (1.f / sc);
+
+    float a1[6][4];
+#pragma unroll
+    for (int q = 0; q < 6; ++q) a1[q][0] = a1[q][1] = a1[q][2] = a1[q][3] = 0.f;
+#pragma unroll
+    for (int st = 0; st < 2; ++st) {
+      uint32_t h1[4][2], h2[4][2];  // [row group][column pair]
+#pragma unroll
+      for (int rg = 0; rg < 4; ++rg)
+#pragma unroll
+        for (int cp = 0; cp < 2; ++cp)
+          split_pair(v[st][rg][2 * cp] * sc, v[st][rg][2 * cp + 1] * sc, h1[rg][cp], h2[rg][cp]);
+      // tile q = (r, s): A rows 16r + {g, g+8} -> row groups 2r, 2r+1; B rows 8s + g -> row group s
+#define PPI_TILE(q, r, s)                                                                              \
+  mma16816(a1[q], h1[2 * r][0], h1[2 * r + 1][0], h1[2 * r][1], h1[2 * r + 1][1], h1[s][0], h1[s][1]); \
+  mma16816(a1[q], h1[2 * r][0], h1[2 * r + 1][0], h1[2 * r][1], h1[2 * r + 1][1], h2[s][0], h2[s][1]); \
+  mma16816(a1[q], h2[2 * r][0], h2[2 * r + 1][0], h2[2 * r][1], h2[2 * r + 1][1], h1[s][0], h1[s][1]);
+      PPI_TILE(0, 0, 0) PPI_TILE(1, 0, 1) PPI_TILE(2, 0, 2) PPI_TILE(3, 0, 3) PPI_TILE(4, 1, 2) PPI_TILE(5, 1, 3)
+#undef PPI_TILE
+    }
+#pragma unroll
+    for (int q = 0; q < 6; ++q)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc2[q][e] = fmaf(a1[q][e], isc2, acc2[q][e]);
+  }
+
+  // block reduction in shared memory (fp32 atomics on <= 8 warps), then fp64 atomics to global
+  const int tr[6] = {0, 0, 0, 0, 1, 1}, ts[6] = {0, 1, 2, 3, 2, 3};
+#pragma unroll
+  for (int q = 0; q < 6; ++q) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int i = 16 * tr[q] + g + 8 * (e >> 1), l = 8 * ts[q] + 2 * t + (e & 1);
+      atomicAdd(&sRed[i * 32 + l], acc2[q][e]);
+    }
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < 32 * 32; e += blockDim.x) {
+    const int i = e >> 5, l = e & 31;
+    if (i < H && l < H && l >= i) {
+      const float s = sRed[e];
+      if (s != 0.f) atomicAdd(acc + (int64_t)i * H + l, (double)s);
+    }
+  }
+}
+
+}  // namespace ppi
+
+using namespace ppi;
+
+// called from moments.cu for H <= 32
+int ppi_wmoments_matnorm_mma(const float* x, const float* nw, int64_t K, int H, int d, const float* shift,
+                             const float* inv_cov_out, double* acc, cudaStream_t st) {
+  const size_t smem = ((size_t)H * d + d + 32 * 32) * sizeof(float);
+  PPI_REQUIRE(smem <= 200 * 1024, PPI_ERR_UNSUPPORTED, "ppi_wmoments_matnorm: H=%d d=%d does not fit shared memory", H, d);
+  if (smem > 48 * 1024)
+    PPI_CUDA_TRY(cudaFuncSetAttribute(wmoments_matnorm_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem));
+  const int64_t nchunks = (K * (int64_t)d + 31) / 32;
+  int64_t grid = ceil_div(nchunks, (int64_t)kMmaWarps * 4);  // >= 4 chunks per warp
+  if (grid > (int64_t)kNumSMs * 2) grid = (int64_t)kNumSMs * 2;
+  if (grid < 1) grid = 1;
+  wmoments_matnorm_mma_kernel<<<(unsigned)grid, kMmaWarps * 32, smem, st>>>(x, nw, K, H, d, shift,
+                                                                           inv_cov_out, acc);
+  return check_launch("wmoments_matnorm_mma_kernel");
+}

@@ -259,6 +259,10 @@ finalize_matnorm_kernel(const double* __restrict__ s1, const double* __restrict_
 
 using namespace ppi;
 
+// mma_small.cu
+int ppi_wmoments_matnorm_mma(const float* x, const float* nw, int64_t K, int H, int d, const float* shift,
+                             const float* inv_cov_out, double* acc, cudaStream_t st);
+
 extern "C" int ppi_wmoments_diag(const float* x, const float* nw, int64_t K, int64_t D,
                                  const float* shift1, const float* shift2, double* s1, double* s2,
                                  float* absdev_max, void* stream) {
@@ -296,6 +300,10 @@ extern "C" int ppi_wmoments_matnorm(const float* x, const float* nw, int64_t K, 
   PPI_REQUIRE(H <= 128, PPI_ERR_UNSUPPORTED, "ppi_wmoments_matnorm supports H <= 128 (got %d)", H);
   if (K == 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
+  if (H <= 32) {  // warp-level tensor-core kernel (mma_small.cu)
+    ProfileScope prof(PPI_PROF_WMOMENTS_MATNORM, st);
+    return ppi_wmoments_matnorm_mma(x, nw, K, H, d, shift, inv_cov_out, acc, st);
+  }
   const int Hb = (H + 3) / 4, Hp = Hb * 4, nb = Hb * (Hb + 1) / 2;
   // samples per staged group: aim for a contraction length of ~256 within the smem budget
   int S = 256 / d;

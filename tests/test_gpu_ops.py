@@ -425,7 +425,8 @@ def test_m_projection_mavn_golden(ops, golden):
 
 
 @pytest.mark.parametrize("K,H,d", [(4096, 30, 28), (1000, 21, 2), (257, 128, 1), (300, 100, 3), (64, 2, 1),
-                                   (50, 65, 28)])
+                                   (50, 65, 28), (20000, 32, 7), (5000, 17, 5), (333, 8, 33), (3, 32, 1),
+                                   (70000, 30, 28)])
 def test_wmoments_matnorm_oracle(ops, K, H, d):
     rng = np.random.default_rng(H * d)
     x = f32r(rng.standard_normal((K, H, d)) * (0.5 + rng.random((1, H, d))))
@@ -443,6 +444,27 @@ def test_wmoments_matnorm_oracle(ops, K, H, d):
         mu2, sigma2, _ = O.m_projection(lw, x[:, :, 0], naive=False)
         acc = ops.wmoments_matnorm(x, nw, shift=host(s1).reshape(H, 1))
         assert nerr(host(ops.finalize_matnorm(s1, acc, H, 1)["cov64"]), sigma2) < TOL
+
+
+def test_wmoments_matnorm_zero_weight_nan_rows(ops):
+    """Failed rollouts (NaN rows, weight 0) must not leak into the warp-level tensor-core kernel, and
+    widely different per-sample magnitudes must not hurt (the fp16 operand scale is per 32 columns)."""
+    rng = np.random.default_rng(3)
+    K, H, d = 3000, 30, 28
+    x = f32r(rng.standard_normal((K, H, d)) * np.exp(4 * rng.standard_normal((K, 1, 1))))
+    nw = f32r(rng.random(K))
+    nw[::7] = 0.0
+    nw /= nw.sum()
+    nw = f32r(nw)
+    xb = x.copy()
+    xb[::7] = np.nan
+    shift = f32r(rng.standard_normal((H, d)))
+    inv = f32r(1.0 + rng.random(d))
+    a = np.nan_to_num(xb) - shift
+    ref = np.einsum("b,bij,j,blj->il", nw.astype(np.float64), a, inv.astype(np.float64), a)
+    acc = host(ops.wmoments_matnorm(xb, nw, shift=shift, inv_cov_out=inv))
+    assert np.isfinite(acc).all()
+    assert nerr(np.triu(acc), np.triu(ref)) < TOL
 
 
 def test_finalize_gaussian(ops):
