@@ -39,12 +39,44 @@ __device__ __forceinline__ void split_pair(float v0, float v1, uint32_t& h1, uin
   h2 = *reinterpret_cast<const uint32_t*>(&b);
 }
 
+// predicated read-only loads (no branch: the compiler turns an `if` around a vector load into a
+// divergent region)
+__device__ __forceinline__ float2 ldg2_if(const float* p, bool pred) {
+  float2 v;
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "setp.ne.b32 q, %3, 0;\n\t"
+      "mov.f32 %0, 0f00000000;\n\t"
+      "mov.f32 %1, 0f00000000;\n\t"
+      "@q ld.global.nc.v2.f32 {%0, %1}, [%2];\n\t}"
+      : "=f"(v.x), "=f"(v.y)
+      : "l"(p), "r"((int)pred));
+  return v;
+}
+__device__ __forceinline__ float ldg1_if(const float* p, bool pred) {
+  float v;
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "setp.ne.b32 q, %2, 0;\n\t"
+      "mov.f32 %0, 0f00000000;\n\t"
+      "@q ld.global.nc.f32 %0, [%1];\n\t}"
+      : "=f"(v)
+      : "l"(p), "r"((int)pred));
+  return v;
+}
+
+// single-instruction square root (MUFU.SQRT, relative error <= 2^-23, no slow path)
+__device__ __forceinline__ float sqrt_fast(float v) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r;
+}
+
 // 2^e with amax 2^e in [2^13, 2^14)
 __device__ __forceinline__ float chunk_scale(float amax) {
-  if (!(amax > 0.f) || !isfinite(amax)) return 1.f;
-  int e = (int)((__float_as_uint(amax) >> 23) & 0xff) - 126;  // amax = m 2^e, m in [0.5, 1)
+  const int e = (int)((__float_as_uint(amax) >> 23) & 0xff) - 126;  // amax = m 2^e, m in [0.5, 1)
   int s = 14 - e;
-  s = s < -60 ? -60 : (s > 60 ? 60 : s);
+  s = max(-60, min(60, s));   // inf / nan (exponent 255) clamp to 2^-60, zero never gets here
   return __uint_as_float((uint32_t)(s + 127) << 23);
 }
 
@@ -56,18 +88,25 @@ constexpr int kMmaWarps = 8;  // warps per block
 // consecutive columns (any d, ragged across samples).  Per chunk and thread: rows {g, g+8, g+16,
 // g+24} x columns {2t, 2t+1, 2t+8, 2t+9} (+16 for the second k-step), g = lane / 4, t = lane % 4:
 // exactly the A (and, transposed, B) fragments of the 6 upper-triangular 16 x 8 output tiles.
+// VEC2 (d even, x 8-byte aligned): the column pair (2t, 2t+1) is one 8-byte load.
+// The loop body is branch-free: masked rows read a zero pad behind the shift table and their
+// (predicated) load is skipped; zero-weight samples (possibly NaN rollouts) are never loaded.
 // ------------------------------------------------------------------------------------------
+template <bool VEC2>
 __global__ void __launch_bounds__(kMmaWarps * 32)
 wmoments_matnorm_mma_kernel(const float* __restrict__ x, const float* __restrict__ nw, int64_t K, int H,
                             int d, const float* __restrict__ shift, const float* __restrict__ inv_cov,
                             double* __restrict__ acc) {
   extern __shared__ float smem[];
-  float* sShift = smem;            // H*d
-  float* sInv = sShift + H * d;    // d
-  float* sRed = sInv + d;          // 32*32 block reduction buffer
   const int HD = H * d;
-  for (int i = threadIdx.x; i < HD; i += blockDim.x) sShift[i] = shift ? shift[i] : 0.f;
-  for (int i = threadIdx.x; i < d; i += blockDim.x) sInv[i] = inv_cov ? inv_cov[i] : 1.f;
+  const int HDp = (HD + 3) & ~3;           // the zero pad (d + 2 values) starts here
+  const int padn = (d + 5) & ~3;
+  float* sShift = smem;                    // HD values, then zeros
+  float* sSqInv = sShift + HDp + padn;     // sqrt(inv_cov_out[j]), d values (+ pad)
+  float* sRed = sSqInv + ((d + 3) & ~3);   // 32*32 block reduction buffer
+  for (int i = threadIdx.x; i < HDp + padn; i += blockDim.x) sShift[i] = (i < HD && shift) ? shift[i] : 0.f;
+  for (int i = threadIdx.x; i < ((d + 3) & ~3); i += blockDim.x)
+    sSqInv[i] = i < d ? (inv_cov ? sqrtf(inv_cov[i]) : 1.f) : 0.f;
   for (int i = threadIdx.x; i < 32 * 32; i += blockDim.x) sRed[i] = 0.f;
   __syncthreads();
 
@@ -77,15 +116,17 @@ wmoments_matnorm_mma_kernel(const float* __restrict__ x, const float* __restrict
   const int64_t nchunks = (ncols + 31) / 32;
   const int64_t wid = (int64_t)blockIdx.x * kMmaWarps + warp, nwarps = (int64_t)gridDim.x * kMmaWarps;
   const float inv_d = 1.0f / (float)d;
+  const bool cols32 = ncols < (int64_t)0x7fffffff;  // 32-bit column arithmetic (no 64-bit division)
 
-  // row offsets (elements) of this thread's 4 row groups; rows >= H are masked
-  int roff[4];
+  // element offsets of this thread's 4 row groups inside a sample / inside the shift table
+  int roff[4], soff[4];
   bool rok[4];
 #pragma unroll
   for (int rg = 0; rg < 4; ++rg) {
     const int i = g + 8 * rg;
     rok[rg] = i < H;
-    roff[rg] = (rok[rg] ? i : 0) * d;
+    roff[rg] = rok[rg] ? i * d : 0;
+    soff[rg] = rok[rg] ? i * d : HDp;  // masked rows: the zero pad behind the table
   }
 
   // tiles: (r,s) = (0,0) (0,1) (0,2) (0,3) (1,2) (1,3)
@@ -95,35 +136,59 @@ wmoments_matnorm_mma_kernel(const float* __restrict__ x, const float* __restrict
 
   for (int64_t ch = wid; ch < nchunks; ch += nwarps) {
     const int64_t c0 = ch * 32;
-    const int64_t b0 = c0 / d;
+    const int64_t b0 = cols32 ? (int64_t)((uint32_t)c0 / (uint32_t)d) : c0 / d;
     const int rel0 = (int)(c0 - b0 * d);
-    // values v[step][rg][4 columns]
-    float v[2][4][4];
+    const int ncol_here = (int)min((int64_t)32, ncols - c0);
+    const float* xb = x + b0 * HD;  // offsets below fit 32 bits: <= (32 / d + 1) HD
+    const float* wb = nw + b0;
+    float dv[2][4][4];              // x - shift, [k-step][row group][4 columns]
+    float fcol[2][4];               // sqrt(nw_b inv_j) per column
     float amax = 0.f;
 #pragma unroll
     for (int st = 0; st < 2; ++st) {
 #pragma unroll
-      for (int cp = 0; cp < 2; ++cp) {    // column pair: 2t (+8)
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          const int lc = 16 * st + 8 * cp + 2 * t + u;
+      for (int cp = 0; cp < 2; ++cp) {  // column pair 2t, 2t+1 (+8)
+        const int lc = 16 * st + 8 * cp + 2 * t;
+        if (VEC2) {
           const int rel = rel0 + lc;
           const int bq = __float2int_rd(((float)rel + 0.5f) * inv_d);
           const int j = rel - bq * d;
-          const int64_t b = b0 + bq;
-          const bool ok = (c0 + lc) < ncols;
-          float f = 0.f;
-          if (ok) {
-            const float w = __ldg(nw + b);
-            f = (w != 0.f) ? sqrtf(w * sInv[j]) : 0.f;
-          }
-          const float* px = x + b * HD + j;
+          const float w = ldg1_if(wb + bq, lc < ncol_here);
+          const float sw = sqrt_fast(w);
+          const float2 si = *reinterpret_cast<const float2*>(sSqInv + j);
+          fcol[st][2 * cp] = sw * si.x;
+          fcol[st][2 * cp + 1] = sw * si.y;
+          const int off = bq * HD + j;
+          float m = 0.f;
 #pragma unroll
           for (int rg = 0; rg < 4; ++rg) {
-            float val = 0.f;
-            if (f != 0.f && rok[rg]) val = (__ldg(px + roff[rg]) - sShift[roff[rg] + j]) * f;
-            v[st][rg][2 * cp + u] = val;
-            amax = fmaxf(amax, fabsf(val));
+            const float2 xv = ldg2_if(xb + off + roff[rg], w != 0.f && rok[rg]);
+            const float2 sv = *reinterpret_cast<const float2*>(sShift + soff[rg] + j);
+            const float d0 = xv.x - sv.x, d1 = xv.y - sv.y;
+            dv[st][rg][2 * cp] = d0;
+            dv[st][rg][2 * cp + 1] = d1;
+            m = fmaxf(m, fmaxf(fabsf(d0) * si.x, fabsf(d1) * si.y));
+          }
+          amax = fmaxf(amax, m * sw);
+        } else {
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int rel = rel0 + lc + u;
+            const int bq = __float2int_rd(((float)rel + 0.5f) * inv_d);
+            const int j = rel - bq * d;
+            const float w = ldg1_if(wb + bq, (lc + u) < ncol_here);
+            const float f = sqrt_fast(w) * sSqInv[j];
+            fcol[st][2 * cp + u] = f;
+            const int off = bq * HD + j;
+            float m = 0.f;
+#pragma unroll
+            for (int rg = 0; rg < 4; ++rg) {
+              const float xv = ldg1_if(xb + off + roff[rg], w != 0.f && rok[rg]);
+              const float d0 = xv - sShift[soff[rg] + j];
+              dv[st][rg][2 * cp + u] = d0;
+              m = fmaxf(m, fabsf(d0));
+            }
+            amax = fmaxf(amax, m * f);
           }
         }
       }
@@ -138,12 +203,16 @@ wmoments_matnorm_mma_kernel(const float* __restrict__ x, const float* __restrict
     for (int q = 0; q < 6; ++q) a1[q][0] = a1[q][1] = a1[q][2] = a1[q][3] = 0.f;
 #pragma unroll
     for (int st = 0; st < 2; ++st) {
+      float fs[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) fs[c] = fcol[st][c] * sc;
       uint32_t h1[4][2], h2[4][2];  // [row group][column pair]
 #pragma unroll
       for (int rg = 0; rg < 4; ++rg)
 #pragma unroll
         for (int cp = 0; cp < 2; ++cp)
-          split_pair(v[st][rg][2 * cp] * sc, v[st][rg][2 * cp + 1] * sc, h1[rg][cp], h2[rg][cp]);
+          split_pair(dv[st][rg][2 * cp] * fs[2 * cp], dv[st][rg][2 * cp + 1] * fs[2 * cp + 1], h1[rg][cp],
+                     h2[rg][cp]);
       // tile q = (r, s): A rows 16r + {g, g+8} -> row groups 2r, 2r+1; B rows 8s + g -> row group s
 #define PPI_TILE(q, r, s)                                                                              \
   mma16816(a1[q], h1[2 * r][0], h1[2 * r + 1][0], h1[2 * r][1], h1[2 * r + 1][1], h1[s][0], h1[s][1]); \
@@ -185,16 +254,25 @@ using namespace ppi;
 // called from moments.cu for H <= 32
 int ppi_wmoments_matnorm_mma(const float* x, const float* nw, int64_t K, int H, int d, const float* shift,
                              const float* inv_cov_out, double* acc, cudaStream_t st) {
-  const size_t smem = ((size_t)H * d + d + 32 * 32) * sizeof(float);
-  PPI_REQUIRE(smem <= 200 * 1024, PPI_ERR_UNSUPPORTED, "ppi_wmoments_matnorm: H=%d d=%d does not fit shared memory", H, d);
-  if (smem > 48 * 1024)
-    PPI_CUDA_TRY(cudaFuncSetAttribute(wmoments_matnorm_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem));
+  const size_t smem = ((size_t)H * d + 2 * (size_t)d + 24 + 32 * 32) * sizeof(float);
+  PPI_REQUIRE(smem <= 200 * 1024, PPI_ERR_UNSUPPORTED,
+              "ppi_wmoments_matnorm: H=%d d=%d does not fit shared memory", H, d);
+  const bool vec2 = (d % 2 == 0) && ((reinterpret_cast<uintptr_t>(x) & 7) == 0);
+  if (smem > 48 * 1024) {
+    PPI_CUDA_TRY(cudaFuncSetAttribute(wmoments_matnorm_mma_kernel<true>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PPI_CUDA_TRY(cudaFuncSetAttribute(wmoments_matnorm_mma_kernel<false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
   const int64_t nchunks = (K * (int64_t)d + 31) / 32;
   int64_t grid = ceil_div(nchunks, (int64_t)kMmaWarps * 4);  // >= 4 chunks per warp
   if (grid > (int64_t)kNumSMs * 2) grid = (int64_t)kNumSMs * 2;
   if (grid < 1) grid = 1;
-  wmoments_matnorm_mma_kernel<<<(unsigned)grid, kMmaWarps * 32, smem, st>>>(x, nw, K, H, d, shift,
-                                                                           inv_cov_out, acc);
+  if (vec2)
+    wmoments_matnorm_mma_kernel<true><<<(unsigned)grid, kMmaWarps * 32, smem, st>>>(x, nw, K, H, d, shift,
+                                                                                   inv_cov_out, acc);
+  else
+    wmoments_matnorm_mma_kernel<false><<<(unsigned)grid, kMmaWarps * 32, smem, st>>>(x, nw, K, H, d, shift,
+                                                                                    inv_cov_out, acc);
   return check_launch("wmoments_matnorm_mma_kernel");
 }
