@@ -247,6 +247,191 @@ wmoments_matnorm_mma_kernel(const float* __restrict__ x, const float* __restrict
   }
 }
 
+
+// ------------------------------------------------------------------------------------------
+// x_b = clip(mean_fn + mean + L_in z_b diag(l_out)),  H <= 32, d <= 32, one warp per sample.
+// (L_in z_b) runs as M = 32 rows x N = d columns x K = 32 contraction rows of mma.sync; the
+// diagonal output factor is applied to the fp32 result in the epilogue, so in Philox mode the B
+// operand is the raw normal, an exact single fp16 (2 products L1 z + L2 z); injected normals are
+// split into an fp16 pair under a per-sample power-of-two scale (3 products).  The warp first
+// builds the sample's z tile in shared memory, TRANSPOSED ([column][row], row stride 40 halves =
+// bank-conflict-free fragment reads), because a B fragment packs two contraction rows per
+// register; the L_in fragments (3 non-zero 16 x 16 blocks of the lower triangle, pair-split under a
+// block-wide scale) stay in registers for the whole kernel.
+// ------------------------------------------------------------------------------------------
+constexpr int kTileStride = 40;              // halves per tile row (column of z)
+constexpr int kTileHalves = 32 * kTileStride;
+
+template <bool PHILOX, bool VEC2>
+__global__ void __launch_bounds__(kMmaWarps * 32)
+sample_matnorm_mma_kernel(const float* __restrict__ z, uint64_t seed, uint64_t draw, uint64_t row_offset,
+                          int64_t K, int H, int d, const float* __restrict__ mean_fn,
+                          const float* __restrict__ mean, const float* __restrict__ l_in,
+                          const float* __restrict__ l_out, const float* __restrict__ lower,
+                          const float* __restrict__ upper, float* __restrict__ x) {
+  extern __shared__ float smem[];
+  const int HD = H * d;
+  float* sBias = smem;                       // HD (+ pad to even)
+  float* sFo = sBias + ((HD + 3) & ~3);      // 32: l_out[j][j]
+  float* sLo = sFo + 32;                     // 32
+  float* sHi = sLo + 32;                     // 32
+  float* sMax = sHi + 32;                    // 32 (block max of |L_in|)
+  __half* sTiles = reinterpret_cast<__half*>(sMax + 32);  // per warp: T1 (and T2 when !PHILOX)
+  constexpr int kTilesPerWarp = PHILOX ? 1 : 2;
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+
+  float lmax = 0.f;
+  for (int i = threadIdx.x; i < HD; i += blockDim.x) sBias[i] = mean_fn[i % d] + mean[i];
+  for (int i = threadIdx.x; i < 32; i += blockDim.x) {
+    sFo[i] = i < d ? l_out[i * d + i] : 0.f;
+    sLo[i] = (lower && i < d) ? lower[i] : -INFINITY;
+    sHi[i] = (upper && i < d) ? upper[i] : INFINITY;
+  }
+  for (int i = threadIdx.x; i < H * H; i += blockDim.x) lmax = fmaxf(lmax, fabsf(l_in[i]));
+  for (int i = threadIdx.x; i < kMmaWarps * kTilesPerWarp * kTileHalves; i += blockDim.x)
+    sTiles[i] = __float2half(0.f);
+  lmax = warp_max(lmax);
+  if (lane == 0) sMax[warp] = lmax;
+  __syncthreads();
+  lmax = 0.f;
+#pragma unroll
+  for (int w = 0; w < kMmaWarps; ++w) lmax = fmaxf(lmax, sMax[w]);
+  const float sL = lmax > 0.f ? chunk_scale(lmax) : 1.f;
+
+  // A fragments of L_in 2^eL: blocks (m,k) = (0,0), (1,0), (1,1)
+  uint32_t A1[3][4], A2[3][4];
+  {
+    const int bm[3] = {0, 1, 1}, bk[3] = {0, 0, 1};
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {  // a0: (g, 2t) a1: (g+8, 2t) a2: (g, 2t+8) a3: (g+8, 2t+8)
+        const int i = 16 * bm[q] + g + 8 * (e & 1), k = 16 * bk[q] + 2 * t + 8 * (e >> 1);
+        const float v0 = (i < H && k < H && k <= i) ? l_in[i * H + k] * sL : 0.f;
+        const float v1 = (i < H && k + 1 < H && k + 1 <= i) ? l_in[i * H + k + 1] * sL : 0.f;
+        split_pair(v0, v1, A1[q][e], A2[q][e]);
+      }
+    }
+  }
+
+  __half* T1 = sTiles + (size_t)warp * kTilesPerWarp * kTileHalves;
+  __half* T2 = T1 + kTileHalves;  // only when !PHILOX
+  const uint32_t* T1w = reinterpret_cast<const uint32_t*>(T1);
+  const uint32_t* T2w = reinterpret_cast<const uint32_t*>(T2);
+  const int nt = (d + 7) >> 3;
+  const float inv_d = 1.0f / (float)d;
+  const int64_t wid = (int64_t)blockIdx.x * kMmaWarps + warp, nwarps = (int64_t)gridDim.x * kMmaWarps;
+
+  for (int64_t b = wid; b < K; b += nwarps) {
+    float inv_scale = 1.f / sL;
+    __syncwarp();  // the previous sample's fragment reads are done
+    if (PHILOX) {
+      const uint64_t e0 = (row_offset + (uint64_t)b) * (uint64_t)HD;
+      const uint64_t q0 = e0 >> 2;
+      const int lead = (int)(e0 & 3);          // elements of the first quad that belong to the previous sample
+      const int nq = (HD + lead + 3) >> 2;
+      for (int qi = lane; qi < nq; qi += 32) {
+        float v[4];
+        philox_normal4(seed, draw, q0 + (uint64_t)qi, v);
+        const int el0 = 4 * qi - lead;
+        int ip = __float2int_rd(((float)max(el0, 0) + 0.5f) * inv_d);
+        int j = max(el0, 0) - ip * d;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int el = el0 + k;
+          if (el >= 0 && el < HD) {
+            T1[j * kTileStride + ip] = __float2half_rn(v[k]);  // exact: Philox normals are half values
+            if (++j == d) { j = 0; ++ip; }
+          }
+        }
+      }
+    } else {
+      const float* zb = z + b * HD;
+      float v[32];
+      float amax = 0.f;
+#pragma unroll
+      for (int it = 0; it < 32; ++it) {
+        const int el = it * 32 + lane;
+        v[it] = el < HD ? __ldg(zb + el) : 0.f;
+        amax = fmaxf(amax, fabsf(v[it]));
+      }
+      amax = warp_max(amax);
+      const float sz = amax > 0.f ? chunk_scale(amax) : 1.f;
+      inv_scale *= 1.f / sz;
+#pragma unroll
+      for (int it = 0; it < 32; ++it) {
+        const int el = it * 32 + lane;
+        if (el < HD) {
+          const int ip = __float2int_rd(((float)el + 0.5f) * inv_d);
+          const int j = el - ip * d;
+          const float vs = v[it] * sz;
+          const __half h1 = __float2half_rn(vs);
+          T1[j * kTileStride + ip] = h1;
+          T2[j * kTileStride + ip] = __float2half_rn(vs - __half2float(h1));
+        }
+      }
+    }
+    __syncwarp();
+
+    float acc[2][4][4];
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+      for (int s = 0; s < 4; ++s) acc[m][s][0] = acc[m][s][1] = acc[m][s][2] = acc[m][s][3] = 0.f;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      if (s < nt) {  // warp-uniform
+        const int w0 = (8 * s + g) * (kTileStride / 2) + t;  // word index of rows (2t, 2t+1) of column 8s+g
+        const uint32_t b00 = T1w[w0], b01 = T1w[w0 + 4], b10 = T1w[w0 + 8], b11 = T1w[w0 + 12];
+        mma16816(acc[0][s], A1[0][0], A1[0][1], A1[0][2], A1[0][3], b00, b01);
+        mma16816(acc[0][s], A2[0][0], A2[0][1], A2[0][2], A2[0][3], b00, b01);
+        mma16816(acc[1][s], A1[1][0], A1[1][1], A1[1][2], A1[1][3], b00, b01);
+        mma16816(acc[1][s], A2[1][0], A2[1][1], A2[1][2], A2[1][3], b00, b01);
+        mma16816(acc[1][s], A1[2][0], A1[2][1], A1[2][2], A1[2][3], b10, b11);
+        mma16816(acc[1][s], A2[2][0], A2[2][1], A2[2][2], A2[2][3], b10, b11);
+        if (!PHILOX) {
+          const uint32_t c00 = T2w[w0], c01 = T2w[w0 + 4], c10 = T2w[w0 + 8], c11 = T2w[w0 + 12];
+          mma16816(acc[0][s], A1[0][0], A1[0][1], A1[0][2], A1[0][3], c00, c01);
+          mma16816(acc[1][s], A1[1][0], A1[1][1], A1[1][2], A1[1][3], c00, c01);
+          mma16816(acc[1][s], A1[2][0], A1[2][1], A1[2][2], A1[2][3], c10, c11);
+        }
+      }
+    }
+
+    // epilogue: D fragment (rows 16m + g (+8), columns 8s + 2t (+1)) -> bias, factor, clip, store
+    float* xb = x + b * HD;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const int j0 = 8 * s + 2 * t;
+      if (s < nt && j0 < d) {
+        const bool two = j0 + 1 < d;
+        const float f0 = sFo[j0] * inv_scale, f1 = sFo[j0 + 1] * inv_scale;
+        const float lo0 = sLo[j0], lo1 = sLo[j0 + 1], hi0 = sHi[j0], hi1 = sHi[j0 + 1];
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const int i = 16 * m + g + 8 * hh;
+            if (i < H) {
+              const int o = i * d + j0;
+              const float v0 = clipf(fmaf(acc[m][s][2 * hh], f0, sBias[o]), lo0, hi0);
+              if (VEC2) {
+                const float v1 = clipf(fmaf(acc[m][s][2 * hh + 1], f1, sBias[o + 1]), lo1, hi1);
+                *reinterpret_cast<float2*>(xb + o) = make_float2(v0, v1);
+              } else {
+                xb[o] = v0;
+                if (two) xb[o + 1] = clipf(fmaf(acc[m][s][2 * hh + 1], f1, sBias[o + 1]), lo1, hi1);
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
 }  // namespace ppi
 
 using namespace ppi;
@@ -275,4 +460,29 @@ int ppi_wmoments_matnorm_mma(const float* x, const float* nw, int64_t K, int H, 
     wmoments_matnorm_mma_kernel<false><<<(unsigned)grid, kMmaWarps * 32, smem, st>>>(x, nw, K, H, d, shift,
                                                                                     inv_cov_out, acc);
   return check_launch("wmoments_matnorm_mma_kernel");
+}
+
+// called from sample.cu for H <= 32, d <= 32, diagonal l_out
+int ppi_sample_matnorm_mma(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset, int64_t K,
+                           int H, int d, const float* mean_fn, const float* mean, const float* l_in,
+                           const float* l_out, const float* lower, const float* upper, float* x,
+                           cudaStream_t st) {
+  const size_t tiles = (size_t)kMmaWarps * (z ? 2 : 1) * kTileHalves * sizeof(__half);
+  const size_t smem = ((((size_t)H * d + 3) & ~(size_t)3) + 4 * 32) * sizeof(float) + tiles;
+  const bool vec2 = (d % 2 == 0) && ((reinterpret_cast<uintptr_t>(x) & 7) == 0);
+  int64_t grid = ceil_div(K, (int64_t)kMmaWarps * 2);  // >= 2 samples per warp
+  if (grid > (int64_t)kNumSMs * 2) grid = (int64_t)kNumSMs * 2;
+  if (grid < 1) grid = 1;
+#define PPI_LAUNCH_SMM(P, V)                                                                            \
+  do {                                                                                                  \
+    if (smem > 48 * 1024)                                                                               \
+      PPI_CUDA_TRY(cudaFuncSetAttribute(sample_matnorm_mma_kernel<P, V>,                                \
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
+    sample_matnorm_mma_kernel<P, V><<<(unsigned)grid, kMmaWarps * 32, smem, st>>>(                      \
+        z, seed, draw_id, row_offset, K, H, d, mean_fn, mean, l_in, l_out, lower, upper, x);            \
+  } while (0)
+  if (z == nullptr) { if (vec2) PPI_LAUNCH_SMM(true, true); else PPI_LAUNCH_SMM(true, false); }
+  else              { if (vec2) PPI_LAUNCH_SMM(false, true); else PPI_LAUNCH_SMM(false, false); }
+#undef PPI_LAUNCH_SMM
+  return check_launch("sample_matnorm_mma_kernel");
 }

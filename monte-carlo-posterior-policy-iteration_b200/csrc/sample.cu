@@ -417,6 +417,12 @@ static int grid_for(int64_t work_items, int per_sm) {
 
 using namespace ppi;
 
+// mma_small.cu
+int ppi_sample_matnorm_mma(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset, int64_t K,
+                           int H, int d, const float* mean_fn, const float* mean, const float* l_in,
+                           const float* l_out, const float* lower, const float* upper, float* x,
+                           cudaStream_t st);
+
 extern "C" int ppi_philox_normal(float* out, int64_t rows, int64_t cols, uint64_t seed,
                                  uint64_t draw_id, uint64_t row_offset, void* stream) {
   PPI_REQUIRE(out && rows >= 0 && cols > 0, PPI_ERR_INVALID, "ppi_philox_normal: bad arguments");
@@ -470,6 +476,11 @@ extern "C" int ppi_sample_matnorm(const float* z, uint64_t seed, uint64_t draw_i
   PPI_REQUIRE((lower == nullptr) == (upper == nullptr), PPI_ERR_INVALID,
               "lower and upper must both be given or both be NULL");
   if (K == 0) return 0;
+  if (H <= 32 && d <= 32 && l_out_is_diag) {  // warp-level tensor-core kernel (mma_small.cu)
+    ProfileScope prof(PPI_PROF_SAMPLE_SMALL, (cudaStream_t)stream);
+    return ppi_sample_matnorm_mma(z, seed, draw_id, row_offset, K, H, d, mean_fn, mean, l_in, l_out, lower,
+                                  upper, x, (cudaStream_t)stream);
+  }
   const size_t fixed = ((size_t)H * H + (size_t)d * d + (size_t)H * d) * sizeof(float);
   auto need = [&](int S) { return fixed + 2 * (size_t)S * H * d * sizeof(float); };
   cudaStream_t st = (cudaStream_t)stream;
