@@ -254,12 +254,21 @@ wmoments_matnorm_mma_kernel(const float* __restrict__ x, const float* __restrict
 // diagonal output factor is applied to the fp32 result in the epilogue, so in Philox mode the B
 // operand is the raw normal, an exact single fp16 (2 products L1 z + L2 z); injected normals are
 // split into an fp16 pair under a per-sample power-of-two scale (3 products).  The warp first
-// builds the sample's z tile in shared memory, TRANSPOSED ([column][row], row stride 40 halves =
-// bank-conflict-free fragment reads), because a B fragment packs two contraction rows per
-// register; the L_in fragments (3 non-zero 16 x 16 blocks of the lower triangle, pair-split under a
+// builds the sample's z tile in shared memory ([row][column] halves, row stride 40 halves = 80 B:
+// 16-byte aligned, conflict-free rows for ldmatrix); the B fragments, which pack two contraction
+// rows per register, come out of ldmatrix.x4.trans, one instruction per 8 output columns; the L_in
+// fragments (3 non-zero 16 x 16 blocks of the lower triangle, pair-split under a
 // block-wide scale) stay in registers for the whole kernel.
 // ------------------------------------------------------------------------------------------
-constexpr int kTileStride = 40;              // halves per tile row (column of z)
+// B fragments of one 8-column tile for both k-steps: four 8 x 8 (k x n) blocks, transposed on the fly
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2,
+                                                  uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr));
+}
+
+constexpr int kTileStride = 40;              // halves per tile row (contraction row i' of z)
 constexpr int kTileHalves = 32 * kTileStride;
 
 template <bool PHILOX, bool VEC2>
@@ -318,8 +327,11 @@ sample_matnorm_mma_kernel(const float* __restrict__ z, uint64_t seed, uint64_t d
 
   __half* T1 = sTiles + (size_t)warp * kTilesPerWarp * kTileHalves;
   __half* T2 = T1 + kTileHalves;  // only when !PHILOX
-  const uint32_t* T1w = reinterpret_cast<const uint32_t*>(T1);
-  const uint32_t* T2w = reinterpret_cast<const uint32_t*>(T2);
+  // ldmatrix row address of this lane: block lane / 8 (contraction rows 8 blk ..), row lane % 8
+  const uint32_t ld1 = (uint32_t)__cvta_generic_to_shared(T1 + lane * kTileStride);
+  const uint32_t ld2 = (uint32_t)__cvta_generic_to_shared(T2 + lane * kTileStride);
+  const PhiloxKeys keys = philox_keys(seed);
+  const bool quad_rows = (d & 3) == 0;
   const int nt = (d + 7) >> 3;
   const float inv_d = 1.0f / (float)d;
   const int64_t wid = (int64_t)blockIdx.x * kMmaWarps + warp, nwarps = (int64_t)gridDim.x * kMmaWarps;
@@ -334,16 +346,22 @@ sample_matnorm_mma_kernel(const float* __restrict__ z, uint64_t seed, uint64_t d
       const int nq = (HD + lead + 3) >> 2;
       for (int qi = lane; qi < nq; qi += 32) {
         float v[4];
-        philox_normal4(seed, draw, q0 + (uint64_t)qi, v);
+        philox_normal4(keys, draw, q0 + (uint64_t)qi, v);
         const int el0 = 4 * qi - lead;
         int ip = __float2int_rd(((float)max(el0, 0) + 0.5f) * inv_d);
         int j = max(el0, 0) - ip * d;
+        if (quad_rows) {  // d % 4 == 0: a quad never straddles a row and is 8-byte aligned in the tile
+          const __half2 p0 = __floats2half2_rn(v[0], v[1]), p1 = __floats2half2_rn(v[2], v[3]);  // exact
+          *reinterpret_cast<uint2*>(T1 + ip * kTileStride + j) =
+              make_uint2(*reinterpret_cast<const uint32_t*>(&p0), *reinterpret_cast<const uint32_t*>(&p1));
+        } else {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const int el = el0 + k;
-          if (el >= 0 && el < HD) {
-            T1[j * kTileStride + ip] = __float2half_rn(v[k]);  // exact: Philox normals are half values
-            if (++j == d) { j = 0; ++ip; }
+          for (int k = 0; k < 4; ++k) {
+            const int el = el0 + k;
+            if (el >= 0 && el < HD) {
+              T1[ip * kTileStride + j] = __float2half_rn(v[k]);  // exact: Philox normals are half values
+              if (++j == d) { j = 0; ++ip; }
+            }
           }
         }
       }
@@ -368,8 +386,8 @@ sample_matnorm_mma_kernel(const float* __restrict__ z, uint64_t seed, uint64_t d
           const int j = el - ip * d;
           const float vs = v[it] * sz;
           const __half h1 = __float2half_rn(vs);
-          T1[j * kTileStride + ip] = h1;
-          T2[j * kTileStride + ip] = __float2half_rn(vs - __half2float(h1));
+          T1[ip * kTileStride + j] = h1;
+          T2[ip * kTileStride + j] = __float2half_rn(vs - __half2float(h1));
         }
       }
     }
@@ -383,8 +401,8 @@ sample_matnorm_mma_kernel(const float* __restrict__ z, uint64_t seed, uint64_t d
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
       if (s < nt) {  // warp-uniform
-        const int w0 = (8 * s + g) * (kTileStride / 2) + t;  // word index of rows (2t, 2t+1) of column 8s+g
-        const uint32_t b00 = T1w[w0], b01 = T1w[w0 + 4], b10 = T1w[w0 + 8], b11 = T1w[w0 + 12];
+        uint32_t b00, b01, b10, b11;  // rows (2t, 2t+1) + {0, 8, 16, 24} of column 8s + g
+        ldmatrix_x4_trans(ld1 + 16u * s, b00, b01, b10, b11);
         mma16816(acc[0][s], A1[0][0], A1[0][1], A1[0][2], A1[0][3], b00, b01);
         mma16816(acc[0][s], A2[0][0], A2[0][1], A2[0][2], A2[0][3], b00, b01);
         mma16816(acc[1][s], A1[1][0], A1[1][1], A1[1][2], A1[1][3], b00, b01);
@@ -392,7 +410,8 @@ sample_matnorm_mma_kernel(const float* __restrict__ z, uint64_t seed, uint64_t d
         mma16816(acc[1][s], A1[2][0], A1[2][1], A1[2][2], A1[2][3], b10, b11);
         mma16816(acc[1][s], A2[2][0], A2[2][1], A2[2][2], A2[2][3], b10, b11);
         if (!PHILOX) {
-          const uint32_t c00 = T2w[w0], c01 = T2w[w0 + 4], c10 = T2w[w0 + 8], c11 = T2w[w0 + 12];
+          uint32_t c00, c01, c10, c11;
+          ldmatrix_x4_trans(ld2 + 16u * s, c00, c01, c10, c11);
           mma16816(acc[0][s], A1[0][0], A1[0][1], A1[0][2], A1[0][3], c00, c01);
           mma16816(acc[1][s], A1[1][0], A1[1][1], A1[1][2], A1[1][3], c00, c01);
           mma16816(acc[1][s], A1[2][0], A1[2][1], A1[2][2], A1[2][3], c10, c11);

@@ -37,31 +37,38 @@ wmoments_diag_kernel(const float* __restrict__ x, const float* __restrict__ nw, 
     d1[v] = d2[v] = 0.0;
   }
   if (active) {
+    constexpr int UB = 8;  // rows in flight per thread: loads of a batch are issued before any use
     for (int64_t rb = r0 + rl; rb < r1; rb += (int64_t)nrl * 64) {
       float f1[VEC], f2[VEC];
 #pragma unroll
       for (int v = 0; v < VEC; ++v) f1[v] = f2[v] = 0.f;
-#pragma unroll 4
-      for (int it = 0; it < 64; ++it) {
-        const int64_t r = rb + (int64_t)it * nrl;
-        if (r >= r1) break;
-        const float w = __ldg(nw + r);
-        float xv[VEC];
-        if (VEC == 4) {
-          const float4 t = __ldg(reinterpret_cast<const float4*>(x + r * D) + cg);
-          xv[0] = t.x; xv[1] = t.y; xv[2] = t.z; xv[3] = t.w;
-        } else {
-          xv[0] = __ldg(x + r * D + cg);
-        }
-        if (w != 0.f) {  // zero-weight rows (NaN rollouts) may hold non-finite samples
+      const int nrows = (int)min((int64_t)64, (r1 - rb + nrl - 1) / nrl);
+      for (int it0 = 0; it0 < nrows; it0 += UB) {
+        float w[UB], xv[UB][VEC];
 #pragma unroll
-          for (int v = 0; v < VEC; ++v) {
-            const float d0 = xv[v] - a[v];
-            dev = fmaxf(dev, fabsf(d0));
-            f1[v] = fmaf(w, d0, f1[v]);
-            if (SECOND) {
-              const float dv = xv[v] - b[v];
-              f2[v] = fmaf(w * dv, dv, f2[v]);
+        for (int u = 0; u < UB; ++u) {
+          const bool ok = it0 + u < nrows;
+          const int64_t r = ok ? rb + (int64_t)(it0 + u) * nrl : rb;
+          w[u] = ok ? __ldg(nw + r) : 0.f;
+          if (VEC == 4) {
+            const float4 t = __ldg(reinterpret_cast<const float4*>(x + r * D) + cg);
+            xv[u][0] = t.x; xv[u][1] = t.y; xv[u][2] = t.z; xv[u][3] = t.w;
+          } else {
+            xv[u][0] = __ldg(x + r * D + cg);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+          if (w[u] != 0.f) {  // zero-weight rows (NaN rollouts) may hold non-finite samples
+#pragma unroll
+            for (int v = 0; v < VEC; ++v) {
+              const float d0 = xv[u][v] - a[v];
+              dev = fmaxf(dev, fabsf(d0));
+              f1[v] = fmaf(w[u], d0, f1[v]);
+              if (SECOND) {
+                const float dv = xv[u][v] - b[v];
+                f2[v] = fmaf(w[u] * dv, dv, f2[v]);
+              }
             }
           }
         }

@@ -525,6 +525,7 @@ extern "C" int ppi_sample_features(const float* z, uint64_t seed, uint64_t draw_
   gx = (int)ceil_div(gx, ty);
   if (gx < 1) gx = 1;
   dim3 grid(gx, ty);
+  ProfileScope prof(PPI_PROF_SAMPLE_SMALL, (cudaStream_t)stream);
   sample_features_kernel<S><<<grid, 256, smem, (cudaStream_t)stream>>>(
       z, seed, draw_id, row_offset, K, F, d, T, mean_fn, mean, l_in, l_out, feat, dfeat, lower, upper,
       w, y);

@@ -744,6 +744,7 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
   const float scale = (src && scale_ptr) ? *scale_ptr : 1.f;
   const int nq_row = (int)(cols_p / 4);
   const bool quad_rng = (cols & 3) == 0;
+  const PhiloxKeys keys = philox_keys(seed);
   // one row per block iteration; threads stride over the row's quads (no 64-bit divisions)
   for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
     const uint64_t e_row = (row_offset + (uint64_t)r) * (uint64_t)cols;
@@ -761,7 +762,7 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
             if (c + u < cols && (!lower_only || c + u <= r)) v[u] = scale * __ldg(src + r * cols + c + u);
         }
       } else if (quad_rng) {
-        if (c < cols) philox_normal4(seed, draw, (e_row + (uint64_t)c) >> 2, v);
+        if (c < cols) philox_normal4(keys, draw, (e_row + (uint64_t)c) >> 2, v);
       } else {
 #pragma unroll
         for (int u = 0; u < 4; ++u)
