@@ -49,7 +49,7 @@ WORKLOADS = {
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
 # `ncu --set full` capture under profiles/ (see profiles/README.md); keyed by (kernel, D).
-NCU_TRAFFIC = {("syrk", 2048): 541.2e6}  # profiles/r1_gemm_ncu_full_summary.csv (537.0 MB read + 4.2 MB written)
+NCU_TRAFFIC = {("syrk_pair", 2048): 541.2e6}  # profiles/r1_gemm_ncu_full_summary.csv (537.0 MB read + 4.2 MB written)
 
 
 def peaks():
@@ -270,6 +270,8 @@ def run_b200(args, wl):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
+    if args.overlap is not None:
+        _lib.call("ppi_set_option", _lib.OPT_GEMM_OVERLAP, args.overlap)
 
     def barrier():
         if world > 1:
@@ -354,16 +356,22 @@ def run_b200(args, wl):
         algorithmic = 2.0 * rows_per_launch * D * D        # 2 D^2 useful flops per sample
         t = tot_ms / n * 1e-3
         scheme = lib.ppi_get_option(_lib.OPT_GEMM_SCHEME)
+        # the policy's own Philox draws take the whitened path: A = nw z (fp16 pair) x B = z (exact fp16)
+        white = scheme == _lib.GEMM_FP16X2
+        products = 2 if white else 3
+        name = ("syrk_gemm_kernel<PAIR_SINGLE> (tcgen05 kind::f16, whitened moments: nw z as an fp16 pair x "
+                "exact fp16 z, 2 partial products)" if white else "syrk_gemm_kernel<TF32X3> (tcgen05 kind::tf32)")
         roofline = {
-            "kernel": "syrk_gemm_kernel<FP16X2> (tcgen05 kind::f16, 3 partial products of fp16 pairs)"
-                      if scheme == _lib.GEMM_FP16X2 else "syrk_gemm_kernel<TF32X3> (tcgen05 kind::tf32)",
+            "kernel": name,
             "bound": "tensor", "achieved": algorithmic / t / 1e12, "peak": pk["bf16"], "unit": "TFLOP/s",
-            "frac": algorithmic / t / 1e12 / pk["bf16"], "traffic": NCU_TRAFFIC.get(("syrk", wl["D"])),
+            "frac": algorithmic / t / 1e12 / pk["bf16"],
+            "traffic": NCU_TRAFFIC.get(("syrk_white" if white else "syrk_pair", wl["D"])),
             "peak_source": f"dense 16-bit tensor peak, sustained, {pk['source']}",
             "algorithmic_flops_per_launch": algorithmic,
-            "executed_tflops": executed_syrk_flops(rows_per_launch, D) / t / 1e12,
-            "executed_note": "MMA flops actually issued: 3 partial products on the 72 upper-triangular "
-                             "128x256 tiles; executed / peak is the tensor-pipe utilisation",
+            "executed_tflops": executed_syrk_flops(rows_per_launch, D, products) / t / 1e12,
+            "executed_note": f"MMA flops actually issued: {products} partial products on the upper-triangular "
+                             "128x256 tiles (72 of 64 tile-equivalents at D = 2048); executed / peak is the "
+                             "tensor-pipe utilisation",
             "launches": n, "avg_launch_ms": tot_ms / n,
             "share_of_step": tot_ms / (ms_per_step * args.steps),
         }
@@ -394,8 +402,8 @@ def run_b200(args, wl):
         "metric": "PPI update samples/sec", "value": value, "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "dtype_note": "fp32 samples and results; dense products on tcgen05 as exact fp16-pair partial products "
-                      "with fp32 accumulation; fp64 scalars in the temperature solve and small-matrix tails",
+        "dtype_note": "fp32 samples and results; dense products on tcgen05 as exact fp16 / fp16-pair partial "
+                      "products with fp32 accumulation; fp64 scalars in the temperature solve and D x D tails",
         "data": "synthetic",
         "config": {"workload": wl["desc"], "samples_per_gpu": wl["K"], "samples_total": K_total,
                    "elements_per_s": value * (wl.get("D") or wl.get("H", 21) * wl["d"]),
@@ -411,12 +419,12 @@ def run_b200(args, wl):
         dist.destroy_process_group()
 
 
-def executed_syrk_flops(rows, D):
-    """MMA flops actually issued: 3 products on the upper-triangular 128 x 256 tiles."""
+def executed_syrk_flops(rows, D, products=3):
+    """MMA flops actually issued: `products` partial products on the upper-triangular 128 x 256 tiles."""
     dp = (D + 127) // 128 * 128
     tiles_n = (dp + 255) // 256
     ntiles = sum(tiles_n - (tm * 128) // 256 for tm in range(dp // 128))
-    return 3 * 2.0 * rows * ntiles * 128 * 256
+    return products * 2.0 * rows * ntiles * 128 * 256
 
 
 def _claim_stdout():
@@ -447,6 +455,8 @@ def main():
     ap.add_argument("--workload", default="C5", choices=sorted(WORKLOADS))
     ap.add_argument("--samples", type=int, default=None, help="samples per GPU (overrides the workload's K)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--overlap", type=int, default=None, choices=[0, 1],
+                    help="override PPI_OPT_GEMM_OVERLAP (operand staging on a side stream)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     if args.samples:

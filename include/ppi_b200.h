@@ -124,6 +124,17 @@ int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_id, uint64_
                         int64_t K, int64_t D, const float* mu, const float* L, float* x,
                         void* workspace, size_t workspace_bytes, void* stream);
 
+/* a7 + a16  the same draw, keeping the base normals for the whitened moment match below.
+ * zstore (caller-owned, 1 KB aligned, ppi_zstore_bytes(K, D, z != NULL) bytes) receives a 1 KB header
+ * (operand scales of this call) and the K rows of base normals as tensor-core operands: one exact
+ * fp16 per value for Philox normals, an fp16 pair (scaled by a power of two) for injected ones.
+ * D > 128 and PPI_GEMM_FP16X2 only.  x is written exactly as by ppi_sample_gaussian.         */
+size_t ppi_zstore_bytes(int64_t K, int64_t D, int injected);
+int ppi_sample_gaussian_keep(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
+                             int64_t K, int64_t D, const float* mu, const float* L, float* x,
+                             void* zstore, size_t zstore_bytes, void* workspace,
+                             size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * a9  cost evaluation                                     optimization/functions.py:21-104
  * fn: 0 Himmelblau, 1 Rosenbrock, 2 Styblinski, 3 Rastrigin, 4 NoisySphere (aux = A (D,D),
@@ -223,6 +234,21 @@ int ppi_wmoments_matnorm(const float* x, const float* nw, int64_t K, int H, int 
 size_t ppi_wmoments_dense_workspace_bytes(int64_t K, int64_t D);
 int ppi_wmoments_dense(const float* x, const float* nw, int64_t K, int64_t D, const float* shift,
                        const float* dev_bound, float* cov, int accumulate, void* workspace,
+                       size_t workspace_bytes, void* stream);
+
+/* a16 in whitened coordinates                                       ppi/policies.py:84-92
+ * For the samples x_k = mu + L z_k of ppi_sample_gaussian_keep the M-projection factorises:
+ *   sum_k nw_k x_k = mu + L m,                       m = sum_k nw_k z_k
+ *   sum_k nw_k (x_k - mu_new)(x_k - mu_new)^T = L (S - m m^T) L^T,   S = sum_k nw_k z_k z_k^T
+ * so the K-long contraction runs on the stored base normals: operand A = nw z (fp16 pair), operand
+ * B = z -- one exact fp16 for Philox normals, i.e. two partial products instead of three and no
+ * pass over x.  s1 (D, fp64, zeroed by the caller) += m;  cov (D,D) receives S symmetrised (+= when
+ * accumulate != 0).  K-sharded ranks all-reduce both.  `injected` must match the store.
+ * The caller finishes with D x D algebra: chol(new sigma) = L chol(S - m m^T),
+ * KL(new || old) = (tr(C) + |m|^2 - D - log det C) / 2 with C = S - m m^T.                   */
+size_t ppi_wmoments_white_workspace_bytes(int64_t K, int64_t D, int injected);
+int ppi_wmoments_white(const void* zstore, int injected, const float* nw, int64_t K, int64_t D,
+                       double* s1, float* cov, int accumulate, void* workspace,
                        size_t workspace_bytes, void* stream);
 
 /* a17 tail: sigma = cov - delta delta^T (delta = new mean - shift), optional factorized() and

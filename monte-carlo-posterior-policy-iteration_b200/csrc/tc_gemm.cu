@@ -287,16 +287,25 @@ struct SyrkParams {
   int accumulate;    // partial += acc
 };
 
-template <bool FP16>
+// MODE (one "k-unit" = one pipeline stage):
+//   SYRK_TF32X3       unit = 32 steps: A_hi | A_lo | B_hi | B_lo (fp32 rows),               2 stages
+//   SYRK_PAIR         unit = 32 steps: A pair (16 KB) | B pair (32 KB),                      4 stages
+//   SYRK_PAIR_SINGLE  unit = 64 steps: A pair x2 (32 KB) | B exact single fp16 (32 KB),      3 stages
+//                     (whitened moments: A = nw z as a pair, B = z, 2 partial products)
+enum { SYRK_TF32X3 = 0, SYRK_PAIR = 1, SYRK_PAIR_SINGLE = 2 };
+
+template <int MODE>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 syrk_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_a2,
                  const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_b2,
                  const SyrkParams p) {
-  // FP16: stage = A pair (16 KB) | B pair (32 KB), 4 stages.  TF32X3: A_hi | A_lo | B_hi | B_lo, 2 stages.
-  constexpr int kStages = FP16 ? 4 : 2;
-  constexpr uint32_t kStageBytes = FP16 ? (kABytes + kBBytes) : 2 * (kABytes + kBBytes);
+  constexpr bool FP16 = MODE != SYRK_TF32X3;
+  constexpr bool kSingle = MODE == SYRK_PAIR_SINGLE;
+  constexpr int kStages = kSingle ? 3 : (FP16 ? 4 : 2);
+  constexpr uint32_t kStageBytes = kSingle ? (2 * kABytes + kBBytes)
+                                           : (FP16 ? (kABytes + kBBytes) : 2 * (kABytes + kBBytes));
   static_assert(kStages * kStageBytes == kPipeBytes, "pipeline must fill the smem budget");
-  constexpr int kx = FP16 ? 2 * BK : BK;  // elements per k-block in the operand array
+  constexpr int kx = FP16 ? 2 * BK : BK;  // elements per 32-step k-block in a pair / fp32 operand array
 
   extern __shared__ uint8_t smem_raw[];
   GemmSmem gs;
@@ -333,7 +342,11 @@ syrk_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         mbar_wait(gs.empty_bar(stage), phase ^ 1u);
         const uint32_t sb = gs.base + stage * kStageBytes;
         mbar_expect_tx(gs.full_bar(stage), kStageBytes);
-        if (FP16) {
+        if (kSingle) {
+          tma_load_2d(sb, &map_a, gs.full_bar(stage), (2 * kb) * kx, tm * BM);
+          tma_load_2d(sb + kABytes, &map_a, gs.full_bar(stage), (2 * kb + 1) * kx, tm * BM);
+          tma_load_2d(sb + 2 * kABytes, &map_b, gs.full_bar(stage), kb * 64, tn * BN);  // 64 exact fp16 per row
+        } else if (FP16) {
           tma_load_2d(sb, &map_a, gs.full_bar(stage), kb * kx, tm * BM);
           tma_load_2d(sb + kABytes, &map_b, gs.full_bar(stage), kb * kx, tn * BN);
         } else {
@@ -362,8 +375,14 @@ syrk_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           mbar_wait(gs.full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sb = gs.base + stage * kStageBytes;
-          if (FP16) issue_f16_pair_pair(tmem_d, sb, sb + kABytes, accumulate);
-          else issue_tf32x3(tmem_d, sb, accumulate, true, true);
+          if (kSingle) {
+            issue_f16_pair_single(tmem_d, sb, sb + 2 * kABytes, 0, accumulate);
+            issue_f16_pair_single(tmem_d, sb + kABytes, sb + 2 * kABytes, 1, accumulate);
+          } else if (FP16) {
+            issue_f16_pair_pair(tmem_d, sb, sb + kABytes, accumulate);
+          } else {
+            issue_tf32x3(tmem_d, sb, accumulate, true, true);
+          }
           tc_commit(gs.empty_bar(stage));  // frees the smem stage once these MMAs retire
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
@@ -838,6 +857,7 @@ static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t kp,
 }
 
 static int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+static size_t zstore_row_bytes(int64_t D, int injected) { return (size_t)round_up(D, 64) * (injected ? 4 : 2); }
 static int grid_cap(int64_t work, int per_sm) {
   const int64_t cap = (int64_t)kNumSMs * per_sm;
   return (int)(work < 1 ? 1 : (work < cap ? work : cap));
@@ -970,7 +990,7 @@ static int wmoments_dense_impl(const float* x, const float* nw, int64_t K, int64
 
   static bool attr_set = false;
   if (!attr_set) {
-    if (int rc = set_gemm_smem(syrk_gemm_kernel<FP16>)) return rc;
+    if (int rc = set_gemm_smem(syrk_gemm_kernel<FP16 ? SYRK_PAIR : SYRK_TF32X3>)) return rc;
     attr_set = true;
   }
   SideStream* ss = nullptr;
@@ -999,7 +1019,7 @@ static int wmoments_dense_impl(const float* x, const float* nw, int64_t K, int64
     p.accumulate = pass > 0;
     {
       ProfileScope prof(PPI_PROF_SYRK_GEMM, st);
-      syrk_gemm_kernel<FP16><<<(unsigned)(pl.ntiles * pl.splits), kGemmThreads, kGemmSmemBytes, st>>>(
+      syrk_gemm_kernel<FP16 ? SYRK_PAIR : SYRK_TF32X3><<<(unsigned)(pl.ntiles * pl.splits), kGemmThreads, kGemmSmemBytes, st>>>(
           a[bi], a2[bi], b[bi], b2[bi], p);
       if (int rc = check_launch("syrk_gemm_kernel")) return rc;
     }
@@ -1027,6 +1047,195 @@ extern "C" int ppi_wmoments_dense(const float* x, const float* nw, int64_t K, in
                                     (cudaStream_t)stream);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Whitened moment match.  The samples of ppi_sample_gaussian_keep are x_k = mu + L z_k, so
+//   sum_k nw_k x_k                    = mu + L m,          m = sum_k nw_k z_k
+//   sum_k nw_k (x_k - mu')(x_k - mu')^T = L (S - m m^T) L^T,  S = sum_k nw_k z_k z_k^T
+// and the contraction runs on the stored base normals instead of x: operand A = nw z (fp16 pair),
+// operand B = z, which for Philox normals is ONE exact fp16 -- two partial products instead of
+// three, 2 bytes per value read instead of 4, no pass over x at all.
+// ---------------------------------------------------------------------------------------------
+constexpr float kPhiloxAbsMax = 8.0f;  // |Box-Muller normal| <= sqrt(-2 ln 2^-33) = 6.8 (common.cuh)
+
+// whitened operand scale: A = nw z;  injected normals are stored scaled by zs->scale_b
+__global__ void white_scale_kernel(GemmScalars* s, const GemmScalars* zs, int injected) {
+  const float wmax = __uint_as_float(s->amax_a_bits);
+  const float zmax = injected ? __uint_as_float(zs->amax_b_bits) : kPhiloxAbsMax;
+  const float sa = pow2_scale(wmax * zmax);
+  const float sb = injected ? zs->scale_b : 1.f;
+  s->scale_a = sa;
+  s->scale_b = sb;
+  s->inv_scale = (1.f / sa) * (1.f / sb);
+}
+
+// One block = `tiles` consecutive 32-sample tiles x 128 columns of the store rows of this pass:
+//   op_a[i][k] = scale_a nw_k z_ki  (pair, K-major)     op_b[i][k] = z_ki as stored (single / pair)
+//   s1[i] += sum_k nw_k z_ki        (fp64, one atomic per column per block)
+template <bool ZPAIR>
+__global__ void __launch_bounds__(256)
+white_operand_kernel(const uint16_t* __restrict__ zrows, const float* __restrict__ nw,
+                     int64_t rows_valid, int64_t Dk, int64_t Kc, int64_t Dp, int tiles,
+                     const GemmScalars* __restrict__ scalars, void* __restrict__ op_a,
+                     void* __restrict__ op_b, double* __restrict__ s1, int64_t D) {
+  __shared__ float tile[32][129];
+  __shared__ float wsc[32];
+  const float sa = scalars->scale_a;
+  const float unz = 1.f / scalars->scale_b;         // undoes the scale of stored injected normals (1 for Philox)
+  const int64_t it = (int64_t)blockIdx.y * 128;     // column offset
+  const int64_t row_halfs = ZPAIR ? 2 * Dk : Dk;
+  double colsum = 0.0;
+  for (int tl = 0; tl < tiles; ++tl) {
+    const int64_t kt = ((int64_t)blockIdx.x * tiles + tl) * 32;  // local sample offset in the pass
+    if (kt >= Kc) break;
+    if (threadIdx.x < 32) {
+      const int64_t k = kt + threadIdx.x;
+      wsc[threadIdx.x] = k < rows_valid ? __ldg(nw + k) * sa * unz : 0.f;
+    }
+    for (int e = threadIdx.x; e < 32 * 32; e += 256) {
+      const int r = e / 32, c4 = (e % 32) * 4;
+      const int64_t k = kt + r, i = it + c4;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (k < rows_valid && i < Dk) {
+        const uint16_t* row = zrows + k * row_halfs;
+        if (ZPAIR) {
+          const uint16_t* b = row + (i >> 5) * 64 + (i & 31);
+          const uint2 h1 = __ldg(reinterpret_cast<const uint2*>(b));
+          const uint2 h2 = __ldg(reinterpret_cast<const uint2*>(b + 32));
+          const float2 a0 = __half22float2(*reinterpret_cast<const __half2*>(&h1.x));
+          const float2 a1 = __half22float2(*reinterpret_cast<const __half2*>(&h1.y));
+          const float2 b0 = __half22float2(*reinterpret_cast<const __half2*>(&h2.x));
+          const float2 b1 = __half22float2(*reinterpret_cast<const __half2*>(&h2.y));
+          v[0] = a0.x + b0.x; v[1] = a0.y + b0.y; v[2] = a1.x + b1.x; v[3] = a1.y + b1.y;  // exact
+        } else {
+          const uint2 h = __ldg(reinterpret_cast<const uint2*>(row + i));
+          const float2 a0 = __half22float2(*reinterpret_cast<const __half2*>(&h.x));
+          const float2 a1 = __half22float2(*reinterpret_cast<const __half2*>(&h.y));
+          v[0] = a0.x; v[1] = a0.y; v[2] = a1.x; v[3] = a1.y;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) tile[r][c4 + u] = v[u];
+    }
+    __syncthreads();
+    if (threadIdx.x < 128) {
+      float cs = 0.f;
+#pragma unroll 8
+      for (int r = 0; r < 32; ++r) cs = fmaf(wsc[r], tile[r][threadIdx.x], cs);
+      colsum += (double)cs;
+    }
+    for (int e = threadIdx.x; e < 128 * 8; e += 256) {
+      const int il = e / 8, k4 = (e % 8) * 4;
+      const int64_t i = it + il;
+      if (i >= Dp) continue;
+      float v[4], wv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        v[u] = tile[k4 + u][il];
+        wv[u] = v[u] * wsc[k4 + u];
+      }
+      store_split4<OP_F16_PAIR>(wv, i, kt + k4, Kc, op_a, nullptr);
+      store_split4<ZPAIR ? OP_F16_PAIR : OP_F16_SINGLE>(v, i, kt + k4, Kc, op_b, nullptr);
+    }
+    __syncthreads();
+  }
+  if (s1 && threadIdx.x < 128 && it + threadIdx.x < D)
+    atomicAdd(s1 + it + threadIdx.x, colsum * (double)(1.f / sa));
+}
+
+static size_t white_op_bytes(const SyrkPlan& pl, int injected) {
+  // A pair (4 B) + B single (2 B) or pair (4 B) per (column, sample)
+  return (size_t)pl.Dp * pl.Kc * (injected ? 8 : 6);
+}
+
+extern "C" size_t ppi_wmoments_white_workspace_bytes(int64_t K, int64_t D, int injected) {
+  if (K <= 0 || D <= 0) return 0;
+  const SyrkPlan pl = syrk_plan(K, D);
+  return kScalarBytes + white_op_bytes(pl, injected) + pl.partial_bytes + 2048;
+}
+
+template <bool ZPAIR>
+static int wmoments_white_impl(const void* zstore, const float* nw, int64_t K, int64_t D, double* s1,
+                               float* cov, int accumulate, void* workspace, cudaStream_t st) {
+  constexpr int MODE = ZPAIR ? SYRK_PAIR : SYRK_PAIR_SINGLE;
+  const SyrkPlan pl = syrk_plan(K, D);
+  const int64_t Dk = round_up(D, 64);
+  char* wsp = (char*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
+  GemmScalars* scalars = (GemmScalars*)wsp;
+  const GemmScalars* zs = (const GemmScalars*)zstore;
+  const char* store_rows = (const char*)zstore + kScalarBytes;
+  const size_t store_row_bytes = zstore_row_bytes(D, ZPAIR ? 1 : 0);
+  void* op_a = (void*)(wsp + kScalarBytes);
+  void* op_b = (void*)(wsp + kScalarBytes + (size_t)pl.Dp * pl.Kc * 4);
+  float* partials = (float*)(wsp + kScalarBytes + white_op_bytes(pl, ZPAIR ? 1 : 0));
+  partials = (float*)(((uintptr_t)partials + 1023) & ~(uintptr_t)1023);
+
+  {
+    ProfileScope prof(PPI_PROF_SYRK_OPERAND, st);
+    PPI_CUDA_TRY(cudaMemsetAsync(scalars, 0, sizeof(GemmScalars), st));
+    absmax_kernel<<<grid_cap(ceil_div(K, 1024), 4), 256, 0, st>>>(nw, K, &scalars->amax_a_bits);
+    white_scale_kernel<<<1, 1, 0, st>>>(scalars, zs, ZPAIR ? 1 : 0);
+    if (int rc = check_launch("white scale kernels", 2)) return rc;
+  }
+  CUtensorMap a, b;
+  if (int rc = make_map(&a, op_a, pl.Dp, pl.Kc, BM, OP_F16_PAIR)) return rc;
+  if (int rc = make_map(&b, op_b, pl.Dp, pl.Kc, BN, ZPAIR ? OP_F16_PAIR : OP_F16_SINGLE)) return rc;
+
+  SyrkParams p;
+  const int unit = ZPAIR ? BK : 2 * BK;                      // contraction steps per pipeline stage
+  const int chunk_units = ZPAIR ? gemm_chunk() : gemm_chunk() / 2;  // same 32-step chunk boundaries
+  p.num_kb = (int)(pl.Kc / unit);
+  p.chunk_kb = chunk_units < 1 ? 1 : chunk_units;
+  p.kb_per_split = (int)round_up((p.num_kb + pl.splits - 1) / pl.splits, p.chunk_kb);
+  p.splits = pl.splits;
+  p.tiles_n = (int)pl.tiles_n;
+  p.out = partials;
+  p.ld = pl.Dp;
+  p.split_stride = pl.Dp * pl.Dp;
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (int rc = set_gemm_smem(syrk_gemm_kernel<MODE>)) return rc;
+    attr_set = true;
+  }
+  constexpr int kTilesPerBlock = 8;
+  int pass = 0;
+  for (int64_t k0 = 0; k0 < K; k0 += pl.Kc, ++pass) {
+    const int64_t rows = (K - k0) < pl.Kc ? (K - k0) : pl.Kc;
+    {
+      ProfileScope prof(PPI_PROF_SYRK_OPERAND, st);
+      dim3 og((unsigned)ceil_div(pl.Kc / 32, kTilesPerBlock), (unsigned)ceil_div(pl.Dp, 128));
+      white_operand_kernel<ZPAIR><<<og, 256, 0, st>>>(
+          (const uint16_t*)(store_rows + (size_t)k0 * store_row_bytes), nw + k0, rows, Dk, pl.Kc, pl.Dp,
+          kTilesPerBlock, scalars, op_a, op_b, s1, D);
+      if (int rc = check_launch("white_operand_kernel")) return rc;
+    }
+    p.accumulate = pass > 0;
+    {
+      ProfileScope prof(PPI_PROF_SYRK_GEMM, st);
+      syrk_gemm_kernel<MODE><<<(unsigned)(pl.ntiles * pl.splits), kGemmThreads, kGemmSmemBytes, st>>>(
+          a, a, b, b, p);
+      if (int rc = check_launch("syrk_gemm_kernel(white)")) return rc;
+    }
+  }
+  ProfileScope prof(PPI_PROF_SYRK_REDUCE, st);
+  syrk_reduce_kernel<<<grid_cap(ceil_div(D * D, 256), 8), 256, 0, st>>>(partials, pl.splits, pl.Dp,
+                                                                         pl.Dp * pl.Dp, D, cov, accumulate,
+                                                                         scalars);
+  return check_launch("syrk_reduce_kernel");
+}
+
+extern "C" int ppi_wmoments_white(const void* zstore, int injected, const float* nw, int64_t K,
+                                  int64_t D, double* s1, float* cov, int accumulate, void* workspace,
+                                  size_t workspace_bytes, void* stream) {
+  PPI_REQUIRE(zstore && nw && cov && K > 0 && D > 128 && workspace, PPI_ERR_INVALID,
+              "ppi_wmoments_white: bad arguments");
+  PPI_REQUIRE(workspace_bytes >= ppi_wmoments_white_workspace_bytes(K, D, injected), PPI_ERR_WORKSPACE,
+              "ppi_wmoments_white: workspace too small");
+  if (injected)
+    return wmoments_white_impl<true>(zstore, nw, K, D, s1, cov, accumulate, workspace, (cudaStream_t)stream);
+  return wmoments_white_impl<false>(zstore, nw, K, D, s1, cov, accumulate, workspace, (cudaStream_t)stream);
+}
+
 // sample.cu
 int ppi_sample_gaussian_small(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
                               int64_t K, int D, const float* mu, const float* L, float* x,
@@ -1043,10 +1252,16 @@ extern "C" size_t ppi_sample_gaussian_workspace_bytes(int64_t K, int64_t D) {
 
 // FP16: L -> fp16 pair; z -> one exact fp16 (Philox, ZPAIR = false) or an fp16 pair (injected).
 // !FP16: TF32X3 (ZPAIR ignored; the low-order z operand is skipped for Philox normals).
+// Base-normal store kept for the whitened moment match (ppi_sample_gaussian_keep /
+// ppi_wmoments_white): a 1 KB header (GemmScalars of the sampling call: scale_b = power-of-two scale
+// of the stored injected normals, amax_b_bits = max |z|) followed by round_up(K, 256) rows of
+//   Philox    round_up(D, 64) exact fp16 normals                       (2 B per value)
+//   injected  round_up(D, 64) / 32 blocks of [h1 x 32 | h2 x 32] fp16  (4 B per value, scaled)
+
 template <bool FP16, bool ZPAIR>
 static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
                                 int64_t K, int64_t D, const float* mu, const float* L, float* x,
-                                void* workspace, cudaStream_t st) {
+                                void* workspace, void* zstore, cudaStream_t st) {
   constexpr int LMODE = FP16 ? OP_F16_PAIR : OP_TF32X3;
   constexpr int ZMODE = FP16 ? (ZPAIR ? OP_F16_PAIR : OP_F16_SINGLE) : OP_TF32X3;
   constexpr int KS = (FP16 && !ZPAIR) ? 64 : 32;
@@ -1076,15 +1291,20 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
       L, D, D, Dk, 0, 0, 0, 1, FP16 ? &scalars->scale_a : nullptr, l_a, l_b);
   if (int rc = check_launch("split_rows_kernel(L)")) return rc;
 
-  const bool overlap = FP16 && gemm_overlap() && K > Kc;
+  // with a store every pass stages its rows straight into the store (no ping-pong, nothing to overlap)
+  char* store_rows = zstore ? (char*)zstore + kScalarBytes : nullptr;
+  const size_t store_row_bytes = zstore_row_bytes(D, ZPAIR ? 1 : 0);
+  const bool overlap = FP16 && gemm_overlap() && K > Kc && !zstore;
   void* zbufs[2] = {z_a, FP16 ? z_b : z_a};
   CUtensorMap ml, ml2, mz[2], mz2[2];
   if (int rc = make_map(&ml, l_a, D, Dk, BM, LMODE)) return rc;
   ml2 = ml;
-  for (int i = 0; i < (FP16 ? 2 : 1); ++i) {
+  for (int i = 0; i < (FP16 ? 2 : 1) && !zstore; ++i) {
     if (int rc = make_map(&mz[i], zbufs[i], Kc, Dk, BN, ZMODE)) return rc;
     mz2[i] = mz[i];
   }
+  if (zstore && FP16)  // header: the scales of this call (read by ppi_wmoments_white)
+    PPI_CUDA_TRY(cudaMemcpyAsync(zstore, scalars, sizeof(GemmScalars), cudaMemcpyDeviceToDevice, st));
   if (!FP16) {
     if (int rc = make_map(&ml2, l_b, D, Dk, BM, LMODE)) return rc;
     if (int rc = make_map(&mz2[0], z_b, Kc, Dk, BN, ZMODE)) return rc;
@@ -1118,6 +1338,11 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
     const int bi = overlap ? (pass & 1) : 0;
     const int64_t rows = (K - k0) < Kc ? (K - k0) : Kc;
     const int64_t rows_p = round_up(rows, BN);
+    if (zstore) {
+      zbufs[0] = store_rows + (size_t)k0 * store_row_bytes;
+      if (int rc = make_map(&mz[0], zbufs[0], rows_p, Dk, BN, ZMODE)) return rc;
+      mz2[0] = mz[0];
+    }
     // injected: rows beyond `rows` keep stale workspace values whose products are never stored;
     // Philox: they are generated too (harmless)
     {
@@ -1158,8 +1383,30 @@ extern "C" int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_
   PPI_REQUIRE(workspace && workspace_bytes >= ppi_sample_gaussian_workspace_bytes(K, D),
               PPI_ERR_WORKSPACE, "ppi_sample_gaussian: workspace too small");
   if (gemm_scheme() == PPI_GEMM_FP16X2) {
-    if (z) return sample_gaussian_impl<true, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, st);
-    return sample_gaussian_impl<true, false>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, st);
+    if (z) return sample_gaussian_impl<true, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, nullptr, st);
+    return sample_gaussian_impl<true, false>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, nullptr, st);
   }
-  return sample_gaussian_impl<false, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, st);
+  return sample_gaussian_impl<false, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, nullptr, st);
+}
+
+extern "C" size_t ppi_zstore_bytes(int64_t K, int64_t D, int injected) {
+  if (K <= 0 || D <= 128) return 0;
+  return kScalarBytes + (size_t)round_up(K, BN) * zstore_row_bytes(D, injected) + 1024;
+}
+
+extern "C" int ppi_sample_gaussian_keep(const float* z, uint64_t seed, uint64_t draw_id,
+                                        uint64_t row_offset, int64_t K, int64_t D, const float* mu,
+                                        const float* L, float* x, void* zstore, size_t zstore_bytes,
+                                        void* workspace, size_t workspace_bytes, void* stream) {
+  PPI_REQUIRE(mu && L && x && K > 0 && D > 128 && zstore, PPI_ERR_INVALID,
+              "ppi_sample_gaussian_keep: bad arguments (needs K > 0, D > 128, a store)");
+  PPI_REQUIRE(gemm_scheme() == PPI_GEMM_FP16X2, PPI_ERR_UNSUPPORTED,
+              "ppi_sample_gaussian_keep: the base-normal store exists under PPI_GEMM_FP16X2 only");
+  PPI_REQUIRE(((uintptr_t)zstore & 1023) == 0 && zstore_bytes >= ppi_zstore_bytes(K, D, z != nullptr),
+              PPI_ERR_WORKSPACE, "ppi_sample_gaussian_keep: store misaligned (1 KB) or too small");
+  PPI_REQUIRE(workspace && workspace_bytes >= ppi_sample_gaussian_workspace_bytes(K, D),
+              PPI_ERR_WORKSPACE, "ppi_sample_gaussian_keep: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (z) return sample_gaussian_impl<true, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, zstore, st);
+  return sample_gaussian_impl<true, false>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, zstore, st);
 }

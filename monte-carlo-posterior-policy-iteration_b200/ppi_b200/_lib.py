@@ -50,6 +50,10 @@ SIGNATURES = {
     "ppi_sample_iid": (_i, [_p, _u64, _u64, _u64, _i64, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
     "ppi_sample_gaussian_workspace_bytes": (_sz, [_i64, _i64]),
     "ppi_sample_gaussian": (_i, [_p, _u64, _u64, _u64, _i64, _i64, _p, _p, _p, _p, _sz, _p]),
+    "ppi_zstore_bytes": (_sz, [_i64, _i64, _i]),
+    "ppi_sample_gaussian_keep": (_i, [_p, _u64, _u64, _u64, _i64, _i64, _p, _p, _p, _p, _sz, _p, _sz, _p]),
+    "ppi_wmoments_white_workspace_bytes": (_sz, [_i64, _i64, _i]),
+    "ppi_wmoments_white": (_i, [_p, _i, _p, _i64, _i64, _p, _p, _i, _p, _sz, _p]),
     "ppi_cost_function": (_i, [_i, _p, _i64, _i64, _p, _p, _p, _p]),
     "ppi_cost_tracking": (_i, [_p, _i64, _i, _i, _p, _i, _p, _p]),
     "ppi_solve_temperature_workspace_bytes": (_sz, [_i64]),

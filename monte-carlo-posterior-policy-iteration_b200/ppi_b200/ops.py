@@ -143,6 +143,47 @@ def sample_gaussian(K, mu, L, z=None, seed=0, draw_id=0, row_offset=0, out=None)
     return x
 
 
+class BaseNormals:
+    """Base-normal store of one sample_gaussian(keep=True) draw (ppi_sample_gaussian_keep): the
+    tensor-core operand form of z, kept in HBM for the whitened moment match."""
+
+    def __init__(self, store, rows, dim, injected):
+        self.store, self.rows, self.dim, self.injected = store, rows, dim, bool(injected)
+
+
+def sample_gaussian_keep(K, mu, L, z=None, seed=0, draw_id=0, row_offset=0):
+    """sample_gaussian + the base-normal store: -> (x, BaseNormals).  D > 128, FP16X2 scheme."""
+    dev = require_cuda()
+    kp = _Keep(dev)
+    mu = f32(mu, dev)
+    D = mu.numel()
+    x = torch.empty((K, D), dtype=torch.float32, device=dev)
+    zt = None if z is None else f32(z, dev).reshape(K, D)
+    nbytes = _lib.query("ppi_sample_gaussian_workspace_bytes", K, D)
+    ws = workspace("sample_gaussian", nbytes)
+    sbytes = _lib.query("ppi_zstore_bytes", K, D, int(zt is not None))
+    raw = torch.empty(sbytes + 1024, dtype=torch.uint8, device=dev)
+    off = (-raw.data_ptr()) % 1024  # the store header / TMA rows want 1 KB alignment
+    store = raw[off:off + sbytes]
+    _lib.call("ppi_sample_gaussian_keep", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, D,
+              ptr(mu), kp.p(L), ptr(x), ptr(store), sbytes, ptr(ws), nbytes, stream_ptr())
+    return x, BaseNormals(store, K, D, zt is not None)
+
+
+def wmoments_white(base, nw, s1=None, cov=None, accumulate=False):
+    """Whitened moments of a BaseNormals store: s1 (D fp64) += sum nw z, cov (D, D) = sum nw z z^T."""
+    dev = require_cuda()
+    kp = _Keep(dev)
+    K, D = base.rows, base.dim
+    s1 = torch.zeros(D, dtype=torch.float64, device=dev) if s1 is None else s1
+    cov = torch.empty((D, D), dtype=torch.float32, device=dev) if cov is None else cov
+    nbytes = _lib.query("ppi_wmoments_white_workspace_bytes", K, D, int(base.injected))
+    ws = workspace("wmoments_dense", nbytes)
+    _lib.call("ppi_wmoments_white", ptr(base.store), int(base.injected), kp.p(nw), K, D, ptr(s1), ptr(cov),
+              int(bool(accumulate)), ptr(ws), nbytes, stream_ptr())
+    return s1, cov
+
+
 # ------------------------------------------------------------------ a9
 def cost_function(name, x, A=None, noise=None):
     dev = require_cuda()

@@ -15,7 +15,7 @@ import logging
 import numpy as np
 import torch
 
-from . import ops, samplers
+from . import _lib, ops, samplers
 from .device import (DeviceArray, all_reduce_max, all_reduce_sum, broadcast_row, dist_info, f32, f64, require_cuda,
                      shard_rows, to_host64)
 
@@ -219,6 +219,7 @@ class GaussianPolicy(object):
         self._mu_host, self._sigma_host = mu, sigma
         self._mu_dev = self._sigma_dev = self._chol_dev = None
         self._chol64_dev, self._logdet = chol64, logdet
+        self._version = getattr(self, "_version", 0) + 1  # invalidates base-normal stores of earlier draws
 
     @property
     def mu(self):
@@ -229,17 +230,19 @@ class GaussianPolicy(object):
     @mu.setter
     def mu(self, value):
         self._mu_host, self._mu_dev = np.asarray(value, np.float64), None
+        self._version += 1
 
     @property
     def sigma(self):
         if self._sigma_host is None:
-            self._sigma_host = to_host64(self._sigma_dev)
+            self._sigma_host = to_host64(self._sigma64_d())
         return self._sigma_host
 
     @sigma.setter
     def sigma(self, value):
         self._sigma_host, self._sigma_dev = np.asarray(value, np.float64), None
         self._chol_dev = self._chol64_dev = self._logdet = None
+        self._version += 1
 
     def _mu_d(self):
         if self._mu_dev is None:
@@ -249,6 +252,8 @@ class GaussianPolicy(object):
     def _sigma64_d(self):
         if self._sigma_dev is not None:
             return self._sigma_dev.double()
+        if self._sigma_host is None:  # after a whitened update only the factor exists: sigma = L L^T
+            return self._chol64_dev @ self._chol64_dev.T
         return f64(self._sigma_host)
 
     def _factor(self):
@@ -285,6 +290,13 @@ class GaussianPolicy(object):
             handle = DeviceArray(f32(x[begin:end]), begin, x.shape[0])
             return handle, handle
         z, seed, draw, begin, n_local, n_total = _draw(self.sampler, n_samples, d)
+        if d > self.small_dim and not self.diagonal and _lib.load().ppi_get_option(_lib.OPT_GEMM_SCHEME) == _lib.GEMM_FP16X2:
+            # keep the base normals in HBM: weighted_update on this very handle contracts z, not x
+            x, base = ops.sample_gaussian_keep(n_local, self._mu_d(), self._factor(), z=z, seed=seed,
+                                               draw_id=draw, row_offset=begin)
+            handle = DeviceArray(x, begin, n_total)
+            handle.white = (self, self._version, base)
+            return handle, handle
         x = ops.sample_gaussian(n_local, self._mu_d(), self._factor(), z=z, seed=seed, draw_id=draw,
                                 row_offset=begin)
         handle = DeviceArray(x, begin, n_total)
@@ -295,6 +307,10 @@ class GaussianPolicy(object):
         x, row_offset, n_total, replicated = _samples(samples)
         nw = _local(w.nw, row_offset, x.shape[0])
         d = x.shape[1]
+        white = getattr(samples, "white", None)
+        if (white is not None and white[0] is self and white[1] == self._version and update_covariance_in
+                and not self.diagonal):
+            return self._weighted_update_white(w, white[2], nw)
         if d > self.small_dim:
             return self._weighted_update_large(w, x, nw, replicated, update_covariance_in)
         mu_old, sigma_old = self.mu.copy(), self.sigma.copy()
@@ -340,7 +356,43 @@ class GaussianPolicy(object):
                 logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
                 self.sigma = sigma_old + SIGMA_MIN * np.eye(d)
         ess = float(w.stats.ess)
+        self._version += 1
         return ess, float(multivariate_gaussian_kl(self.mu, self.sigma, mu_old, sigma_old))
+
+    def _weighted_update_white(self, w, base, nw):
+        """M-projection in whitened coordinates for samples this policy drew itself (x = mu + L z with
+        the base normals still in HBM, ppi_sample_gaussian_keep).  With m = sum nw z and
+        C = sum nw z z^T - m m^T:  mu' = mu + L m  (ppi/policies.py:88),  sigma' = L C L^T (:89-92), so
+        chol(sigma') = L chol(C), log det sigma' = log det sigma + log det C, and
+        KL(new || old) = (tr C + |m|^2 - D - log det C) / 2 (:146-158) -- no pass over x, no triangular
+        solve.  sigma itself is formed lazily (L' L'^T) when a caller reads it."""
+        d = base.dim
+        self._factor()
+        l_old, mu_old_dev, old_logdet = self._chol64_dev, self._mu_d(), self._logdet
+        m, s = ops.wmoments_white(base, nw)
+        all_reduce_sum(m)
+        all_reduce_sum(s)
+        c = s.double()
+        c.addr_(m, m, alpha=-1.0)
+        g, info = torch.linalg.cholesky_ex(c)
+        scal = torch.stack([info.double(), 2.0 * torch.log(torch.diagonal(g)).sum(), torch.trace(c), m @ m]).cpu()
+        self._mu_host, self._mu_dev = None, (mu_old_dev.double() + l_old @ m).float()
+        if int(scal[0]) == 0:
+            logdet_c = float(scal[1])
+            self._sigma_host = self._sigma_dev = self._chol_dev = None
+            self._chol64_dev, self._logdet = l_old @ g, old_logdet + logdet_c
+            kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(self._logdet) + float(scal[2]) + float(scal[3]) - d)
+        else:  # ppi/policies.py:263-268: keep the old covariance, regularised
+            logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
+            sigma_old = l_old @ l_old.T
+            self._sigma_host, self._chol_dev, self._chol64_dev, self._logdet = None, None, None, None
+            self._sigma_dev = (sigma_old + SIGMA_MIN * torch.eye(d, dtype=torch.float64, device=sigma_old.device)).float()
+            self._factor()
+            tr = torch.linalg.solve_triangular(l_old, self._chol64_dev, upper=False).square().sum()
+            kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(self._logdet) + float(tr.item())
+                        + float(scal[3]) - d)  # (mu' - mu)^T sigma^-1 (mu' - mu) = |m|^2
+        self._version += 1
+        return float(w.stats.ess), kl
 
     def _weighted_update_large(self, w, x, nw, replicated, update_covariance_in):
         """d > small_dim: every array stays in HBM (tcgen05 covariance, device fp64 Cholesky /
@@ -398,6 +450,7 @@ class GaussianPolicy(object):
         sol = torch.linalg.solve_triangular(old_chol64, rhs, upper=False)
         tr_quad = float((sol * sol).sum().item())
         kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(logdet_new) + tr_quad - d)
+        self._version += 1
         return float(w.stats.ess), kl
 
     @staticmethod

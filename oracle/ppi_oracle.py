@@ -214,10 +214,10 @@ def gaussian_entropy(sigma, d):
     return 0.5 * np.log(max(EPS, np.linalg.det(sigma))) + (d / 2) * (1 + np.log(2 * np.pi))
 
 
-def gaussian_weighted_update(mu, sigma, log_w, samples, diagonal=False, update_cov=True):
+def gaussian_weighted_update(mu, sigma, log_w, samples, diagonal=False, update_cov=True, naive=True):
     """GaussianPolicy.weighted_update                        ppi/policies.py:251-269.
-    Returns (mu', sigma', ess, kl)."""
-    mu_, sigma_, ess = m_projection(log_w, samples)
+    Returns (mu', sigma', ess, kl).  naive: see m_projection."""
+    mu_, sigma_, ess = m_projection(log_w, samples, naive=naive)
     if diagonal:
         sigma_ = np.diag(np.diag(sigma_))
     new_sigma = sigma.copy()

@@ -1,0 +1,160 @@
+"""GPU parity tests of the whitened moment match (ppi_sample_gaussian_keep + ppi_wmoments_white,
+tc_gemm.cu): for samples x = mu + L z drawn by the policy itself the M-projection of
+ppi/policies.py:78-93 is evaluated on the stored base normals z.  Checked against the oracle's
+m_projection on x (fp64) -- tolerance 1e-5 norm-wise (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+from scipy.special import logsumexp
+
+from oracle import ppi_oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def nerr(a, ref):
+    a, ref = np.asarray(a, np.float64), np.asarray(ref, np.float64)
+    assert a.shape == ref.shape, (a.shape, ref.shape)
+    return np.max(np.abs(a - ref)) / max(np.max(np.abs(ref)), 1e-300)
+
+
+def host(t):
+    return t.detach().cpu().numpy().astype(np.float64)
+
+
+def f32r(x):
+    return np.asarray(x, np.float32).astype(np.float64)
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import torch
+
+    assert torch.cuda.is_available()
+    from ppi_b200 import _lib, ops as _ops
+
+    _lib.call("ppi_set_option", _lib.OPT_GEMM_SCHEME, _lib.GEMM_FP16X2)
+    return _ops
+
+
+def _factor(D, rng):
+    a = rng.standard_normal((D, D + 8))
+    return f32r(np.linalg.cholesky(a @ a.T / D + 0.2 * np.eye(D))), f32r(rng.standard_normal(D))
+
+
+def _weights(K, rng, spread=8.0):
+    lw = f32r(-spread * rng.random(K))
+    return lw, f32r(np.exp(lw - logsumexp(lw)))
+
+
+@pytest.mark.parametrize("K,D", [(512, 256), (1000, 200), (3000, 384), (600, 130), (8192, 1024),
+                                 (150000, 256), (70001, 640)])
+@pytest.mark.parametrize("injected", [False, True])
+def test_wmoments_white_ops(ops, K, D, injected):
+    rng = np.random.default_rng(K + D)
+    L, mu = _factor(D, rng)
+    lw, nw = _weights(K, rng)
+    if injected:
+        z = f32r(rng.standard_normal((K, D)))
+        x, base = ops.sample_gaussian_keep(K, mu, L, z=z)
+        ref_x = ops.sample_gaussian(K, mu, L, z=z)
+    else:
+        z = host(ops.philox_normal(K, D, seed=5, draw_id=3, row_offset=11))
+        x, base = ops.sample_gaussian_keep(K, mu, L, seed=5, draw_id=3, row_offset=11)
+        ref_x = ops.sample_gaussian(K, mu, L, seed=5, draw_id=3, row_offset=11)
+    import torch
+
+    assert torch.equal(x, ref_x)                               # the store changes nothing in x
+    s1, s = ops.wmoments_white(base, nw)
+    m_ref = nw @ z
+    s_ref = (nw[:, None] * z).T @ z
+    assert nerr(host(s1), m_ref) < TOL
+    cov = host(s)
+    assert nerr(cov, s_ref) < TOL
+    assert np.array_equal(cov, cov.T)
+    # whitened identities against the M-projection of x itself (ppi/policies.py:84-92)
+    mu_x, sigma_x, _ = O.m_projection(lw, host(x), naive=False)
+    m = host(s1)
+    assert nerr(mu + L @ m, mu_x) < TOL
+    assert nerr(L @ (cov - np.outer(m, m)) @ L.T, sigma_x) < 2 * TOL
+    # linearity: accumulate on top of an existing partial
+    s1b, sb = ops.wmoments_white(base, 0.25 * nw)
+    s1b, sb = ops.wmoments_white(base, 0.75 * nw, s1=s1b, cov=sb, accumulate=True)
+    assert nerr(host(s1b), m_ref) < TOL and nerr(host(sb), s_ref) < TOL
+
+
+def test_wmoments_white_zero_and_one_hot(ops):
+    """Rows with zero weight (failed rollouts) contribute nothing; a one-hot weight vector gives the
+    outer product of that base-normal row (the alpha -> infinity limit)."""
+    K, D = 4096, 256
+    rng = np.random.default_rng(2)
+    L, mu = _factor(D, rng)
+    z = host(ops.philox_normal(K, D, seed=1))
+    _, base = ops.sample_gaussian_keep(K, mu, L, seed=1)
+    _, nw = _weights(K, rng, spread=30.0)   # 13 decades of dynamic range
+    nw[::3] = 0.0
+    nw /= nw.sum()
+    nw = f32r(nw)
+    s1, s = ops.wmoments_white(base, nw)
+    assert nerr(host(s1), nw @ z) < TOL and nerr(host(s), (nw[:, None] * z).T @ z) < TOL
+    hot = np.zeros(K)
+    hot[1234] = 1.0
+    s1, s = ops.wmoments_white(base, hot)
+    assert nerr(host(s1), z[1234]) < TOL and nerr(host(s), np.outer(z[1234], z[1234])) < TOL
+
+
+@pytest.mark.parametrize("philox", [False, True])
+def test_gaussian_policy_white_update(ops, philox):
+    """Two iterations of sample -> Rastrigin -> ESSPS -> moment match through the public classes at
+    D = 384; the fitted mu / sigma / KL / entropy equal the oracle's update computed from x."""
+    from ppi_b200 import algorithms as alg, functions as fn, policies as pol, samplers as smp
+
+    K, D = 16384, 384
+    rng = np.random.default_rng(0)
+    if philox:
+        sampler = smp.MonteCarlo(D, seed=77)
+    else:
+        smp.InjectedNormals.queue = [np.asarray(rng.standard_normal((K, D)), np.float32) for _ in range(2)]
+        sampler = smp.InjectedNormals(D)
+    policy = pol.GaussianPolicy(np.ones(D), 0.5 * np.eye(D), sampler)
+    solver = alg.Essps(n_elites=K // 16)
+    solver.reset(policy)
+    for it in range(2):
+        mu_old, sigma_old = policy.mu.copy(), policy.sigma.copy()
+        samples, params = policy(K)
+        assert getattr(samples, "white", None) is not None
+        costs = fn.Rastrigin(D)(samples)
+        x32, c32 = np.asarray(samples), np.asarray(costs)
+        solver.update(costs, params, policy)
+        log_w, alpha = O.essps_log_w(c32, K // 16)
+        mu, sigma, ess, kl = O.gaussian_weighted_update(mu_old, sigma_old, log_w, x32, naive=False)
+        assert abs(solver.trace["alpha"][-1] - alpha) < TOL * alpha
+        assert abs(solver.trace["ess"][-1] - ess) < TOL * ess
+        assert nerr(policy.mu, mu) < TOL, it
+        assert nerr(policy.sigma, sigma) < 2 * TOL, it
+        assert abs(solver.trace["kl"][-1] - kl) < 1e-4 * max(1.0, abs(kl))
+        ent = O.gaussian_entropy(sigma, D)
+        assert abs(solver.trace["ent"][-1] - ent) < 1e-4 * abs(ent)
+
+
+def test_white_handle_goes_stale(ops):
+    """A handle drawn before the policy changed must not take the whitened path (its z no longer
+    maps to x through the current mu / L): the generic path gives the same answer as a host copy."""
+    from ppi_b200 import policies as pol, samplers as smp
+
+    K, D = 4096, 256
+    rng = np.random.default_rng(4)
+    policy = pol.GaussianPolicy(np.zeros(D), np.eye(D), smp.MonteCarlo(D, seed=3))
+    samples, _ = policy(K)
+    lw = f32r(-4.0 * rng.random(K))
+    policy.mu = np.ones(D)                                    # state change after the draw
+    policy.weighted_update(lw, samples)
+    mu, sigma, _ = O.m_projection(lw, np.asarray(samples), naive=False)
+    assert nerr(policy.mu, mu) < TOL and nerr(policy.sigma, sigma) < TOL
+    # and a handle reused after its own update is stale as well
+    samples2, _ = policy(K)
+    policy.weighted_update(lw, samples2)
+    first = policy.sigma.copy()
+    policy.weighted_update(lw, samples2)
+    mu2, sigma2, _ = O.m_projection(lw, np.asarray(samples2), naive=False)
+    assert nerr(policy.sigma, sigma2) < TOL and nerr(first, sigma2) < 2 * TOL
