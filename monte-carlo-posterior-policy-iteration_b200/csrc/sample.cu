@@ -248,6 +248,146 @@ sample_features_kernel(const float* __restrict__ z, uint64_t seed, uint64_t draw
 }
 
 // ------------------------------------------------------------------------------------------
+// Feature sampler, register-tiled (d <= 4): one thread per time step of a 256-step tile, 32
+// samples per block iteration.  The tiny w = mean + L_in z L_out^T of the 32 samples goes to
+// shared memory as [f][sample][c]; the output product then reads, per feature, one Phi / Phi'
+// value and the w of 8 samples (broadcast 16-byte loads) for 8 * dy FMAs, and every thread stores
+// its dy outputs of one (sample, time step) as one vector -- a warp writes 32 * dy * 4 contiguous
+// bytes.  HBM-bound on the (K, T, dy) write when F is small (C4: F = 21, dy = 4).
+// ------------------------------------------------------------------------------------------
+constexpr int kFeatTile = 256;  // time steps per block (= threads)
+constexpr int kFeatS = 32;      // samples per block iteration
+constexpr int kFeatSB = 8;      // samples per register block
+
+__host__ __device__ inline int pad4(int n) { return (n + 3) & ~3; }
+
+template <int DY>
+__device__ __forceinline__ void store_row(float* dst, const float (&v)[DY]) {
+  if constexpr (DY % 4 == 0) {
+#pragma unroll
+    for (int i = 0; i < DY; i += 4)
+      *reinterpret_cast<float4*>(dst + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+  } else if constexpr (DY % 2 == 0) {
+#pragma unroll
+    for (int i = 0; i < DY; i += 2) *reinterpret_cast<float2*>(dst + i) = make_float2(v[i], v[i + 1]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < DY; ++i) dst[i] = v[i];
+  }
+}
+
+template <int DD, bool DERIV>
+__global__ void __launch_bounds__(kFeatTile)
+sample_features_tiled_kernel(const float* __restrict__ z, uint64_t seed, uint64_t draw,
+                             uint64_t row_offset, int64_t K, int F, int T,
+                             const float* __restrict__ mean_fn, const float* __restrict__ mean,
+                             const float* __restrict__ l_in, const float* __restrict__ l_out,
+                             const float* __restrict__ feat, const float* __restrict__ dfeat,
+                             const float* __restrict__ lower, const float* __restrict__ upper,
+                             float* __restrict__ w, float* __restrict__ y) {
+  extern __shared__ __align__(16) float smem[];
+  constexpr int DY = DERIV ? 2 * DD : DD;
+  const int FD = F * DD;
+  float* sPhi = smem;                                   // F * 256 (transposed tile)
+  float* sdPhi = sPhi + F * kFeatTile;                  // F * 256 (DERIV)
+  float* sLin = sdPhi + (DERIV ? F * kFeatTile : 0);    // F * F
+  float* sLout = sLin + pad4(F * F);                    // d * d
+  float* sMean = sLout + pad4(DD * DD);                 // F * d
+  float* sZ = sMean + pad4(FD);                         // 32 * F * d
+  float* sU = sZ + pad4(kFeatS * FD);                   // 32 * F * d
+  float* sW = sU + pad4(kFeatS * FD);                   // [F][32][d]
+
+  const int t0 = blockIdx.y * kFeatTile;
+  const int nt = min(kFeatTile, T - t0);
+  for (int i = threadIdx.x; i < F * kFeatTile; i += blockDim.x) {
+    const int f = i / kFeatTile, tl = i % kFeatTile;
+    const bool ok = tl < nt;
+    sPhi[i] = ok ? feat[(int64_t)(t0 + tl) * F + f] : 0.f;
+    if (DERIV) sdPhi[i] = ok ? dfeat[(int64_t)(t0 + tl) * F + f] : 0.f;
+  }
+  for (int i = threadIdx.x; i < F * F; i += blockDim.x) sLin[i] = l_in[i];
+  for (int i = threadIdx.x; i < DD * DD; i += blockDim.x) sLout[i] = l_out[i];
+  for (int i = threadIdx.x; i < FD; i += blockDim.x) sMean[i] = mean[i];
+  float lo[DY], hi[DY], mf[DY];
+#pragma unroll
+  for (int c = 0; c < DY; ++c) {
+    lo[c] = lower ? lower[c] : -INFINITY;
+    hi[c] = upper ? upper[c] : INFINITY;
+    mf[c] = c < DD ? mean_fn[c] : 0.f;
+  }
+  __syncthreads();
+
+  const int tl = threadIdx.x;
+  const bool active = tl < nt;
+  const int64_t n_groups = ceil_div(K, kFeatS);
+  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+    const int64_t b0 = g * kFeatS;
+    const int ns = (int)min((int64_t)kFeatS, K - b0);
+    load_normals(sZ, ns * FD, z, (uint64_t)b0 * FD, (row_offset + (uint64_t)b0) * FD, seed, draw);
+    __syncthreads();
+    for (int e = threadIdx.x; e < ns * FD; e += blockDim.x) {
+      const int l = e % DD;
+      const float* zr = sZ + (e - l);
+      float u = 0.f;
+#pragma unroll
+      for (int j = 0; j < DD; ++j) u = fmaf(zr[j], sLout[l * DD + j], u);
+      sU[e] = u;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < kFeatS * FD; e += blockDim.x) {
+      const int s = e / FD, r = e % FD, k = r / DD, l = r % DD;
+      float a = 0.f;
+      if (s < ns) {
+        const float* row = sLin + k * F;
+        for (int i = 0; i <= k; ++i) a = fmaf(row[i], sU[s * FD + i * DD + l], a);
+        a += sMean[r];
+        if (blockIdx.y == 0) w[(b0 + s) * FD + r] = a;
+      }
+      sW[(k * kFeatS + s) * DD + l] = a;
+    }
+    __syncthreads();
+    for (int sb = 0; sb * kFeatSB < ns; ++sb) {
+      float acc[kFeatSB][DY];
+#pragma unroll
+      for (int s = 0; s < kFeatSB; ++s)
+#pragma unroll
+        for (int c = 0; c < DY; ++c) acc[s][c] = 0.f;
+      for (int f = 0; f < F; ++f) {
+        const float ph = sPhi[f * kFeatTile + tl];
+        const float dph = DERIV ? sdPhi[f * kFeatTile + tl] : 0.f;
+        float wv[kFeatSB * DD];
+        const float4* wp = reinterpret_cast<const float4*>(sW + (f * kFeatS + sb * kFeatSB) * DD);
+#pragma unroll
+        for (int q = 0; q < kFeatSB * DD / 4; ++q) {
+          const float4 t = wp[q];
+          wv[4 * q] = t.x; wv[4 * q + 1] = t.y; wv[4 * q + 2] = t.z; wv[4 * q + 3] = t.w;
+        }
+#pragma unroll
+        for (int s = 0; s < kFeatSB; ++s)
+#pragma unroll
+          for (int c = 0; c < DD; ++c) {
+            acc[s][c] = fmaf(ph, wv[s * DD + c], acc[s][c]);
+            if (DERIV) acc[s][DD + c] = fmaf(dph, wv[s * DD + c], acc[s][DD + c]);
+          }
+      }
+      if (active) {
+#pragma unroll
+        for (int s = 0; s < kFeatSB; ++s) {
+          const int sl = sb * kFeatSB + s;
+          if (sl < ns) {
+            float out[DY];
+#pragma unroll
+            for (int c = 0; c < DY; ++c) out[c] = clipf(mf[c] + acc[s][c], lo[c], hi[c]);
+            store_row<DY>(y + ((b0 + sl) * (int64_t)T + (t0 + tl)) * DY, out);
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // iid sampler: element-wise, one quad of the base-normal matrix per thread iteration.
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
@@ -514,6 +654,35 @@ extern "C" int ppi_sample_features(const float* z, uint64_t seed, uint64_t draw_
   PPI_REQUIRE((lower == nullptr) == (upper == nullptr), PPI_ERR_INVALID,
               "lower and upper must both be given or both be NULL");
   if (K == 0) return 0;
+  if (d <= 4) {
+    const int FD = F * d;
+    const size_t smem_t = ((size_t)(dfeat ? 2 : 1) * F * kFeatTile + pad4(F * F) + pad4(d * d) + pad4(FD) +
+                           3 * (size_t)pad4(kFeatS * FD)) * sizeof(float);
+    const bool y_ok = (reinterpret_cast<uintptr_t>(y) & 15) == 0;
+    if (smem_t <= 100 * 1024 && y_ok) {
+      const int ty = (int)ceil_div(T, kFeatTile);
+      int gx = (int)ceil_div(grid_for(ceil_div(K, kFeatS), 3), ty);
+      if (gx < 1) gx = 1;
+      dim3 grid(gx, ty);
+      ProfileScope prof(PPI_PROF_SAMPLE_SMALL, (cudaStream_t)stream);
+#define PPI_LAUNCH_FEAT(DD, DERIV)                                                                  \
+  do {                                                                                              \
+    if (int rc = set_smem(sample_features_tiled_kernel<DD, DERIV>, smem_t)) return rc;              \
+    sample_features_tiled_kernel<DD, DERIV><<<grid, kFeatTile, smem_t, (cudaStream_t)stream>>>(     \
+        z, seed, draw_id, row_offset, K, F, T, mean_fn, mean, l_in, l_out, feat, dfeat, lower,      \
+        upper, w, y);                                                                               \
+  } while (0)
+      if (dfeat) {
+        if (d == 1) PPI_LAUNCH_FEAT(1, true); else if (d == 2) PPI_LAUNCH_FEAT(2, true);
+        else if (d == 3) PPI_LAUNCH_FEAT(3, true); else PPI_LAUNCH_FEAT(4, true);
+      } else {
+        if (d == 1) PPI_LAUNCH_FEAT(1, false); else if (d == 2) PPI_LAUNCH_FEAT(2, false);
+        else if (d == 3) PPI_LAUNCH_FEAT(3, false); else PPI_LAUNCH_FEAT(4, false);
+      }
+#undef PPI_LAUNCH_FEAT
+      return check_launch("sample_features_tiled_kernel");
+    }
+  }
   constexpr int S = 4;
   const size_t smem = (2 * (size_t)F * kFeatTT + (size_t)F * F + (size_t)d * d + (size_t)F * d +
                        3 * (size_t)S * F * d) * sizeof(float);
