@@ -272,6 +272,8 @@ def run_b200(args, wl):
     lib = _lib.load()
     if args.overlap is not None:
         _lib.call("ppi_set_option", _lib.OPT_GEMM_OVERLAP, args.overlap)
+    if args.chunk is not None:
+        _lib.call("ppi_set_option", _lib.OPT_GEMM_CHUNK, args.chunk)
 
     def barrier():
         if world > 1:
@@ -455,6 +457,7 @@ def main():
     ap.add_argument("--workload", default="C5", choices=sorted(WORKLOADS))
     ap.add_argument("--samples", type=int, default=None, help="samples per GPU (overrides the workload's K)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--chunk", type=int, default=None, help="override PPI_OPT_GEMM_CHUNK")
     ap.add_argument("--overlap", type=int, default=None, choices=[0, 1],
                     help="override PPI_OPT_GEMM_OVERLAP (operand staging on a side stream)")
     args = ap.parse_args()

@@ -792,6 +792,64 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
   }
 }
 
+// Philox normals of `rows` sample rows (rows % 64 == 0) written twice: sample-major exact fp16
+// rows [rows][cols_p] (operand of the sampling GEMM, contraction over columns) and K-major into the
+// base-normal store zt[i][k0 + r] (operand of the whitened moment match, contraction over samples).
+// Tile = 64 samples x 128 columns through shared memory.
+__global__ void __launch_bounds__(256)
+philox_dual_kernel(int64_t rows, int64_t cols, int64_t cols_p, uint64_t seed, uint64_t draw,
+                   uint64_t row_offset, uint16_t* __restrict__ op_rows, uint16_t* __restrict__ zt,
+                   int64_t zt_rows, int64_t kt, int64_t k0) {
+  constexpr int kPitch = 130;  // halfs per tile row (65 words: the 8-sample column gathers spread over banks)
+  __shared__ __half tile[64 * kPitch];
+  const bool quad_rng = (cols & 3) == 0;
+  const PhiloxKeys keys = philox_keys(seed);
+  const int64_t tiles_c = ceil_div(zt_rows, 128);
+  const int64_t n_tiles = (rows / 64) * tiles_c;
+  for (int64_t tile_id = blockIdx.x; tile_id < n_tiles; tile_id += gridDim.x) {
+    const int64_t tr = tile_id / tiles_c, tc = tile_id % tiles_c;
+    for (int q = threadIdx.x; q < 64 * 32; q += 256) {
+      const int r = q >> 5, c4 = (q & 31) * 4;
+      const int64_t row = tr * 64 + r, col = tc * 128 + c4;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      const uint64_t e_row = (row_offset + (uint64_t)row) * (uint64_t)cols;
+      if (col < cols) {
+        if (quad_rng) {
+          philox_normal4(keys, draw, (e_row + (uint64_t)col) >> 2, v);
+        } else {
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (col + u < cols) v[u] = philox_normal1(seed, draw, e_row + (uint64_t)col + u);
+        }
+      }
+      const __half2 h01 = __floats2half2_rn(v[0], v[1]), h23 = __floats2half2_rn(v[2], v[3]);
+      if (col < cols_p)
+        *reinterpret_cast<uint2*>(op_rows + row * cols_p + col) =
+            make_uint2(*reinterpret_cast<const uint32_t*>(&h01), *reinterpret_cast<const uint32_t*>(&h23));
+      __half2* t2 = reinterpret_cast<__half2*>(tile + r * kPitch + c4);
+      t2[0] = h01;
+      t2[1] = h23;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < 128 * 8; e += 256) {
+      const int g = e & 7, cl = e >> 3;
+      const int64_t col = tc * 128 + cl;
+      if (col < zt_rows) {
+        uint16_t h[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) h[u] = *reinterpret_cast<const uint16_t*>(tile + (g * 8 + u) * kPitch + cl);
+        uint4 o;
+        o.x = (uint32_t)h[0] | ((uint32_t)h[1] << 16);
+        o.y = (uint32_t)h[2] | ((uint32_t)h[3] << 16);
+        o.z = (uint32_t)h[4] | ((uint32_t)h[5] << 16);
+        o.w = (uint32_t)h[6] | ((uint32_t)h[7] << 16);
+        *reinterpret_cast<uint4*>(zt + col * kt + k0 + tr * 64 + g * 8) = o;
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // cov[i][j] (+)= inv_scale * sum_s partial[s][min(i,j)][max(i,j)]
 __global__ void syrk_reduce_kernel(const float* __restrict__ partials, int splits, int64_t Dp,
                                    int64_t split_stride, int64_t D, float* __restrict__ cov,
@@ -857,7 +915,10 @@ static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t kp,
 }
 
 static int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
-static size_t zstore_row_bytes(int64_t D, int injected) { return (size_t)round_up(D, 64) * (injected ? 4 : 2); }
+// injected-normal store: sample-major rows of fp16 pairs
+static size_t zstore_row_bytes(int64_t D) { return (size_t)round_up(D, 64) * 4; }
+// Philox store: K-major, zT[i][k] = z[k][i], round_up(D, 128) rows of round_up(K, 256) exact fp16
+static int64_t zstore_kt(int64_t K) { return round_up(K, 256); }
 static int grid_cap(int64_t work, int per_sm) {
   const int64_t cap = (int64_t)kNumSMs * per_sm;
   return (int)(work < 1 ? 1 : (work < cap ? work : cap));
@@ -1142,6 +1203,303 @@ white_operand_kernel(const uint16_t* __restrict__ zrows, const float* __restrict
     atomicAdd(s1 + it + threadIdx.x, colsum * (double)(1.f / sa));
 }
 
+// ---------------------------------------------------------------------------------------------
+// Whitened covariance straight from the K-major Philox store: no operand pre-pass.
+//   C[m][n] = sum_k (nw_k zT[m][k]) zT[n][k]
+// Both operands are TMA boxes of the same fp16 array.  A "transform" warpgroup turns each A box
+// (128 columns x 64 samples, exact fp16) into the fp16 pair of scale_a nw_k z in shared memory
+// (two 32-sample pair tiles in the canonical K-major 128-byte-swizzle layout) while the previous
+// stage multiplies; the B box feeds the MMA as it lands.  m = sum_k nw_k z_k comes from
+// white_mean_kernel (one HBM pass over the 2-byte store).
+// CTA = 4 warpgroups: WG0 = TMA producer + MMA issuer, WG1-2 = TMEM drain (fp32 register
+// accumulators, as syrk_gemm_kernel), WG3 = transform; register budget moved with setmaxnreg.
+// ---------------------------------------------------------------------------------------------
+// scale_a nw_k split into two fp16 (wa = rn(v), wb = rn(v - wa)); entries k >= K are zero.
+__global__ void __launch_bounds__(256)
+white_weights_kernel(const float* __restrict__ nw, int64_t K, int64_t kt, const GemmScalars* __restrict__ scalars,
+                     uint16_t* __restrict__ wa, uint16_t* __restrict__ wb) {
+  const float sa = scalars->scale_a;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < kt; k += stride) {
+    const float v = k < K ? __ldg(nw + k) * sa : 0.f;
+    const __half a = __float2half_rn(v);
+    const __half b = __float2half_rn(v - __half2float(a));
+    wa[k] = *reinterpret_cast<const uint16_t*>(&a);
+    wb[k] = *reinterpret_cast<const uint16_t*>(&b);
+  }
+}
+
+// s1[i] += sum_k nw_k zT[i][k]: block = 8 store rows x 16384 samples, weights loaded once per 8 rows.
+constexpr int kMeanRows = 8, kMeanChunk = 16384;
+__global__ void __launch_bounds__(256)
+white_mean_kernel(const uint16_t* __restrict__ zt, int64_t kt, const float* __restrict__ nw, int64_t K,
+                  int64_t D, double* __restrict__ s1) {
+  __shared__ double red[kMeanRows][8];
+  const int64_t i0 = (int64_t)blockIdx.x * kMeanRows;
+  const int64_t kc0 = (int64_t)blockIdx.y * kMeanChunk;
+  const bool w_vec = (reinterpret_cast<uintptr_t>(nw) & 15) == 0;
+  float acc[kMeanRows];
+#pragma unroll
+  for (int r = 0; r < kMeanRows; ++r) acc[r] = 0.f;
+  for (int it = 0; it < kMeanChunk / (256 * 8); ++it) {
+    const int64_t k = kc0 + ((int64_t)it * 256 + threadIdx.x) * 8;
+    if (k >= K) break;
+    float w[8];
+    if (k + 8 <= K && w_vec) {
+      const float4 w0 = __ldg(reinterpret_cast<const float4*>(nw + k));
+      const float4 w1 = __ldg(reinterpret_cast<const float4*>(nw + k) + 1);
+      w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w; w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
+    } else {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) w[u] = (k + u < K) ? __ldg(nw + k + u) : 0.f;
+    }
+    uint4 zr[kMeanRows];
+#pragma unroll
+    for (int r = 0; r < kMeanRows; ++r)
+      zr[r] = (i0 + r < D) ? __ldg(reinterpret_cast<const uint4*>(zt + (i0 + r) * kt + k)) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int r = 0; r < kMeanRows; ++r) {
+      const uint32_t zw[4] = {zr[r].x, zr[r].y, zr[r].z, zr[r].w};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float2 zf = __half22float2(*reinterpret_cast<const __half2*>(&zw[u]));
+        acc[r] = fmaf(zf.x, w[2 * u], acc[r]);
+        acc[r] = fmaf(zf.y, w[2 * u + 1], acc[r]);
+      }
+    }
+  }
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+#pragma unroll
+  for (int r = 0; r < kMeanRows; ++r) {
+    const double v = warp_sum((double)acc[r]);
+    if (lane == 0) red[r][wp] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < kMeanRows && i0 + threadIdx.x < D) {
+    double v = 0.0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v += red[threadIdx.x][q];
+    atomicAdd(s1 + i0 + threadIdx.x, v);
+  }
+}
+
+constexpr int kWhiteThreads = 512;
+constexpr int kWStages = 3;                               // TMA ring: A source (16 KB) | B (32 KB)
+constexpr int kWPairStages = 2;                           // transformed A: 2 pair tiles (32 KB)
+constexpr uint32_t kWStageBytes = kABytes + kBBytes;      // 48 KB
+constexpr uint32_t kWPairBytes = 2 * kABytes;             // 32 KB
+constexpr uint32_t kWPipeBytes = kWStages * kWStageBytes + kWPairStages * kWPairBytes;  // 208 KB
+constexpr uint32_t kWhiteSmemBytes = kWPipeBytes + 1024 /*align*/ + 256 /*barriers*/;
+
+struct WhiteParams {
+  int num_st;         // 64-sample stages in the store row (kt / 64)
+  int chunk_st;       // stages per TMEM accumulation chunk
+  int st_per_split;   // stages handled by one CTA
+  int splits, tiles_n;
+  float* out;         // partials [splits][ld][ld]
+  int64_t ld, split_stride;
+  const uint16_t* wa; // scale_a nw_k = wa_k + wb_k as two fp16 arrays of kt entries (zero beyond K)
+  const uint16_t* wb;
+};
+
+template <int N>
+__device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N>
+__device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+
+__global__ void __launch_bounds__(kWhiteThreads, 1)
+syrk_white_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                  const WhiteParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t pair_base = base + kWStages * kWStageBytes;
+  const uint32_t bar_base = base + kWPipeBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (3 + s); };
+  auto pfull_bar = [&](int s) { return bar_base + 8u * (6 + s); };
+  auto pempty_bar = [&](int s) { return bar_base + 8u * (8 + s); };
+  auto tfull_bar = [&](int b) { return bar_base + 8u * (10 + b); };
+  auto tempty_bar = [&](int b) { return bar_base + 8u * (12 + b); };
+  uint8_t* smem = smem_raw + (base - raw);
+  volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem + kWPipeBytes + 8 * 14);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kWStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < kWPairStages; ++s) { mbar_init(pfull_bar(s), 4); mbar_init(pempty_bar(s), 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 ::"r"(smem_u32((const void*)tmem_ptr_smem)), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  // ---- tile / k-range of this CTA (upper-triangular tiles, as syrk_gemm_kernel) ----
+  int t = blockIdx.x / p.splits;
+  const int split = blockIdx.x % p.splits;
+  int tm = 0, tn = 0;
+  for (;; ++tm) {
+    const int tn_min = (tm * BM) / BN;
+    const int cnt = p.tiles_n - tn_min;
+    if (t < cnt) { tn = tn_min + t; break; }
+    t -= cnt;
+  }
+  const int st_begin = split * p.st_per_split;
+  const int st_end = min(p.num_st, st_begin + p.st_per_split);
+  const int nst = max(0, st_end - st_begin);
+  const int nchunks = (nst + p.chunk_st - 1) / p.chunk_st;
+
+  if (warp < 4) {
+    reg_dec<48>();
+    if (warp == 0 && lane == 0 && nst > 0) {
+      // ================= TMA producer =================
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int st = st_begin; st < st_end; ++st) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        const uint32_t sb = base + stage * kWStageBytes;
+        mbar_expect_tx(full_bar(stage), kWStageBytes);
+        tma_load_2d(sb, &map_a, full_bar(stage), st * 64, tm * BM);
+        tma_load_2d(sb + kABytes, &map_b, full_bar(stage), st * 64, tn * BN);
+        if (++stage == kWStages) { stage = 0; phase ^= 1u; }
+      }
+    } else if (warp == 1 && lane == 0 && nst > 0) {
+      // ================= MMA issuer =================
+      int stage = 0, ps = 0;
+      uint32_t phase = 0, pphase = 0;
+      int st = 0;
+      for (int c = 0; c < nchunks; ++c) {
+        const int buf = c & 1;
+        mbar_wait(tempty_bar(buf), (((uint32_t)c >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)buf * BN;
+        const int st_chunk_end = min(nst, st + p.chunk_st);
+        uint32_t accumulate = 0;
+        for (; st < st_chunk_end; ++st) {
+          mbar_wait(full_bar(stage), phase);    // B landed
+          mbar_wait(pfull_bar(ps), pphase);     // A transformed
+          tc_fence_after();
+          const uint32_t bt = base + stage * kWStageBytes + kABytes;
+          const uint32_t pa = pair_base + ps * kWPairBytes;
+          issue_f16_pair_single(tmem_d, pa, bt, 0, accumulate);
+          issue_f16_pair_single(tmem_d, pa + kABytes, bt, 1, accumulate);
+          tc_commit(empty_bar(stage));
+          tc_commit(pempty_bar(ps));
+          if (++stage == kWStages) { stage = 0; phase ^= 1u; }
+          if (++ps == kWPairStages) { ps = 0; pphase ^= 1u; }
+        }
+        tc_commit(tfull_bar(buf));
+      }
+    }
+  } else if (warp < 12) {
+    reg_inc<176>();
+    // ================= drain TMEM chunks into fp32 registers =================
+    const int e = warp - 4;
+    const int q = warp & 3;   // TMEM lane quarter this warp may access
+    const int h = e >> 2;     // column half
+    float acc[128];
+#pragma unroll
+    for (int i = 0; i < 128; ++i) acc[i] = 0.f;
+    for (int c = 0; c < nchunks; ++c) {
+      const int buf = c & 1;
+      mbar_wait(tfull_bar(buf), ((uint32_t)c >> 1) & 1u);
+      tc_fence_after();
+      drain_add(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN + h * 128), acc);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(buf));
+    }
+    const int64_t m = (int64_t)tm * BM + q * 32 + lane;
+    const int64_t n0 = (int64_t)tn * BN + h * 128;
+    if (m < p.ld) {
+      float* dst = p.out + (int64_t)split * p.split_stride + m * p.ld + n0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (n0 + 4 * j < p.ld)
+          reinterpret_cast<float4*>(dst)[j] = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
+    }
+  } else {
+    reg_dec<112>();
+    // ================= transform: A box (exact fp16 z) -> fp16 pair of (scale_a nw_k) z =================
+    // All in packed half arithmetic.  With the weight itself split as wa + wb (fp16 each, white_weights_kernel):
+    //   h1 = rn(wa z)            HMUL2
+    //   r  = wa z - h1           HFMA2, exact (the rounding error of an fp16 product is an fp16 number)
+    //   h2 = rn(wb z + r)        HFMA2
+    // so h1 + h2 = (wa + wb) z up to 2^-22 relative, three instructions per two values.
+    const int tt = threadIdx.x - 384;   // 0..127
+    const int c = tt & 7;               // 16-byte chunk of the 128-byte source row: samples 8c .. 8c+7
+    const int r0 = tt >> 3;             // rows r0 + 16 j
+    int stage = 0, ps = 0;
+    uint32_t phase = 0, pphase = 0;
+    // the split weights of the next stage are fetched one stage ahead (an L2 round trip per stage would
+    // otherwise sit on the transform -> MMA critical path); the arrays are zero-padded to kt
+    uint4 wa_n = make_uint4(0, 0, 0, 0), wb_n = wa_n;
+    if (nst > 0) {
+      const int64_t k = (int64_t)st_begin * 64 + c * 8;
+      wa_n = __ldg(reinterpret_cast<const uint4*>(p.wa + k));
+      wb_n = __ldg(reinterpret_cast<const uint4*>(p.wb + k));
+    }
+    for (int st = st_begin; st < st_end; ++st) {
+      const uint32_t wa[4] = {wa_n.x, wa_n.y, wa_n.z, wa_n.w}, wb[4] = {wb_n.x, wb_n.y, wb_n.z, wb_n.w};
+      if (st + 1 < st_end) {
+        const int64_t k = (int64_t)(st + 1) * 64 + c * 8;
+        wa_n = __ldg(reinterpret_cast<const uint4*>(p.wa + k));
+        wb_n = __ldg(reinterpret_cast<const uint4*>(p.wb + k));
+      }
+      mbar_wait(full_bar(stage), phase);
+      mbar_wait(pempty_bar(ps), pphase ^ 1u);
+      const uint8_t* src = smem + stage * kWStageBytes;
+      uint8_t* dst = smem + kWStages * kWStageBytes + ps * kWPairBytes + (c >> 2) * kABytes;
+      const int jj = c & 3;
+      const bool lo_half = c < 4;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int r = r0 + 16 * j;
+        const int x = r & 7;
+        const uint4 zr = *reinterpret_cast<const uint4*>(src + r * 128 + ((c ^ x) << 4));
+        const uint32_t zw[4] = {zr.x, zr.y, zr.z, zr.w};
+        uint32_t h1[4], h2[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const __half2 z2 = *reinterpret_cast<const __half2*>(&zw[u]);
+          const __half2 a2 = *reinterpret_cast<const __half2*>(&wa[u]);
+          const __half2 b2 = *reinterpret_cast<const __half2*>(&wb[u]);
+          const __half2 hi = __hmul2_rn(a2, z2);
+          const __half2 rem = __hfma2(a2, z2, __hneg2(hi));
+          const __half2 lo = __hfma2(b2, z2, rem);
+          h1[u] = *reinterpret_cast<const uint32_t*>(&hi);
+          h2[u] = *reinterpret_cast<const uint32_t*>(&lo);
+        }
+        // lanes c < 4 (first pair tile) store h1 then h2, lanes c >= 4 (second tile, same banks 16 KB further)
+        // h2 then h1: the 8 lanes of a quarter warp always hit 8 different 16-byte bank groups
+        const uint4 v1 = make_uint4(h1[0], h1[1], h1[2], h1[3]), v2 = make_uint4(h2[0], h2[1], h2[2], h2[3]);
+        const int p1 = (jj ^ x) << 4, p2 = ((4 + jj) ^ x) << 4;
+        *reinterpret_cast<uint4*>(dst + r * 128 + (lo_half ? p1 : p2)) = lo_half ? v1 : v2;
+        *reinterpret_cast<uint4*>(dst + r * 128 + (lo_half ? p2 : p1)) = lo_half ? v2 : v1;
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> tcgen05 reads
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pfull_bar(ps));
+      if (++stage == kWStages) { stage = 0; phase ^= 1u; }
+      if (++ps == kWPairStages) { ps = 0; pphase ^= 1u; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+  }
+}
+
 static size_t white_op_bytes(const SyrkPlan& pl, int injected) {
   // A pair (4 B) + B single (2 B) or pair (4 B) per (column, sample)
   return (size_t)pl.Dp * pl.Kc * (injected ? 8 : 6);
@@ -1150,6 +1508,9 @@ static size_t white_op_bytes(const SyrkPlan& pl, int injected) {
 extern "C" size_t ppi_wmoments_white_workspace_bytes(int64_t K, int64_t D, int injected) {
   if (K <= 0 || D <= 0) return 0;
   const SyrkPlan pl = syrk_plan(K, D);
+  if (!injected)  // direct kernel: scalars + one fp32 partial per split (splits <= SMs / tiles)
+    return kScalarBytes + (size_t)round_up(4 * zstore_kt(K), 1024) +
+           (size_t)(kNumSMs / pl.ntiles < 1 ? 1 : kNumSMs / pl.ntiles) * pl.Dp * pl.Dp * sizeof(float) + 2048;
   return kScalarBytes + white_op_bytes(pl, injected) + pl.partial_bytes + 2048;
 }
 
@@ -1163,7 +1524,7 @@ static int wmoments_white_impl(const void* zstore, const float* nw, int64_t K, i
   GemmScalars* scalars = (GemmScalars*)wsp;
   const GemmScalars* zs = (const GemmScalars*)zstore;
   const char* store_rows = (const char*)zstore + kScalarBytes;
-  const size_t store_row_bytes = zstore_row_bytes(D, ZPAIR ? 1 : 0);
+  const size_t store_row_bytes = zstore_row_bytes(D);
   void* op_a = (void*)(wsp + kScalarBytes);
   void* op_b = (void*)(wsp + kScalarBytes + (size_t)pl.Dp * pl.Kc * 4);
   float* partials = (float*)(wsp + kScalarBytes + white_op_bytes(pl, ZPAIR ? 1 : 0));
@@ -1224,6 +1585,66 @@ static int wmoments_white_impl(const void* zstore, const float* nw, int64_t K, i
   return check_launch("syrk_reduce_kernel");
 }
 
+// Philox store (K-major): one launch over all K samples, no operand pre-pass.
+static int wmoments_white_direct(const void* zstore, const float* nw, int64_t K, int64_t D, double* s1,
+                                 float* cov, int accumulate, void* workspace, cudaStream_t st) {
+  const SyrkPlan pl = syrk_plan(K, D);
+  const int64_t kt = zstore_kt(K);
+  char* wsp = (char*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
+  GemmScalars* scalars = (GemmScalars*)wsp;
+  uint16_t* wa = (uint16_t*)(wsp + kScalarBytes);
+  uint16_t* wb = wa + kt;
+  float* partials = (float*)(wsp + kScalarBytes + round_up(4 * kt, 1024));
+  const uint16_t* zt = (const uint16_t*)((const char*)zstore + kScalarBytes);
+  {
+    ProfileScope prof(PPI_PROF_SYRK_OPERAND, st);
+    PPI_CUDA_TRY(cudaMemsetAsync(scalars, 0, sizeof(GemmScalars), st));
+    absmax_kernel<<<grid_cap(ceil_div(K, 1024), 4), 256, 0, st>>>(nw, K, &scalars->amax_a_bits);
+    white_scale_kernel<<<1, 1, 0, st>>>(scalars, (const GemmScalars*)zstore, 0);
+    white_weights_kernel<<<grid_cap(ceil_div(kt, 256), 8), 256, 0, st>>>(nw, K, kt, scalars, wa, wb);
+    if (int rc = check_launch("white scale kernels", 3)) return rc;
+  }
+  if (s1) {
+    ProfileScope prof(PPI_PROF_WMOMENTS_DIAG, st);
+    dim3 mg((unsigned)ceil_div(D, kMeanRows), (unsigned)ceil_div(K, kMeanChunk));
+    white_mean_kernel<<<mg, 256, 0, st>>>(zt, kt, nw, K, D, s1);
+    if (int rc = check_launch("white_mean_kernel")) return rc;
+  }
+  CUtensorMap a, b;
+  if (int rc = make_map(&a, zt, pl.Dp, kt, BM, OP_F16_SINGLE)) return rc;
+  if (int rc = make_map(&b, zt, pl.Dp, kt, BN, OP_F16_SINGLE)) return rc;
+  WhiteParams p;
+  p.num_st = (int)(kt / 64);
+  p.chunk_st = gemm_chunk() / 2 < 1 ? 1 : gemm_chunk() / 2;
+  int64_t splits = kNumSMs / pl.ntiles;
+  if (splits > p.num_st / p.chunk_st) splits = p.num_st / p.chunk_st;
+  if (splits < 1) splits = 1;
+  p.splits = (int)splits;
+  p.st_per_split = (int)round_up((p.num_st + splits - 1) / splits, p.chunk_st);
+  p.tiles_n = (int)pl.tiles_n;
+  p.out = partials;
+  p.ld = pl.Dp;
+  p.split_stride = pl.Dp * pl.Dp;
+  p.wa = wa;
+  p.wb = wb;
+  static bool attr_set = false;
+  if (!attr_set) {
+    PPI_CUDA_TRY(cudaFuncSetAttribute(syrk_white_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)kWhiteSmemBytes));
+    attr_set = true;
+  }
+  {
+    ProfileScope prof(PPI_PROF_SYRK_GEMM, st);
+    syrk_white_kernel<<<(unsigned)(pl.ntiles * splits), kWhiteThreads, kWhiteSmemBytes, st>>>(a, b, p);
+    if (int rc = check_launch("syrk_white_kernel")) return rc;
+  }
+  ProfileScope prof(PPI_PROF_SYRK_REDUCE, st);
+  syrk_reduce_kernel<<<grid_cap(ceil_div(D * D, 256), 8), 256, 0, st>>>(partials, (int)splits, pl.Dp,
+                                                                         pl.Dp * pl.Dp, D, cov, accumulate,
+                                                                         scalars);
+  return check_launch("syrk_reduce_kernel");
+}
+
 extern "C" int ppi_wmoments_white(const void* zstore, int injected, const float* nw, int64_t K,
                                   int64_t D, double* s1, float* cov, int accumulate, void* workspace,
                                   size_t workspace_bytes, void* stream) {
@@ -1233,7 +1654,7 @@ extern "C" int ppi_wmoments_white(const void* zstore, int injected, const float*
               "ppi_wmoments_white: workspace too small");
   if (injected)
     return wmoments_white_impl<true>(zstore, nw, K, D, s1, cov, accumulate, workspace, (cudaStream_t)stream);
-  return wmoments_white_impl<false>(zstore, nw, K, D, s1, cov, accumulate, workspace, (cudaStream_t)stream);
+  return wmoments_white_direct(zstore, nw, K, D, s1, cov, accumulate, workspace, (cudaStream_t)stream);
 }
 
 // sample.cu
@@ -1254,9 +1675,11 @@ extern "C" size_t ppi_sample_gaussian_workspace_bytes(int64_t K, int64_t D) {
 // !FP16: TF32X3 (ZPAIR ignored; the low-order z operand is skipped for Philox normals).
 // Base-normal store kept for the whitened moment match (ppi_sample_gaussian_keep /
 // ppi_wmoments_white): a 1 KB header (GemmScalars of the sampling call: scale_b = power-of-two scale
-// of the stored injected normals, amax_b_bits = max |z|) followed by round_up(K, 256) rows of
-//   Philox    round_up(D, 64) exact fp16 normals                       (2 B per value)
-//   injected  round_up(D, 64) / 32 blocks of [h1 x 32 | h2 x 32] fp16  (4 B per value, scaled)
+// of the stored injected normals, amax_b_bits = max |z|) followed by
+//   Philox    zT: round_up(D, 128) rows (one per column of z) of round_up(K, 256) exact fp16 normals,
+//             i.e. already K-major for the contraction over samples (2 B per value)
+//   injected  round_up(K, 256) sample rows of round_up(D, 64) / 32 blocks [h1 x 32 | h2 x 32] fp16
+//             (4 B per value, scaled by scale_b)
 
 template <bool FP16, bool ZPAIR>
 static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
@@ -1291,15 +1714,17 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
       L, D, D, Dk, 0, 0, 0, 1, FP16 ? &scalars->scale_a : nullptr, l_a, l_b);
   if (int rc = check_launch("split_rows_kernel(L)")) return rc;
 
-  // with a store every pass stages its rows straight into the store (no ping-pong, nothing to overlap)
+  // injected normals + store: every pass stages its (pair) rows straight into the store (no ping-pong);
+  // Philox + store: the staging kernel writes the ping-pong rows AND the K-major store
   char* store_rows = zstore ? (char*)zstore + kScalarBytes : nullptr;
-  const size_t store_row_bytes = zstore_row_bytes(D, ZPAIR ? 1 : 0);
-  const bool overlap = FP16 && gemm_overlap() && K > Kc && !zstore;
+  const size_t store_row_bytes = zstore_row_bytes(D);
+  const bool store_pairs = zstore && ZPAIR;
+  const bool overlap = FP16 && gemm_overlap() && K > Kc && !store_pairs;
   void* zbufs[2] = {z_a, FP16 ? z_b : z_a};
   CUtensorMap ml, ml2, mz[2], mz2[2];
   if (int rc = make_map(&ml, l_a, D, Dk, BM, LMODE)) return rc;
   ml2 = ml;
-  for (int i = 0; i < (FP16 ? 2 : 1) && !zstore; ++i) {
+  for (int i = 0; i < (FP16 ? 2 : 1) && !store_pairs; ++i) {
     if (int rc = make_map(&mz[i], zbufs[i], Kc, Dk, BN, ZMODE)) return rc;
     mz2[i] = mz[i];
   }
@@ -1338,7 +1763,7 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
     const int bi = overlap ? (pass & 1) : 0;
     const int64_t rows = (K - k0) < Kc ? (K - k0) : Kc;
     const int64_t rows_p = round_up(rows, BN);
-    if (zstore) {
+    if (store_pairs) {
       zbufs[0] = store_rows + (size_t)k0 * store_row_bytes;
       if (int rc = make_map(&mz[0], zbufs[0], rows_p, Dk, BN, ZMODE)) return rc;
       mz2[0] = mz[0];
@@ -1349,10 +1774,18 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
       if (overlap && pass >= 2) PPI_CUDA_TRY(cudaStreamWaitEvent(st_op, ss->gemm_done[bi], 0));
       ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st_op);
       const int64_t nrows = z ? rows : rows_p;
-      split_rows_kernel<ZMODE><<<grid_cap(nrows, 8), 256, 0, st_op>>>(
-          z ? z + k0 * D : nullptr, nrows, D, Dk, seed, draw_id, row_offset + (uint64_t)k0, 0,
-          FP16 ? &scalars->scale_b : nullptr, zbufs[bi], (!FP16 && !z_exact) ? z_b : nullptr);
-      if (int rc = check_launch("split_rows_kernel(z)")) return rc;
+      if (zstore && !ZPAIR) {
+        const int64_t zt_rows = round_up(D, BM);
+        philox_dual_kernel<<<grid_cap((nrows / 64) * ceil_div(zt_rows, 128), 6), 256, 0, st_op>>>(
+            nrows, D, Dk, seed, draw_id, row_offset + (uint64_t)k0, (uint16_t*)zbufs[bi],
+            (uint16_t*)store_rows, zt_rows, zstore_kt(K), k0);
+        if (int rc = check_launch("philox_dual_kernel")) return rc;
+      } else {
+        split_rows_kernel<ZMODE><<<grid_cap(nrows, 8), 256, 0, st_op>>>(
+            z ? z + k0 * D : nullptr, nrows, D, Dk, seed, draw_id, row_offset + (uint64_t)k0, 0,
+            FP16 ? &scalars->scale_b : nullptr, zbufs[bi], (!FP16 && !z_exact) ? z_b : nullptr);
+        if (int rc = check_launch("split_rows_kernel(z)")) return rc;
+      }
     }
     if (overlap) {
       PPI_CUDA_TRY(cudaEventRecord(ss->op_done[bi], st_op));
@@ -1391,7 +1824,8 @@ extern "C" int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_
 
 extern "C" size_t ppi_zstore_bytes(int64_t K, int64_t D, int injected) {
   if (K <= 0 || D <= 128) return 0;
-  return kScalarBytes + (size_t)round_up(K, BN) * zstore_row_bytes(D, injected) + 1024;
+  if (injected) return kScalarBytes + (size_t)round_up(K, BN) * zstore_row_bytes(D) + 1024;
+  return kScalarBytes + (size_t)round_up(D, BM) * zstore_kt(K) * 2 + 1024;
 }
 
 extern "C" int ppi_sample_gaussian_keep(const float* z, uint64_t seed, uint64_t draw_id,
