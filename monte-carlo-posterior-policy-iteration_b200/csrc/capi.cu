@@ -48,10 +48,12 @@ ProfileScope::~ProfileScope() {
 namespace ppi {
 static std::atomic<int> g_gemm_scheme{PPI_GEMM_FP16X2};
 int gemm_scheme() { return g_gemm_scheme.load(std::memory_order_relaxed); }
-static std::atomic<int> g_gemm_chunk{4};
+static std::atomic<int> g_gemm_chunk{8};
 int gemm_chunk() { return g_gemm_chunk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_gemm_overlap{0};
 int gemm_overlap() { return g_gemm_overlap.load(std::memory_order_relaxed); }
+static std::atomic<int> g_gemm_pair{0};
+int gemm_pair() { return g_gemm_pair.load(std::memory_order_relaxed); }
 }  // namespace ppi
 
 extern "C" int ppi_set_option(int key, int value) {
@@ -68,13 +70,15 @@ extern "C" int ppi_set_option(int key, int value) {
     return 0;
   }
   if (key == PPI_OPT_GEMM_OVERLAP) { ppi::g_gemm_overlap.store(value != 0); return 0; }
+  if (key == PPI_OPT_GEMM_PAIR) { ppi::g_gemm_pair.store(value != 0); return 0; }
   PPI_REQUIRE(false, PPI_ERR_INVALID, "ppi_set_option: unknown key %d", key);
 }
 
 extern "C" int ppi_get_option(int key) {
   return key == PPI_OPT_GEMM_SCHEME ? ppi::gemm_scheme()
        : key == PPI_OPT_GEMM_CHUNK ? ppi::gemm_chunk()
-       : key == PPI_OPT_GEMM_OVERLAP ? ppi::gemm_overlap() : -1;
+       : key == PPI_OPT_GEMM_OVERLAP ? ppi::gemm_overlap()
+       : key == PPI_OPT_GEMM_PAIR ? ppi::gemm_pair() : -1;
 }
 
 extern "C" int64_t ppi_launch_count(void) { return ppi::g_launches.load(); }

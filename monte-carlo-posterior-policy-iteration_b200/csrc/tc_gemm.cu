@@ -54,6 +54,12 @@ constexpr int kMaxStages = 4;
 constexpr uint32_t kPipeBytes = 192 * 1024; // every variant uses stages * stage_bytes = 192 KB
 constexpr uint32_t kGemmSmemBytes = kPipeBytes + 1024 /*align*/ + 256 /*barriers*/;
 
+// K-major base-normal store (ppi_sample_gaussian_keep, Philox): blocks of kZBlock samples
+constexpr int64_t kZBlock = 2048;
+__host__ __device__ inline int64_t zt_index(int64_t k, int64_t i, int64_t rows) {
+  return ((k / kZBlock) * rows + i) * kZBlock + (k % kZBlock);
+}
+
 // ---------------------------------------------------------------------------------------------
 // PTX wrappers
 // ---------------------------------------------------------------------------------------------
@@ -591,6 +597,247 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
 }
 
 // ---------------------------------------------------------------------------------------------
+// 2-CTA helpers (cta_group::2): a cluster of two CTAs on one TPC issues one UMMA of M = 256; every
+// CTA keeps its own 128 A rows and HALF of the B rows in its shared memory, so the shared-memory
+// traffic per MMA (the resource that bounds the 1-CTA kernels: 12 KB of operand reads per 128-cycle
+// MMA + the TMA fill, against 128 B/clk) drops by a third.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `addr` (a shared::cta address of this CTA) in CTA `rank`
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+// TMA load whose completion bytes are counted on the LEADER CTA's mbarrier (peer bit cleared)
+__device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                                int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_2sm(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16_2sm(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// kind::f16, fp32 accumulate, K-major operands, M = 256 (two CTAs x 128 rows), N = 256
+constexpr uint32_t kIdescF16Pair = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+
+// pair x single over one 64-step stage: A = two pair tiles (32 steps each), B = this CTA's half of the
+// 256 B rows (128 rows x 64 exact fp16)
+__device__ __forceinline__ void issue_f16_pair_single_2sm(uint32_t tmem_d, uint32_t a, uint32_t b, int half,
+                                                          uint32_t& accumulate) {
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const uint32_t off = (uint32_t)k * 32u;
+    const uint64_t bz = make_desc(b + (uint32_t)half * 64u + off);
+    tc_mma_f16_2sm(tmem_d, make_desc(a + off), bz, kIdescF16Pair, accumulate);
+    accumulate = 1u;
+    tc_mma_f16_2sm(tmem_d, make_desc(a + 64u + off), bz, kIdescF16Pair, 1u);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sampling kernel, CTA pairs (Philox normals):  x[s, j] = mu[j] + sum_{k<=j} L[j,k] z[s,k]
+//   One UMMA = 256 output columns j (CTA r owns j-tile 2t + r) x 256 samples; CTA r loads its own L
+//   rows (pair, 2 x 16 KB per 64-step stage) and samples [128 r, 128 r + 128) of the z block (16 KB).
+//   Work unit = (sample block, p): double tiles t = T2-1-p then t = p (equal triangular cost).
+//   Barriers: full[s] lives in the leader (both CTAs' TMA bytes complete on it); empty[s] / tfull[b]
+//   are multicast commits to both CTAs; tempty[b] lives in the leader (8 drain warps per CTA arrive).
+// ---------------------------------------------------------------------------------------------
+constexpr int kS2Stages = 4;
+constexpr uint32_t kS2StageBytes = 2 * kABytes + kABytes;  // L pair x2 (32 KB) | z half (16 KB) = 48 KB
+static_assert(kS2Stages * kS2StageBytes == kPipeBytes, "pipeline must fill the smem budget");
+
+struct Sample2Params {
+  int tiles2;           // double j-tiles: ceil(D / 256)
+  int units_per_block;  // ceil(tiles2 / 2)
+  int num_st;           // 64-step stages covering the padded contraction length
+  int chunk_st;         // stages per TMEM accumulation chunk
+  int64_t n_units;      // sample blocks * units_per_block
+  int64_t rows;         // valid samples in this pass
+  int64_t D;
+  float* x;             // [rows][D]
+  const float* mu;
+  const GemmScalars* scalars;
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+sample_gemm2_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_constant__ CUtensorMap map_z,
+                    const Sample2Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  GemmSmem gs;
+  gs.base = (raw + 1023u) & ~1023u;
+  gs.bar_base = gs.base + kPipeBytes;
+  uint8_t* smem = smem_raw + (gs.base - raw);
+  volatile uint32_t* tmem_ptr_smem =
+      reinterpret_cast<volatile uint32_t*>(smem + kPipeBytes + 8 * (2 * kMaxStages + 4));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kMaxStages; ++s) { mbar_init(gs.full_bar(s), 1); mbar_init(gs.empty_bar(s), 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(gs.tfull_bar(b), 1); mbar_init(gs.tempty_bar(b), 16); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;"
+                 ::"r"(smem_u32((const void*)tmem_ptr_smem)), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  const int64_t cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;   // cluster index / count
+  auto tile2 = [&](int pr, int tt) { return tt == 0 ? p.tiles2 - 1 - pr : pr; };
+  auto tiles_in_unit = [&](int pr) { return (p.tiles2 - 1 - pr != pr) ? 2 : 1; };
+  auto stages_of = [&](int t2) { return min(p.num_st, ((t2 + 1) * 256 + 63) / 64); };  // L lower triangular
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ================= TMA producer (both CTAs) =================
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_l) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_z) : "memory");
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int64_t u = cid; u < p.n_units; u += ncl) {
+        const int nb = (int)(u / p.units_per_block), pr = (int)(u % p.units_per_block);
+        for (int tt = 0; tt < tiles_in_unit(pr); ++tt) {
+          const int t2 = tile2(pr, tt), nst = stages_of(t2);
+          const int jrow = (2 * t2 + (int)rank) * BM;
+          for (int s = 0; s < nst; ++s) {
+            mbar_wait(gs.empty_bar(stage), phase ^ 1u);
+            const uint32_t sb = gs.base + stage * kS2StageBytes;
+            const uint32_t fb = gs.full_bar(stage);
+            if (leader) mbar_expect_tx(fb, 2 * kS2StageBytes);   // the bytes of both CTAs
+            tma_load_2d_2sm(sb, &map_l, fb, (2 * s) * 64, jrow);
+            tma_load_2d_2sm(sb + kABytes, &map_l, fb, (2 * s + 1) * 64, jrow);
+            tma_load_2d_2sm(sb + 2 * kABytes, &map_z, fb, s * 64, nb * BN + (int)rank * 128);
+            if (++stage == kS2Stages) { stage = 0; phase ^= 1u; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && leader) {
+      // ================= MMA issuer (leader CTA only) =================
+      int stage = 0;
+      uint32_t phase = 0, ccount = 0;
+      for (int64_t u = cid; u < p.n_units; u += ncl) {
+        const int pr = (int)(u % p.units_per_block);
+        for (int tt = 0; tt < tiles_in_unit(pr); ++tt) {
+          const int nst = stages_of(tile2(pr, tt));
+          for (int s0 = 0; s0 < nst; s0 += p.chunk_st, ++ccount) {
+            const uint32_t buf = ccount & 1u;
+            mbar_wait_cluster(gs.tempty_bar(buf), ((ccount >> 1) & 1u) ^ 1u);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + buf * BN;
+            uint32_t accumulate = 0;
+            const int s1 = min(nst, s0 + p.chunk_st);
+            for (int s = s0; s < s1; ++s) {
+              mbar_wait_cluster(gs.full_bar(stage), phase);
+              tc_fence_after();
+              const uint32_t sb = gs.base + stage * kS2StageBytes;
+              issue_f16_pair_single_2sm(tmem_d, sb, sb + 2 * kABytes, 0, accumulate);
+              issue_f16_pair_single_2sm(tmem_d, sb + kABytes, sb + 2 * kABytes, 1, accumulate);
+              tc_commit_2sm(gs.empty_bar(stage));
+              if (++stage == kS2Stages) { stage = 0; phase ^= 1u; }
+            }
+            tc_commit_2sm(gs.tfull_bar(buf));
+          }
+        }
+      }
+    }
+  } else {
+    // ================= epilogue (both CTAs): TMEM -> registers -> global =================
+    const int e = warp - 2;
+    const int q = warp & 3;   // TMEM lane quarter
+    const int h = e >> 2;     // sample (column) half
+    const float inv_scale = p.scalars ? p.scalars->inv_scale : 1.0f;
+    uint32_t ccount = 0;
+    for (int64_t u = cid; u < p.n_units; u += ncl) {
+      const int nb = (int)(u / p.units_per_block), pr = (int)(u % p.units_per_block);
+      for (int tt = 0; tt < tiles_in_unit(pr); ++tt) {
+        const int t2 = tile2(pr, tt), nst = stages_of(t2);
+        const int64_t j = (int64_t)(2 * t2 + (int)rank) * BM + q * 32 + lane;
+        const bool jok = j < p.D;
+        const float bias = jok ? __ldg(p.mu + j) : 0.f;
+        float acc[128];
+#pragma unroll
+        for (int i = 0; i < 128; ++i) acc[i] = 0.f;
+        for (int s0 = 0; s0 < nst; s0 += p.chunk_st, ++ccount) {
+          const uint32_t buf = ccount & 1u;
+          mbar_wait(gs.tfull_bar(buf), (ccount >> 1) & 1u);
+          tc_fence_after();
+          drain_add(tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + (uint32_t)(h * 128), acc);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_rank(gs.tempty_bar(buf), 0));
+        }
+        const int64_t s_first = (int64_t)nb * BN + h * 128;
+        const int64_t left = p.rows - s_first;
+        if (jok && left > 0) {
+          float* dst = p.x + s_first * p.D + j;
+          if (left >= 128) {
+#pragma unroll
+            for (int c = 0; c < 128; ++c) dst[(int64_t)c * p.D] = fmaf(acc[c], inv_scale, bias);
+          } else {
+#pragma unroll
+            for (int c = 0; c < 128; ++c)
+              if (c < left) dst[(int64_t)c * p.D] = fmaf(acc[c], inv_scale, bias);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512)
+                 : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // operand pre-passes
 // ---------------------------------------------------------------------------------------------
 enum { OP_TF32X3 = 0, OP_F16_PAIR = 1, OP_F16_SINGLE = 2 };
@@ -799,7 +1046,7 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
 __global__ void __launch_bounds__(256)
 philox_dual_kernel(int64_t rows, int64_t cols, int64_t cols_p, uint64_t seed, uint64_t draw,
                    uint64_t row_offset, uint16_t* __restrict__ op_rows, uint16_t* __restrict__ zt,
-                   int64_t zt_rows, int64_t kt, int64_t k0) {
+                   int64_t zt_rows, int64_t k0) {
   constexpr int kPitch = 130;  // halfs per tile row (65 words: the 8-sample column gathers spread over banks)
   __shared__ __half tile[64 * kPitch];
   const bool quad_rng = (cols & 3) == 0;
@@ -843,7 +1090,7 @@ philox_dual_kernel(int64_t rows, int64_t cols, int64_t cols_p, uint64_t seed, ui
         o.y = (uint32_t)h[2] | ((uint32_t)h[3] << 16);
         o.z = (uint32_t)h[4] | ((uint32_t)h[5] << 16);
         o.w = (uint32_t)h[6] | ((uint32_t)h[7] << 16);
-        *reinterpret_cast<uint4*>(zt + col * kt + k0 + tr * 64 + g * 8) = o;
+        *reinterpret_cast<uint4*>(zt + zt_index(k0 + tr * 64 + g * 8, col, zt_rows)) = o;
       }
     }
     __syncthreads();
@@ -917,8 +1164,10 @@ static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t kp,
 static int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
 // injected-normal store: sample-major rows of fp16 pairs
 static size_t zstore_row_bytes(int64_t D) { return (size_t)round_up(D, 64) * 4; }
-// Philox store: K-major, zT[i][k] = z[k][i], round_up(D, 128) rows of round_up(K, 256) exact fp16
-static int64_t zstore_kt(int64_t K) { return round_up(K, 256); }
+// Philox store: K-major and blocked over samples, zT[k / 2048][i][k % 2048] = z[k][i]: blocks of 2048
+// samples x round_up(D, 128) rows of exact fp16 (a TMA box of 128 / 256 rows then spans 0.5 / 1 MB instead
+// of one row pitch of 2 K bytes per row: measured 30 % faster at K = 2^20, where that pitch is a 2 MB page)
+static int64_t zstore_kt(int64_t K) { return round_up(K, kZBlock); }
 static int grid_cap(int64_t work, int per_sm) {
   const int64_t cap = (int64_t)kNumSMs * per_sm;
   return (int)(work < 1 ? 1 : (work < cap ? work : cap));
@@ -956,6 +1205,7 @@ static int side_stream(SideStream** out) {
   return 0;
 }
 int gemm_overlap();  // capi.cu: 1 = stage operands on the side stream
+int gemm_pair();     // capi.cu: 1 = CTA-pair (cta_group::2) kernels where they exist
 
 constexpr int64_t kSyrkKc = 65536;    // samples staged per pass
 constexpr int64_t kSampleKc = 65536;  // sample rows staged per pass
@@ -1232,7 +1482,7 @@ white_weights_kernel(const float* __restrict__ nw, int64_t K, int64_t kt, const 
 // s1[i] += sum_k nw_k zT[i][k]: block = 8 store rows x 16384 samples, weights loaded once per 8 rows.
 constexpr int kMeanRows = 8, kMeanChunk = 16384;
 __global__ void __launch_bounds__(256)
-white_mean_kernel(const uint16_t* __restrict__ zt, int64_t kt, const float* __restrict__ nw, int64_t K,
+white_mean_kernel(const uint16_t* __restrict__ zt, int64_t zt_rows, const float* __restrict__ nw, int64_t K,
                   int64_t D, double* __restrict__ s1) {
   __shared__ double red[kMeanRows][8];
   const int64_t i0 = (int64_t)blockIdx.x * kMeanRows;
@@ -1256,7 +1506,8 @@ white_mean_kernel(const uint16_t* __restrict__ zt, int64_t kt, const float* __re
     uint4 zr[kMeanRows];
 #pragma unroll
     for (int r = 0; r < kMeanRows; ++r)
-      zr[r] = (i0 + r < D) ? __ldg(reinterpret_cast<const uint4*>(zt + (i0 + r) * kt + k)) : make_uint4(0, 0, 0, 0);
+      zr[r] = (i0 + r < D) ? __ldg(reinterpret_cast<const uint4*>(zt + zt_index(k, i0 + r, zt_rows)))
+                           : make_uint4(0, 0, 0, 0);
 #pragma unroll
     for (int r = 0; r < kMeanRows; ++r) {
       const uint32_t zw[4] = {zr[r].x, zr[r].y, zr[r].z, zr[r].w};
@@ -1367,8 +1618,10 @@ syrk_white_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         mbar_wait(empty_bar(stage), phase ^ 1u);
         const uint32_t sb = base + stage * kWStageBytes;
         mbar_expect_tx(full_bar(stage), kWStageBytes);
-        tma_load_2d(sb, &map_a, full_bar(stage), st * 64, tm * BM);
-        tma_load_2d(sb + kABytes, &map_b, full_bar(stage), st * 64, tn * BN);
+        const int c0 = (st % (int)(kZBlock / 64)) * 64;                 // sample within its 2048-block
+        const int rb = (st / (int)(kZBlock / 64)) * (int)p.ld;          // first store row of that block
+        tma_load_2d(sb, &map_a, full_bar(stage), c0, rb + tm * BM);
+        tma_load_2d(sb + kABytes, &map_b, full_bar(stage), c0, rb + tn * BN);
         if (++stage == kWStages) { stage = 0; phase ^= 1u; }
       }
     } else if (warp == 1 && lane == 0 && nst > 0) {
@@ -1607,12 +1860,12 @@ static int wmoments_white_direct(const void* zstore, const float* nw, int64_t K,
   if (s1) {
     ProfileScope prof(PPI_PROF_WMOMENTS_DIAG, st);
     dim3 mg((unsigned)ceil_div(D, kMeanRows), (unsigned)ceil_div(K, kMeanChunk));
-    white_mean_kernel<<<mg, 256, 0, st>>>(zt, kt, nw, K, D, s1);
+    white_mean_kernel<<<mg, 256, 0, st>>>(zt, pl.Dp, nw, K, D, s1);
     if (int rc = check_launch("white_mean_kernel")) return rc;
   }
   CUtensorMap a, b;
-  if (int rc = make_map(&a, zt, pl.Dp, kt, BM, OP_F16_SINGLE)) return rc;
-  if (int rc = make_map(&b, zt, pl.Dp, kt, BN, OP_F16_SINGLE)) return rc;
+  if (int rc = make_map(&a, zt, (kt / kZBlock) * pl.Dp, kZBlock, BM, OP_F16_SINGLE)) return rc;
+  if (int rc = make_map(&b, zt, (kt / kZBlock) * pl.Dp, kZBlock, BN, OP_F16_SINGLE)) return rc;
   WhiteParams p;
   p.num_st = (int)(kt / 64);
   p.chunk_st = gemm_chunk() / 2 < 1 ? 1 : gemm_chunk() / 2;
@@ -1676,8 +1929,8 @@ extern "C" size_t ppi_sample_gaussian_workspace_bytes(int64_t K, int64_t D) {
 // Base-normal store kept for the whitened moment match (ppi_sample_gaussian_keep /
 // ppi_wmoments_white): a 1 KB header (GemmScalars of the sampling call: scale_b = power-of-two scale
 // of the stored injected normals, amax_b_bits = max |z|) followed by
-//   Philox    zT: round_up(D, 128) rows (one per column of z) of round_up(K, 256) exact fp16 normals,
-//             i.e. already K-major for the contraction over samples (2 B per value)
+//   Philox    zT[k / 2048][i][k % 2048] = z[k][i]: blocks of 2048 samples x round_up(D, 128) rows of exact
+//             fp16, i.e. already K-major for the contraction over samples (2 B per value)
 //   injected  round_up(K, 256) sample rows of round_up(D, 64) / 32 blocks [h1 x 32 | h2 x 32] fp16
 //             (4 B per value, scaled by scale_b)
 
@@ -1778,8 +2031,12 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
         const int64_t zt_rows = round_up(D, BM);
         philox_dual_kernel<<<grid_cap((nrows / 64) * ceil_div(zt_rows, 128), 6), 256, 0, st_op>>>(
             nrows, D, Dk, seed, draw_id, row_offset + (uint64_t)k0, (uint16_t*)zbufs[bi],
-            (uint16_t*)store_rows, zt_rows, zstore_kt(K), k0);
+            (uint16_t*)store_rows, zt_rows, k0);
         if (int rc = check_launch("philox_dual_kernel")) return rc;
+        const int64_t k_end = k0 + nrows, rem = k_end % kZBlock;
+        if (k_end >= K && rem)  // zero the unwritten tail of the last sample block (finite operands)
+          PPI_CUDA_TRY(cudaMemset2DAsync((uint16_t*)store_rows + zt_index(k_end, 0, zt_rows), kZBlock * 2, 0,
+                                         (kZBlock - rem) * 2, zt_rows, st_op));
       } else {
         split_rows_kernel<ZMODE><<<grid_cap(nrows, 8), 256, 0, st_op>>>(
             z ? z + k0 * D : nullptr, nrows, D, Dk, seed, draw_id, row_offset + (uint64_t)k0, 0,
@@ -1795,7 +2052,31 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
     p.rows = rows;
     p.x = x + k0 * D;
     const unsigned g = (unsigned)(p.n_units < kNumSMs ? p.n_units : kNumSMs);
-    {
+    if (FP16 && !ZPAIR && gemm_pair()) {
+      // CTA pairs (cta_group::2): each CTA loads its own L rows and half of the z block
+      static bool attr2_set = false;
+      if (!attr2_set) {
+        if (int rc = set_gemm_smem(sample_gemm2_kernel)) return rc;
+        attr2_set = true;
+      }
+      CUtensorMap mzh;
+      if (int rc = make_map(&mzh, zbufs[bi], rows_p, Dk, BM, ZMODE)) return rc;
+      Sample2Params p2;
+      p2.tiles2 = (int)ceil_div(D, 2 * BM);
+      p2.units_per_block = (p2.tiles2 + 1) / 2;
+      p2.num_st = p.num_st;
+      p2.chunk_st = p.chunk_st;
+      p2.n_units = (rows_p / BN) * p2.units_per_block;
+      p2.rows = rows;
+      p2.D = D;
+      p2.x = p.x;
+      p2.mu = mu;
+      p2.scalars = scalars;
+      int64_t ncl = p2.n_units < kNumSMs / 2 ? p2.n_units : kNumSMs / 2;
+      ProfileScope prof(PPI_PROF_SAMPLE_GEMM, st);
+      sample_gemm2_kernel<<<(unsigned)(2 * ncl), kGemmThreads, kGemmSmemBytes, st>>>(ml, mzh, p2);
+      if (int rc = check_launch("sample_gemm2_kernel")) return rc;
+    } else {
       ProfileScope prof(PPI_PROF_SAMPLE_GEMM, st);
       sample_gemm_kernel<FP16, ZPAIR><<<g, kGemmThreads, kGemmSmemBytes, st>>>(ml, ml2, mz[bi], mz2[bi], p);
       if (int rc = check_launch("sample_gemm_kernel")) return rc;
