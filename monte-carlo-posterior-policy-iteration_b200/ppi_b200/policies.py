@@ -209,15 +209,30 @@ class GaussianPolicy(object):
     small_dim = 128  # at or below: SIMT kernels + host fp64 tail; above: tcgen05 + device tail
 
     def __init__(self, mu, sigma, sampler, diagonal=False):
-        self.sigma_init = np.array(sigma, dtype=np.float64)
         self.sampler = sampler
         self.diagonal = diagonal  # factorized covariance
-        self._set(np.array(mu, dtype=np.float64), np.array(sigma, dtype=np.float64))
+        # like the reference (ppi/policies.py:238-241) mu / sigma are kept by reference; the private copy
+        # sigma_init lives in HBM for large D (one H2D of the caller's -- possibly pinned -- array, which
+        # is also the first device copy of sigma) and comes back to the host only if somebody reads it
+        sigma = np.asarray(sigma, dtype=np.float64)
+        self._dim = sigma.shape[0]
+        self._sigma_init_host = self._sigma_init_dev = None
+        self._set(np.asarray(mu, dtype=np.float64), sigma)
+        if self._dim > self.small_dim and torch.cuda.is_available():
+            self._sigma_init_dev = self._sigma64_dev = torch.as_tensor(sigma).to(require_cuda())
+        else:
+            self._sigma_init_host = sigma.copy()
+
+    @property
+    def sigma_init(self):
+        if self._sigma_init_host is None:
+            self._sigma_init_host = to_host64(self._sigma_init_dev)
+        return self._sigma_init_host
 
     # -- state: device fp32 copies used by the kernels, host fp64 mirrors read by callers --------
     def _set(self, mu, sigma, chol64=None, logdet=None):
         self._mu_host, self._sigma_host = mu, sigma
-        self._mu_dev = self._sigma_dev = self._chol_dev = None
+        self._mu_dev = self._sigma_dev = self._chol_dev = self._sigma64_dev = None
         self._chol64_dev, self._logdet = chol64, logdet
         self._version = getattr(self, "_version", 0) + 1  # invalidates base-normal stores of earlier draws
 
@@ -241,7 +256,7 @@ class GaussianPolicy(object):
     @sigma.setter
     def sigma(self, value):
         self._sigma_host, self._sigma_dev = np.asarray(value, np.float64), None
-        self._chol_dev = self._chol64_dev = self._logdet = None
+        self._chol_dev = self._chol64_dev = self._logdet = self._sigma64_dev = None
         self._version += 1
 
     def _mu_d(self):
@@ -250,6 +265,8 @@ class GaussianPolicy(object):
         return self._mu_dev
 
     def _sigma64_d(self):
+        if self._sigma64_dev is not None:   # the constructor's upload, valid until sigma changes
+            return self._sigma64_dev
         if self._sigma_dev is not None:
             return self._sigma_dev.double()
         if self._sigma_host is None:  # after a whitened update only the factor exists: sigma = L L^T
@@ -275,14 +292,14 @@ class GaussianPolicy(object):
 
     @property
     def entropy(self):
-        d = self.sigma_init.shape[0]
+        d = self._dim
         if d <= self.small_dim:
             return multivariate_gaussian_entropy(self.sigma, d)
         self._factor()
         return 0.5 * _clamped_logdet(self._logdet) + (d / 2) * (1 + np.log(2 * np.pi))
 
     def __call__(self, n_samples):
-        d = self.sigma_init.shape[0]
+        d = self._dim
         if not hasattr(self.sampler, "device_normals"):
             # foreign sampler: it owns the transform (ppi/policies.py:248)
             x = np.asarray(self.sampler(self.mu, self.sigma, n_samples, standard_gaussian=False))
@@ -379,13 +396,14 @@ class GaussianPolicy(object):
         self._mu_host, self._mu_dev = None, (mu_old_dev.double() + l_old @ m).float()
         if int(scal[0]) == 0:
             logdet_c = float(scal[1])
-            self._sigma_host = self._sigma_dev = self._chol_dev = None
+            self._sigma_host = self._sigma_dev = self._chol_dev = self._sigma64_dev = None
             self._chol64_dev, self._logdet = l_old @ g, old_logdet + logdet_c
             kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(self._logdet) + float(scal[2]) + float(scal[3]) - d)
         else:  # ppi/policies.py:263-268: keep the old covariance, regularised
             logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
             sigma_old = l_old @ l_old.T
             self._sigma_host, self._chol_dev, self._chol64_dev, self._logdet = None, None, None, None
+            self._sigma64_dev = None
             self._sigma_dev = (sigma_old + SIGMA_MIN * torch.eye(d, dtype=torch.float64, device=sigma_old.device)).float()
             self._factor()
             tr = torch.linalg.solve_triangular(l_old, self._chol64_dev, upper=False).square().sum()
@@ -431,7 +449,7 @@ class GaussianPolicy(object):
                 pd = int(info.item()) == 0
             # accept / regularise exactly like ppi/policies.py:258-268
             if pd:
-                self._sigma_host, self._sigma_dev = None, cov
+                self._sigma_host, self._sigma_dev, self._sigma64_dev = None, cov, None
                 self._chol64_dev, self._chol_dev = chol64, None
                 self._logdet = float(2.0 * torch.log(torch.diagonal(chol64)).sum().item())
             else:
@@ -439,8 +457,10 @@ class GaussianPolicy(object):
                 if sigma_old_host is not None:
                     self.sigma = sigma_old_host + SIGMA_MIN * np.eye(d)
                 else:
-                    self._sigma_host = None
-                    self._sigma_dev = sigma_old_dev + SIGMA_MIN * torch.eye(d, device=x.device)
+                    sigma_old = self._sigma64_d()  # device state still describes the old covariance
+                    self._sigma_host = self._sigma64_dev = None
+                    self._sigma_dev = (sigma_old + SIGMA_MIN * torch.eye(d, dtype=torch.float64,
+                                                                         device=x.device)).float()
                     self._chol_dev = self._chol64_dev = self._logdet = None
                 self._factor()
         # KL(new || old), ppi/policies.py:146-158,269, from the two Cholesky factors:
