@@ -134,15 +134,26 @@ __device__ __forceinline__ float u01(uint32_t r) {
 // this function, so they all see the same numbers.
 __device__ __forceinline__ float round_half(float v) { return __half2float(__float2half_rn(v)); }
 
-__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
-  float u = u01(a), v = u01(b);
+// [0, 1) from the top 23 bits without an integer -> float conversion (those share the 16-lane XU pipe
+// with the MUFU transcendentals, which is what bounds the generator): the angle needs no more.
+__device__ __forceinline__ float u01_23(uint32_t r) { return __uint_as_float(0x3F800000u | (r >> 9)) - 1.0f; }
+
+// One Box-Muller pair as a packed half2 (z0 low, z1 high) -- the form the tensor-core operand
+// stores want; box_muller() below widens exactly these values.
+__device__ __forceinline__ __half2 box_muller_h2(uint32_t a, uint32_t b) {
+  const float u = u01(a), v = u01_23(b);
   // every transcendental is a single MUFU instruction (lg2 / sqrt / sin / cos, no slow paths): the
   // result is rounded to 11 bits anyway
   float r, s, c;
   asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(-1.3862943611198906f * __log2f(u)));  // sqrt(-2 ln u)
   __sincosf(6.283185307179586f * v, &s, &c);
-  z0 = round_half(r * c);
-  z1 = round_half(r * s);
+  return __floats2half2_rn(r * c, r * s);
+}
+
+__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
+  const float2 z = __half22float2(box_muller_h2(a, b));
+  z0 = z.x;
+  z1 = z.y;
 }
 
 // The four normals of element quad q (elements 4q..4q+3 of the row-major global (K_total, n)
@@ -159,6 +170,14 @@ __device__ __forceinline__ void philox_normal4(const PhiloxKeys& ks, uint64_t dr
   Philox4 p = philox4x32_10(quad, draw_id, ks);
   box_muller(p.x, p.y, out[0], out[1]);
   box_muller(p.z, p.w, out[2], out[3]);
+}
+
+// Same four normals as two packed half2 (elements 4q, 4q+1 | 4q+2, 4q+3).
+__device__ __forceinline__ void philox_normal4_h2(const PhiloxKeys& ks, uint64_t draw_id, uint64_t quad,
+                                                  __half2& lo, __half2& hi) {
+  Philox4 p = philox4x32_10(quad, draw_id, ks);
+  lo = box_muller_h2(p.x, p.y);
+  hi = box_muller_h2(p.z, p.w);
 }
 
 // Single element e of the global matrix (slow path for unaligned access).

@@ -1058,18 +1058,20 @@ philox_dual_kernel(int64_t rows, int64_t cols, int64_t cols_p, uint64_t seed, ui
     for (int q = threadIdx.x; q < 64 * 32; q += 256) {
       const int r = q >> 5, c4 = (q & 31) * 4;
       const int64_t row = tr * 64 + r, col = tc * 128 + c4;
-      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      __half2 h01 = __floats2half2_rn(0.f, 0.f), h23 = h01;
       const uint64_t e_row = (row_offset + (uint64_t)row) * (uint64_t)cols;
       if (col < cols) {
         if (quad_rng) {
-          philox_normal4(keys, draw, (e_row + (uint64_t)col) >> 2, v);
+          philox_normal4_h2(keys, draw, (e_row + (uint64_t)col) >> 2, h01, h23);
         } else {
+          float v[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
           for (int u = 0; u < 4; ++u)
             if (col + u < cols) v[u] = philox_normal1(seed, draw, e_row + (uint64_t)col + u);
+          h01 = __floats2half2_rn(v[0], v[1]);
+          h23 = __floats2half2_rn(v[2], v[3]);
         }
       }
-      const __half2 h01 = __floats2half2_rn(v[0], v[1]), h23 = __floats2half2_rn(v[2], v[3]);
       if (col < cols_p)
         *reinterpret_cast<uint2*>(op_rows + row * cols_p + col) =
             make_uint2(*reinterpret_cast<const uint32_t*>(&h01), *reinterpret_cast<const uint32_t*>(&h23));
@@ -1082,14 +1084,12 @@ philox_dual_kernel(int64_t rows, int64_t cols, int64_t cols_p, uint64_t seed, ui
       const int g = e & 7, cl = e >> 3;
       const int64_t col = tc * 128 + cl;
       if (col < zt_rows) {
-        uint16_t h[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) h[u] = *reinterpret_cast<const uint16_t*>(tile + (g * 8 + u) * kPitch + cl);
+        const uint16_t* tp = reinterpret_cast<const uint16_t*>(tile) + (g * 8) * kPitch + cl;
         uint4 o;
-        o.x = (uint32_t)h[0] | ((uint32_t)h[1] << 16);
-        o.y = (uint32_t)h[2] | ((uint32_t)h[3] << 16);
-        o.z = (uint32_t)h[4] | ((uint32_t)h[5] << 16);
-        o.w = (uint32_t)h[6] | ((uint32_t)h[7] << 16);
+        o.x = (uint32_t)tp[0] | ((uint32_t)tp[kPitch] << 16);
+        o.y = (uint32_t)tp[2 * kPitch] | ((uint32_t)tp[3 * kPitch] << 16);
+        o.z = (uint32_t)tp[4 * kPitch] | ((uint32_t)tp[5 * kPitch] << 16);
+        o.w = (uint32_t)tp[6 * kPitch] | ((uint32_t)tp[7 * kPitch] << 16);
         *reinterpret_cast<uint4*>(zt + zt_index(k0 + tr * 64 + g * 8, col, zt_rows)) = o;
       }
     }
