@@ -75,7 +75,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
                  "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
@@ -361,7 +361,7 @@ def run_b200(args, wl):
         # the policy's own Philox draws take the whitened path: A = nw z (fp16 pair) x B = z (exact fp16)
         white = scheme == _lib.GEMM_FP16X2
         products = 2 if white else 3
-        name = ("syrk_gemm_kernel<PAIR_SINGLE> (tcgen05 kind::f16, whitened moments: nw z as an fp16 pair x "
+        name = ("syrk_white_kernel (tcgen05 kind::f16, whitened moments: in-kernel nw z as an fp16 pair x "
                 "exact fp16 z, 2 partial products)" if white else "syrk_gemm_kernel<TF32X3> (tcgen05 kind::tf32)")
         roofline = {
             "kernel": name,
