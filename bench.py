@@ -49,7 +49,12 @@ WORKLOADS = {
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
 # `ncu --set full` capture under profiles/ (see profiles/README.md); keyed by (kernel, D).
-NCU_TRAFFIC = {("syrk_pair", 2048): 541.2e6}  # profiles/r1_gemm_ncu_full_summary.csv (537.0 MB read + 4.2 MB written)
+# (kernel, D, samples per launch)
+NCU_TRAFFIC = {
+    ("syrk_pair", 2048, 65536): 541.2e6,     # profiles/r1_gemm_ncu_full_summary.csv (537.0 MB read + 4.2 MB written)
+    ("syrk_white", 2048, 1 << 20): 4.3052e9,  # profiles/README.md: 4.301 GB read (= the 2-byte store, once) + 4.1 MB written
+    ("syrk_white", 2048, 1 << 18): 1.0793e9,  # profiles/r1_syrk_white_ncu.csv
+}
 
 
 def peaks():
@@ -274,6 +279,8 @@ def run_b200(args, wl):
         _lib.call("ppi_set_option", _lib.OPT_GEMM_OVERLAP, args.overlap)
     if args.chunk is not None:
         _lib.call("ppi_set_option", _lib.OPT_GEMM_CHUNK, args.chunk)
+    if args.pair is not None:
+        _lib.call("ppi_set_option", _lib.OPT_GEMM_PAIR, args.pair)
 
     def barrier():
         if world > 1:
@@ -367,7 +374,7 @@ def run_b200(args, wl):
             "kernel": name,
             "bound": "tensor", "achieved": algorithmic / t / 1e12, "peak": pk["bf16"], "unit": "TFLOP/s",
             "frac": algorithmic / t / 1e12 / pk["bf16"],
-            "traffic": NCU_TRAFFIC.get(("syrk_white" if white else "syrk_pair", wl["D"])),
+            "traffic": NCU_TRAFFIC.get(("syrk_white" if white else "syrk_pair", wl["D"], int(rows_per_launch))),
             "peak_source": f"dense 16-bit tensor peak, sustained, {pk['source']}",
             "algorithmic_flops_per_launch": algorithmic,
             "executed_tflops": executed_syrk_flops(rows_per_launch, D, products) / t / 1e12,
@@ -458,6 +465,7 @@ def main():
     ap.add_argument("--samples", type=int, default=None, help="samples per GPU (overrides the workload's K)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--chunk", type=int, default=None, help="override PPI_OPT_GEMM_CHUNK")
+    ap.add_argument("--pair", type=int, default=None, choices=[0, 1], help="override PPI_OPT_GEMM_PAIR")
     ap.add_argument("--overlap", type=int, default=None, choices=[0, 1],
                     help="override PPI_OPT_GEMM_OVERLAP (operand staging on a side stream)")
     args = ap.parse_args()
