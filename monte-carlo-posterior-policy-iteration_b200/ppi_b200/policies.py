@@ -1058,19 +1058,215 @@ class WhiteNoiseIid(object):
         return mean if only_mean else (mean, self.std ** 2)
 
 
-def _next_row(name, where):
-    class _NotYet(object):
-        def __init__(self, *a, **k):
-            raise NotImplementedError(
-                f"{name} ({where}) is a 'next' row of the scope table (SURVEY 8(f) row 2) and is "
-                "not built yet")
+def ema_filter_matrix(n, beta):
+    """The reference's `convolve(signal, [1 - beta, beta])` (ppi/policies.py:1257-1267, :1283) as a
+    lower-triangular matrix: s[0] = x[0], s[t] = (1 - beta) s[t-1] + beta x[t] (the loop reads the
+    already smoothed s[t-1]); identity when the horizon is not longer than the filter."""
+    f = np.eye(n)
+    for t in range(1, n):
+        f[t] = (1.0 - beta) * f[t - 1]
+        f[t, t] = beta
+    return f
 
-    _NotYet.__name__ = name
-    return _NotYet
+
+def powerlaw_mixing_matrix(n, beta):
+    """colorednoise.powerlaw_psd_gaussian(beta, size=(.., n)) (third-party, colorednoise==2.0.0,
+    ppi.yaml:23; Timmer & Koenig 1995) is a LINEAR map of its 2 (n//2 + 1) frequency-domain normals:
+    y = M xi with  s_k ~ N(0, f_k^-beta) (f_0 := f_1, DC and Nyquist real and scaled by sqrt 2),
+    y = irfft(s) / sigma,  sigma = 2 sqrt(sum_k w_k^2) / n.  Returns M (n, 2 m)."""
+    f = np.fft.rfftfreq(n)
+    f[0] = f[1]  # fmin = 1 / n
+    scale = f ** (-beta / 2.0)
+    w = scale[1:].copy()
+    w[-1] *= (1 + (n % 2)) / 2.0
+    sigma = 2.0 * np.sqrt(np.sum(w ** 2)) / n
+    m = f.shape[0]
+    cols = []
+    for part in (0, 1):  # real draws, then imaginary draws
+        for k in range(m):
+            s = np.zeros(m, dtype=np.complex128)
+            amp = scale[k]
+            if part == 0:
+                if k == 0 or (k == m - 1 and n % 2 == 0):
+                    amp *= np.sqrt(2.0)
+                s[k] = amp
+            else:
+                if k == 0 or (k == m - 1 and n % 2 == 0):
+                    amp = 0.0
+                s[k] = 1j * amp
+            cols.append(np.fft.irfft(s, n=n) / sigma)
+    return np.stack(cols, axis=1)
 
 
-ColouredNoise = _next_row("ColouredNoise", "ppi/policies.py:1198-1254")
-SmoothExplorationNoise = _next_row("SmoothExplorationNoise", "ppi/policies.py:1257-1290")
-SmoothActionNoise = _next_row("SmoothActionNoise", "ppi/policies.py:1293-1326")
-LinearGaussianDynamicalSystemKernel = _next_row("LinearGaussianDynamicalSystemKernel",
-                                                "ppi/policies.py:1329-1410")
+class _FilteredNoise(WhiteNoiseIid):
+    """iid prior whose base normals pass through a fixed H x H lower-triangular map before the
+    element-wise transform: both steps run on the device (ppi_sample_matnorm with L_out = I, then
+    ppi_sample_iid on its output)."""
+
+    def _mix(self):
+        raise NotImplementedError
+
+    def _base_normals(self, n_local, n_samples, begin, end):
+        H, d = self.dim_features, self.dim_out
+        if self.injected_normals:
+            z = f32(self.injected_normals.pop(0)).reshape(n_samples, -1)[begin:end].contiguous()
+            seed = draw = 0
+        else:
+            z, seed, draw = self._rng.device_normals(n_samples, H * d)
+        return ops.sample_matnorm(n_local, np.zeros(d), np.zeros((H, d)), self._mix(), np.eye(d), z=z,
+                                  seed=seed, draw_id=draw, row_offset=begin, l_out_is_diag=True)
+
+
+class SmoothExplorationNoise(_FilteredNoise):
+    """Exponentially smoothed exploration noise (ppi/policies.py:1270-1303): the noise, not the
+    mean, goes through the causal filter [1 - beta, beta]."""
+
+    def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out, sampler=None,
+                 beta=2.0, limiter=null_limiter, use_derivatives=False, *args, **kwargs):
+        assert 0.0 < beta < 1.0, f"beta is {beta}"
+        self.beta = beta
+        self.filter_coef = np.array([1 - beta, beta])
+        super().__init__(time_sequence, action_dimension, mean, covariance_in, covariance_out,
+                         use_derivatives, limiter)
+
+    def _mix(self):
+        return ema_filter_matrix(self.dim_features, self.beta)
+
+    def __call__(self, n_samples):
+        lo, hi = _limits(self.limiter)
+        begin, end = shard_rows(n_samples)
+        zs = self._base_normals(end - begin, n_samples, begin, end)
+        xs = ops.sample_iid(end - begin, self.mean_fn, self.mean, self.std, z=zs.reshape(end - begin, -1),
+                            lower=lo, upper=hi)
+        handle = DeviceArray(xs, begin, n_samples)
+        return handle, handle
+
+
+class SmoothActionNoise(SmoothExplorationNoise):
+    """The variant that smooths the whole action sequence, mean included (ppi/policies.py:1306-1319)."""
+
+    def __call__(self, n_samples):
+        lo, hi = _limits(self.limiter)
+        begin, end = shard_rows(n_samples)
+        H, d = self.dim_features, self.dim_out
+        if self.injected_normals:
+            z = f32(self.injected_normals.pop(0)).reshape(n_samples, -1)[begin:end].contiguous()
+            seed = draw = 0
+        else:
+            z, seed, draw = self._rng.device_normals(n_samples, H * d)
+        xs = ops.sample_iid(end - begin, self.mean_fn, self.mean, self.std, z=z, seed=seed, draw_id=draw,
+                            row_offset=begin)
+        smooth = ops.sample_matnorm(end - begin, np.zeros(d), np.zeros((H, d)), self._mix(), np.eye(d),
+                                    z=xs.reshape(end - begin, -1), lower=lo, upper=hi, l_out_is_diag=True)
+        handle = DeviceArray(smooth, begin, n_samples)
+        return handle, handle
+
+
+class ColouredNoise(_FilteredNoise):
+    """Power-law (1/f^beta) noise over the time axis (ppi/policies.py:1198-1254).  The reference
+    draws with colorednoise.powerlaw_psd_gaussian, a linear map M of frequency-domain normals; here
+    the same stationary process is drawn as chol(M M^T) xi on the device (equal in distribution, not
+    draw by draw: the third-party package is absent, parity is on the covariance)."""
+
+    def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out, sampler=None,
+                 use_derivatives=False, beta=2.0, limiter=null_limiter, *args, **kwargs):
+        self.beta = beta
+        self.sampler = sampler(0) if sampler is not None else samplers.MonteCarlo(0)
+        super().__init__(time_sequence, action_dimension, mean, covariance_in, covariance_out,
+                         use_derivatives, limiter)
+        self._mix_cache = None
+
+    def _mix(self):
+        H = self.dim_features
+        if self._mix_cache is None or self._mix_cache[0] != (H, self.beta):
+            if H > 1:
+                m = powerlaw_mixing_matrix(H, self.beta)
+                c = m @ m.T
+                mix = np.linalg.cholesky(0.5 * (c + c.T) + 1e-12 * np.eye(H))
+            else:
+                mix = np.eye(1)
+            self._mix_cache = ((H, self.beta), mix)
+        return self._mix_cache[1]
+
+    def update_timesteps(self, time_sequence, anneal=1.0, eps=1e-7):
+        super().update_timesteps(time_sequence, anneal)
+        if isinstance(self.sampler, samplers.Particles) and self.sampler.has_particles:
+            particles = np.copy(self.sampler.particles)
+            last_action = particles[:, -1, :]
+            particles[:, :-1, :] = self.sampler.particles[:, 1:, :]
+            particles[:, -1, :] = last_action
+            self.sampler.particles = particles
+
+    def __call__(self, n_samples):
+        lo, hi = _limits(self.limiter)
+        begin, end = shard_rows(n_samples)
+        zs = self._base_normals(end - begin, n_samples, begin, end)
+        if getattr(self.sampler, "particles", None) is not None:  # ppi/policies.py:1245-1246
+            parts = np.asarray(self.sampler.particles)
+            n = min(parts.shape[0], n_samples)
+            lo_r, hi_r = max(begin, 0), min(end, n)
+            if hi_r > lo_r:
+                zs[lo_r - begin:hi_r - begin] = f32(parts[lo_r:hi_r, :zs.shape[1], :])
+        xs = ops.sample_iid(end - begin, self.mean_fn, self.mean, self.std, z=zs.reshape(end - begin, -1),
+                            lower=lo, upper=hi)
+        handle = DeviceArray(xs, begin, n_samples)
+        return handle, handle
+
+
+class LinearGaussianDynamicalSystemKernel(BaseKernel):
+    """GP prior of a discrete-time integrator chain (ppi/policies.py:1329-1410).  The Gram matrix
+    is a once-per-construction H x H host computation (block algebra on (H order)^2 matrices); the
+    per-iteration sampling / update path is BaseKernel's device path."""
+
+    can_optimize = False
+
+    def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out, order, sampler,
+                 use_derivatives=False, limiter=null_limiter, *args, **kwargs):
+        self.dim_features = time_sequence.shape[0]
+        assert order in [1, 2, 3]
+        assert mean.shape == (action_dimension,)
+        assert covariance_in.shape == (1,)
+        self.mean_fn = mean
+        self.order = order
+        self.sigma = covariance_in.item()
+        self.Q = np.zeros((order, order))
+        self.Q[-1, -1] = self.sigma
+        mean_ = np.zeros((self.dim_features, action_dimension))
+        covariance_in = self.k(time_sequence, time_sequence)
+        super().__init__(time_sequence, action_dimension, mean_, covariance_in, covariance_out, sampler,
+                         limiter, use_derivatives)
+
+    def k(self, t1, t2):
+        from scipy.linalg import block_diag
+
+        n, o = t1.shape[0], self.order
+        a = self.transition_matrx(t1[1], t1[0], d=o)   # constant time step assumed (:1375)
+        a_ = np.kron(np.eye(n), np.eye(o))
+        for i in range(1, n):
+            a_ += np.kron(np.eye(n, k=-i), np.linalg.matrix_power(a, i))
+        q_ = block_diag(*([1e-3 * np.eye(o)] + [self.Q] * (n - 1)))
+        disturbance = block_diag(*([1e-6 * np.eye(o)] * n))
+        gram = a_ @ q_ @ a_.T + disturbance
+        return gram[::o, ::o]
+
+    def _condition(self, t, action):
+        idx = (t == self.t).nonzero()[0]
+        cov_0 = self.covariance_in
+        cov_p = cov_0[np.ix_(idx, idx)]
+        cov_tp = cov_0[:, idx]
+        self.mean = cov_tp @ np.linalg.solve(cov_p, action - self.mean_fn[None, :])
+        self.covariance_in = cov_0 - cov_tp @ np.linalg.solve(cov_p, cov_tp.T)
+
+    @staticmethod
+    def transition_matrx(t2, t1, d=3):
+        a = np.eye(d)
+        dt = t2 - t1
+        if d == 3:
+            a[0, 1] = dt
+            a[0, 2] = 0.5 * dt ** 2
+            a[1, 2] = dt
+        elif d == 2:
+            a[0, 1] = dt
+        elif d != 1:
+            raise ValueError("Only defined for d = 1-3")
+        return a

@@ -434,3 +434,88 @@ def synthetic_return(xs, target):
     Uses the first target.shape[1] channels of xs (the reference's map_actions_to_joints split)."""
     q = xs[..., : target.shape[1]]
     return np.einsum("bij->b", np.power(q - target[None, :, :], 2)) / (q.shape[1] * q.shape[2])
+
+
+# ------------------------------------------------------------------------------------------------
+# Noise priors of SURVEY 8(f) row 2
+# ------------------------------------------------------------------------------------------------
+def convolve(signal, kernel):
+    """ppi/policies.py:1257-1267: causal filter that reads its own already-filtered output."""
+    n, h, d = signal.shape
+    w_ = kernel.shape[0] - 1
+    smoothed = signal.copy()
+    if h > w_:
+        for t in range(w_, h):
+            smoothed[:, t, :] = np.einsum("bij,i->bj", smoothed[:, t - w_:t + 1, :], kernel)
+    return smoothed
+
+
+def sample_smooth_exploration(z, mean_fn, mean, std, beta, lower=None, upper=None):
+    """SmoothExplorationNoise.__call__                       ppi/policies.py:1292-1303."""
+    xs = mean_fn[None, None, :] + mean[None, ...] + std[None, ...] * convolve(z, np.array([1 - beta, beta]))
+    return xs if lower is None else np.clip(xs, lower, upper)
+
+
+def sample_smooth_action(z, mean_fn, mean, std, beta, lower=None, upper=None):
+    """SmoothActionNoise.__call__                            ppi/policies.py:1309-1319."""
+    xs = convolve(mean_fn[None, None, :] + mean[None, ...] + std[None, ...] * z, np.array([1 - beta, beta]))
+    return xs if lower is None else np.clip(xs, lower, upper)
+
+
+def iid_weighted_update(mean_fn, log_w, samples):
+    """WhiteNoiseIid.weighted_update                         ppi/policies.py:1152-1164."""
+    log_nw = log_w - logsumexp(log_w)
+    nw = np.exp(log_nw)
+    ess = np.exp(-logsumexp(2 * log_nw))
+    mean = np.einsum("b,bij->ij", nw, samples - mean_fn[None, None, :])
+    diff = samples - mean_fn[None, None, :] - mean[None, ...]
+    std = np.sqrt(np.einsum("b,bij->ij", nw, diff ** 2))
+    return mean, std, ess, samples[np.argmax(log_w)]
+
+
+def lgds_gram(t, order, sigma):
+    """LinearGaussianDynamicalSystemKernel.k                 ppi/policies.py:1371-1385."""
+    from scipy.linalg import block_diag
+
+    n = t.shape[0]
+    a = np.eye(order)
+    dt = t[1] - t[0]
+    if order == 3:
+        a[0, 1], a[0, 2], a[1, 2] = dt, 0.5 * dt ** 2, dt
+    elif order == 2:
+        a[0, 1] = dt
+    q = np.zeros((order, order))
+    q[-1, -1] = sigma
+    a_ = np.kron(np.eye(n), np.eye(order))
+    for i in range(1, n):
+        a_ += np.kron(np.eye(n, k=-i), np.linalg.matrix_power(a, i))
+    q_ = block_diag(*([1e-3 * np.eye(order)] + [q] * (n - 1)))
+    gram = a_ @ q_ @ a_.T + block_diag(*([1e-6 * np.eye(order)] * n))
+    return gram[::order, ::order]
+
+
+def powerlaw_psd_gaussian(exponent, size, rng):
+    """colorednoise.powerlaw_psd_gaussian, colorednoise==2.0.0 (ppi.yaml:23; not vendored, not
+    installed -- restated from its published algorithm, Timmer & Koenig 1995).  Call site:
+    ppi/policies.py:1241-1243."""
+    size = list(size)
+    samples = size[-1]
+    f = np.fft.rfftfreq(samples)
+    fmin = 1.0 / samples
+    s_scale = f.copy()
+    ix = np.sum(s_scale < fmin)
+    if ix and ix < len(s_scale):
+        s_scale[:ix] = s_scale[ix]
+    s_scale = s_scale ** (-exponent / 2.0)
+    w = s_scale[1:].copy()
+    w[-1] *= (1 + (samples % 2)) / 2.0
+    sigma = 2 * np.sqrt(np.sum(w ** 2)) / samples
+    size[-1] = len(f)
+    sr = rng.standard_normal(size) * s_scale
+    si = rng.standard_normal(size) * s_scale
+    if not (samples % 2):
+        si[..., -1] = 0
+        sr[..., -1] *= np.sqrt(2)
+    si[..., 0] = 0
+    sr[..., 0] *= np.sqrt(2)
+    return np.fft.irfft(sr + 1j * si, n=samples, axis=-1) / sigma
