@@ -23,7 +23,7 @@
 namespace ppi {
 
 constexpr int kSolveThreads = 256;
-constexpr int kMaxSolveBlocks = kNumSMs;
+constexpr int kMaxSolveBlocks = 4 * kNumSMs;  // cooperative grid: up to 4 co-resident blocks per SM
 constexpr int NP = 8;               // doubles per block partial
 constexpr int kModeUserLogW = 100;  // internal: input holds log-weights, not costs
 constexpr double kAlphaLower = 1e-5, kAlphaUpper = 5e2;  // ppi/algorithms.py:36-37 (REPS only)
@@ -45,6 +45,7 @@ __device__ __forceinline__ void grid_sync(unsigned int* bar, unsigned int nblock
                                           unsigned int& target) {
   target += nblocks;
   __syncthreads();
+  if (nblocks == 1) return;  // single block (K <= 4096, the MPC shapes): the block barrier is the grid barrier
   if (threadIdx.x == 0) {
     __threadfence();
     atomicAdd(bar, 1u);
@@ -519,9 +520,15 @@ static int launch_solve(const float* in, int64_t K, int mode, double hyper, floa
               "solve workspace too small: %zu < %zu", workspace_bytes, sizeof(SolveWorkspace));
   SolveWorkspace* ws = (SolveWorkspace*)workspace;
   PPI_CUDA_TRY(cudaMemsetAsync(&ws->barrier, 0, sizeof(unsigned int), st));
+  static int blocks_per_sm = 0;  // co-residency limit of the cooperative launch
+  if (blocks_per_sm == 0) {
+    int occ = 0;
+    PPI_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, solve_temperature_kernel, kSolveThreads, 0));
+    blocks_per_sm = occ < 1 ? 1 : (occ > 4 ? 4 : occ);
+  }
   int64_t g = ceil_div(K, 4096);
   if (g < 1) g = 1;
-  if (g > kMaxSolveBlocks) g = kMaxSolveBlocks;
+  if (g > (int64_t)blocks_per_sm * kNumSMs) g = (int64_t)blocks_per_sm * kNumSMs;
   void* args[] = {(void*)&in, (void*)&K, (void*)&mode, (void*)&hyper, (void*)&nw, (void*)&log_w,
                   (void*)&stats, (void*)&ws};
   ProfileScope prof(PPI_PROF_SOLVE, st);
