@@ -620,14 +620,27 @@ class BaseFeatures(BasePrimitive):
 
     def __call__(self, n_samples):
         """-> (limited trajectories ys (K,T,d or 2d), feature weights ws (K,F,d))."""
-        feat_t = self.feat(self.t)
-        dfeat_t = self.dfeat(self.t) if self.use_derivatives else None
+        feat_t, dfeat_t = self._device_features()
         lo, hi = _limits(self.limiter) if self.limiter else (None, None)
         z, seed, draw, begin, n_local, n_total = _draw(self.sampler, n_samples, self.dim_sample)
         ys, ws = ops.sample_features(n_local, self.mean_fn, self.mean, self.covariance_in_sqrt,
                                      self.cov_out_sqrt, feat_t, dfeat_t, z=z, seed=seed, draw_id=draw,
                                      row_offset=begin, lower=lo, upper=hi)
         return DeviceArray(ys, begin, n_total), DeviceArray(ws, begin, n_total)
+
+    def _device_features(self):
+        """Phi(t) / Phi'(t) as device tensors, rebuilt only when the time grid (object, shape or end
+        points) or the feature parameters change: the reference recomputes them on every call
+        (ppi/policies.py:406-408), 0.45 ms of host NumPy per draw at T = 1000."""
+        t = self.t
+        key = (id(t), t.shape, float(t[0]), float(t[-1]), getattr(self, "ls", None),
+               getattr(self, "order", None), self.dim_features, bool(self.use_derivatives))
+        cache = getattr(self, "_feat_cache", None)
+        if cache is None or cache[0] != key:
+            feat_t = f32(self.feat(t))
+            dfeat_t = f32(self.dfeat(t)) if self.use_derivatives else None
+            self._feat_cache = cache = (key, feat_t, dfeat_t)
+        return cache[1], cache[2]
 
     def predict(self, only_mean=False):
         feat_t = self.feat(self.t)
