@@ -44,6 +44,29 @@ def f32(a, device=None):
     return torch.as_tensor(np.ascontiguousarray(np.asarray(a, dtype=np.float32)), device=device)
 
 
+_small_cache = {}
+
+
+def f32_cached(a, device=None):
+    """f32() for small host arrays that are re-sent on every call (policy state: mean_fn, mean, factors,
+    limits): the device copy is reused while the SAME array object still holds the same numbers (shape,
+    sum and end points are re-checked, so in-place edits are seen)."""
+    if not isinstance(a, np.ndarray) or a.size == 0 or a.size > 1 << 16:
+        return f32(a, device)
+    device = device or require_cuda()
+    flat = a.reshape(-1)
+    sig = (a.shape, a.dtype.str, float(flat.sum()), float(flat[0]), float(flat[-1]), float(flat[a.size // 2]))
+    key = (id(a), device.index)
+    hit = _small_cache.get(key)
+    if hit is not None and hit[0] == sig:
+        return hit[1]
+    if len(_small_cache) > 512:
+        _small_cache.clear()
+    t = f32(a, device)
+    _small_cache[key] = (sig, t)
+    return t
+
+
 def f64(a, device=None):
     device = device or require_cuda()
     if isinstance(a, torch.Tensor):

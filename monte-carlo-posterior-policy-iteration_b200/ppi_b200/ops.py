@@ -10,13 +10,13 @@ import numpy as np
 import torch
 
 from . import _lib
-from .device import f32, f64, ptr, read_stats, require_cuda, stream_ptr, workspace
+from .device import f32, f32_cached, f64, ptr, read_stats, require_cuda, stream_ptr, workspace
 
 _u64 = lambda v: C.c_uint64(int(v) & 0xFFFFFFFFFFFFFFFF)  # noqa: E731
 
 
 def _opt(t, dev):
-    return None if t is None else f32(t, dev)
+    return None if t is None else f32_cached(t, dev)
 
 
 class _Keep:
@@ -26,10 +26,10 @@ class _Keep:
     def __init__(self, dev):
         self.dev, self.alive = dev, []
 
-    def p(self, a):
+    def p(self, a, cached=False):
         if a is None:
             return ptr(None)
-        t = f32(a, self.dev)
+        t = f32_cached(a, self.dev) if cached else f32(a, self.dev)
         self.alive.append(t)
         return ptr(t)
 
@@ -83,13 +83,13 @@ def sample_matnorm(K, mean_fn, mean, l_in, l_out, z=None, seed=0, draw_id=0, row
                    lower=None, upper=None, l_out_is_diag=False):
     dev = require_cuda()
     kp = _Keep(dev)
-    mean = f32(mean, dev)
+    mean = f32_cached(mean, dev)
     H, d = mean.shape
     x = torch.empty((K, H, d), dtype=torch.float32, device=dev)
     zt = None if z is None else f32(z, dev).reshape(K, H * d)
     lo, hi = _opt(lower, dev), _opt(upper, dev)
     _lib.call("ppi_sample_matnorm", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, H, d,
-              kp.p(mean_fn), ptr(mean), kp.p(l_in), kp.p(l_out),
+              kp.p(mean_fn, cached=True), ptr(mean), kp.p(l_in, cached=True), kp.p(l_out, cached=True),
               int(bool(l_out_is_diag)), ptr(lo), ptr(hi), ptr(x), stream_ptr())
     return x
 
@@ -98,7 +98,7 @@ def sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat=None, z=None, see
                     row_offset=0, lower=None, upper=None):
     dev = require_cuda()
     kp = _Keep(dev)
-    mean = f32(mean, dev)
+    mean = f32_cached(mean, dev)
     F, d = mean.shape
     feat = f32(feat, dev)
     T = feat.shape[0]
@@ -108,7 +108,7 @@ def sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat=None, z=None, see
     zt = None if z is None else f32(z, dev).reshape(K, F * d)
     lo, hi = _opt(lower, dev), _opt(upper, dev)
     _lib.call("ppi_sample_features", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, F, d, T,
-              kp.p(mean_fn), ptr(mean), kp.p(l_in), kp.p(l_out), ptr(feat),
+              kp.p(mean_fn, cached=True), ptr(mean), kp.p(l_in, cached=True), kp.p(l_out, cached=True), ptr(feat),
               kp.p(dfeat), ptr(lo), ptr(hi), ptr(w), ptr(y), stream_ptr())
     return y, w
 
@@ -117,13 +117,13 @@ def sample_iid(K, mean_fn, mean, std, z=None, seed=0, draw_id=0, row_offset=0, l
                upper=None):
     dev = require_cuda()
     kp = _Keep(dev)
-    mean = f32(mean, dev)
+    mean = f32_cached(mean, dev)
     H, d = mean.shape
     x = torch.empty((K, H, d), dtype=torch.float32, device=dev)
     zt = None if z is None else f32(z, dev).reshape(K, H * d)
     lo, hi = _opt(lower, dev), _opt(upper, dev)
     _lib.call("ppi_sample_iid", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, H, d,
-              kp.p(mean_fn), ptr(mean), kp.p(std), ptr(lo), ptr(hi), ptr(x),
+              kp.p(mean_fn, cached=True), ptr(mean), kp.p(std, cached=True), ptr(lo), ptr(hi), ptr(x),
               stream_ptr())
     return x
 
