@@ -222,7 +222,9 @@ __device__ __forceinline__ T block_sum(T v, T* scratch) {
 
 __device__ __forceinline__ float clipf(float v, float lo, float hi) {
   // np.clip(x, a_min, a_max) = minimum(maximum(x, a_min), a_max); NaN propagates.
-  return (v != v) ? v : fminf(fmaxf(v, lo), hi);
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;\n\tmin.NaN.f32 %0, %0, %3;" : "=&f"(r) : "f"(v), "f"(lo), "f"(hi));
+  return r;
 }
 
 // In-place right-looking Cholesky of the n x n matrix in shared memory `a` (lower part used).

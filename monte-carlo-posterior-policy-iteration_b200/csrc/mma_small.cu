@@ -451,6 +451,190 @@ sample_matnorm_mma_kernel(const float* __restrict__ z, uint64_t seed, uint64_t d
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Feature expansion  y_b = clip([mean_fn + Phi w_b, Phi' w_b])  for d = 2, F <= 32
+// (ppi/policies.py:1009-1016: actions of an RBF / RFF feature policy from its sampled weights).
+// One (T x F) x (F x 2K) product whose output (K, T, dy) is the only large HBM stream: 21 multiply-
+// adds per output float on the SIMT pipes cost as much as writing it, so the product runs on
+// mma.sync with the FP16X2 split instead.  A block owns 256 time steps: each warp keeps the (h1, h2)
+// fragments of its 32 rows of Phi (and Phi') in registers for the whole kernel and walks over groups
+// of 32 samples whose weights are split once per group (power-of-two scale from the group maximum)
+// into a shared tile [column n = (sample, channel)][feature], 40 halves apart so that the B-fragment
+// loads of a warp hit 32 different banks.  With n = 2 s + c the accumulator pair of a thread is the
+// two channels of one sample at one time step: value and derivative leave as one 16-byte store,
+// eight consecutive time steps of a sample forming one 128-byte line.
+// ------------------------------------------------------------------------------------------
+constexpr int kFxS = 32;       // samples per group
+constexpr int kFxStride = 40;  // halves between columns of the split-weight tile
+constexpr int kFxTile = 256;   // time steps per block
+
+template <bool DERIV>
+__global__ void __launch_bounds__(256)
+features_expand_mma_kernel(const float* __restrict__ w, int64_t K, int F, int T,
+                           const float* __restrict__ mean_fn, const float* __restrict__ feat,
+                           const float* __restrict__ dfeat, const float* __restrict__ lower,
+                           const float* __restrict__ upper, float* __restrict__ y) {
+  __shared__ __align__(16) __half sW1[2 * kFxS * kFxStride];
+  __shared__ __align__(16) __half sW2[2 * kFxS * kFxStride];
+  __shared__ float sRed[16];
+  constexpr int DY = DERIV ? 4 : 2;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
+  const int tb = blockIdx.y * kFxTile;
+  const int t0 = tb + warp * 32;
+
+  // block-wide scales of the Phi / Phi' tiles
+  float pmax = 0.f, dmax = 0.f;
+  {
+    const int nt = min(kFxTile, T - tb);
+    for (int i = threadIdx.x; i < nt * F; i += blockDim.x) {
+      pmax = fmaxf(pmax, fabsf(feat[(int64_t)tb * F + i]));
+      if (DERIV) dmax = fmaxf(dmax, fabsf(dfeat[(int64_t)tb * F + i]));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, o));
+      dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+    }
+    if (lane == 0) { sRed[warp] = pmax; sRed[8 + warp] = dmax; }
+    for (int i = threadIdx.x; i < 2 * kFxS * kFxStride; i += blockDim.x) {
+      sW1[i] = __float2half(0.f);
+      sW2[i] = __float2half(0.f);
+    }
+    __syncthreads();
+    pmax = dmax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { pmax = fmaxf(pmax, sRed[i]); dmax = fmaxf(dmax, sRed[8 + i]); }
+    __syncthreads();
+  }
+  const float psc = pmax > 0.f ? chunk_scale(pmax) : 1.f;
+  const float dsc = dmax > 0.f ? chunk_scale(dmax) : 1.f;
+
+  // A fragments: [row tile][k-step][register], (h1, h2) of Phi and Phi'
+  uint32_t a1[2][2][4], a2[2][2][4], e1[2][2][4], e2[2][2][4];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int t = t0 + 16 * i + g + 8 * (r & 1);
+        const int f = 16 * ks + 2 * q + 8 * (r >> 1);
+        const bool ok0 = t < T && f < F, ok1 = t < T && f + 1 < F;
+        const int64_t o = (int64_t)t * F + f;
+        split_pair(ok0 ? feat[o] * psc : 0.f, ok1 ? feat[o + 1] * psc : 0.f, a1[i][ks][r], a2[i][ks][r]);
+        if (DERIV)
+          split_pair(ok0 ? dfeat[o] * dsc : 0.f, ok1 ? dfeat[o + 1] * dsc : 0.f, e1[i][ks][r], e2[i][ks][r]);
+      }
+
+  float lo[DY], hi[DY], mf[2];
+#pragma unroll
+  for (int c = 0; c < DY; ++c) {
+    lo[c] = lower ? lower[c] : -INFINITY;
+    hi[c] = upper ? upper[c] : INFINITY;
+  }
+  mf[0] = mean_fn[0];
+  mf[1] = mean_fn[1];
+  uint32_t tmask = 0;   // bit 2 i + hh: row t0 + 16 i + g + 8 hh exists
+#pragma unroll
+  for (int j = 0; j < 4; ++j) tmask |= (t0 + 16 * (j >> 1) + g + 8 * (j & 1) < T ? 1u : 0u) << j;
+
+  const int FD = 2 * F;
+  const int per_group = kFxS * FD;             // <= 2048 values: <= 8 per thread
+  const int64_t n_groups = ceil_div(K, (int64_t)kFxS);
+  float wv[8];
+  auto fetch = [&](int64_t grp) {
+    const int64_t base = grp * per_group;
+    const int64_t lim = K * FD;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int e = threadIdx.x + 256 * j;
+      wv[j] = ldg1_if(w + base + e, e < per_group && base + e < lim);
+    }
+  };
+  if ((int64_t)blockIdx.x < n_groups) fetch(blockIdx.x);
+  for (int64_t grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+    const int64_t b0 = grp * kFxS;
+    const int ns = (int)min((int64_t)kFxS, K - b0);
+    float amax = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(wv[j]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    if (lane == 0) sRed[warp] = amax;
+    __syncthreads();   // previous group's B loads are done as well
+    amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) amax = fmaxf(amax, sRed[i]);
+    const float wsc = amax > 0.f ? chunk_scale(amax) : 1.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int e = threadIdx.x + 256 * j;
+      if (e < per_group) {
+        const int s = e / FD, r = e - s * FD;       // r = 2 f + c
+        const float v = wv[j] * wsc;
+        const __half h1 = __float2half_rn(v);
+        const __half h2 = __float2half_rn(v - __half2float(h1));
+        const int o = (2 * s + (r & 1)) * kFxStride + (r >> 1);
+        sW1[o] = h1;
+        sW2[o] = h2;
+      }
+    }
+    const int64_t nxt = grp + gridDim.x;
+    if (nxt < n_groups) fetch(nxt);
+    __syncthreads();
+    const float py = 1.f / (psc * wsc), dy = 1.f / (dsc * wsc);
+    const bool full = ns == kFxS;
+    float* yb = y + ((b0 + q) * (int64_t)T + t0 + g) * DY;   // sample b0 + 4 nt + q, row t0 + g
+#pragma unroll 2
+    for (int nt = 0; nt < 8; ++nt, yb += 4 * (int64_t)T * DY) {
+      const int col = (nt * 8 + g) * kFxStride + 2 * q;
+      uint32_t b1[2][2], b2[2][2];
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          b1[ks][r] = *reinterpret_cast<const uint32_t*>(sW1 + col + 16 * ks + 8 * r);
+          b2[ks][r] = *reinterpret_cast<const uint32_t*>(sW2 + col + 16 * ks + 8 * r);
+        }
+      // four independent accumulation chains (2 row tiles x {Phi, Phi'}), issued round-robin
+      float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+      float dac[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+        for (int p = 0; p < 3; ++p)
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const uint32_t* fa = p == 2 ? a2[i][ks] : a1[i][ks];
+            const uint32_t* fb = p == 1 ? b2[ks] : b1[ks];
+            mma16816(acc[i], fa[0], fa[1], fa[2], fa[3], fb[0], fb[1]);
+            if (DERIV) {
+              const uint32_t* fe = p == 2 ? e2[i][ks] : e1[i][ks];
+              mma16816(dac[i], fe[0], fe[1], fe[2], fe[3], fb[0], fb[1]);
+            }
+          }
+      if (full || nt * 4 + q < ns) {
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            if (tmask >> (2 * i + hh) & 1) {
+              const float v0 = clipf(fmaf(acc[i][2 * hh], py, mf[0]), lo[0], hi[0]);
+              const float v1 = clipf(fmaf(acc[i][2 * hh + 1], py, mf[1]), lo[1], hi[1]);
+              if (DERIV) {
+                const float v2 = clipf(dac[i][2 * hh] * dy, lo[2], hi[2]);
+                const float v3 = clipf(dac[i][2 * hh + 1] * dy, lo[3], hi[3]);
+                *reinterpret_cast<float4*>(yb + (16 * i + 8 * hh) * 4) = make_float4(v0, v1, v2, v3);
+              } else {
+                *reinterpret_cast<float2*>(yb + (16 * i + 8 * hh) * 2) = make_float2(v0, v1);
+              }
+            }
+          }
+      }
+    }
+  }
+}
+
 }  // namespace ppi
 
 using namespace ppi;
@@ -504,4 +688,21 @@ int ppi_sample_matnorm_mma(const float* z, uint64_t seed, uint64_t draw_id, uint
   else              { if (vec2) PPI_LAUNCH_SMM(false, true); else PPI_LAUNCH_SMM(false, false); }
 #undef PPI_LAUNCH_SMM
   return check_launch("sample_matnorm_mma_kernel");
+}
+
+// called from sample.cu: feature policies with d = 2, F <= 32 (weights w already sampled)
+int ppi_features_expand_mma(const float* w, int64_t K, int F, int T, const float* mean_fn,
+                            const float* feat, const float* dfeat, const float* lower,
+                            const float* upper, float* y, cudaStream_t st) {
+  const int ty = (int)ceil_div(T, kFxTile);
+  int64_t gx = ceil_div((int64_t)kNumSMs * 2, (int64_t)ty);
+  const int64_t n_groups = ceil_div(K, (int64_t)kFxS);
+  if (gx > n_groups) gx = n_groups;
+  if (gx < 1) gx = 1;
+  dim3 grid((unsigned)gx, (unsigned)ty);
+  if (dfeat)
+    features_expand_mma_kernel<true><<<grid, 256, 0, st>>>(w, K, F, T, mean_fn, feat, dfeat, lower, upper, y);
+  else
+    features_expand_mma_kernel<false><<<grid, 256, 0, st>>>(w, K, F, T, mean_fn, feat, dfeat, lower, upper, y);
+  return check_launch("features_expand_mma_kernel");
 }

@@ -388,6 +388,74 @@ sample_features_tiled_kernel(const float* __restrict__ z, uint64_t seed, uint64_
 }
 
 // ------------------------------------------------------------------------------------------
+// Weights of a feature policy alone: w = mean + L_in z L_out^T, (K, F, d)  (ppi/policies.py:1009).
+// First half of the two-kernel feature sampler: the expansion y = [Phi w, Phi' w] then runs on the
+// tensor cores (features_expand_mma_kernel, mma_small.cu) reading w back (1 % of its traffic).
+// Same arithmetic, Philox element order and summation order as the fused kernels above.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+feature_weights_kernel(const float* __restrict__ z, uint64_t seed, uint64_t draw, uint64_t row_offset,
+                       int64_t K, int F, int d, const float* __restrict__ mean,
+                       const float* __restrict__ l_in, const float* __restrict__ l_out,
+                       float* __restrict__ w) {
+  extern __shared__ __align__(16) float smem[];
+  const int FD = F * d;
+  float* sLin = smem;                    // F * F
+  float* sLout = sLin + pad4(F * F);     // d * d
+  float* sMean = sLout + pad4(d * d);    // F * d
+  float* sZ = sMean + pad4(FD);          // 32 * F * d
+  float* sU = sZ + pad4(kFeatS * FD);    // 32 * F * d
+  for (int i = threadIdx.x; i < F * F; i += blockDim.x) sLin[i] = l_in[i];
+  for (int i = threadIdx.x; i < d * d; i += blockDim.x) sLout[i] = l_out[i];
+  for (int i = threadIdx.x; i < FD; i += blockDim.x) sMean[i] = mean[i];
+  // static work split (FD <= 256): thread = (sample sub-group, weight element r = k d + l); an element
+  // of L_in read from shared memory feeds the FMAs of up to 8 samples
+  const int nsub = blockDim.x / FD;
+  const int sub = threadIdx.x / FD, r = threadIdx.x - sub * FD, k = r / d, l = r - k * d;
+  const bool worker = sub < nsub;
+  const int64_t n_groups = ceil_div(K, kFeatS);
+  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+    const int64_t b0 = g * kFeatS;
+    const int ns = (int)min((int64_t)kFeatS, K - b0);
+    __syncthreads();
+    load_normals(sZ, ns * FD, z, (uint64_t)b0 * FD, (row_offset + (uint64_t)b0) * FD, seed, draw);
+    __syncthreads();
+    if (worker) {
+      for (int s = sub; s < ns; s += nsub) {
+        const float* zr = sZ + s * FD + k * d;
+        float u = 0.f;
+        for (int j = 0; j < d; ++j) u = fmaf(zr[j], sLout[l * d + j], u);
+        sU[s * FD + r] = u;
+      }
+    }
+    __syncthreads();
+    if (worker) {
+      for (int s0 = sub; s0 < ns; s0 += 8 * nsub) {
+        float a[8];
+        const float* up[8];
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+          a[m] = 0.f;
+          up[m] = sU + min(s0 + m * nsub, kFeatS - 1) * FD + l;
+        }
+        const float* row = sLin + k * F;
+        for (int i = 0; i <= k; ++i) {
+          const float li = row[i];
+#pragma unroll
+          for (int m = 0; m < 8; ++m) a[m] = fmaf(li, up[m][i * d], a[m]);
+        }
+        const float mr = sMean[r];
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+          const int sm = s0 + m * nsub;
+          if (sm < ns) w[(b0 + sm) * FD + r] = a[m] + mr;
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // iid sampler: element-wise, one quad of the base-normal matrix per thread iteration.
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
@@ -562,6 +630,9 @@ int ppi_sample_matnorm_mma(const float* z, uint64_t seed, uint64_t draw_id, uint
                            int H, int d, const float* mean_fn, const float* mean, const float* l_in,
                            const float* l_out, const float* lower, const float* upper, float* x,
                            cudaStream_t st);
+int ppi_features_expand_mma(const float* w, int64_t K, int F, int T, const float* mean_fn,
+                            const float* feat, const float* dfeat, const float* lower,
+                            const float* upper, float* y, cudaStream_t st);
 
 extern "C" int ppi_philox_normal(float* out, int64_t rows, int64_t cols, uint64_t seed,
                                  uint64_t draw_id, uint64_t row_offset, void* stream) {
@@ -654,6 +725,19 @@ extern "C" int ppi_sample_features(const float* z, uint64_t seed, uint64_t draw_
   PPI_REQUIRE((lower == nullptr) == (upper == nullptr), PPI_ERR_INVALID,
               "lower and upper must both be given or both be NULL");
   if (K == 0) return 0;
+  if (d == 2 && F <= 32 && (reinterpret_cast<uintptr_t>(y) & 15) == 0) {
+    // two kernels: weights (SIMT, tiny), then the expansion on mma.sync (mma_small.cu)
+    const int FD = F * d;
+    const size_t smem_w = ((size_t)pad4(F * F) + pad4(d * d) + pad4(FD) + 2 * (size_t)pad4(kFeatS * FD)) *
+                          sizeof(float);
+    if (int rc = set_smem(feature_weights_kernel, smem_w)) return rc;
+    ProfileScope prof(PPI_PROF_SAMPLE_SMALL, (cudaStream_t)stream);
+    feature_weights_kernel<<<grid_for(ceil_div(K, kFeatS), 4), 256, smem_w, (cudaStream_t)stream>>>(
+        z, seed, draw_id, row_offset, K, F, d, mean, l_in, l_out, w);
+    if (int rc = check_launch("feature_weights_kernel")) return rc;
+    return ppi_features_expand_mma(w, K, F, T, mean_fn, feat, dfeat, lower, upper, y,
+                                   (cudaStream_t)stream);
+  }
   if (d <= 4) {
     const int FD = F * d;
     const size_t smem_t = ((size_t)(dfeat ? 2 : 1) * F * kFeatTile + pad4(F * F) + pad4(d * d) + pad4(FD) +

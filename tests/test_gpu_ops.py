@@ -182,6 +182,51 @@ def test_sample_features_oracle(ops, K, F, d, T, deriv, clip):
     assert nerr(host(ys), ref_y) < TOL
 
 
+@pytest.mark.parametrize("K,F,T,deriv,scale", [(1000, 32, 257, True, 1.0), (65, 5, 17, False, 1.0),
+                                               (300, 21, 1000, True, 1e4), (300, 21, 513, True, 1e-4),
+                                               (31, 1, 256, False, 1.0)])
+def test_sample_features_expand_mma(ops, K, F, T, deriv, scale):
+    """d = 2: weights kernel + tensor-core expansion (mma_small.cu), dense l_out, ragged K / T / F, weights
+    and features of very different magnitudes (per-group and per-tile power-of-two scales)."""
+    d = 2
+    rng = np.random.default_rng(K + F + T)
+    z = f32r(rng.standard_normal((K, F, d)))
+    a = rng.standard_normal((F, F + 2))
+    l_in = f32r(scale * np.linalg.cholesky(a @ a.T / F + 0.1 * np.eye(F)))
+    l_out = f32r(np.linalg.cholesky(np.array([[1.0, 0.4], [0.4, 0.5]])))
+    mean_fn, mean = f32r(scale * rng.standard_normal(d)), f32r(scale * rng.standard_normal((F, d)))
+    feat = f32r(rng.standard_normal((T, F)) * 10.0 ** rng.uniform(-3, 0, size=(T, 1)))
+    dfeat = f32r(30.0 * rng.standard_normal((T, F)))
+    dy = 2 * d if deriv else d
+    lo, hi = f32r(-scale * (20.0 + rng.random(dy))), f32r(scale * (20.0 + rng.random(dy)))
+    ref_y, ref_w = O.sample_features(z, mean_fn, mean, l_in, l_out, feat, dfeat if deriv else None,
+                                     lo, hi, naive=False)
+    ys, ws = ops.sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat if deriv else None, z=z,
+                                 lower=lo, upper=hi)
+    assert nerr(host(ws), ref_w) < TOL
+    ys = host(ys)
+    assert nerr(ys[..., :d], ref_y[..., :d]) < TOL
+    if deriv:
+        assert nerr(ys[..., d:], ref_y[..., d:]) < TOL
+    # every time step individually (rows with small features are not hidden by the global maximum)
+    row_scale = np.maximum(np.max(np.abs(ref_y[..., :d]), axis=(0, 2)), 1e-300)
+    rel = np.max(np.abs(ys[..., :d] - ref_y[..., :d]), axis=(0, 2)) / row_scale
+    assert np.max(rel) < 20 * TOL, float(np.max(rel))
+
+
+def test_sample_features_expand_philox_matches_injected(ops):
+    K, F, d, T = 513, 21, 2, 300
+    rng = np.random.default_rng(0)
+    l_in = f32r(np.linalg.cholesky(np.eye(F) + 0.1))
+    l_out = f32r(np.diag([0.3, 0.2]))
+    mean_fn, mean = f32r(rng.standard_normal(d)), f32r(rng.standard_normal((F, d)))
+    feat, dfeat = f32r(rng.standard_normal((T, F))), f32r(rng.standard_normal((T, F)))
+    z = ops.philox_normal(K, F * d, seed=3, draw_id=4, row_offset=77)
+    ya, wa = ops.sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat, z=z)
+    yb, wb = ops.sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat, seed=3, draw_id=4, row_offset=77)
+    assert (host(wa) == host(wb)).all() and (host(ya) == host(yb)).all()
+
+
 def test_sample_iid_golden(ops, golden):
     g = golden
     K, H, d = 64, 8, 3
