@@ -86,6 +86,26 @@ int ppi_kernel_gram_chol(const double* t1, int n1, const double* t2, int n2, int
                          double lengthscale, double period, double* gram64, float* gram32,
                          double* chol64, float* chol32, int* status, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * f1  MPC time shift of a kernel prior onto the next window, one launch, fp64
+ *     BaseKernel.update_timesteps, ppi/policies.py:761-791 (caller mpc/mpc.py:64-65).
+ *   gain = P^-1 (P - Sigma) P^-T;  cross = k(t_new, t_old)
+ *   mean_new = clip(cross P^-1 mean + mean_fn, lower, upper) - mean_fn          (n_new, d)
+ *   cov_new  = k(t_new, t_new) - anneal cross gain cross^T + jitter I          (n_new, n_new)
+ *   chol_new = lower Cholesky factor of cov_new; *status = 0, else 1 + index of the failing pivot
+ * prior (P) / prior_inv are the cached Gram matrix of the old window and its inverse (:747-753,
+ * 766-768), cov_in (Sigma) and mean (n_old, d) the current moments, all fp64 row-major on the
+ * device; jitter = eps * sigma (:785).  lower/upper (d) may both be NULL (no limiter).
+ * n_new <= 160.  workspace: ppi_kernel_shift_workspace_bytes(n_old, n_new) bytes.
+ * ---------------------------------------------------------------------------------------- */
+size_t ppi_kernel_shift_workspace_bytes(int n_old, int n_new);
+int ppi_kernel_shift(int kind, double sigma, double lengthscale, double period, const double* t_old,
+                     int n_old, const double* t_new, int n_new, const double* prior,
+                     const double* prior_inv, const double* cov_in, const double* mean, int d,
+                     const double* mean_fn, const double* lower, const double* upper, double anneal,
+                     double jitter, double* mean_new, double* cov_new, double* chol_new,
+                     double* status, void* workspace, void* stream);
+
 /* np.linalg.cholesky of a small fp64 matrix (n <= 160), one thread block; a may alias l64.
  * ppi/policies.py:312,321,481,819                                                          */
 int ppi_cholesky_small(const double* a, int n, double* l64, float* l32, int* status, void* stream);

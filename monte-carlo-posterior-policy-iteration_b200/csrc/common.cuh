@@ -230,30 +230,37 @@ __device__ __forceinline__ float clipf(float v, float lo, float hi) {
 // In-place right-looking Cholesky of the n x n matrix in shared memory `a` (lower part used).
 // Returns through *fail the 1-based index of the first non-positive pivot (0 = success).
 __device__ inline void block_cholesky(double* a, int n, int* fail_smem) {
-  if (threadIdx.x == 0) *fail_smem = 0;
+  // Right-looking, ONE barrier per column: the trailing update uses the unscaled column j,
+  // a[i][k] -= a[i][j] a[k][j] / a[j][j]; column j is final after step j and is scaled by
+  // 1 / sqrt(pivot) in a last pass.  Every thread reads the same pivot, so the failure exit is uniform.
+  int fail = 0;
   __syncthreads();
   for (int j = 0; j < n; ++j) {
-    if (threadIdx.x == 0) {
-      const double p = a[j * n + j];
-      if (!(p > 0.0) || !isfinite(p)) {
-        if (*fail_smem == 0) *fail_smem = j + 1;
-        a[j * n + j] = nan("");
-      } else {
-        a[j * n + j] = sqrt(p);
+    const double p = a[j * n + j];
+    if (!(p > 0.0) || !isfinite(p)) {
+      fail = j + 1;
+      break;
+    }
+    const double inv = 1.0 / p;
+    const int m = n - j - 1;  // trailing size
+    for (int e = threadIdx.x; e < m * m; e += blockDim.x) {
+      const int r = e / m, c = e - r * m;
+      if (c <= r) {
+        const int i = j + 1 + r, k = j + 1 + c;
+        a[i * n + k] -= a[i * n + j] * a[k * n + j] * inv;
       }
     }
     __syncthreads();
-    if (*fail_smem) break;
-    const double dj = a[j * n + j];
-    for (int i = j + 1 + threadIdx.x; i < n; i += blockDim.x) a[i * n + j] /= dj;
-    __syncthreads();
-    const int m = n - j - 1;  // trailing size
-    for (int e = threadIdx.x; e < m * m; e += blockDim.x) {
-      const int i = j + 1 + e / m, k = j + 1 + e % m;
-      if (k <= i) a[i * n + k] -= a[i * n + j] * a[k * n + j];
-    }
-    __syncthreads();
   }
+  const int done = fail ? fail - 1 : n;  // columns with a valid pivot
+  for (int e = threadIdx.x; e < n * done; e += blockDim.x) {
+    const int i = e / done, j = e - i * done;
+    if (j < i) a[i * n + j] /= sqrt(a[j * n + j]);
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < n; j += blockDim.x)
+    a[j * n + j] = j < done ? sqrt(a[j * n + j]) : nan("");
+  if (threadIdx.x == 0) *fail_smem = fail;
   __syncthreads();
 }
 

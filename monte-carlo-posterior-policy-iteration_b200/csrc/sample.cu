@@ -588,6 +588,116 @@ gram_chol_kernel(const double* __restrict__ t1, int n1, const double* __restrict
   if (threadIdx.x == 0 && status) *status = fail;
 }
 
+// ------------------------------------------------------------------------------------------
+// MPC time shift of a kernel prior (BaseKernel.update_timesteps, ppi/policies.py:761-791), fp64,
+// one block: the step mpc/mpc.py:64-65 runs before every planner update.
+//   gain  = P^-1 (P - Sigma) P^-T                 covariance reduction of the old window
+//   cross = k(t_new, t_old)
+//   mean' = clip(cross P^-1 mean + mean_fn) - mean_fn
+//   cov'  = k(t_new, t_new) - anneal cross gain cross^T + jitter I,   chol' = cholesky(cov')
+// Five H x H products, the two Gram matrices and the factorisation in ONE launch (the host mirror
+// needed three Gram launches with a device->host read each plus NumPy).  The matrices live in a
+// global workspace (L1/L2 resident at these sizes); cov' is factorised in shared memory.
+// ------------------------------------------------------------------------------------------
+// C (m x n) = A (m x k) B (k x n);  TB: B is given transposed, (n x k).  A single SM moves 128 B
+// per clock through L1, i.e. 16 B per thread and clock at most: a one-output-per-thread product
+// (16 B of loads per FMA) is bound by that, not by the fp64 pipe.  Each thread therefore owns a
+// 4 x 4 block of C (8 loads per 16 FMAs).  (No __restrict__ / read-only loads: the operands may
+// have been written earlier in this kernel.)
+template <bool TB>
+__device__ __forceinline__ void block_gemm64(const double* A, const double* B, double* C, int m, int n,
+                                             int k) {
+  const int tm = (m + 3) >> 2, tn = (n + 3) >> 2;
+  for (int e = threadIdx.x; e < tm * tn; e += blockDim.x) {
+    // interleaved ownership: rows ti + tm r, columns tj + tn c, so that the threads of a warp read
+    // consecutive columns of B (one or two 128-byte lines per load) and mostly the same rows of A
+    const int ti = e / tn, tj = e - ti * tn;
+    const double* a[4];
+    const double* b[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      a[r] = A + (size_t)min(ti + tm * r, m - 1) * k;
+      const int c = min(tj + tn * r, n - 1);
+      b[r] = TB ? B + (size_t)c * k : B + c;
+    }
+    const size_t sb = TB ? 1 : (size_t)n;
+    double acc[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc[r][c] = 0.0;
+    for (int l = 0; l < k; ++l) {
+      double av[4], bv[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        av[r] = a[r][l];
+        bv[r] = b[r][(size_t)l * sb];
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[r][c] = fma(av[r], bv[c], acc[r][c]);
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (ti + tm * r < m && tj + tn * c < n) C[(size_t)(ti + tm * r) * n + tj + tn * c] = acc[r][c];
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(512)
+kernel_shift_kernel(int kind, double sigma, double ls, double period, const double* __restrict__ t_old,
+                    int n_old, const double* __restrict__ t_new, int n_new,
+                    const double* __restrict__ prior, const double* __restrict__ prior_inv,
+                    const double* __restrict__ cov_in, const double* __restrict__ mean, int d,
+                    const double* __restrict__ mean_fn, const double* __restrict__ lower,
+                    const double* __restrict__ upper, double anneal, double jitter,
+                    double* __restrict__ mean_new, double* __restrict__ cov_new,
+                    double* __restrict__ chol_new, double* __restrict__ status, double* ws) {
+  extern __shared__ double sa[];   // n_new x n_new
+  __shared__ int fail;
+  double* w0 = ws;                                  // n_old^2: P - Sigma, later gain
+  double* w1 = w0 + (size_t)n_old * n_old;          // n_old^2: P^-1 (P - Sigma)
+  double* cross = w1 + (size_t)n_old * n_old;       // n_new x n_old
+  double* w2 = cross + (size_t)n_new * n_old;       // n_new x n_old: cross P^-1, later cross gain
+  for (int e = threadIdx.x; e < n_old * n_old; e += blockDim.x) w0[e] = prior[e] - cov_in[e];
+  for (int e = threadIdx.x; e < n_new * n_old; e += blockDim.x) {
+    const int i = e / n_old, j = e - i * n_old;
+    cross[e] = gram_entry(kind, t_new[i], t_old[j], sigma, ls, period, n_new == n_old, i == j);
+  }
+  __syncthreads();
+  block_gemm64<false>(prior_inv, w0, w1, n_old, n_old, n_old);
+  block_gemm64<true>(w1, prior_inv, w0, n_old, n_old, n_old);       // gain = w1 P^-T
+  block_gemm64<false>(cross, prior_inv, w2, n_new, n_old, n_old);   // cross P^-1
+  for (int e = threadIdx.x; e < n_new * d; e += blockDim.x) {
+    const int i = e / d, c = e - i * d;
+    double acc = 0.0;
+    for (int l = 0; l < n_old; ++l) acc = fma(w2[(size_t)i * n_old + l], mean[(size_t)l * d + c], acc);
+    double v = acc + mean_fn[c];
+    if (lower) v = fmin(fmax(v, lower[c]), upper[c]);
+    mean_new[e] = v - mean_fn[c];
+  }
+  __syncthreads();
+  block_gemm64<false>(cross, w0, w2, n_new, n_old, n_old);          // cross gain
+  block_gemm64<true>(w2, cross, cov_new, n_new, n_new, n_old);      // (cross gain) cross^T
+  for (int e = threadIdx.x; e < n_new * n_new; e += blockDim.x) {
+    const int i = e / n_new, j = e - i * n_new;
+    double v = gram_entry(kind, t_new[i], t_new[j], sigma, ls, period, true, i == j) - anneal * cov_new[e];
+    if (i == j) v += jitter;
+    cov_new[e] = v;
+    sa[e] = v;
+  }
+  __syncthreads();
+  block_cholesky(sa, n_new, &fail);
+  for (int e = threadIdx.x; e < n_new * n_new; e += blockDim.x) {
+    const int i = e / n_new, j = e - i * n_new;
+    chol_new[e] = (j <= i) ? sa[e] : 0.0;
+  }
+  if (threadIdx.x == 0) *status = (double)fail;
+}
+
 __global__ void __launch_bounds__(256)
 chol_small_kernel(const double* __restrict__ a, int n, double* __restrict__ l64,
                   float* __restrict__ l32, int* __restrict__ status) {
@@ -664,6 +774,35 @@ extern "C" int ppi_kernel_gram_chol(const double* t1, int n1, const double* t2, 
                                                            period, gram64, gram32, chol64, chol32,
                                                            status);
   return check_launch("gram_chol_kernel");
+}
+
+extern "C" size_t ppi_kernel_shift_workspace_bytes(int n_old, int n_new) {
+  if (n_old <= 0 || n_new <= 0) return 0;
+  return (2 * (size_t)n_old * n_old + 2 * (size_t)n_new * n_old) * sizeof(double);
+}
+
+extern "C" int ppi_kernel_shift(int kind, double sigma, double lengthscale, double period,
+                                const double* t_old, int n_old, const double* t_new, int n_new,
+                                const double* prior, const double* prior_inv, const double* cov_in,
+                                const double* mean, int d, const double* mean_fn, const double* lower,
+                                const double* upper, double anneal, double jitter, double* mean_new,
+                                double* cov_new, double* chol_new, double* status, void* workspace,
+                                void* stream) {
+  PPI_REQUIRE(t_old && t_new && n_old > 0 && n_new > 0 && d > 0 && prior && prior_inv && cov_in && mean &&
+                  mean_fn && mean_new && cov_new && chol_new && status && workspace,
+              PPI_ERR_INVALID, "ppi_kernel_shift: bad arguments");
+  PPI_REQUIRE(kind >= 0 && kind <= PPI_KERNEL_WHITE, PPI_ERR_INVALID, "unknown kernel kind %d", kind);
+  PPI_REQUIRE((lower == nullptr) == (upper == nullptr), PPI_ERR_INVALID,
+              "lower and upper must both be given or both be NULL");
+  PPI_REQUIRE(anneal >= 0.0 && anneal <= 1.0, PPI_ERR_INVALID, "anneal must lie in [0, 1]");
+  const size_t smem = (size_t)n_new * n_new * sizeof(double);
+  PPI_REQUIRE(smem <= (size_t)kMaxSmemBytes, PPI_ERR_UNSUPPORTED,
+              "single-block Cholesky supports n <= 160 (got %d)", n_new);
+  if (int rc = set_smem(kernel_shift_kernel, smem)) return rc;
+  kernel_shift_kernel<<<1, 512, smem, (cudaStream_t)stream>>>(
+      kind, sigma, lengthscale, period, t_old, n_old, t_new, n_new, prior, prior_inv, cov_in, mean, d,
+      mean_fn, lower, upper, anneal, jitter, mean_new, cov_new, chol_new, status, (double*)workspace);
+  return check_launch("kernel_shift_kernel");
 }
 
 extern "C" int ppi_cholesky_small(const double* a, int n, double* l64, float* l32, int* status,

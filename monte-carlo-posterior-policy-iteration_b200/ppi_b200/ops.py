@@ -62,6 +62,55 @@ def gram(kind, t1, t2, sigma, ls=1.0, period=1.0, chol=False):
     return g, l, int(status.item())
 
 
+_shift_staging = {}
+
+
+def kernel_shift(kind, sigma, ls, period, t_old, t_new, prior, prior_inv, cov_in, mean, mean_fn, lower,
+                 upper, anneal, jitter):
+    """MPC time shift of a kernel prior (BaseKernel.update_timesteps, ppi/policies.py:761-791) in one
+    launch: one packed host->device copy of the window's moments, one device->host read of the result,
+    both through pinned staging buffers kept per window shape.
+    prior / prior_inv are device fp64 tensors (cached by the policy between control steps).
+    -> (mean_new, cov_new, chol_new, status) as host fp64 arrays."""
+    dev = require_cuda()
+    n_old, n_new, d = t_old.shape[0], t_new.shape[0], mean.shape[1]
+    has_lim = lower is not None
+    sizes = [n_old, n_new, n_old * n_old, n_old * d, d] + ([d, d] if has_lim else [])
+    key = (dev, n_old, n_new, d, has_lim)
+    st = _shift_staging.get(key)
+    if st is None:
+        offs = np.cumsum([0] + sizes)
+        n_out = n_new * d + 2 * n_new * n_new + 1
+        h_in = torch.empty(int(offs[-1]), dtype=torch.float64, pin_memory=True)
+        h_out = torch.empty(n_out, dtype=torch.float64, pin_memory=True)
+        d_in = torch.empty(int(offs[-1]), dtype=torch.float64, device=dev)
+        d_out = torch.empty(n_out, dtype=torch.float64, device=dev)
+        ws = torch.empty(max(1, _lib.query("ppi_kernel_shift_workspace_bytes", n_old, n_new) // 8),
+                         dtype=torch.float64, device=dev)
+        a, b = n_new * d, n_new * d + n_new * n_new
+        st = _shift_staging[key] = dict(
+            h_in=h_in, h_out=h_out, d_in=d_in, d_out=d_out, ws=ws, np_in=h_in.numpy(), np_out=h_out.numpy(),
+            offs=[int(o) for o in offs], in_ptrs=[d_in.data_ptr() + 8 * int(o) for o in offs[:-1]],
+            out_ptrs=[d_out.data_ptr(), d_out.data_ptr() + 8 * a, d_out.data_ptr() + 8 * b,
+                      d_out.data_ptr() + 8 * (n_out - 1)], cut=(a, b, b + n_new * n_new))
+    buf, offs = st["np_in"], st["offs"]
+    parts = [t_old, t_new, cov_in, mean, mean_fn] + ([lower, upper] if has_lim else [])
+    for i, part in enumerate(parts):
+        buf[offs[i]:offs[i + 1]] = np.asarray(part, np.float64).reshape(-1)
+    st["d_in"].copy_(st["h_in"], non_blocking=True)
+    ip, op = st["in_ptrs"], st["out_ptrs"]
+    _lib.call("ppi_kernel_shift", _lib.KERNEL_KINDS[kind], float(sigma), float(ls), float(period),
+              ip[0], n_old, ip[1], n_new, ptr(prior), ptr(prior_inv), ip[2], ip[3], d, ip[4],
+              ip[5] if has_lim else None, ip[6] if has_lim else None, float(anneal), float(jitter),
+              op[0], op[1], op[2], op[3], ptr(st["ws"]), stream_ptr())
+    st["h_out"].copy_(st["d_out"], non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    host = st["np_out"]
+    a, b, c = st["cut"]
+    return (host[:a].reshape(n_new, d).copy(), host[a:b].reshape(n_new, n_new).copy(),
+            host[b:c].reshape(n_new, n_new).copy(), int(host[-1]))
+
+
 def cholesky_small(a):
     """np.linalg.cholesky of a small fp64 matrix on the device; returns (L fp64, status)."""
     dev = require_cuda()

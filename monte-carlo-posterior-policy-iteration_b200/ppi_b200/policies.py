@@ -792,6 +792,15 @@ class BaseKernel(BasePrimitive):
     def timesteps_match(self, t):
         return t.shape == self.t.shape and bool((t == self.t).all())
 
+    def _prior_device(self):
+        """(prior, prior_inv) as device fp64 tensors, re-uploaded when the host arrays were replaced."""
+        key = (id(self.covariance_in_prior), id(self.covariance_in_prior_inv))
+        cache = getattr(self, "_prior_dev", None)
+        if cache is None or cache[0] != key:
+            self._prior_dev = cache = (key, f64(self.covariance_in_prior), f64(self.covariance_in_prior_inv),
+                                       self.covariance_in_prior, self.covariance_in_prior_inv)
+        return cache[1], cache[2]
+
     def update_timesteps(self, time_sequence, anneal=1.0, eps=1e-5):
         """GP shift of mean / covariance onto a new time window (ppi/policies.py:761-791)."""
         assert 0.0 <= anneal <= 1.0
@@ -801,6 +810,21 @@ class BaseKernel(BasePrimitive):
         if n_new != self.covariance_in_prior.shape[0]:
             self.covariance_in_prior = self.k(self.t, self.t)
             self.covariance_in_prior_inv = np.linalg.inv(self.covariance_in_prior)
+        if self.kernel_kind in _lib.KERNEL_KINDS and n_new <= 160:
+            # one fp64 launch for the whole shift (ppi_kernel_shift): the Gram matrices, the five H x H
+            # products and the factorisation never leave the device; the cached prior and its inverse
+            # are uploaded only when compute_prior / a change of window length replaced them
+            lo, hi = _limits(self.limiter)
+            mean, cov, chol, status = ops.kernel_shift(
+                self.kernel_kind, self.sigma, getattr(self, "ls", 1.0), getattr(self, "period", 1.0), self.t,
+                time_sequence, *self._prior_device(), self.covariance_in, self.mean, self.mean_fn, lo, hi,
+                anneal, eps * self.sigma)
+            if status != 0:
+                raise np.linalg.LinAlgError("Matrix is not positive definite")
+            self.mean, self.covariance_in, self.covariance_in_sqrt = mean, cov, chol
+            self.t = time_sequence
+            self.dim_features = n_new
+            return
         p_inv = self.covariance_in_prior_inv
         gain = p_inv @ (self.covariance_in_prior - self.covariance_in) @ p_inv.T
         cross = self.k(time_sequence, self.t)
@@ -847,7 +871,9 @@ class BaseKernel(BasePrimitive):
         mu_y = self.mean_fn[None, :] + self.mean
         if only_mean:
             return mu_y
-        sigma_y = np.sqrt(np.outer(np.diag(self.covariance_in), np.diag(self.covariance_out)))
+        # the reference reshapes diag(kron(cov_out, cov_in)) -- actuator-major -- row by row into
+        # (H, d) (ppi/policies.py:856-859); the same element order is kept here
+        sigma_y = np.sqrt(np.outer(np.diag(self.covariance_out), np.diag(self.covariance_in)).reshape(mu_y.shape))
         return mu_y, self.covariance_in, self.covariance_out, sigma_y
 
 
@@ -887,6 +913,7 @@ class StationaryKernel(BaseKernel):
 
 
 class SquaredExponentialKernel(StationaryKernel):
+    kernel_kind = "se"
     can_optimize = True
     param_bounds = ((1e-5, None), (1e-5, 1e3))
 
@@ -896,24 +923,28 @@ class SquaredExponentialKernel(StationaryKernel):
 
 
 class Matern12Kernel(StationaryKernel):
+    kernel_kind = "matern12"
     @staticmethod
     def _k(t1, t2, sigma, ls, eps=1e-8, lib=np):
         return _gram_host("matern12", t1, t2, sigma, ls)
 
 
 class Matern32Kernel(StationaryKernel):
+    kernel_kind = "matern32"
     @staticmethod
     def _k(t1, t2, sigma, ls, eps=1e-8, lib=np):
         return _gram_host("matern32", t1, t2, sigma, ls)
 
 
 class Matern52Kernel(StationaryKernel):
+    kernel_kind = "matern52"
     @staticmethod
     def _k(t1, t2, sigma, ls, eps=1e-8, lib=np):
         return _gram_host("matern52", t1, t2, sigma, ls)
 
 
 class PeriodicKernel(StationaryKernel):
+    kernel_kind = "periodic"
     param_bounds = ((1e-3, None), (1e-4, 1e3), (1e-3, 1e3))
 
     def __init__(self, time_sequence, action_dimension, mean, covariance_in, covariance_out, lengthscale,

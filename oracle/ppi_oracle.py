@@ -519,3 +519,57 @@ def powerlaw_psd_gaussian(exponent, size, rng):
     si[..., 0] = 0
     sr[..., 0] *= np.sqrt(2)
     return np.fft.irfft(sr + 1j * si, n=samples, axis=-1) / sigma
+
+
+# ---------------------------------------------------------------------------------------------
+# the MPC time shift of the prior (mpc/mpc.py:64-65 -> policy.update_timesteps)
+# ---------------------------------------------------------------------------------------------
+def kernel_shift(gram_fn, t_old, t_new, prior, prior_inv, cov_in, mean, mean_fn, lower, upper, anneal, sigma,
+                 eps=1e-5):
+    """BaseKernel.update_timesteps (ppi/policies.py:761-791): GP regression of the posterior mean and
+    of the covariance reduction `prior - cov_in` from the old window onto the new one.
+    `gram_fn(t1, t2)` is the kernel; prior / prior_inv are the cached Gram matrix of the old window and
+    its inverse (recomputed by the caller when the window length changes, :766-768).
+    Returns (mean_new, cov_new, chol_new)."""
+    gain = prior_inv @ (prior - cov_in) @ prior_inv.T                                   # :770-774
+    cross = gram_fn(t_new, t_old)                                                       # :776
+    mean_new = cross @ prior_inv @ mean                                                 # :778
+    shifted = mean_new + mean_fn[None, :]
+    if lower is not None:
+        shifted = np.clip(shifted, lower, upper)                                        # :779
+    mean_new = shifted - mean_fn[None, :]                                               # :780
+    cov_new = (gram_fn(t_new, t_new) - anneal * cross @ gain @ cross.T
+               + eps * sigma * np.eye(t_new.shape[0]))                                  # :782-786
+    return mean_new, cov_new, np.linalg.cholesky(cov_new)
+
+
+def white_kernel_shift(t_old, t_new, mean, cov_in, sigma):
+    """WhiteNoiseKernel.update_timesteps (ppi/policies.py:1093-1104): kept time steps carry their
+    moments over, new ones start from the prior sigma I."""
+    remap = 1.0 * ((t_new.reshape(-1, 1) - t_old.reshape(1, -1)) == 0.0)
+    n = t_new.shape[0]
+    cov = remap @ cov_in @ remap.T + (np.eye(n) - remap @ remap.T) @ (sigma * np.eye(n))
+    return remap @ mean, cov, np.linalg.cholesky(cov)
+
+
+def iid_shift(t_old, t_new, mean, std, sigma_out, anneal):
+    """WhiteNoiseIid.update_timesteps (ppi/policies.py:1176-1188); sigma_out = sqrt(cov_out * cov_in)
+    (:1130), a (d, d) matrix the initial std is `ones @ sigma_out` of."""
+    remap = 1.0 * ((t_new.reshape(-1, 1) - t_old.reshape(1, -1)) == 0.0)
+    n = t_new.shape[0]
+    std_new = np.ones((n, sigma_out.shape[0])) @ sigma_out
+    s = np.sqrt((remap @ std) ** 2 + ((np.eye(n) - remap @ remap.T) @ std_new) ** 2)
+    return remap @ mean, anneal * s + (1 - anneal) * std_new
+
+
+def features_anneal(cov_in, cov_init, anneal):
+    """BaseFeatures.update_timesteps (ppi/policies.py:396-402)."""
+    cov = anneal * cov_in + (1 - anneal) * cov_init
+    return cov, np.linalg.cholesky(cov)
+
+
+def kernel_predict(mean_fn, mean, cov_in, cov_out):
+    """BaseKernel.predict (ppi/policies.py:850-860): (mu_y, std_y) with std_y the square root of the
+    diagonal of kron(cov_out, cov_in) in the reference's (row-major reshape) element order."""
+    mu = mean_fn[None, :] + mean
+    return mu, np.sqrt(np.diag(np.kron(cov_out, cov_in)).reshape(mu.shape))
