@@ -185,6 +185,102 @@ def _row(samples_t, row_offset, n_total, replicated, index):
     return broadcast_row(samples_t, index, n_total).cpu().numpy().astype(np.float64)
 
 
+def _full_from_upper(acc):
+    """Symmetric host matrix from a device accumulator that holds the upper triangle."""
+    u = np.triu(to_host64(acc))
+    return u + u.T - np.diag(np.diag(u))
+
+
+def m_projection(log_w, samples):
+    """Weighted Gaussian moment match, ppi/policies.py:78-93, on the device: weight normalisation
+    (ppi_normalise_log_weights), weighted mean (ppi_wmoments_diag) and covariance (ppi_wmoments_dense).
+    samples: (K, D) host array or DeviceArray.  -> (mu, sigma, ess), host fp64."""
+    w = _weights(log_w)
+    x, row_offset, n_total, replicated = _samples(samples)
+    x = x.reshape(x.shape[0], -1)
+    nw = _local(w.nw, row_offset, x.shape[0])
+    s1 = ops.wmoments_diag(x, nw)
+    if not replicated:
+        all_reduce_sum(s1)
+    cov = ops.wmoments_dense(x, nw, shift=s1.float())
+    if not replicated:
+        all_reduce_sum(cov)
+    sigma = to_host64(cov)
+    return to_host64(s1), symmetric(sigma), float(w.stats.ess)
+
+
+def m_projection_mavn(log_w, samples, covariance_in, covariance_out, iterations=1, update_out=False,
+                      use_tqdm=False):
+    """Weighted matrix-normal moment match, ppi/policies.py:96-143, on the device, including the
+    iterated MLE: `iterations` rounds, the output factor re-estimated when `update_out` (the same
+    contraction kernel on the transposed samples).  -> (mean, covariance_in, covariance_out, ess)."""
+    assert iterations > 0
+    w = _weights(log_w)
+    x, row_offset, n_total, replicated = _samples(samples)
+    K_local, H, d = x.shape
+    nw = _local(w.nw, row_offset, K_local)
+    s1 = ops.wmoments_diag(x, nw)
+    if not replicated:
+        all_reduce_sum(s1)
+    shift = s1.float().reshape(H, d)
+    cov_out = np.asarray(covariance_out, np.float64)
+    cov_in = np.asarray(covariance_in, np.float64)
+    xt = shift_t = None
+    for _ in range(iterations):
+        acc = ops.wmoments_matnorm(x, nw, shift=shift, inv_cov_out=1.0 / np.diag(cov_out))
+        if not replicated:
+            all_reduce_sum(acc)
+        cov_in = _full_from_upper(acc) / d
+        if update_out:
+            if xt is None:
+                xt, shift_t = x.transpose(1, 2).contiguous(), shift.t().contiguous()
+            acc_o = ops.wmoments_matnorm(xt, nw, shift=shift_t, inv_cov_out=1.0 / np.diag(cov_in))
+            if not replicated:
+                all_reduce_sum(acc_o)
+            cov_out = _full_from_upper(acc_o) / H
+    return to_host64(s1).reshape(H, d), cov_in, cov_out, float(w.stats.ess)
+
+
+def vec(x):
+    """Column-major vectorisation, ppi/policies.py:161-171."""
+    if x.ndim == 3:
+        a, b, c = x.shape
+        return x.reshape((a, b * c), order="F")
+    return x.reshape((-1, 1), order="F")
+
+
+def matrix_gaussian_kl(mean_1, cov_in_1, cov_out_1, mean_2, cov_in_2, cov_out_2):
+    """KL between two matrix normals, ppi/policies.py:174-210 (host, H x H and d x d algebra; the
+    determinants are taken as clamped log-determinants so that they cannot under- or overflow)."""
+    n, p = mean_1.shape
+    diff = mean_2 - mean_1
+    sf1, sf2 = p / np.trace(cov_out_1), p / np.trace(cov_out_2)
+    cov_out_1, cov_out_2 = cov_out_1 * sf1, cov_out_2 * sf2
+    cov_in_1, cov_in_2 = cov_in_1 / sf1, cov_in_2 / sf2
+
+    def logdet(m):
+        sign, ld = np.linalg.slogdet(m)
+        return _clamped_logdet(ld, sign > 0)
+
+    quad = vec(diff).T @ vec(np.linalg.solve(cov_in_2, np.linalg.solve(cov_out_2, diff.T).T))
+    trace = np.trace(np.linalg.solve(cov_out_2, cov_out_1)) * np.trace(np.linalg.solve(cov_in_2, cov_in_1))
+    return float(0.5 * (n * logdet(cov_out_2) - n * logdet(cov_out_1) + p * logdet(cov_in_2)
+                        - p * logdet(cov_in_1) + trace + quad.item() - n * p))
+
+
+def convolve(signal_samples, kernel):
+    """Causal recursive filter of the smooth-noise priors over the time axis of (n, h, d) samples,
+    ppi/policies.py:1257-1267: each step replaces x[t] by the kernel-weighted sum of the ALREADY
+    filtered window ending at t.  Host helper; the policies apply the same filter on the device as a
+    lower-triangular matrix (ema_filter_matrix)."""
+    out = np.array(signal_samples, copy=True)
+    width = kernel.shape[0]
+    assert width > 1
+    for t in range(width - 1, out.shape[1]):
+        out[:, t, :] = np.tensordot(kernel, out[:, t - width + 1:t + 1, :], axes=([0], [1]))
+    return out
+
+
 def _draw(sampler, n_total, d):
     """Base normals for this rank's rows: (z_local or None, seed, draw_id, row_offset, n_local)."""
     begin, end = shard_rows(n_total)
@@ -788,6 +884,40 @@ class BaseKernel(BasePrimitive):
         self.t = plan_time
         self.covariance_in_prior = self.k(plan_time, plan_time)
         self.covariance_in_prior_inv = np.linalg.inv(self.covariance_in_prior)
+
+    def optimize_hyperparams(self, target_matrix):
+        """Kernel hyper-parameters by maximum likelihood of a target trajectory (ppi/policies.py:696-714):
+        offline, SciPy L-BFGS-B on the host over the Gram matrices of the device kernel."""
+        from scipy.optimize import minimize
+        from scipy.stats import multivariate_normal
+
+        target = vec(np.asarray(target_matrix, np.float64))[:, 0]
+        zero = np.zeros(self.dim_features * self.dim_out)
+
+        def objective(param):
+            cov = np.kron(self.covariance_out, self._k(self.t, self.t, *param))
+            return -multivariate_normal.logpdf(target, mean=zero, cov=cov)
+
+        res = minimize(objective, x0=np.ones_like(np.array(self.param, dtype=np.float64)),
+                       bounds=self.param_bounds, method="L-BFGS-B")
+        logging.info(res)
+        self.param = res.x
+
+    def loglikelihood(self, x):
+        """Mean matrix-normal log-likelihood of (n, H, d) samples, ppi/policies.py:716-733."""
+        x = np.asarray(x, np.float64)
+        n, d_i, d_o = x.shape
+        assert d_i == self.dim_features and d_o == self.dim_out
+        out_sqrt = np.linalg.cholesky(self.covariance_out)
+        in_inv = np.linalg.solve(self.covariance_in_sqrt, self.covariance_in_sqrt.T).T
+        out_inv = np.linalg.solve(out_sqrt, out_sqrt.T).T
+        diff = x - self.mean[None, ...] - self.mean_fn[None, None, :]
+        op = np.einsum("bij,ik,bkl->bjl", diff, in_inv, diff)
+        llh = -0.5 * np.trace(np.einsum("ij,bjk->bik", out_inv, op)) / n
+        llh -= 0.5 * self.dim_sample * np.log(2 * np.pi)
+        llh -= 0.5 * self.dim_out * np.linalg.slogdet(self.covariance_in)[1]
+        llh -= 0.5 * self.dim_features * np.linalg.slogdet(self.covariance_out)[1]
+        return llh
 
     def timesteps_match(self, t):
         return t.shape == self.t.shape and bool((t == self.t).all())

@@ -176,24 +176,55 @@ def m_projection(log_w, samples, naive=True):
     return mu, sigma, ess
 
 
-def m_projection_mavn(log_w, samples, covariance_in, covariance_out, naive=True):
-    """ppi/policies.py:96-143 with the defaults iterations=1, update_out=False."""
-    d_out = covariance_out.shape[0]
+def m_projection_mavn(log_w, samples, covariance_in, covariance_out, naive=True, iterations=1,
+                      update_out=False):
+    """ppi/policies.py:96-143: matrix-normal MLE; `iterations` rounds of the flip-flop update, the output
+    covariance re-estimated only when update_out (both use the DIAGONAL of the other factor, :123,128)."""
+    assert iterations > 0
+    d_in, d_out = samples.shape[1], covariance_out.shape[0]
     lse_w = logsumexp(log_w)
     log_nw = log_w - lse_w
     nw = np.exp(log_nw)
     ess = np.exp(-logsumexp(2 * log_nw))
     mu = np.einsum("b, bij->ij", nw, samples)
     diff = samples - mu[None, ...]
-    out_inv = np.diag(1.0 / np.diag(covariance_out))
-    if naive:
-        cov_in = np.einsum("b,bij,jk,blk->il", nw, diff, out_inv, diff) / d_out
-    else:
-        s = diff * np.sqrt(nw[:, None, None] / np.diag(covariance_out)[None, None, :])
-        a = s.transpose(1, 0, 2).reshape(s.shape[1], -1)
-        cov_in = a @ a.T / d_out
-    cov_in = 0.5 * (cov_in + cov_in.T)
+    for _ in range(iterations):
+        out_inv = np.diag(1.0 / np.diag(covariance_out))
+        if naive:
+            cov_in = np.einsum("b,bij,jk,blk->il", nw, diff, out_inv, diff) / d_out
+        else:
+            s = diff * np.sqrt(nw[:, None, None] / np.diag(covariance_out)[None, None, :])
+            a = s.transpose(1, 0, 2).reshape(s.shape[1], -1)
+            cov_in = a @ a.T / d_out
+        cov_in = 0.5 * (cov_in + cov_in.T)
+        if update_out:
+            in_inv = np.diag(1.0 / np.diag(cov_in))
+            covariance_out = np.einsum("b,bij,ik,bkl->jl", nw, diff, in_inv, diff) / d_in   # :131-133
+            covariance_out = 0.5 * (covariance_out + covariance_out.T)
     return mu, cov_in, covariance_out, ess
+
+
+def vec(x):
+    """ppi/policies.py:161-171: column-major vectorisation."""
+    if x.ndim == 3:
+        a, b, c = x.shape
+        return x.reshape((a, b * c), order="F")
+    return x.reshape((-1, 1), order="F")
+
+
+def matrix_gaussian_kl(mean_1, cov_in_1, cov_out_1, mean_2, cov_in_2, cov_out_2):
+    """ppi/policies.py:174-210 (output factors normalised to trace p before the determinants)."""
+    eps = np.finfo(np.float64).tiny
+    n, p = mean_1.shape
+    diff = mean_2 - mean_1
+    sf1, sf2 = p / np.trace(cov_out_1), p / np.trace(cov_out_2)
+    cov_out_1, cov_out_2 = cov_out_1 * sf1, cov_out_2 * sf2
+    cov_in_1, cov_in_2 = cov_in_1 / sf1, cov_in_2 / sf2
+    return (0.5 * (n * np.log(max(eps, np.linalg.det(cov_out_2))) - n * np.log(max(eps, np.linalg.det(cov_out_1)))
+                   + p * np.log(max(eps, np.linalg.det(cov_in_2))) - p * np.log(max(eps, np.linalg.det(cov_in_1)))
+                   + np.trace(np.kron(np.linalg.solve(cov_out_2, cov_out_1), np.linalg.solve(cov_in_2, cov_in_1)))
+                   + vec(diff).T @ vec(np.linalg.solve(cov_in_2, np.linalg.solve(cov_out_2, diff.T).T))
+                   - n * p)).item()
 
 
 def gaussian_kl(mu_1, sigma_1, mu_2, sigma_2):

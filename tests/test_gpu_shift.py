@@ -66,6 +66,8 @@ def test_kernel_shift_sequence(mods, g, name):
     policy.weighted_update(g["log_w"], g[f"{name}_xs"])
     assert nerr(policy.mean, g[f"{name}_mean_0"]) < TOL
     assert nerr(policy.covariance_in, g[f"{name}_cov_0"]) < 2 * TOL
+    # (the reference's trace over a (b, d, d) stack returns one value per actuator column, :729)
+    assert nerr(policy.loglikelihood(g[f"{name}_xs"]), g[f"{name}_llh"]) < 1e-4
     # the whole control sequence, errors of the fp32 update included
     for i, t, anneal in windows(g):
         policy.update_timesteps(t, anneal)
@@ -171,3 +173,47 @@ def test_features_anneal(mods, g):
     policy.update_timesteps(float(g["dt"]) * np.arange(1, g["t0"].shape[0] + 1), 0.6)
     assert nerr(policy.covariance_in, g["feat_cov_1"]) < 2 * TOL
     assert nerr(policy.covariance_in_sqrt, g["feat_chol_1"]) < 2 * TOL
+
+
+# ---------------------------------------------------------------------------------------------
+# module-level moment matchers called directly, iterated matrix-normal MLE
+# ---------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def gm():
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_golden_mavn.npz"))
+
+
+def test_m_projection_function(mods, gm):
+    pol, _ = mods
+    K = gm["xs"].shape[0]
+    mu, sigma, ess = pol.m_projection(gm["log_w"], gm["xs"].reshape(K, -1))
+    assert nerr(mu, gm["mp_mu"]) < TOL and nerr(sigma, gm["mp_sigma"]) < TOL
+    assert abs(ess - float(gm["mp_ess"])) < TOL * ess
+    assert np.array_equal(sigma, sigma.T)
+
+
+@pytest.mark.parametrize("iters,upd", [(1, False), (1, True), (3, True), (4, False)])
+def test_m_projection_mavn_iterated(mods, gm, iters, upd):
+    pol, _ = mods
+    mean, cin, cout, ess = pol.m_projection_mavn(gm["log_w"], gm["xs"], gm["cov_in0"], gm["cov_out0"],
+                                                 iterations=iters, update_out=upd)
+    tag = f"mavn_{iters}_{int(upd)}"
+    assert nerr(mean, gm[tag + "_mean"]) < TOL
+    assert nerr(cin, gm[tag + "_cin"]) < 2 * TOL
+    assert nerr(cout, gm[tag + "_cout"]) < 2 * TOL
+    assert abs(ess - float(gm[tag + "_ess"])) < TOL * ess
+
+
+def test_matrix_normal_helpers(mods, gm):
+    pol, _ = mods
+    kl = pol.matrix_gaussian_kl(gm["kl_m1"], gm["mavn_3_1_cin"], gm["mavn_3_1_cout"], gm["kl_m2"], gm["kl_c2"],
+                                gm["cov_out0"])
+    assert abs(kl - float(gm["kl"])) < 1e-9 * abs(float(gm["kl"]))
+    same = pol.matrix_gaussian_kl(gm["kl_m1"], gm["mavn_3_1_cin"], gm["mavn_3_1_cout"], gm["kl_m1"],
+                                  gm["mavn_3_1_cin"], gm["mavn_3_1_cout"])
+    assert abs(same) < 1e-9
+    assert np.array_equal(pol.vec(gm["kl_m1"]), gm["vec2"])
+    assert np.array_equal(pol.vec(gm["xs"][:3].astype(np.float64)), gm["vec3"])
+    z = np.random.default_rng(0).standard_normal((5, 9, 2))
+    k = np.array([0.3, 0.7])
+    assert nerr(pol.convolve(z, k), O.convolve(z, k)) < 1e-14
