@@ -73,6 +73,21 @@ int ppi_philox_normal(float* out, int64_t rows, int64_t cols, uint64_t seed, uin
                       uint64_t row_offset, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * f2  quasi-Monte-Carlo base normals                              ppi/samplers.py:25-44
+ * out (rows, cols) fp32 = sqrt(2) erfinv(2 shrinkage x - 1), x the points first_index ..
+ * first_index + rows - 1 of a scrambled Sobol sequence in `cols` dimensions, bit-identical to
+ * scipy.stats.qmc.Sobol(d, scramble=True).random(): sv (cols, bits) and shift (cols) are the
+ * engine's direction numbers and digital shift after scrambling (uint32, bits = 30 in SciPy),
+ * x_i = 2^-bits (shift ^ XOR_{b set in i ^ (i >> 1)} sv[:, b]).  Every row is a pure function of its
+ * index: K-sharded ranks pass their row offset in first_index.
+ * ---------------------------------------------------------------------------------------- */
+int ppi_sobol_normal(float* out, int64_t rows, int64_t cols, const uint32_t* sv, const uint32_t* shift,
+                     int bits, uint64_t first_index, double shrinkage, void* stream);
+
+/* f2  cubature sigma points sqrt(d) [I; -I], out (2 d, d) fp32       ppi/samplers.py:47-53 */
+int ppi_cubature_points(float* out, int d, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * a22 kernel Gram matrix + Cholesky, one thread block, fp64 inside   ppi/policies.py:923-932,
  * 935-974,1026-1037,1087-1091 (Gram) and :312,692-694 (np.linalg.cholesky).
  * kind: 0 squared-exponential, 1 Matern12, 2 Matern32, 3 Matern52, 4 periodic, 5 white noise.

@@ -519,6 +519,65 @@ sample_gaussian_small_kernel(const float* __restrict__ z, uint64_t seed, uint64_
 }
 
 // ------------------------------------------------------------------------------------------
+// Scrambled-Sobol base normals (QuasiMonteCarlo, ppi/samplers.py:25-44): out[r][c] =
+// sqrt(2) erfinv(2 shrinkage x_{first + r, c} - 1) with x_i = 2^-bits (shift ^ XOR_{b in gray(i)} sv[c][b]),
+// the closed form of the Gray-code recurrence of scipy.stats.qmc.Sobol (direction numbers with the
+// Owen-type scrambling already folded into sv / shift by the engine's constructor).  A block stages
+// the direction numbers of 128 columns in shared memory ([bit][column]: conflict-free); each thread
+// owns one column, builds its first point from the set bits of the Gray code and then walks down
+// its rows with one XOR per point (the bit that flips between i and i + 1 is the lowest zero bit of
+// i).  The inverse error function runs in fp64: 2 x - 1 needs all 30 bits near the tails.
+// ------------------------------------------------------------------------------------------
+constexpr int kSobolCols = 128;   // columns per block (= threads)
+constexpr int kSobolRows = 64;    // consecutive rows per thread
+
+__global__ void __launch_bounds__(kSobolCols)
+sobol_normal_kernel(float* __restrict__ out, int64_t rows, int64_t cols, const uint32_t* __restrict__ sv,
+                    const uint32_t* __restrict__ shift, int bits, uint64_t first, double shrink_scale) {
+  __shared__ uint32_t s_sv[32 * kSobolCols];
+  const int64_t c0 = (int64_t)blockIdx.x * kSobolCols;
+  const int nc = (int)min((int64_t)kSobolCols, cols - c0);
+  for (int e = threadIdx.x; e < nc * bits; e += blockDim.x) {
+    const int c = e / bits, b = e - c * bits;
+    s_sv[b * kSobolCols + c] = sv[(c0 + c) * bits + b];
+  }
+  __syncthreads();
+  if ((int)threadIdx.x >= nc) return;
+  const int64_t c = c0 + threadIdx.x;
+  const uint32_t sh = shift[c];
+  for (int64_t r0 = (int64_t)blockIdx.y * kSobolRows; r0 < rows; r0 += (int64_t)gridDim.y * kSobolRows) {
+    uint64_t i = first + (uint64_t)r0;
+    uint64_t gray = i ^ (i >> 1);
+    uint32_t q = sh;
+    while (gray) {
+      const int b = __ffsll((long long)gray) - 1;
+      gray &= gray - 1;
+      q ^= s_sv[b * kSobolCols + threadIdx.x];
+    }
+    const int nr = (int)min((int64_t)kSobolRows, rows - r0);
+    float* o = out + r0 * cols + c;
+    for (int r = 0; r < nr; ++r) {
+      const double u = (double)q * shrink_scale;                      // shrinkage * x
+      o[(int64_t)r * cols] = (float)(1.4142135623730951 * erfinv(2.0 * u - 1.0));
+      const int b = __ffsll((long long)~i) - 1;                       // lowest zero bit of i
+      q ^= s_sv[min(b, 31) * kSobolCols + threadIdx.x];
+      ++i;
+    }
+  }
+}
+
+// Cubature sigma points sqrt(d) [I; -I]  (CubatureQuadrature, ppi/samplers.py:47-53), (2 d, d).
+__global__ void __launch_bounds__(256)
+cubature_points_kernel(float* __restrict__ out, int d) {
+  const float s = sqrtf((float)d);
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < 2 * (int64_t)d * d;
+       e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = e / d, c = e - r * d;
+    out[e] = (r == c) ? s : (r - d == c ? -s : 0.f);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // Kernel Gram matrix + Cholesky, fp64, one block.
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ double gram_entry(int kind, double a, double b, double sigma, double ls,
@@ -774,6 +833,32 @@ extern "C" int ppi_kernel_gram_chol(const double* t1, int n1, const double* t2, 
                                                            period, gram64, gram32, chol64, chol32,
                                                            status);
   return check_launch("gram_chol_kernel");
+}
+
+extern "C" int ppi_sobol_normal(float* out, int64_t rows, int64_t cols, const uint32_t* sv,
+                                const uint32_t* shift, int bits, uint64_t first_index, double shrinkage,
+                                void* stream) {
+  PPI_REQUIRE(out && sv && shift && rows >= 0 && cols > 0, PPI_ERR_INVALID, "ppi_sobol_normal: bad arguments");
+  PPI_REQUIRE(bits > 0 && bits <= 32, PPI_ERR_INVALID, "ppi_sobol_normal: bits must lie in [1, 32] (got %d)", bits);
+  PPI_REQUIRE(first_index + (uint64_t)rows <= (1ull << bits), PPI_ERR_INVALID,
+              "ppi_sobol_normal: the sequence holds 2^%d points", bits);
+  if (rows == 0) return 0;
+  const int64_t gx = ceil_div(cols, kSobolCols);
+  int64_t gy = ceil_div(rows, kSobolRows);
+  const int64_t cap = ceil_div((int64_t)kNumSMs * 16, gx);
+  if (gy > cap) gy = cap;
+  if (gy > 65535) gy = 65535;
+  dim3 grid((unsigned)gx, (unsigned)gy);
+  sobol_normal_kernel<<<grid, kSobolCols, 0, (cudaStream_t)stream>>>(out, rows, cols, sv, shift, bits, first_index,
+                                                                     shrinkage * ldexp(1.0, -bits));
+  return check_launch("sobol_normal_kernel");
+}
+
+extern "C" int ppi_cubature_points(float* out, int d, void* stream) {
+  PPI_REQUIRE(out && d > 0, PPI_ERR_INVALID, "ppi_cubature_points: bad arguments");
+  const int grid = (int)min((int64_t)kNumSMs * 4, ceil_div(2 * (int64_t)d * d, 256));
+  cubature_points_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(out, d);
+  return check_launch("cubature_points_kernel");
 }
 
 extern "C" size_t ppi_kernel_shift_workspace_bytes(int n_old, int n_new) {

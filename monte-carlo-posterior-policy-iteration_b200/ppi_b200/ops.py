@@ -62,6 +62,24 @@ def gram(kind, t1, t2, sigma, ls=1.0, period=1.0, chol=False):
     return g, l, int(status.item())
 
 
+def sobol_normal(rows, cols, sv, shift, bits, first_index, shrinkage=0.9999):
+    """Scrambled-Sobol base normals on the device (ppi/samplers.py:31-37); sv (cols, bits) / shift (cols)
+    are uint32 device tensors holding the state of a scipy.stats.qmc.Sobol engine."""
+    dev = require_cuda()
+    out = torch.empty((rows, cols), dtype=torch.float32, device=dev)
+    _lib.call("ppi_sobol_normal", ptr(out), rows, cols, ptr(sv), ptr(shift), int(bits), _u64(first_index),
+              float(shrinkage), stream_ptr())
+    return out
+
+
+def cubature_points(d):
+    """sqrt(d) [I; -I] as a (2 d, d) device tensor (ppi/samplers.py:47-53)."""
+    dev = require_cuda()
+    out = torch.empty((2 * d, d), dtype=torch.float32, device=dev)
+    _lib.call("ppi_cubature_points", ptr(out), int(d), stream_ptr())
+    return out
+
+
 _shift_staging = {}
 
 

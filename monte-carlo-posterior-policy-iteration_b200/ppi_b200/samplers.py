@@ -4,8 +4,9 @@
 On top of the protocol, native samplers expose `device_normals(n, d, row_offset)` which the
 ppi_b200 policies use to keep the draw on the GPU: MonteCarlo returns Philox parameters (the
 normals are generated inside the sampling kernel), InjectedNormals returns a device tensor.
-QuasiMonteCarlo / CubatureQuadrature are "next" rows; the reference's
-classes can be passed to the policies unchanged and are consumed through the protocol.
+QuasiMonteCarlo generates its scrambled-Sobol points and the erfinv transform on the device from the
+state of a SciPy engine, CubatureQuadrature its sigma points; the reference's own
+sampler classes can still be passed to the policies unchanged and are consumed through the protocol.
 """
 from __future__ import annotations
 
@@ -80,30 +81,45 @@ class InjectedNormals(BaseSampler):
 
 
 class QuasiMonteCarlo(BaseSampler):
-    """Scrambled-Sobol + erfinv base normals (ppi/samplers.py:25-44).  "Next" row:
-    the low-discrepancy points still come from SciPy on the host and are uploaded as injected
-    normals; the transform / sampling kernels run on the device."""
+    """Scrambled-Sobol + erfinv base normals (ppi/samplers.py:25-44), generated on the device.
+    SciPy's engine is only constructed (Joe-Kuo direction numbers + the random linear scramble and
+    digital shift, a (d, 30) uint32 table); the points themselves -- bit-identical to
+    `engine.random()` -- and the inverse-normal transform come from `ppi_sobol_normal`, every row a pure
+    function of its index, so K-sharded ranks draw their own rows.  Like the reference, each call
+    consumes the next power of two >= n_samples points of the sequence."""
 
-    def __init__(self, dimension):
+    def __init__(self, dimension, seed=None):
         from scipy.stats import qmc
 
         self.d = dimension
-        self.sampler = qmc.Sobol(d=dimension, scramble=True)
+        self.sampler = qmc.Sobol(d=dimension, scramble=True, seed=seed)
+        self.bits = int(self.sampler._sv.shape[1])
+        self._state = None
+        self.generated = 0
 
-    def _base(self, n_samples, shrinkage=0.9999):
-        from scipy.special import erfinv
+    def _device_state(self):
+        if self._state is None:
+            dev = require_cuda()
+            sv = np.ascontiguousarray(self.sampler._sv, dtype=np.uint32).view(np.int32)
+            sh = np.ascontiguousarray(self.sampler._shift, dtype=np.uint32).view(np.int32)
+            self._state = (torch.from_numpy(sv.copy()).to(dev), torch.from_numpy(sh.copy()).to(dev))
+        return self._state
 
-        with np.errstate(invalid="ignore"):
-            n_b2 = 2 ** int(np.ceil(np.log(n_samples) / np.log(2)))
-            sobol = shrinkage * self.sampler.random(n_b2)[:n_samples]
-            return np.sqrt(2) * erfinv(2 * sobol - 1)
+    def _base(self, n_samples, shrinkage=0.9999, row_offset=0, n_local=None):
+        """Rows [row_offset, row_offset + n_local) of this call's (n_samples, d) base-normal matrix."""
+        sv, sh = self._device_state()
+        n_b2 = 2 ** int(np.ceil(np.log(n_samples) / np.log(2)))
+        first = self.generated
+        self.generated += n_b2
+        n_local = n_samples if n_local is None else n_local
+        return ops.sobol_normal(n_local, self.d, sv, sh, self.bits, first + row_offset, shrinkage)
 
     def device_normals(self, n_samples, d):
         assert d == self.d
-        return f32(self._base(n_samples)), 0, 0
+        return self._base(n_samples), 0, 0
 
     def __call__(self, mu, sigma, n_samples, shrinkage=0.9999, standard_gaussian=False):
-        base = self._base(n_samples, shrinkage)
+        base = self._base(n_samples, shrinkage).cpu().numpy().astype(np.float64)
         if standard_gaussian:
             return base
         return mu[None, :] + base @ np.linalg.cholesky(sigma).T
@@ -118,10 +134,16 @@ class CubatureQuadrature(BaseSampler):
 
     def __init__(self, dimension):
         self.d = dimension
-        self.base_points = np.sqrt(self.d) * np.concatenate((np.eye(dimension), -np.eye(dimension)))
+        self._points = None
+
+    @property
+    def base_points(self):
+        return np.sqrt(self.d) * np.concatenate((np.eye(self.d), -np.eye(self.d)))
 
     def device_normals(self, n_samples, d):
-        return f32(self.base_points), 0, 0
+        if self._points is None:
+            self._points = ops.cubature_points(self.d)
+        return self._points, 0, 0
 
     def __call__(self, mu, sigma, n_samples, standard_gaussian=False):
         if standard_gaussian:

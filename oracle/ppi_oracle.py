@@ -604,3 +604,29 @@ def kernel_predict(mean_fn, mean, cov_in, cov_out):
     diagonal of kron(cov_out, cov_in) in the reference's (row-major reshape) element order."""
     mu = mean_fn[None, :] + mean
     return mu, np.sqrt(np.diag(np.kron(cov_out, cov_in)).reshape(mu.shape))
+
+
+# ---------------------------------------------------------------------------------------------
+# SURVEY 8(f) row 2: quasi-Monte-Carlo base normals (ppi/samplers.py:25-44)
+# ---------------------------------------------------------------------------------------------
+def sobol_points(sv, shift, first, n):
+    """Points first .. first + n - 1 of the scrambled Sobol sequence whose engine state is (sv (d, bits),
+    shift (d)) -- scipy.stats.qmc.Sobol after construction -- in closed form: the Gray-code recurrence
+    of the engine (quasi ^= sv[:, lowest zero bit of the running index]) unrolled to
+    x_i = 2^-bits (shift ^ XOR_{b set in i ^ (i >> 1)} sv[:, b])."""
+    sv, shift = np.asarray(sv, np.uint64), np.asarray(shift, np.uint64)
+    bits = sv.shape[1]
+    i = np.arange(first, first + n, dtype=np.uint64)
+    gray = i ^ (i >> np.uint64(1))
+    q = np.tile(shift[None, :], (n, 1))
+    for b in range(bits):
+        on = ((gray >> np.uint64(b)) & np.uint64(1)).astype(bool)
+        q[on] ^= sv[:, b][None, :]
+    return q.astype(np.float64) * 2.0 ** -bits
+
+
+def qmc_base_normals(points, shrinkage=0.9999):
+    """QuasiMonteCarlo.__call__(standard_gaussian=True), ppi/samplers.py:33-37."""
+    from scipy.special import erfinv
+
+    return np.sqrt(2) * erfinv(2 * shrinkage * points - 1)
