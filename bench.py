@@ -226,6 +226,8 @@ def build_workload(wl, world, pinned=None):
         mu = pinned["mu"] if pinned else np.ones(D)
         sigma = pinned["sigma"] if pinned else 0.5 * np.eye(D)
         policy = pol.GaussianPolicy(mu, sigma, smp.MonteCarlo(D, seed=1234))
+        if wl.get("prefetch") is not None:
+            policy.prefetch_normals = None if wl["prefetch"] == "none" else wl["prefetch"]
         solver = alg.Essps(n_elites=max(1, K_total // 64))
         cost = getattr(fn, wl["fn"])(D)
     elif wl["kind"] == "kernel":
@@ -501,8 +503,12 @@ def main():
     ap.add_argument("--pair", type=int, default=None, choices=[0, 1], help="override PPI_OPT_GEMM_PAIR")
     ap.add_argument("--overlap", type=int, default=None, choices=[0, 1],
                     help="override PPI_OPT_GEMM_OVERLAP (operand staging on a side stream)")
+    ap.add_argument("--prefetch", default=None, choices=["none", "sample", "update"],
+                    help="override GaussianPolicy.prefetch_normals (base normals of the next draw generated "
+                         "ahead on a side stream)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
+    wl["prefetch"] = args.prefetch
     if args.samples:
         wl["K"] = args.samples
         wl["desc"] += f" [K overridden to {args.samples}]"

@@ -173,6 +173,19 @@ int ppi_sample_gaussian_keep(const float* z, uint64_t seed, uint64_t draw_id, ui
                              void* zstore, size_t zstore_bytes, void* workspace,
                              size_t workspace_bytes, void* stream);
 
+/* Base normals of a Philox draw generated ahead of the sampling call (they depend on (seed, draw_id,
+ * global row) only): zrows = sample-major exact-fp16 operand rows, round_up(K, 256) x round_up(D, 64),
+ * zstore = the K-major store of ppi_sample_gaussian_keep; both 1 KB aligned, sizes from
+ * ppi_philox_rows_bytes / ppi_zstore_bytes(K, D, 0).  Issued on a side stream this hides the generator
+ * (ppi/samplers.py:18-20, np.random.randn) under the HBM- and latency-bound part of the previous update.
+ * ppi_sample_gaussian_pre is ppi_sample_gaussian_keep for such a draw: only the GEMM passes run. */
+size_t ppi_philox_rows_bytes(int64_t K, int64_t D);
+int ppi_philox_prefetch(uint64_t seed, uint64_t draw_id, uint64_t row_offset, int64_t K, int64_t D,
+                        void* zrows, size_t zrows_bytes, void* zstore, size_t zstore_bytes, void* stream);
+int ppi_sample_gaussian_pre(int64_t K, int64_t D, const float* mu, const float* L, float* x,
+                            const void* zrows, void* zstore, void* workspace, size_t workspace_bytes,
+                            void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * a9  cost evaluation                                     optimization/functions.py:21-104
  * fn: 0 Himmelblau, 1 Rosenbrock, 2 Styblinski, 3 Rastrigin, 4 NoisySphere (aux = A (D,D),

@@ -1937,7 +1937,10 @@ extern "C" size_t ppi_sample_gaussian_workspace_bytes(int64_t K, int64_t D) {
 template <bool FP16, bool ZPAIR>
 static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
                                 int64_t K, int64_t D, const float* mu, const float* L, float* x,
-                                void* workspace, void* zstore, cudaStream_t st) {
+                                void* workspace, void* zstore, cudaStream_t st,
+                                const void* zrows_pre = nullptr) {
+  // zrows_pre: the draw's sample-major fp16 operand rows AND its K-major store were generated ahead of
+  // time (ppi_philox_prefetch): no staging passes, the GEMMs read the rows in place
   constexpr int LMODE = FP16 ? OP_F16_PAIR : OP_TF32X3;
   constexpr int ZMODE = FP16 ? (ZPAIR ? OP_F16_PAIR : OP_F16_SINGLE) : OP_TF32X3;
   constexpr int KS = (FP16 && !ZPAIR) ? 64 : 32;
@@ -1972,7 +1975,7 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
   char* store_rows = zstore ? (char*)zstore + kScalarBytes : nullptr;
   const size_t store_row_bytes = zstore_row_bytes(D);
   const bool store_pairs = zstore && ZPAIR;
-  const bool overlap = FP16 && gemm_overlap() && K > Kc && !store_pairs;
+  const bool overlap = FP16 && gemm_overlap() && K > Kc && !store_pairs && !zrows_pre;
   void* zbufs[2] = {z_a, FP16 ? z_b : z_a};
   CUtensorMap ml, ml2, mz[2], mz2[2];
   if (int rc = make_map(&ml, l_a, D, Dk, BM, LMODE)) return rc;
@@ -2021,9 +2024,14 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
       if (int rc = make_map(&mz[0], zbufs[0], rows_p, Dk, BN, ZMODE)) return rc;
       mz2[0] = mz[0];
     }
+    if (zrows_pre) {
+      zbufs[0] = (char*)zrows_pre + (size_t)k0 * Dk * sizeof(uint16_t);
+      if (int rc = make_map(&mz[0], zbufs[0], rows_p, Dk, BN, ZMODE)) return rc;
+      mz2[0] = mz[0];
+    }
     // injected: rows beyond `rows` keep stale workspace values whose products are never stored;
     // Philox: they are generated too (harmless)
-    {
+    if (!zrows_pre) {
       if (overlap && pass >= 2) PPI_CUDA_TRY(cudaStreamWaitEvent(st_op, ss->gemm_done[bi], 0));
       ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st_op);
       const int64_t nrows = z ? rows : rows_p;
@@ -2107,6 +2115,54 @@ extern "C" size_t ppi_zstore_bytes(int64_t K, int64_t D, int injected) {
   if (K <= 0 || D <= 128) return 0;
   if (injected) return kScalarBytes + (size_t)round_up(K, BN) * zstore_row_bytes(D) + 1024;
   return kScalarBytes + (size_t)round_up(D, BM) * zstore_kt(K) * 2 + 1024;
+}
+
+// Base normals of a whole Philox draw generated ahead of the sampling call (they depend on (seed, draw,
+// row) only, not on the policy): sample-major exact-fp16 operand rows for the sampling GEMMs + the K-major
+// store of the whitened moment match, one launch.  Issued on a side stream it runs under the HBM- and
+// latency-bound part of the previous update (cost, temperature solve, dense fp64 tail).
+extern "C" size_t ppi_philox_rows_bytes(int64_t K, int64_t D) {
+  if (K <= 0 || D <= 128) return 0;
+  return (size_t)round_up(K, BN) * round_up(D, 64) * sizeof(uint16_t) + 1024;
+}
+
+extern "C" int ppi_philox_prefetch(uint64_t seed, uint64_t draw_id, uint64_t row_offset, int64_t K,
+                                   int64_t D, void* zrows, size_t zrows_bytes, void* zstore,
+                                   size_t zstore_bytes, void* stream) {
+  PPI_REQUIRE(K > 0 && D > 128 && zrows && zstore, PPI_ERR_INVALID, "ppi_philox_prefetch: bad arguments");
+  PPI_REQUIRE(((uintptr_t)zrows & 1023) == 0 && zrows_bytes >= ppi_philox_rows_bytes(K, D), PPI_ERR_WORKSPACE,
+              "ppi_philox_prefetch: row buffer misaligned (1 KB) or too small");
+  PPI_REQUIRE(((uintptr_t)zstore & 1023) == 0 && zstore_bytes >= ppi_zstore_bytes(K, D, 0), PPI_ERR_WORKSPACE,
+              "ppi_philox_prefetch: store misaligned (1 KB) or too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t Dk = round_up(D, 64), zt_rows = round_up(D, BM), nrows = round_up(K, BN);
+  uint16_t* store_rows = (uint16_t*)((char*)zstore + kScalarBytes);
+  ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st);
+  philox_dual_kernel<<<grid_cap((nrows / 64) * ceil_div(zt_rows, 128), 6), 256, 0, st>>>(
+      nrows, D, Dk, seed, draw_id, row_offset, (uint16_t*)zrows, store_rows, zt_rows, 0);
+  if (int rc = check_launch("philox_dual_kernel")) return rc;
+  const int64_t rem = nrows % kZBlock;
+  if (rem)  // zero the unwritten tail of the last sample block (finite operands)
+    PPI_CUDA_TRY(cudaMemset2DAsync(store_rows + zt_index(nrows, 0, zt_rows), kZBlock * 2, 0, (kZBlock - rem) * 2,
+                                   zt_rows, st));
+  return 0;
+}
+
+// ppi_sample_gaussian_keep for a draw whose base normals were prefetched: zrows / zstore as written by
+// ppi_philox_prefetch for the same (K, D); only the GEMM passes run.
+extern "C" int ppi_sample_gaussian_pre(int64_t K, int64_t D, const float* mu, const float* L, float* x,
+                                       const void* zrows, void* zstore, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+  PPI_REQUIRE(mu && L && x && K > 0 && D > 128 && zrows && zstore, PPI_ERR_INVALID,
+              "ppi_sample_gaussian_pre: bad arguments (needs K > 0, D > 128, prefetched rows and store)");
+  PPI_REQUIRE(gemm_scheme() == PPI_GEMM_FP16X2, PPI_ERR_UNSUPPORTED,
+              "ppi_sample_gaussian_pre: the base-normal store exists under PPI_GEMM_FP16X2 only");
+  PPI_REQUIRE(((uintptr_t)zrows & 1023) == 0 && ((uintptr_t)zstore & 1023) == 0, PPI_ERR_WORKSPACE,
+              "ppi_sample_gaussian_pre: rows / store misaligned (1 KB)");
+  PPI_REQUIRE(workspace && workspace_bytes >= ppi_sample_gaussian_workspace_bytes(K, D),
+              PPI_ERR_WORKSPACE, "ppi_sample_gaussian_pre: workspace too small");
+  return sample_gaussian_impl<true, false>(nullptr, 0, 0, 0, K, D, mu, L, x, workspace, zstore,
+                                           (cudaStream_t)stream, zrows);
 }
 
 extern "C" int ppi_sample_gaussian_keep(const float* z, uint64_t seed, uint64_t draw_id,

@@ -216,6 +216,7 @@ class BaseNormals:
 
     def __init__(self, store, rows, dim, injected):
         self.store, self.rows, self.dim, self.injected = store, rows, dim, bool(injected)
+        self.valid = True   # cleared when a later prefetch recycles the store
 
 
 def sample_gaussian_keep(K, mu, L, z=None, seed=0, draw_id=0, row_offset=0):
@@ -235,6 +236,50 @@ def sample_gaussian_keep(K, mu, L, z=None, seed=0, draw_id=0, row_offset=0):
     _lib.call("ppi_sample_gaussian_keep", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, D,
               ptr(mu), kp.p(L), ptr(x), ptr(store), sbytes, ptr(ws), nbytes, stream_ptr())
     return x, BaseNormals(store, K, D, zt is not None)
+
+
+def _aligned_bytes(nbytes, dev):
+    raw = torch.empty(nbytes + 1024, dtype=torch.uint8, device=dev)
+    off = (-raw.data_ptr()) % 1024
+    return raw[off:off + nbytes]
+
+
+class PrefetchedNormals:
+    """Base normals of one Philox draw generated ahead of the sampling call (ppi_philox_prefetch) on a
+    side stream: operand rows for the sampling GEMMs + the K-major store, and the event that marks them
+    complete.  `key` identifies the draw; `base` is the BaseNormals the consuming call hands out."""
+
+    def __init__(self, key, rows, store, done):
+        self.key, self.rows, self.store, self.done = key, rows, store, done
+
+
+def philox_prefetch(K, D, seed, draw_id, row_offset, rows, store, side, key):
+    """Enqueue the generation of draw (seed, draw_id) rows [row_offset, row_offset + K) on `side` after
+    everything already enqueued on the current stream.  rows / store: persistent 1 KB-aligned buffers."""
+    main = torch.cuda.current_stream()
+    fork = torch.cuda.Event()
+    fork.record(main)
+    side.wait_event(fork)
+    _lib.call("ppi_philox_prefetch", _u64(seed), _u64(draw_id), _u64(row_offset), K, D, ptr(rows), rows.numel(),
+              ptr(store), store.numel(), C.c_void_p(side.cuda_stream))
+    done = torch.cuda.Event()
+    done.record(side)
+    return PrefetchedNormals(key, rows, store, done)
+
+
+def sample_gaussian_pre(K, mu, L, pre):
+    """sample_gaussian_keep for a prefetched draw: only the GEMM passes run.  -> (x, BaseNormals)."""
+    dev = require_cuda()
+    kp = _Keep(dev)
+    mu = f32(mu, dev)
+    D = mu.numel()
+    x = torch.empty((K, D), dtype=torch.float32, device=dev)
+    nbytes = _lib.query("ppi_sample_gaussian_workspace_bytes", K, D)
+    ws = workspace("sample_gaussian", nbytes)
+    torch.cuda.current_stream().wait_event(pre.done)
+    _lib.call("ppi_sample_gaussian_pre", K, D, ptr(mu), kp.p(L), ptr(x), ptr(pre.rows), ptr(pre.store), ptr(ws),
+              nbytes, stream_ptr())
+    return x, BaseNormals(pre.store, K, D, False)
 
 
 def wmoments_white(base, nw, s1=None, cov=None, accumulate=False):

@@ -405,15 +405,59 @@ class GaussianPolicy(object):
         z, seed, draw, begin, n_local, n_total = _draw(self.sampler, n_samples, d)
         if d > self.small_dim and not self.diagonal and _lib.load().ppi_get_option(_lib.OPT_GEMM_SCHEME) == _lib.GEMM_FP16X2:
             # keep the base normals in HBM: weighted_update on this very handle contracts z, not x
-            x, base = ops.sample_gaussian_keep(n_local, self._mu_d(), self._factor(), z=z, seed=seed,
-                                               draw_id=draw, row_offset=begin)
+            pre, self._pre = self._pre, None
+            if z is None and pre is not None and pre.key == (id(self.sampler), seed, draw, begin, n_local, d):
+                x, base = ops.sample_gaussian_pre(n_local, self._mu_d(), self._factor(), pre)
+                self._pre_owner[pre.slot] = base
+            else:
+                x, base = ops.sample_gaussian_keep(n_local, self._mu_d(), self._factor(), z=z, seed=seed,
+                                                   draw_id=draw, row_offset=begin)
             handle = DeviceArray(x, begin, n_total)
             handle.white = (self, self._version, base)
+            if z is None and self.prefetch_normals == "sample":
+                self._prefetch_next(n_samples)
             return handle, handle
         x = ops.sample_gaussian(n_local, self._mu_d(), self._factor(), z=z, seed=seed, draw_id=draw,
                                 row_offset=begin)
         handle = DeviceArray(x, begin, n_total)
         return handle, handle
+
+    # Base normals of the NEXT draw generated ahead of time (they depend on the sampler's (seed, draw
+    # counter, row) only, not on the policy): "sample" = right behind the sampling GEMMs, on a side stream,
+    # under the cost / temperature / moment kernels of this update; "update" = behind the covariance
+    # kernel, under the dense fp64 tail; None = off.  Only for draws of at least prefetch_min_elements.
+    # Off by default: measured at C5 it buys 0.3 ms of 22.9 ("sample") or nothing ("update") -- the
+    # generator fills every SM, so the cooperative temperature solver and the cuSOLVER panels queue behind
+    # it, and under the 1 kW cap concurrent kernels share one power budget.
+    prefetch_normals = None
+    prefetch_min_elements = 1 << 26
+    _pre = None
+
+    def _prefetch_next(self, n_samples):
+        sampler = self.sampler
+        d = self._dim
+        begin, end = shard_rows(n_samples)
+        n_local = end - begin
+        if (not isinstance(sampler, samplers.MonteCarlo) or n_local * d < self.prefetch_min_elements
+                or d <= self.small_dim):
+            return
+        dev = require_cuda()
+        st = self.__dict__.setdefault("_pre_state", {})
+        if st.get("shape") != (n_local, d):
+            rows = ops._aligned_bytes(_lib.query("ppi_philox_rows_bytes", n_local, d), dev)
+            sbytes = _lib.query("ppi_zstore_bytes", n_local, d, 0)
+            st.update(shape=(n_local, d), rows=rows, stores=[ops._aligned_bytes(sbytes, dev) for _ in range(2)],
+                      side=torch.cuda.Stream(), slot=0)
+            self._pre_owner = [None, None]
+        slot = st["slot"] = 1 - st["slot"]
+        owner = self._pre_owner[slot]
+        if owner is not None:
+            owner.valid = False     # a handle that still holds this store falls back to the x-space update
+            self._pre_owner[slot] = None
+        key = (id(sampler), sampler.seed, sampler.draw_id, begin, n_local, d)
+        self._pre = ops.philox_prefetch(n_local, d, sampler.seed, sampler.draw_id, begin, st["rows"],
+                                        st["stores"][slot], st["side"], key)
+        self._pre.slot = slot
 
     def weighted_update(self, log_weights, samples, update_covariance_in=True):
         w = _weights(log_weights)
@@ -422,8 +466,8 @@ class GaussianPolicy(object):
         d = x.shape[1]
         white = getattr(samples, "white", None)
         if (white is not None and white[0] is self and white[1] == self._version and update_covariance_in
-                and not self.diagonal):
-            return self._weighted_update_white(w, white[2], nw)
+                and not self.diagonal and white[2].valid):
+            return self._weighted_update_white(w, white[2], nw, n_total)
         if d > self.small_dim:
             return self._weighted_update_large(w, x, nw, replicated, update_covariance_in)
         mu_old, sigma_old = self.mu.copy(), self.sigma.copy()
@@ -472,7 +516,7 @@ class GaussianPolicy(object):
         self._version += 1
         return ess, float(multivariate_gaussian_kl(self.mu, self.sigma, mu_old, sigma_old))
 
-    def _weighted_update_white(self, w, base, nw):
+    def _weighted_update_white(self, w, base, nw, n_total=None):
         """M-projection in whitened coordinates for samples this policy drew itself (x = mu + L z with
         the base normals still in HBM, ppi_sample_gaussian_keep).  With m = sum nw z and
         C = sum nw z z^T - m m^T:  mu' = mu + L m  (ppi/policies.py:88),  sigma' = L C L^T (:89-92), so
@@ -483,6 +527,8 @@ class GaussianPolicy(object):
         self._factor()
         l_old, mu_old_dev, old_logdet = self._chol64_dev, self._mu_d(), self._logdet
         m, s = ops.wmoments_white(base, nw)
+        if self.prefetch_normals == "update" and n_total is not None and not base.injected:
+            self._prefetch_next(n_total)
         all_reduce_sum(m)
         all_reduce_sum(s)
         c = s.double()

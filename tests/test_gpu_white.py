@@ -158,3 +158,66 @@ def test_white_handle_goes_stale(ops):
     policy.weighted_update(lw, samples2)
     mu2, sigma2, _ = O.m_projection(lw, np.asarray(samples2), naive=False)
     assert nerr(policy.sigma, sigma2) < TOL and nerr(first, sigma2) < 2 * TOL
+
+
+@pytest.mark.parametrize("trigger", ["sample", "update"])
+def test_prefetched_normals_are_the_same_draws(ops, trigger):
+    """Base normals generated ahead of the sampling call on a side stream (ppi_philox_prefetch +
+    ppi_sample_gaussian_pre): the same Philox matrix, hence bit-identical samples and updates."""
+    from ppi_b200 import policies as pol, samplers as smp
+
+    K, D = 3000, 384          # ragged: K is not a multiple of the 256-row GEMM block
+    rng = np.random.default_rng(8)
+    lws = [f32r(-3.0 * rng.random(K)) for _ in range(4)]
+
+    def run(prefetch):
+        policy = pol.GaussianPolicy(0.3 * np.ones(D), 0.5 * np.eye(D) + 0.01, smp.MonteCarlo(D, seed=11))
+        policy.prefetch_normals = prefetch
+        policy.prefetch_min_elements = 0
+        xs, used = [], []
+        for lw in lws:
+            used.append(policy._pre is not None)      # a prefetched draw is waiting for this call
+            samples, _ = policy(K)
+            xs.append(np.asarray(samples).copy())
+            policy.weighted_update(lw, samples)
+        return xs, policy.mu.copy(), policy.sigma.copy(), used
+
+    xs0, mu0, sig0, _ = run(None)
+    xs1, mu1, sig1, used = run(trigger)
+    assert any(used)
+    for a, b in zip(xs0, xs1):
+        assert np.array_equal(a, b)
+    assert np.array_equal(mu0, mu1) and np.array_equal(sig0, sig1)
+
+
+def test_prefetch_recycles_a_store_only_after_invalidating_its_handle(ops):
+    """Two draws without an update in between: the older handle's base-normal store is recycled by the
+    next prefetch, so its update must take the x-space path -- and still be right."""
+    from ppi_b200 import policies as pol, samplers as smp
+
+    K, D = 2048, 256
+    rng = np.random.default_rng(9)
+    policy = pol.GaussianPolicy(np.zeros(D), np.eye(D), smp.MonteCarlo(D, seed=5))
+    policy.prefetch_normals = "sample"
+    policy.prefetch_min_elements = 0
+    handles = [policy(K)[0] for _ in range(4)]          # draws 1.. come from prefetched stores
+    assert not handles[1].white[2].valid and handles[3].white[2].valid
+    lw = f32r(-4.0 * rng.random(K))
+    x1 = np.asarray(handles[1]).copy()
+    policy.weighted_update(lw, handles[1])
+    mu, sigma, _ = O.m_projection(lw, x1, naive=False)
+    assert nerr(policy.mu, mu) < TOL and nerr(policy.sigma, sigma) < TOL
+
+
+def test_prefetch_c_abi_errors(ops):
+    import torch
+    from ppi_b200 import _lib
+
+    buf = torch.zeros(1 << 20, dtype=torch.uint8, device="cuda")
+    p = buf.data_ptr() + (-buf.data_ptr()) % 1024
+    with pytest.raises(_lib.PpiError):     # buffers far too small for K x D
+        _lib.call("ppi_philox_prefetch", 1, 0, 0, 65536, 2048, p, 1 << 19, p, 1 << 19, None)
+    with pytest.raises(_lib.PpiError):     # misaligned rows
+        _lib.call("ppi_philox_prefetch", 1, 0, 0, 256, 256, p + 8, 1 << 19, p, 1 << 19, None)
+    with pytest.raises(_lib.PpiError):     # D <= 128 has no tensor-core path
+        _lib.call("ppi_philox_prefetch", 1, 0, 0, 256, 64, p, 1 << 19, p, 1 << 19, None)
