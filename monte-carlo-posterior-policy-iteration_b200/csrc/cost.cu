@@ -114,10 +114,42 @@ cost_tracking_kernel(const float* __restrict__ x, int64_t K, int T, int dy,
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   const int n = T * dt;
   const float inv = 1.f / (float)n;
+  // 16-byte loads need aligned bases and sample rows that are a whole number of 16-byte words
+  const bool vec_ok = (((uintptr_t)x | (uintptr_t)target) & 15) == 0 && (((int64_t)T * dy) & 3) == 0;
   for (int64_t b = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < K; b += nwarps) {
     const float* xb = x + b * (int64_t)T * dy;
     float acc = 0.f;
-    if (dt == dy) {
+    if (dy == 4 && dt == 2 && vec_ok) {
+      // value + derivative rows (feature policies with use_derivatives): one 16-byte load per time step,
+      // the two value channels enter the cost; four time steps in flight per lane
+      const float4* x4 = reinterpret_cast<const float4*>(xb);
+      const float2* t2 = reinterpret_cast<const float2*>(target);
+      float a0 = 0.f, a1 = 0.f;
+      int t = lane;
+      for (; t + 96 < T; t += 128) {
+        float4 v[4];
+        float2 g[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          v[u] = __ldg(x4 + t + 32 * u);
+          g[u] = __ldg(t2 + t + 32 * u);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const float d0 = v[u].x - g[u].x, d1 = v[u].y - g[u].y;
+          a0 = fmaf(d0, d0, a0);
+          a1 = fmaf(d1, d1, a1);
+        }
+      }
+      for (; t < T; t += 32) {
+        const float4 v = __ldg(x4 + t);
+        const float2 g = __ldg(t2 + t);
+        const float d0 = v.x - g.x, d1 = v.y - g.y;
+        a0 = fmaf(d0, d0, a0);
+        a1 = fmaf(d1, d1, a1);
+      }
+      acc = a0 + a1;
+    } else if (dt == dy) {
       for (int e = lane; e < n; e += 32) {
         const float df = __ldg(xb + e) - __ldg(target + e);
         acc = fmaf(df, df, acc);

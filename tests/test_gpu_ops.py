@@ -275,7 +275,7 @@ def test_cost_functions_oracle(ops, K, D):
 
 def test_cost_tracking(ops):
     rng = np.random.default_rng(3)
-    for K, T, dy, dt in [(50, 30, 28, 28), (20, 1000, 4, 2), (3, 7, 3, 1)]:
+    for K, T, dy, dt in [(50, 30, 28, 28), (20, 1000, 4, 2), (3, 7, 3, 1), (9, 131, 4, 2), (4, 9, 5, 5), (6, 33, 4, 4)]:
         t = np.linspace(0, 2, T)
         tgt = f32r(O.tracking_target(t, dt))
         x = f32r(rng.standard_normal((K, T, dy)))
