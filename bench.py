@@ -284,6 +284,8 @@ def run_b200(args, wl):
         _lib.call("ppi_set_option", _lib.OPT_GEMM_CHUNK, args.chunk)
     if args.pair is not None:
         _lib.call("ppi_set_option", _lib.OPT_GEMM_PAIR, args.pair)
+    if args.prefetch_blocks is not None:
+        _lib.call("ppi_set_option", _lib.OPT_PREFETCH_BLOCKS, args.prefetch_blocks)
 
     def barrier():
         if world > 1:
@@ -506,6 +508,7 @@ def main():
     ap.add_argument("--prefetch", default=None, choices=["none", "sample", "update"],
                     help="override GaussianPolicy.prefetch_normals (base normals of the next draw generated "
                          "ahead on a side stream)")
+    ap.add_argument("--prefetch-blocks", type=int, default=None, help="override PPI_OPT_PREFETCH_BLOCKS")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     wl["prefetch"] = args.prefetch

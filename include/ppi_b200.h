@@ -48,15 +48,18 @@ const char* ppi_last_error(void);
  *                    (error ~2^-21 |a||b| at any magnitude; 8 bytes per value, twice the MMA time).
  * PPI_OPT_GEMM_CHUNK = 32-deep k-blocks accumulated inside the tensor core before the partial sum is
  * promoted to fp32 registers (tcgen05 accumulation truncates: ~3e-8 relative per MMA instruction).
- * Even, default 4.
+ * Even, default 8.
  * PPI_OPT_GEMM_OVERLAP != 0: the FP16X2 kernels stage the operands of pass p+1 on an internal side
  * stream while pass p multiplies (two staging buffers, event-ordered against the caller's stream;
  * the call stays asynchronous and stream-ordered for the caller).  Default 0: measured gain on
  * B200 is ~1 % of a step because both kernels contend for L2 / HBM.
- * PPI_OPT_GEMM_PAIR != 0 (default): kernels that have a CTA-pair form (tcgen05 cta_group::2, clusters of
- * two CTAs sharing the B operand) use it; 0 selects the single-CTA kernels.  Results are identical up
- * to fp32 summation order. */
-enum { PPI_OPT_GEMM_SCHEME = 0, PPI_OPT_GEMM_CHUNK = 1, PPI_OPT_GEMM_OVERLAP = 2, PPI_OPT_GEMM_PAIR = 3 };
+ * PPI_OPT_GEMM_PAIR != 0: kernels that have a CTA-pair form (tcgen05 cta_group::2, clusters of
+ * two CTAs sharing the B operand) use it; 0 (default: measured faster) selects the single-CTA kernels.
+ * Results are identical up to fp32 summation order.
+ * PPI_OPT_PREFETCH_BLOCKS = resident CTAs per SM of ppi_philox_prefetch, 1..6 (default 6): fewer leave
+ * room for the kernels of the stream it runs beside. */
+enum { PPI_OPT_GEMM_SCHEME = 0, PPI_OPT_GEMM_CHUNK = 1, PPI_OPT_GEMM_OVERLAP = 2, PPI_OPT_GEMM_PAIR = 3,
+       PPI_OPT_PREFETCH_BLOCKS = 4 };
 enum { PPI_GEMM_TF32X3 = 0, PPI_GEMM_FP16X2 = 1 };
 int ppi_set_option(int key, int value);
 int ppi_get_option(int key);

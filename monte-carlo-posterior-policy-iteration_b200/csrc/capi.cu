@@ -54,6 +54,8 @@ static std::atomic<int> g_gemm_overlap{0};
 int gemm_overlap() { return g_gemm_overlap.load(std::memory_order_relaxed); }
 static std::atomic<int> g_gemm_pair{0};
 int gemm_pair() { return g_gemm_pair.load(std::memory_order_relaxed); }
+static std::atomic<int> g_prefetch_blocks{6};
+int prefetch_blocks() { return g_prefetch_blocks.load(std::memory_order_relaxed); }
 }  // namespace ppi
 
 extern "C" int ppi_set_option(int key, int value) {
@@ -71,6 +73,11 @@ extern "C" int ppi_set_option(int key, int value) {
   }
   if (key == PPI_OPT_GEMM_OVERLAP) { ppi::g_gemm_overlap.store(value != 0); return 0; }
   if (key == PPI_OPT_GEMM_PAIR) { ppi::g_gemm_pair.store(value != 0); return 0; }
+  if (key == PPI_OPT_PREFETCH_BLOCKS) {
+    PPI_REQUIRE(value >= 1 && value <= 6, PPI_ERR_INVALID, "ppi_set_option: prefetch CTAs per SM must lie in [1, 6]");
+    ppi::g_prefetch_blocks.store(value);
+    return 0;
+  }
   PPI_REQUIRE(false, PPI_ERR_INVALID, "ppi_set_option: unknown key %d", key);
 }
 
@@ -78,7 +85,8 @@ extern "C" int ppi_get_option(int key) {
   return key == PPI_OPT_GEMM_SCHEME ? ppi::gemm_scheme()
        : key == PPI_OPT_GEMM_CHUNK ? ppi::gemm_chunk()
        : key == PPI_OPT_GEMM_OVERLAP ? ppi::gemm_overlap()
-       : key == PPI_OPT_GEMM_PAIR ? ppi::gemm_pair() : -1;
+       : key == PPI_OPT_GEMM_PAIR ? ppi::gemm_pair()
+       : key == PPI_OPT_PREFETCH_BLOCKS ? ppi::prefetch_blocks() : -1;
 }
 
 extern "C" int64_t ppi_launch_count(void) { return ppi::g_launches.load(); }

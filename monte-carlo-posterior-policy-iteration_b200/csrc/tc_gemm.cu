@@ -1206,6 +1206,7 @@ static int side_stream(SideStream** out) {
 }
 int gemm_overlap();  // capi.cu: 1 = stage operands on the side stream
 int gemm_pair();     // capi.cu: 1 = CTA-pair (cta_group::2) kernels where they exist
+int prefetch_blocks();  // capi.cu: resident CTAs per SM of ppi_philox_prefetch
 
 constexpr int64_t kSyrkKc = 65536;    // samples staged per pass
 constexpr int64_t kSampleKc = 65536;  // sample rows staged per pass
@@ -2138,7 +2139,7 @@ extern "C" int ppi_philox_prefetch(uint64_t seed, uint64_t draw_id, uint64_t row
   const int64_t Dk = round_up(D, 64), zt_rows = round_up(D, BM), nrows = round_up(K, BN);
   uint16_t* store_rows = (uint16_t*)((char*)zstore + kScalarBytes);
   ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st);
-  philox_dual_kernel<<<grid_cap((nrows / 64) * ceil_div(zt_rows, 128), 6), 256, 0, st>>>(
+  philox_dual_kernel<<<grid_cap((nrows / 64) * ceil_div(zt_rows, 128), prefetch_blocks()), 256, 0, st>>>(
       nrows, D, Dk, seed, draw_id, row_offset, (uint16_t*)zrows, store_rows, zt_rows, 0);
   if (int rc = check_launch("philox_dual_kernel")) return rc;
   const int64_t rem = nrows % kZBlock;

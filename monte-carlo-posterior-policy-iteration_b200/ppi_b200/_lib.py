@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libppi_b200.so")
 # enums of include/ppi_b200.h
 KERNEL_KINDS = {"se": 0, "matern12": 1, "matern32": 2, "matern52": 3, "periodic": 4, "white": 5}
 FN_IDS = {"Himmelblau": 0, "Rosenbrock": 1, "Styblinski": 2, "Rastrigin": 3, "NoisySphere": 4}
-OPT_GEMM_SCHEME, OPT_GEMM_CHUNK, OPT_GEMM_OVERLAP, OPT_GEMM_PAIR = 0, 1, 2, 3
+OPT_GEMM_SCHEME, OPT_GEMM_CHUNK, OPT_GEMM_OVERLAP, OPT_GEMM_PAIR, OPT_PREFETCH_BLOCKS = 0, 1, 2, 3, 4
 GEMM_TF32X3, GEMM_FP16X2 = 0, 1
 TEMP_FIXED_NORMALISED, TEMP_FIXED_SHIFTED, TEMP_REPS_KL, TEMP_ESS_TARGET, TEMP_LOWER_BOUND = range(5)
 
