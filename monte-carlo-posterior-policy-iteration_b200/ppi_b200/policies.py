@@ -728,27 +728,46 @@ class BasePrimitive(object):
         c = np.asarray(self.cov_out_sqrt)
         return bool(np.count_nonzero(c - np.diag(np.diag(c))) == 0)
 
-    def _mavn_update(self, w, x, row_offset, replicated, shift1, jitter):
+    def _update_consts(self, shift1, H, d):
+        """Device copies of the per-update constants (the centring shift in fp32 and fp64, 1 / diag(cov_out)),
+        rebuilt only when the host arrays they come from were replaced or edited."""
+        cov_out = np.asarray(self.covariance_out, np.float64)
+        key = (None if shift1 is None else (shift1.shape, float(shift1.sum()), float(shift1.flat[0]), float(shift1.flat[-1])),
+               id(self.covariance_out), float(np.trace(cov_out)), float(cov_out[0, 0]), H, d)
+        c = self.__dict__.get("_consts")
+        if c is None or c[0] != key:
+            s32 = None if shift1 is None else f32(np.ascontiguousarray(shift1))
+            s64 = None if shift1 is None else f64(np.ascontiguousarray(shift1)).reshape(-1)
+            c = self._consts = (key, s32, s64, f32(1.0 / np.diag(cov_out)))
+        return c[1], c[2], c[3]
+
+    def _mavn_update(self, w, x, row_offset, replicated, shift1, jitter, extra=None):
         """m_projection_mavn (ppi/policies.py:96-143, iterations=1, update_out=False) on the
-        device: returns host fp64 (mean, cov_in, chol or None, pd)."""
+        device: returns host fp64 (mean, cov_in, chol or None, pd[, extra]).  `extra`: a device tensor
+        that rides along in the single device->host read of the results."""
         K_local, H, d = x.shape
         nw = _local(w.nw, row_offset, K_local)
-        s1 = ops.wmoments_diag(x, nw, shift1=shift1)
+        s32, s64, inv_out = self._update_consts(shift1, H, d)
+        s1 = ops.wmoments_diag(x, nw, shift1=s32)
         if not replicated:
             all_reduce_sum(s1)
-        base = 0.0 if shift1 is None else f64(shift1).reshape(-1)
-        shift = (s1 + base).float().reshape(H, d)
-        inv_out = 1.0 / np.diag(np.asarray(self.covariance_out, np.float64))
+        shift = (s1 if s64 is None else s1 + s64).float().reshape(H, d)
         acc = ops.wmoments_matnorm(x, nw, shift=shift, inv_cov_out=inv_out)
         if not replicated:
             all_reduce_sum(acc)
         fin = ops.finalize_matnorm(s1, acc, H, d, jitter=jitter)
-        packed = torch.cat([fin["mean64"].reshape(-1), fin["cov64"].reshape(-1),
-                            fin["chol64"].reshape(-1), fin["status"].double()]).cpu().numpy()
+        parts = [fin["mean64"].reshape(-1), fin["cov64"].reshape(-1), fin["chol64"].reshape(-1),
+                 fin["status"].double()]
+        if extra is not None:
+            parts.append(extra.reshape(-1).double())
+        packed = torch.cat(parts).cpu().numpy()
         mean = packed[:H * d].reshape(H, d)
         cov = packed[H * d:H * d + H * H].reshape(H, H)
         chol = packed[H * d + H * H:H * d + 2 * H * H].reshape(H, H)
-        return mean, cov, chol, packed[-1] == 0.0
+        pd = packed[H * d + 2 * H * H] == 0.0
+        if extra is not None:
+            return mean, cov, chol, pd, packed[H * d + 2 * H * H + 1:].reshape(extra.shape)
+        return mean, cov, chol, pd
 
 
 class BaseFeatures(BasePrimitive):
@@ -1025,10 +1044,15 @@ class BaseKernel(BasePrimitive):
         w = _weights(log_weights)
         x, row_offset, n_total, replicated = _samples(samples)
         H, d = x.shape[1], x.shape[2]
-        self.map_sequence = _row(x, row_offset, n_total, replicated, int(w.stats.argmax))
         shift1 = np.broadcast_to(np.asarray(self.mean_fn, np.float64)[None, :], (H, d))
-        mean_, cov_in_, chol_, pd = self._mavn_update(w, x, row_offset, replicated,
-                                                      np.ascontiguousarray(shift1), 0.0)
+        if replicated or dist_info()[1] == 1:
+            # the most likely sequence rides along in the one device->host read of the moments
+            mean_, cov_in_, chol_, pd, best = self._mavn_update(
+                w, x, row_offset, replicated, shift1, 0.0, extra=x[int(w.stats.argmax) - row_offset])
+            self.map_sequence = best
+        else:
+            self.map_sequence = _row(x, row_offset, n_total, replicated, int(w.stats.argmax))
+            mean_, cov_in_, chol_, pd = self._mavn_update(w, x, row_offset, replicated, shift1, 0.0)
         self.mean = mean_
         ess = float(w.stats.ess)
         if update_covariance_in:
