@@ -1,0 +1,156 @@
+"""GPU parity at BASELINE.json's FULL sizes (C5: K = 2^20 samples, D = 2048; the oracle needs hours
+there) through size-independent properties of the path: shift / scale linearity of the sampler, agreement
+of the two independent moment-match routes (whitened base normals vs. dense x-space kernel), one-hot and
+uniform weights, the ESS root of the temperature solve, bit-exact CEM ordering against NumPy's stable sort,
+cost kernels against fp64 NumPy on sampled rows plus a checksum.  Tolerance 1e-5 norm-wise in fp32
+(north_star), bit-exact for indices."""
+import numpy as np
+import pytest
+
+from oracle import ppi_oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+K5, D5 = 1 << 20, 2048
+
+
+@pytest.fixture(scope="module")
+def env():
+    import torch
+
+    assert torch.cuda.is_available()
+    if torch.cuda.get_device_properties(0).total_memory < 60e9:
+        pytest.skip("full-size checks need ~45 GB of device memory")
+    from ppi_b200 import _lib, ops
+
+    _lib.call("ppi_set_option", _lib.OPT_GEMM_SCHEME, _lib.GEMM_FP16X2)
+    return torch, _lib, ops
+
+
+@pytest.fixture(scope="module")
+def factor():
+    rng = np.random.default_rng(2048)
+    # a well-conditioned lower-triangular factor with unit-ish diagonal and dense off-diagonals
+    L = np.tril(rng.standard_normal((D5, D5))) / np.sqrt(D5)
+    L[np.diag_indices(D5)] = 1.0 + 0.1 * rng.random(D5)
+    mu = rng.standard_normal(D5)
+    return mu.astype(np.float32), L.astype(np.float32)
+
+
+def test_sampler_shift_and_scale_linearity(env, factor):
+    """x(mu, L) - x(0, L) = mu and x(0, 4 L) = 4 x(0, L): the same Philox draw through the tensor-core
+    sampler three times (a power-of-two factor must be bit-exact)."""
+    torch, _lib, ops = env
+    mu, L = factor
+    zero = np.zeros(D5, np.float32)
+    x0 = ops.sample_gaussian(K5, zero, L, seed=7, draw_id=3)
+    x1 = ops.sample_gaussian(K5, mu, L, seed=7, draw_id=3)
+    mu_t = torch.as_tensor(mu, device=x0.device)
+    err = (x1 - x0 - mu_t[None, :]).abs().max().item()
+    assert err < TOL * float(x0.abs().max().item())
+    del x1
+    x4 = ops.sample_gaussian(K5, zero, 4.0 * L, seed=7, draw_id=3)
+    assert bool((x4 == 4.0 * x0).all().item())
+    # rows are addressable by index: a shard generated on its own equals the rows of the full matrix
+    part = ops.sample_gaussian(4096, zero, L, seed=7, draw_id=3, row_offset=K5 - 4096)
+    assert bool((part == x0[K5 - 4096:]).all().item())
+
+
+def test_moment_match_routes_agree_at_full_size(env, factor):
+    """Weighted mean / covariance of K = 2^20 samples computed twice by independent kernels: on the
+    stored base normals (mu + L m, L C L^T; syrk_white_kernel) and on x itself (wmoments_diag +
+    syrk_gemm_kernel).  Also: weights sum to one, ESS hits the target."""
+    torch, _lib, ops = env
+    mu, L = factor
+    x, base = ops.sample_gaussian_keep(K5, mu, L, seed=11, draw_id=0)
+    cost = ops.cost_function("Rastrigin", x)
+    n_elites = K5 // 64
+    nw, lw, st = ops.solve_temperature(cost, _lib.TEMP_ESS_TARGET, n_elites)
+    assert abs(float(nw.double().sum().item()) - 1.0) < 1e-6
+    ess = 1.0 / float((nw.double() ** 2).sum().item())
+    assert abs(ess - n_elites) < 1e-4 * n_elites and abs(st.ess - ess) < 1e-6 * ess
+    # route 1: whitened
+    m, s = ops.wmoments_white(base, nw)
+    Ld = torch.as_tensor(L, device=x.device).double()
+    c = s.double() - torch.outer(m, m)
+    mu_w = torch.as_tensor(mu, device=x.device).double() + Ld @ m
+    sig_w = Ld @ c @ Ld.T
+    # route 2: x-space
+    mu_old = torch.as_tensor(mu, device=x.device)
+    s1 = ops.wmoments_diag(x, nw, shift1=mu_old)
+    mu_x = s1 + mu_old.double()
+    sig_x = ops.wmoments_dense(x, nw, shift=mu_x.float()).double()
+    sig_x = 0.5 * (sig_x + sig_x.T)
+    assert float((mu_w - mu_x).abs().max() / mu_x.abs().max()) < TOL
+    assert float((sig_w - sig_x).abs().max() / sig_x.abs().max()) < TOL
+    # the fitted covariance is symmetric positive definite
+    assert int(torch.linalg.cholesky_ex(sig_w)[1].item()) == 0
+
+
+def test_white_moments_uniform_and_one_hot(env, factor):
+    torch, _lib, ops = env
+    mu, L = factor
+    x, base = ops.sample_gaussian_keep(K5, mu, L, seed=5, draw_id=1)
+    del x
+    # uniform weights: m -> 0, S -> I at the Monte Carlo rate
+    nw = torch.full((K5,), 1.0 / K5, dtype=torch.float32, device="cuda")
+    m, s = ops.wmoments_white(base, nw)
+    assert float(m.abs().max()) < 6.0 / np.sqrt(K5)
+    eye = torch.eye(D5, device="cuda")
+    assert float((s - eye).abs().max()) < 8.0 / np.sqrt(K5)
+    assert abs(float(torch.trace(s.double())) / D5 - 1.0) < 1e-4
+    # one-hot weight: the moments of a single base-normal row, reproduced from its Philox index
+    k = 777_777
+    nw = torch.zeros(K5, dtype=torch.float32, device="cuda")
+    nw[k] = 1.0
+    m, s = ops.wmoments_white(base, nw)
+    z = ops.philox_normal(1, D5, seed=5, draw_id=1, row_offset=k)[0].double()
+    assert float((m - z).abs().max()) < 1e-6
+    assert float((s.double() - torch.outer(z, z)).abs().max()) < TOL * float(z.abs().max()) ** 2
+
+
+def test_cem_order_bit_exact_at_full_size(env):
+    torch, _lib, ops = env
+    rng = np.random.default_rng(20)
+    c = rng.standard_normal(K5).astype(np.float32)
+    c[rng.integers(0, K5, 1000)] = np.nan
+    c[rng.integers(0, K5, 5000)] = c[17]          # many exact ties
+    good = ~np.isnan(c)
+    order = np.lexsort((np.arange(K5), np.where(good, c, np.inf)))
+    n_elites = K5 // 64
+    idx, nw, st = ops.cem_weights(c, n_elites)
+    idx = idx.cpu().numpy()
+    n_good = int(good.sum())
+    assert (idx[:n_good] == order[:n_good]).all()
+    assert np.array_equal(np.sort(idx[n_good:]), np.flatnonzero(~good))
+    nwh = nw.cpu().numpy()
+    assert np.count_nonzero(nwh) == n_elites and (nwh[order[:n_elites]] == np.float32(1.0 / n_elites)).all()
+    assert st.argmax == order[0] and st.n_valid == n_good and st.ess == n_elites
+    # idempotence: sorting the sorted costs returns the identity permutation
+    idx2, _, _ = ops.cem_weights(np.where(good, c, np.inf)[order][:n_good], n_elites)
+    assert (idx2.cpu().numpy() == np.arange(n_good)).all()
+
+
+@pytest.mark.parametrize("name", ["Rastrigin", "Rosenbrock", "Styblinski"])
+def test_costs_on_sampled_rows_and_checksum(env, factor, name):
+    torch, _lib, ops = env
+    mu, L = factor
+    x = ops.sample_gaussian(K5, 0.1 * mu, 0.3 * L, seed=13, draw_id=2)
+    c = ops.cost_function(name, x)
+    rows = np.random.default_rng(1).integers(0, K5, 512)
+    xr = x[torch.as_tensor(rows, device=x.device)].cpu().numpy().astype(np.float64)
+    ref = {"Rastrigin": O.rastrigin, "Rosenbrock": O.rosenbrock, "Styblinski": O.styblinski}[name](xr)
+    got = c.cpu().numpy()[rows].astype(np.float64)
+    assert np.max(np.abs(got - ref)) < TOL * np.max(np.abs(ref))
+    # checksum of all K costs against a chunked fp64 evaluation on the device tensor
+    tot = 0.0
+    for i in range(0, K5, 1 << 17):
+        xc = x[i:i + (1 << 17)].double()
+        if name == "Rastrigin":
+            v = 10.0 * D5 + (xc * xc - 10.0 * torch.cos(2.0 * np.pi * xc)).sum(1)
+        elif name == "Rosenbrock":
+            v = (100.0 * (xc[:, 1:] - xc[:, :-1] ** 2) ** 2 + (1.0 - xc[:, :-1]) ** 2).sum(1)
+        else:
+            v = 0.5 * (xc ** 4 - 16.0 * xc ** 2 + 5.0 * xc).sum(1) + 39.16599 * D5
+        tot += float(v.sum().item())
+    assert abs(float(c.double().sum().item()) - tot) < TOL * abs(tot)
