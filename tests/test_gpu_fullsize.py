@@ -154,3 +154,40 @@ def test_costs_on_sampled_rows_and_checksum(env, factor, name):
             v = 0.5 * (xc ** 4 - 16.0 * xc ** 2 + 5.0 * xc).sum(1) + 39.16599 * D5
         tot += float(v.sum().item())
     assert abs(float(c.double().sum().item()) - tot) < TOL * abs(tot)
+
+
+def test_feature_sampler_at_c4_size(env):
+    """C4 (K = 65 536, T = 1000, F = 21, d = 2, value + derivative rows): every trajectory is the feature
+    expansion of its own returned weights, y = clip([mean_fn + Phi w, Phi' w]) -- checked in fp64 on the
+    device for ALL samples; the weights have the matrix-normal moments they were drawn from."""
+    torch, _lib, ops = env
+    K, T, F, d = 65536, 1000, 21, 2
+    rng = np.random.default_rng(4)
+    t = np.linspace(0, 2, T)
+    feat, dfeat = O.rff_features(t, np.sqrt(3e-2), 10, True)
+    dfeat = np.concatenate([np.gradient(feat[:, :-1], t, axis=0), np.zeros((T, 1))], axis=1)  # any (T, F) matrix
+    a = rng.standard_normal((F, F + 2))
+    l_in = np.linalg.cholesky(a @ a.T / F + 0.1 * np.eye(F))
+    l_out = np.diag([0.03, 0.05])
+    mean_fn, mean = np.array([0.0, 1.5707]), 0.2 * rng.standard_normal((F, d))
+    lo, hi = np.array([-2.0, -1.0, -40.0, -40.0]), np.array([2.0, 3.0, 40.0, 40.0])
+    y, w = ops.sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat, seed=21, draw_id=0, lower=lo, upper=hi)
+    assert y.shape == (K, T, 2 * d) and w.shape == (K, F, d)
+    ph, dph = torch.as_tensor(feat, device="cuda"), torch.as_tensor(dfeat, device="cuda")
+    lo_t, hi_t = torch.as_tensor(lo, device="cuda"), torch.as_tensor(hi, device="cuda")
+    worst, scale = 0.0, 0.0
+    for i in range(0, K, 8192):
+        wc = w[i:i + 8192].double()
+        ref = torch.cat([torch.as_tensor(mean_fn, device="cuda")[None, None, :] + torch.einsum("tf,bfd->btd", ph, wc),
+                         torch.einsum("tf,bfd->btd", dph, wc)], dim=2)
+        ref = torch.minimum(torch.maximum(ref, lo_t), hi_t)
+        worst = max(worst, float((y[i:i + 8192].double() - ref).abs().max()))
+        scale = max(scale, float(ref.abs().max()))
+    assert worst < TOL * scale
+    # moments of the weights: E w = mean, E (w - mean) cov_out^-1 (w - mean)^T / d = L_in L_in^T
+    wm = w.double().mean(0).cpu().numpy()
+    assert np.max(np.abs(wm - mean)) < 6.0 * np.max(np.abs(l_in)) * np.max(np.diag(l_out)) / np.sqrt(K)
+    dw = (w.double() - torch.as_tensor(mean, device="cuda")[None]) / torch.as_tensor(np.diag(l_out).copy(), device="cuda")
+    cin = torch.einsum("bid,bjd->ij", dw, dw).cpu().numpy() / (K * d)
+    ref_in = l_in @ l_in.T
+    assert np.max(np.abs(cin - ref_in)) < 0.03 * np.max(np.abs(ref_in))
