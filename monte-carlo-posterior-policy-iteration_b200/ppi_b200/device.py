@@ -8,6 +8,7 @@ ranks solve the temperature identically, and the fp64 / fp32 moment partials are
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 
 import numpy as np
 import torch
@@ -58,12 +59,16 @@ def f32_cached(a, device=None):
     sig = (a.shape, a.dtype.str, float(flat.sum()), float(flat[0]), float(flat[-1]), float(flat[a.size // 2]))
     key = (id(a), device.index)
     hit = _small_cache.get(key)
-    if hit is not None and hit[0] == sig:
+    if hit is not None and hit[0] == sig and hit[2]() is a:   # the weak reference rules out a recycled id
         return hit[1]
     if len(_small_cache) > 512:
         _small_cache.clear()
     t = f32(a, device)
-    _small_cache[key] = (sig, t)
+    try:
+        ref = weakref.ref(a)
+    except TypeError:      # array subclasses without weak-reference support: never cached
+        return t
+    _small_cache[key] = (sig, t, ref)
     return t
 
 
