@@ -732,8 +732,9 @@ class BasePrimitive(object):
         """Device copies of the per-update constants (the centring shift in fp32 and fp64, 1 / diag(cov_out)),
         rebuilt only when the host arrays they come from were replaced or edited."""
         cov_out = np.asarray(self.covariance_out, np.float64)
-        key = (None if shift1 is None else (shift1.shape, float(shift1.sum()), float(shift1.flat[0]), float(shift1.flat[-1])),
-               id(self.covariance_out), float(np.trace(cov_out)), float(cov_out[0, 0]), H, d)
+        key = (None if shift1 is None else (shift1.shape, np.ascontiguousarray(shift1[0]).tobytes(),
+                                            np.ascontiguousarray(shift1[-1]).tobytes(), float(shift1.sum())),
+               np.diagonal(cov_out).tobytes(), H, d)
         c = self.__dict__.get("_consts")
         if c is None or c[0] != key:
             s32 = None if shift1 is None else f32(np.ascontiguousarray(shift1))
