@@ -316,6 +316,18 @@ int ppi_finalize_matnorm(const double* s1, const double* acc, int H, int d, doub
                          double* mean64, float* mean32, double* cov64, float* cov32,
                          double* chol64, float* chol32, int* status, void* stream);
 
+/* a18-a20 fused for one rank: ppi_wmoments_diag -> centre -> ppi_wmoments_matnorm -> ppi_finalize_matnorm
+ * back to back, the result packed for a single device->host read (ppi/policies.py:96-143,804-848,461-516):
+ *   packed (fp64) = [ mean (H d) = sum nw (x - shift1) | cov_in (H H) | chol (H H) | status |
+ *                     x[map_index] (H d, only when map_index >= 0: the argmax sample, :811) ]
+ * shift1 (H, d) may be NULL (feature weights are matched without a mean function); inv_cov_out (d).
+ * workspace: ppi_matnorm_update_workspace_bytes(H, d).  K-sharded ranks use the three separate entry
+ * points with their all-reduces in between. */
+size_t ppi_matnorm_update_workspace_bytes(int H, int d);
+int ppi_matnorm_update(const float* x, const float* nw, int64_t K, int H, int d, const float* shift1,
+                       const float* inv_cov_out, double jitter, int64_t map_index, double* packed,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Measurement hooks (new; the reference has no instrumentation beyond profile_mpc.py:96-108).
  * ppi_launch_count: kernels this library has launched since load.  ppi_profile_enable(1) makes

@@ -262,6 +262,25 @@ finalize_matnorm_kernel(const double* __restrict__ s1, const double* __restrict_
   if (threadIdx.x == 0 && status) *status = fail;
 }
 
+
+// centre of the covariance pass: the new mean in sample coordinates, fp32
+__global__ void __launch_bounds__(256)
+matnorm_centre_kernel(const double* __restrict__ s1, const float* __restrict__ shift1, int n,
+                      float* __restrict__ shift) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    shift[i] = (float)(s1[i] + (shift1 ? (double)shift1[i] : 0.0));
+}
+
+// tail of the packed result: factorisation status and the requested sample row, as doubles
+__global__ void __launch_bounds__(256)
+matnorm_pack_tail_kernel(const int* __restrict__ status, const float* __restrict__ row, int n,
+                         double* __restrict__ tail) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) tail[0] = (double)*status;
+  if (row)
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+      tail[1 + i] = (double)row[i];
+}
+
 }  // namespace ppi
 
 using namespace ppi;
@@ -377,4 +396,44 @@ extern "C" int ppi_finalize_matnorm(const double* s1, const double* acc, int H, 
   finalize_matnorm_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(s1, acc, H, d, jitter, mean64, mean32,
                                                                   cov64, cov32, chol64, chol32, status);
   return check_launch("finalize_matnorm_kernel");
+}
+
+// ------------------------------------------------------------------------------------------
+// a18-a20 in one call (single rank): weighted mean, covariance about the new mean, symmetrise,
+// jitter, Cholesky and the most likely sample, into ONE packed fp64 result the host reads once.
+// ------------------------------------------------------------------------------------------
+extern "C" size_t ppi_matnorm_update_workspace_bytes(int H, int d) {
+  if (H <= 0 || d <= 0) return 0;
+  return ((size_t)H * d + (size_t)H * H) * sizeof(double) + ((size_t)H * d + 4) * sizeof(float) + 64;
+}
+
+extern "C" int ppi_matnorm_update(const float* x, const float* nw, int64_t K, int H, int d,
+                                  const float* shift1, const float* inv_cov_out, double jitter,
+                                  int64_t map_index, double* packed, void* workspace,
+                                  size_t workspace_bytes, void* stream) {
+  PPI_REQUIRE(x && nw && packed && workspace && K > 0 && H > 0 && d > 0, PPI_ERR_INVALID,
+              "ppi_matnorm_update: bad arguments");
+  PPI_REQUIRE(map_index >= -1 && map_index < K, PPI_ERR_INVALID, "ppi_matnorm_update: map_index out of range");
+  PPI_REQUIRE(workspace_bytes >= ppi_matnorm_update_workspace_bytes(H, d), PPI_ERR_WORKSPACE,
+              "ppi_matnorm_update: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int HD = H * d;
+  double* s1 = (double*)workspace;
+  double* acc = s1 + HD;
+  float* shift = (float*)(acc + (size_t)H * H);
+  int* status = (int*)(shift + HD);
+  PPI_CUDA_TRY(cudaMemsetAsync(workspace, 0, ((size_t)HD + (size_t)H * H) * sizeof(double), st));
+  PPI_CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(int), st));
+  if (int rc = ppi_wmoments_diag(x, nw, K, HD, shift1, nullptr, s1, nullptr, nullptr, stream)) return rc;
+  matnorm_centre_kernel<<<(HD + 255) / 256, 256, 0, st>>>(s1, shift1, HD, shift);
+  if (int rc = check_launch("matnorm_centre_kernel")) return rc;
+  if (int rc = ppi_wmoments_matnorm(x, nw, K, H, d, shift, inv_cov_out, acc, stream)) return rc;
+  double* cov = packed + HD;
+  double* chol = cov + (size_t)H * H;
+  if (int rc = ppi_finalize_matnorm(s1, acc, H, d, jitter, packed, nullptr, cov, nullptr, chol, nullptr, status,
+                                    stream))
+    return rc;
+  matnorm_pack_tail_kernel<<<(HD + 255) / 256, 256, 0, st>>>(
+      status, map_index >= 0 ? x + map_index * (int64_t)HD : nullptr, HD, chol + (size_t)H * H);
+  return check_launch("matnorm_pack_tail_kernel");
 }
