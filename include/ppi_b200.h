@@ -319,14 +319,19 @@ int ppi_finalize_matnorm(const double* s1, const double* acc, int H, int d, doub
 /* a18-a20 fused for one rank: ppi_wmoments_diag -> centre -> ppi_wmoments_matnorm -> ppi_finalize_matnorm
  * back to back, the result packed for a single device->host read (ppi/policies.py:96-143,804-848,461-516):
  *   packed (fp64) = [ mean (H d) = sum nw (x - shift1) | cov_in (H H) | chol (H H) | status |
- *                     x[map_index] (H d, only when map_index >= 0: the argmax sample, :811) ]
+ *                     x[map_index] (H d, only when map_index >= 0 or stats: the argmax sample, :811) |
+ *                     *stats as raw 8-byte words (only when stats != NULL) ]
+ * stats: the ppi_weight_stats a preceding ppi_solve_temperature left ON THE DEVICE; the sample row is then
+ * x[stats->argmax] and the statistics travel home in the same read (no synchronisation between the
+ * temperature solve and the match).
  * shift1 (H, d) may be NULL (feature weights are matched without a mean function); inv_cov_out (d).
  * workspace: ppi_matnorm_update_workspace_bytes(H, d).  K-sharded ranks use the three separate entry
  * points with their all-reduces in between. */
 size_t ppi_matnorm_update_workspace_bytes(int H, int d);
 int ppi_matnorm_update(const float* x, const float* nw, int64_t K, int H, int d, const float* shift1,
-                       const float* inv_cov_out, double jitter, int64_t map_index, double* packed,
-                       void* workspace, size_t workspace_bytes, void* stream);
+                       const float* inv_cov_out, double jitter, int64_t map_index,
+                       const ppi_weight_stats* stats, double* packed, void* workspace,
+                       size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Measurement hooks (new; the reference has no instrumentation beyond profile_mpc.py:96-108).

@@ -271,14 +271,21 @@ matnorm_centre_kernel(const double* __restrict__ s1, const float* __restrict__ s
     shift[i] = (float)(s1[i] + (shift1 ? (double)shift1[i] : 0.0));
 }
 
-// tail of the packed result: factorisation status and the requested sample row, as doubles
+// tail of the packed result: factorisation status, the requested sample row (index given by the host
+// or taken from the solver statistics still on the device), and those statistics as raw 8-byte words
 __global__ void __launch_bounds__(256)
-matnorm_pack_tail_kernel(const int* __restrict__ status, const float* __restrict__ row, int n,
+matnorm_pack_tail_kernel(const int* __restrict__ status, const float* __restrict__ x, int64_t K, int n,
+                         int64_t map_index, const ppi_weight_stats* __restrict__ stats,
                          double* __restrict__ tail) {
+  if (stats) map_index = stats->argmax;
+  const bool have_row = map_index >= 0 && map_index < K;
   if (blockIdx.x == 0 && threadIdx.x == 0) tail[0] = (double)*status;
-  if (row)
+  if (map_index >= 0 || stats)
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-      tail[1 + i] = (double)row[i];
+      tail[1 + i] = have_row ? (double)x[map_index * (int64_t)n + i] : nan("");
+  if (stats && blockIdx.x == 0 && threadIdx.x < (int)(sizeof(ppi_weight_stats) / 8))
+    reinterpret_cast<unsigned long long*>(tail + 1 + n)[threadIdx.x] =
+        reinterpret_cast<const unsigned long long*>(stats)[threadIdx.x];
 }
 
 }  // namespace ppi
@@ -409,8 +416,9 @@ extern "C" size_t ppi_matnorm_update_workspace_bytes(int H, int d) {
 
 extern "C" int ppi_matnorm_update(const float* x, const float* nw, int64_t K, int H, int d,
                                   const float* shift1, const float* inv_cov_out, double jitter,
-                                  int64_t map_index, double* packed, void* workspace,
-                                  size_t workspace_bytes, void* stream) {
+                                  int64_t map_index, const ppi_weight_stats* stats, double* packed,
+                                  void* workspace, size_t workspace_bytes, void* stream) {
+  static_assert(sizeof(ppi_weight_stats) % 8 == 0, "statistics are copied as 8-byte words");
   PPI_REQUIRE(x && nw && packed && workspace && K > 0 && H > 0 && d > 0, PPI_ERR_INVALID,
               "ppi_matnorm_update: bad arguments");
   PPI_REQUIRE(map_index >= -1 && map_index < K, PPI_ERR_INVALID, "ppi_matnorm_update: map_index out of range");
@@ -433,7 +441,7 @@ extern "C" int ppi_matnorm_update(const float* x, const float* nw, int64_t K, in
   if (int rc = ppi_finalize_matnorm(s1, acc, H, d, jitter, packed, nullptr, cov, nullptr, chol, nullptr, status,
                                     stream))
     return rc;
-  matnorm_pack_tail_kernel<<<(HD + 255) / 256, 256, 0, st>>>(
-      status, map_index >= 0 ? x + map_index * (int64_t)HD : nullptr, HD, chol + (size_t)H * H);
+  matnorm_pack_tail_kernel<<<(HD + 255) / 256, 256, 0, st>>>(status, x, K, HD, map_index, stats,
+                                                             chol + (size_t)H * H);
   return check_launch("matnorm_pack_tail_kernel");
 }

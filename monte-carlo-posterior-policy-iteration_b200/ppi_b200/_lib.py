@@ -47,7 +47,7 @@ SIGNATURES = {
     "ppi_sobol_normal": (_i, [_p, _i64, _i64, _p, _p, _i, _u64, _d, _p]),
     "ppi_cubature_points": (_i, [_p, _i, _p]),
     "ppi_matnorm_update_workspace_bytes": (_sz, [_i, _i]),
-    "ppi_matnorm_update": (_i, [_p, _p, _i64, _i, _i, _p, _p, _d, _i64, _p, _p, _sz, _p]),
+    "ppi_matnorm_update": (_i, [_p, _p, _i64, _i, _i, _p, _p, _d, _i64, _p, _p, _p, _sz, _p]),
     "ppi_kernel_shift_workspace_bytes": (_sz, [_i, _i]),
     "ppi_kernel_shift": (_i, [_i, _d, _d, _d, _p, _i, _p, _i, _p, _p, _p, _p, _i, _p, _p, _p, _d, _d, _p, _p,
                               _p, _p, _p, _p]),

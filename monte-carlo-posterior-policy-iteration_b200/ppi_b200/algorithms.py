@@ -16,7 +16,7 @@ import numpy as np
 import torch
 
 from . import _lib, ops, samplers
-from .device import DeviceArray, all_gather_rows, dist_info, f32
+from .device import DeviceArray, LazyStats, all_gather_rows, dist_info, f32
 from .policies import DeviceWeights, _row, _samples
 
 __all__ = [
@@ -115,8 +115,10 @@ class Base(object):
     # -- device weights ---------------------------------------------------------------------------
     def _solve(self, costs, samples, mode, hyper):
         c = _global_costs(costs, samples)
-        nw, log_w, st = ops.solve_temperature(c, mode, hyper)
-        self._stats = st
+        # the statistics stay on the device until somebody reads one: a kernel / feature policy takes
+        # them home together with its fitted moments (one synchronisation per update instead of two)
+        nw, log_w, st = ops.solve_temperature(c, mode, hyper, sync=False)
+        self._stats = st = LazyStats(st)
         return DeviceWeights(nw, log_w, st)
 
 

@@ -161,6 +161,33 @@ def workspace(tag, nbytes):
     return buf
 
 
+class LazyStats:
+    """struct ppi_weight_stats still on the device: read (with a synchronisation) on first attribute
+    access, or filled from bytes that came home with another result (ppi_matnorm_update)."""
+
+    __slots__ = ("tensor", "_host")
+
+    def __init__(self, tensor):
+        self.tensor, self._host = tensor, None
+
+    @property
+    def resolved(self):
+        return self._host is not None
+
+    def resolve(self):
+        if self._host is None:
+            self._host = read_stats(self.tensor)
+        return self._host
+
+    def fill(self, raw):
+        from . import _lib
+
+        self._host = _lib.WeightStats.from_buffer_copy(raw)
+
+    def __getattr__(self, name):
+        return getattr(self.resolve(), name)
+
+
 def read_stats(stats_tensor):
     """One D2H copy (with sync) of struct ppi_weight_stats -> _lib.WeightStats."""
     host = stats_tensor.cpu().numpy().tobytes()

@@ -419,21 +419,28 @@ def finalize_gaussian(s1=None, cov=None, shift=None, diagonal_only=False, want_m
     return mu, sigma
 
 
-def matnorm_update(x, nw, shift1, inv_cov_out, jitter=0.0, map_index=-1):
+def matnorm_update(x, nw, shift1, inv_cov_out, jitter=0.0, map_index=-1, stats=None):
     """One-rank matrix-normal moment match in a single call (ppi_matnorm_update): -> host fp64
-    (mean, cov_in, chol, status[, x[map_index]]) after ONE device->host read."""
+    (mean, cov_in, chol, status[, x[map_index]]) after ONE device->host read.
+    stats: a LazyStats whose struct is still on the device -- the sample row is then x[stats.argmax] and
+    the statistics are filled from the same read (no synchronisation since the temperature solve)."""
     dev = require_cuda()
     K, H, d = x.shape
-    n = H * d + 2 * H * H + 1 + (H * d if map_index >= 0 else 0)
+    on_dev = stats is not None and not stats.resolved
+    want_row = map_index >= 0 or on_dev
+    n_stats = _lib.STATS_BYTES // 8 if on_dev else 0
+    n = H * d + 2 * H * H + 1 + (H * d if want_row else 0) + n_stats
     packed = torch.empty(n, dtype=torch.float64, device=dev)
     nbytes = _lib.query("ppi_matnorm_update_workspace_bytes", H, d)
     ws = workspace("matnorm_update", nbytes)
     _lib.call("ppi_matnorm_update", ptr(x), ptr(nw), K, H, d, ptr(shift1), ptr(inv_cov_out), float(jitter),
-              int(map_index), ptr(packed), ptr(ws), nbytes, stream_ptr())
+              int(map_index), ptr(stats.tensor) if on_dev else None, ptr(packed), ptr(ws), nbytes, stream_ptr())
     host = packed.cpu().numpy()
+    if on_dev:
+        stats.fill(host[n - n_stats:].tobytes())
     a, b, c = H * d, H * d + H * H, H * d + 2 * H * H
     out = (host[:a].reshape(H, d), host[a:b].reshape(H, H), host[b:c].reshape(H, H), int(host[c]))
-    return out + ((host[c + 1:].reshape(H, d),) if map_index >= 0 else ())
+    return out + ((host[c + 1:c + 1 + H * d].reshape(H, d),) if want_row else ())
 
 
 def finalize_matnorm(s1, acc, H, d, jitter=0.0):

@@ -16,7 +16,7 @@ import numpy as np
 import torch
 
 from . import _lib, ops, samplers
-from .device import (DeviceArray, all_reduce_max, all_reduce_sum, broadcast_row, dist_info, f32, f64, require_cuda,
+from .device import (DeviceArray, LazyStats, all_reduce_max, all_reduce_sum, broadcast_row, dist_info, f32, f64, require_cuda,
                      shard_rows, to_host64)
 
 __all__ = [
@@ -744,18 +744,24 @@ class BasePrimitive(object):
 
     def _mavn_update(self, w, x, row_offset, replicated, shift1, jitter, extra=None):
         """m_projection_mavn (ppi/policies.py:96-143, iterations=1, update_out=False) on the
-        device: returns host fp64 (mean, cov_in, chol or None, pd[, x[extra]]).  `extra`: local index of a
-        sample row that rides along in the single device->host read of the results."""
+        device: returns host fp64 (mean, cov_in, chol or None, pd[, map row]).  extra="argmax": the most
+        likely sample rides along in the single device->host read of the results."""
         K_local, H, d = x.shape
         nw = _local(w.nw, row_offset, K_local)
         s32, s64, inv_out = self._update_consts(shift1, H, d)
         if (replicated or dist_info()[1] == 1) and H <= 128:
-            # one rank: the whole match is one C call and one device->host read
-            idx = -1 if extra is None else int(extra)
-            res = ops.matnorm_update(x, nw, s32, inv_out, jitter, idx)
+            # one rank: the whole match is one C call and one device->host read; solver statistics that
+            # are still on the device come home in the same read (extra == "argmax": the row they name)
+            lazy = w.stats if isinstance(w.stats, LazyStats) and not w.stats.resolved else None
+            if extra == "argmax":
+                idx = -1 if lazy is not None else int(w.stats.argmax) - row_offset
+                res = ops.matnorm_update(x, nw, s32, inv_out, jitter, idx, stats=lazy)
+            else:
+                res = ops.matnorm_update(x, nw, s32, inv_out, jitter, -1, stats=lazy)
+                res = res[:4]
             return res[:3] + (res[3] == 0,) + res[4:]
         if extra is not None:
-            extra = x[int(extra)]
+            extra = x[int(w.stats.argmax) - row_offset]
         s1 = ops.wmoments_diag(x, nw, shift1=s32)
         if not replicated:
             all_reduce_sum(s1)
@@ -1056,7 +1062,7 @@ class BaseKernel(BasePrimitive):
         if replicated or dist_info()[1] == 1:
             # the most likely sequence rides along in the one device->host read of the moments
             mean_, cov_in_, chol_, pd, best = self._mavn_update(
-                w, x, row_offset, replicated, shift1, 0.0, extra=int(w.stats.argmax) - row_offset)
+                w, x, row_offset, replicated, shift1, 0.0, extra="argmax")
             self.map_sequence = best
         else:
             self.map_sequence = _row(x, row_offset, n_total, replicated, int(w.stats.argmax))
