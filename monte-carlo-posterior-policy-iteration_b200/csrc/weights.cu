@@ -63,7 +63,7 @@ __device__ __forceinline__ double warp_sum_d(double v) {
 }
 
 struct Sums {
-  double s0, s1, sc, scc, s1c;
+  double s0, s1, sc, scc, s1c, sccc, s1cc;  // sum e, e^2, e c, e c^2, e^2 c, e c^3, e^2 c^2
 };
 
 // Grid-wide reduction of NV doubles.  vals[] in: this thread's partial; out: grid total in
@@ -81,6 +81,19 @@ __device__ __forceinline__ void grid_reduce_sum(double (&vals)[NV], SolveWorkspa
     for (int v = 0; v < NV; ++v) s_scratch[warp * NV + v] = vals[v];
   }
   __syncthreads();
+  if (gridDim.x == 1) {
+    // single block (K <= 4096, the MPC shapes): the warp partials in shared memory are the grid's;
+    // no round trip through global memory, every thread adds them in the same order
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      double t = 0.0;
+#pragma unroll
+      for (int w = 0; w < NW; ++w) t += s_scratch[w * NV + v];
+      vals[v] = t;
+    }
+    __syncthreads();
+    return;
+  }
   if (threadIdx.x < NV) {
     double t = 0.0;
     for (int w = 0; w < NW; ++w) t += s_scratch[w * NV + threadIdx.x];
@@ -130,23 +143,25 @@ __device__ __forceinline__ bool elem(const CostView& v, int64_t k, double& cn) {
 
 __device__ __forceinline__ Sums evaluate(const CostView& v, double alpha, SolveWorkspace* ws,
                                          int& buf, unsigned int& bar_target, double* s_scratch) {
-  double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   for (int64_t k = v.begin + threadIdx.x; k < v.end; k += kSolveThreads) {
     double cn;
     if (!elem(v, k, cn)) continue;
     const float t = (float)(-alpha * cn);
     const double e = (double)expf(t);
     if (e > 0.0) {
-      const double e2 = e * e;
+      const double e2 = e * e, ec = e * cn, e2c = e2 * cn;
       acc[0] += e;
       acc[1] += e2;
-      acc[2] += e * cn;
-      acc[3] += e * cn * cn;
-      acc[4] += e2 * cn;
+      acc[2] += ec;
+      acc[3] += ec * cn;
+      acc[4] += e2c;
+      acc[5] += ec * cn * cn;
+      acc[6] += e2c * cn;
     }
   }
-  grid_reduce_sum<5>(acc, ws, buf, bar_target, s_scratch);
-  return Sums{acc[0], acc[1], acc[2], acc[3], acc[4]};
+  grid_reduce_sum<7>(acc, ws, buf, bar_target, s_scratch);
+  return Sums{acc[0], acc[1], acc[2], acc[3], acc[4], acc[5], acc[6]};
 }
 
 // residual whose root is the sought alpha; `dir` = +1 when it increases with alpha
@@ -162,6 +177,27 @@ __device__ __forceinline__ double residual(int mode, const Sums& s, double alpha
       const double ep = s.sc / s.s0, var = s.scc / s.s0 - ep * ep;
       const double eq = s.s1c / s.s1, ess = s.s0 * s.s0 / s.s1;
       return -var + lambda * (ep - eq) / sqrt(ess);
+    }
+  }
+}
+
+// d residual / d alpha from the same sums (moments of c under nw ~ e and under nw^2 ~ e^2): lets the
+// solver take Newton steps, 2-3 evaluations from a bracket to 1e-11 instead of ~8 regula-falsi steps
+__device__ __forceinline__ double residual_slope(int mode, const Sums& s, double alpha, double hyper) {
+  const double ep = s.sc / s.s0, eq = s.s1c / s.s1;
+  const double var = s.scc / s.s0 - ep * ep;
+  switch (mode) {
+    case PPI_TEMP_ESS_TARGET:
+      return 2.0 * (eq - ep);
+    case PPI_TEMP_REPS_KL:
+      return alpha * var;
+    default: {
+      const double lambda = sqrt((1.0 - hyper) / hyper);
+      const double m2 = s.scc / s.s0, m3 = s.sccc / s.s0;
+      const double k3 = m3 - 3.0 * ep * m2 + 2.0 * ep * ep * ep;  // third central moment under nw
+      const double var_q = s.s1cc / s.s1 - eq * eq;
+      const double ess = s.s0 * s.s0 / s.s1;
+      return k3 + lambda * (-var + 2.0 * var_q + (ep - eq) * (ep - eq)) / sqrt(ess);
     }
   }
 }
@@ -308,11 +344,16 @@ solve_temperature_kernel(const float* __restrict__ in, int64_t K, int mode, doub
     ++iterations;
     if (threadIdx.x == 0) {
       const double f = dir * residual(mode, s, alpha, hyper, n_valid);
+      // Newton proposal from this point (f increases through the root: a usable slope is positive)
+      const double df = dir * residual_slope(mode, s, alpha, hyper);
+      const double newton = (df > 0.0 && isfinite(df)) ? alpha - f / df : nan("");
       if (st.phase == 0) {
         st.flo = f;
         if (!(f < 0.0)) {  // already at / beyond the root at the lower end (or NaN)
           st.x = st.lo; st.phase = 3; st.status = 1;
         } else {
+          // first upper point: the tangent's root when there is one (kept within [1e-3, 4]), else 1
+          if (newton > st.lo && isfinite(newton)) st.hi = fmin(fmin(fmax(newton, 1e-3), 4.0), st.hi_cap);
           st.phase = 1; st.x = st.hi;
         }
       } else if (st.phase == 1) {
@@ -324,7 +365,16 @@ solve_temperature_kernel(const float* __restrict__ in, int64_t K, int mode, doub
         } else {
           st.lo = st.hi; st.flo = f;
           if (st.hi >= st.hi_cap) { st.x = st.hi_cap; st.phase = 3; st.status = 1; }
-          else { st.hi = fmin(st.hi * 2.0, st.hi_cap); st.x = st.hi; }
+          else {
+            // still left of the root: follow the tangent (at most 64x, at least the old doubling when
+            // there is no slope); a tangent step that no longer moves the iterate is the root
+            double nxt = st.hi * 2.0;
+            if (newton > st.hi && isfinite(newton)) {
+              if (newton - st.hi <= 1e-11 * st.hi) { st.x = newton; st.phase = 3; }
+              nxt = fmin(newton, st.hi * 64.0);
+            }
+            if (st.phase != 3) { st.hi = fmin(nxt, st.hi_cap); st.x = st.hi; }
+          }
         }
       } else {  // refine
         if (f == 0.0) { st.lo = st.hi = st.x; }
@@ -347,6 +397,7 @@ solve_temperature_kernel(const float* __restrict__ in, int64_t K, int mode, doub
         } else {
           double x = st.hi - st.fhi * width / (st.fhi - st.flo);
           if (!(x > st.lo && x < st.hi)) x = 0.5 * (st.lo + st.hi);
+          if (newton > st.lo && newton < st.hi) x = newton;   // tangent from the point just evaluated
           // the iterate has stopped moving: the secant point is the root to fp64 noise level
           if (fabs(x - st.x_prev) <= 1e-11 * fabs(x)) st.phase = 3;
           st.x_prev = x;
