@@ -395,7 +395,7 @@ sample_features_tiled_kernel(const float* __restrict__ z, uint64_t seed, uint64_
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 feature_weights_kernel(const float* __restrict__ z, uint64_t seed, uint64_t draw, uint64_t row_offset,
-                       int64_t K, int F, int d, const float* __restrict__ mean,
+                       int64_t K, int F, int d, int S, const float* __restrict__ mean,
                        const float* __restrict__ l_in, const float* __restrict__ l_out,
                        float* __restrict__ w) {
   extern __shared__ __align__(16) float smem[];
@@ -403,52 +403,64 @@ feature_weights_kernel(const float* __restrict__ z, uint64_t seed, uint64_t draw
   float* sLin = smem;                    // F * F
   float* sLout = sLin + pad4(F * F);     // d * d
   float* sMean = sLout + pad4(d * d);    // F * d
-  float* sZ = sMean + pad4(FD);          // 32 * F * d
-  float* sU = sZ + pad4(kFeatS * FD);    // 32 * F * d
+  float* sZ = sMean + pad4(FD);          // S * F * d
+  float* sU = sZ + pad4(S * FD);         // S * F * d
   for (int i = threadIdx.x; i < F * F; i += blockDim.x) sLin[i] = l_in[i];
   for (int i = threadIdx.x; i < d * d; i += blockDim.x) sLout[i] = l_out[i];
   for (int i = threadIdx.x; i < FD; i += blockDim.x) sMean[i] = mean[i];
-  // static work split (FD <= 256): thread = (sample sub-group, weight element r = k d + l); an element
-  // of L_in read from shared memory feeds the FMAs of up to 8 samples
-  const int nsub = blockDim.x / FD;
-  const int sub = threadIdx.x / FD, r = threadIdx.x - sub * FD, k = r / d, l = r - k * d;
+  // static work split: thread = (block of 8 samples, row pair (p, F-1-p), output column l).  L_in is
+  // lower triangular, so rows p and F-1-p together cost F + 1 multiply-adds for every thread (no
+  // divergence on the triangle), and each L_in element read from shared memory feeds 8 samples.
+  // S = 8 * (256 / (ceil(F/2) d)) samples per group.
+  const int P = (F + 1) >> 1, PD = P * d;
+  const int nsub = S >> 3;
+  const int sub = threadIdx.x / PD, rem = threadIdx.x - sub * PD, p = rem / d, l = rem - p * d;
+  const int k1 = p, k2 = F - 1 - p;
   const bool worker = sub < nsub;
-  const int64_t n_groups = ceil_div(K, kFeatS);
+  const int64_t n_groups = ceil_div(K, S);
   for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
-    const int64_t b0 = g * kFeatS;
-    const int ns = (int)min((int64_t)kFeatS, K - b0);
+    const int64_t b0 = g * S;
+    const int ns = (int)min((int64_t)S, K - b0);
     __syncthreads();
     load_normals(sZ, ns * FD, z, (uint64_t)b0 * FD, (row_offset + (uint64_t)b0) * FD, seed, draw);
     __syncthreads();
-    if (worker) {
-      for (int s = sub; s < ns; s += nsub) {
-        const float* zr = sZ + s * FD + k * d;
-        float u = 0.f;
-        for (int j = 0; j < d; ++j) u = fmaf(zr[j], sLout[l * d + j], u);
-        sU[s * FD + r] = u;
-      }
+    for (int e = threadIdx.x; e < ns * FD; e += blockDim.x) {
+      const int c = e % d;
+      const float* zr = sZ + (e - c);
+      float u = 0.f;
+      for (int j = 0; j < d; ++j) u = fmaf(zr[j], sLout[c * d + j], u);
+      sU[e] = u;
     }
     __syncthreads();
-    if (worker) {
-      for (int s0 = sub; s0 < ns; s0 += 8 * nsub) {
-        float a[8];
-        const float* up[8];
+    if (worker && sub * 8 < ns) {
+      float a1[8], a2[8];
+      const float* up[8];
+#pragma unroll
+      for (int m = 0; m < 8; ++m) {
+        a1[m] = a2[m] = 0.f;
+        up[m] = sU + min(sub * 8 + m, ns - 1) * FD + l;
+      }
+      const float* row1 = sLin + k1 * F;
+      const float* row2 = sLin + k2 * F;
+      for (int i = 0; i <= k2; ++i) {
+        const float li2 = row2[i];
+        const float li1 = i <= k1 ? row1[i] : 0.f;   // a zero coefficient leaves the sum bit-identical
 #pragma unroll
         for (int m = 0; m < 8; ++m) {
-          a[m] = 0.f;
-          up[m] = sU + min(s0 + m * nsub, kFeatS - 1) * FD + l;
+          const float u = up[m][i * d];
+          a2[m] = fmaf(li2, u, a2[m]);
+          a1[m] = fmaf(li1, u, a1[m]);
         }
-        const float* row = sLin + k * F;
-        for (int i = 0; i <= k; ++i) {
-          const float li = row[i];
+      }
+      const int r1 = k1 * d + l, r2 = k2 * d + l;
+      const float m1 = sMean[r1], m2 = sMean[r2];
 #pragma unroll
-          for (int m = 0; m < 8; ++m) a[m] = fmaf(li, up[m][i * d], a[m]);
-        }
-        const float mr = sMean[r];
-#pragma unroll
-        for (int m = 0; m < 8; ++m) {
-          const int sm = s0 + m * nsub;
-          if (sm < ns) w[(b0 + sm) * FD + r] = a[m] + mr;
+      for (int m = 0; m < 8; ++m) {
+        const int sm = sub * 8 + m;
+        if (sm < ns) {
+          float* wr = w + (b0 + sm) * FD;
+          wr[r2] = a2[m] + m2;
+          if (k1 != k2) wr[r1] = a1[m] + m1;
         }
       }
     }
@@ -952,12 +964,13 @@ extern "C" int ppi_sample_features(const float* z, uint64_t seed, uint64_t draw_
   if (d == 2 && F <= 32 && (reinterpret_cast<uintptr_t>(y) & 15) == 0) {
     // two kernels: weights (SIMT, tiny), then the expansion on mma.sync (mma_small.cu)
     const int FD = F * d;
-    const size_t smem_w = ((size_t)pad4(F * F) + pad4(d * d) + pad4(FD) + 2 * (size_t)pad4(kFeatS * FD)) *
+    const int S = 8 * (256 / (((F + 1) / 2) * d));   // samples per group (>= 64 for F <= 32, d = 2)
+    const size_t smem_w = ((size_t)pad4(F * F) + pad4(d * d) + pad4(FD) + 2 * (size_t)pad4(S * FD)) *
                           sizeof(float);
     if (int rc = set_smem(feature_weights_kernel, smem_w)) return rc;
     ProfileScope prof(PPI_PROF_SAMPLE_SMALL, (cudaStream_t)stream);
-    feature_weights_kernel<<<grid_for(ceil_div(K, kFeatS), 4), 256, smem_w, (cudaStream_t)stream>>>(
-        z, seed, draw_id, row_offset, K, F, d, mean, l_in, l_out, w);
+    feature_weights_kernel<<<grid_for(ceil_div(K, S), 4), 256, smem_w, (cudaStream_t)stream>>>(
+        z, seed, draw_id, row_offset, K, F, d, S, mean, l_in, l_out, w);
     if (int rc = check_launch("feature_weights_kernel")) return rc;
     return ppi_features_expand_mma(w, K, F, T, mean_fn, feat, dfeat, lower, upper, y,
                                    (cudaStream_t)stream);
