@@ -46,6 +46,16 @@ __device__ __forceinline__ void grid_sync(unsigned int* bar, unsigned int nblock
   target += nblocks;
   __syncthreads();
   if (nblocks == 1) return;  // single block (K <= 4096, the MPC shapes): the block barrier is the grid barrier
+  {
+    // the whole grid is ONE thread-block cluster (K <= 65536): the hardware cluster barrier with
+    // release / acquire semantics replaces the atomic counter and its spin loop
+    unsigned int cluster_ctas;
+    asm volatile("mov.u32 %0, %%cluster_nctaid.x;" : "=r"(cluster_ctas));
+    if (cluster_ctas == nblocks) {
+      asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+      return;
+    }
+  }
   if (threadIdx.x == 0) {
     __threadfence();
     atomicAdd(bar, 1u);
@@ -577,12 +587,39 @@ static int launch_solve(const float* in, int64_t K, int mode, double hyper, floa
     PPI_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, solve_temperature_kernel, kSolveThreads, 0));
     blocks_per_sm = occ < 1 ? 1 : (occ > 4 ? 4 : occ);
   }
-  int64_t g = ceil_div(K, 4096);
-  if (g < 1) g = 1;
-  if (g > (int64_t)blocks_per_sm * kNumSMs) g = (int64_t)blocks_per_sm * kNumSMs;
   void* args[] = {(void*)&in, (void*)&K, (void*)&mode, (void*)&hyper, (void*)&nw, (void*)&log_w,
                   (void*)&stats, (void*)&ws};
   ProfileScope prof(PPI_PROF_SOLVE, st);
+  if (K <= 65536) {
+    // up to 16 CTAs of 4096 costs each as one cluster (non-portable size, supported on B200; the
+    // per-element fp64 work binds one SM to ~0.1 us per 256 costs, so more CTAs beat larger slices):
+    // co-scheduled by the hardware, synchronised by the cluster barrier; one CTA needs no barrier at all
+    static bool np_set = false;
+    if (!np_set) {
+      PPI_CUDA_TRY(cudaFuncSetAttribute(solve_temperature_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      np_set = true;
+    }
+    const unsigned gc = (unsigned)ceil_div(K, 4096);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(gc);
+    cfg.blockDim = dim3(kSolveThreads);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = gc;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = gc > 1 ? 1 : 0;
+    if (cudaLaunchKernelExC(&cfg, (const void*)solve_temperature_kernel, args) == cudaSuccess) {
+      count_launch(1);
+      return 0;
+    }
+    (void)cudaGetLastError();  // fall back to the cooperative grid below
+  }
+  int64_t g = ceil_div(K, 4096);
+  if (g < 1) g = 1;
+  if (g > (int64_t)blocks_per_sm * kNumSMs) g = (int64_t)blocks_per_sm * kNumSMs;
   PPI_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)solve_temperature_kernel, dim3((unsigned)g),
                                            dim3(kSolveThreads), args, 0, st));
   count_launch(1);
