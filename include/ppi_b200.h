@@ -74,6 +74,12 @@ int ppi_get_option(int key);
  * ---------------------------------------------------------------------------------------- */
 int ppi_philox_normal(float* out, int64_t rows, int64_t cols, uint64_t seed, uint64_t draw_id,
                       uint64_t row_offset, void* stream);
+/* The same draw WITHOUT the rounding to the fp16 grid: full fp32 Box-Muller values of the same Philox
+ * words (|difference| <= 2^-12 |z|).  These are not exact tensor-core operands: a policy that samples
+ * from them goes through the injected-normal path (fp16 pair operands, three partial products).  Used by
+ * the distribution tests and by `bench.py --normals fp32`, which prices the quantisation. */
+int ppi_philox_normal_full(float* out, int64_t rows, int64_t cols, uint64_t seed, uint64_t draw_id,
+                           uint64_t row_offset, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * f2  quasi-Monte-Carlo base normals                              ppi/samplers.py:25-44

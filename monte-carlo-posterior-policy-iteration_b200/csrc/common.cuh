@@ -144,10 +144,24 @@ __device__ __forceinline__ __half2 box_muller_h2(uint32_t a, uint32_t b) {
   const float u = u01(a), v = u01_23(b);
   // every transcendental is a single MUFU instruction (lg2 / sqrt / sin / cos, no slow paths): the
   // result is rounded to 11 bits anyway
+  // the radicand is clamped from below: MUFU.LG2 carries an absolute error of 2^-22, so for u in the top
+  // float bins below 1 nothing guarantees a non-positive logarithm (sqrt of a negative number would be a NaN
+  // that poisons a whole D x D moment), and u01() returns exactly 1 for r >= 2^32 - 128 (an atom at z = 0)
   float r, s, c;
-  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(-1.3862943611198906f * __log2f(u)));  // sqrt(-2 ln u)
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaxf(-1.3862943611198906f * __log2f(u), 1e-12f)));  // sqrt(-2 ln u)
   __sincosf(6.283185307179586f * v, &s, &c);
   return __floats2half2_rn(r * c, r * s);
+}
+
+// The same pair WITHOUT the rounding to the fp16 grid (ppi_philox_normal_full): what the generator
+// would emit if the normals were not made exact tensor-core operands.  Same Philox words, same angles.
+__device__ __forceinline__ void box_muller_full(uint32_t a, uint32_t b, float& z0, float& z1) {
+  const float u = u01(a), v = u01_23(b);
+  float r, s, c;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaxf(-1.3862943611198906f * __log2f(u), 1e-12f)));
+  __sincosf(6.283185307179586f * v, &s, &c);
+  z0 = r * c;
+  z1 = r * s;
 }
 
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {

@@ -14,6 +14,7 @@ namespace ppi {
 // ------------------------------------------------------------------------------------------
 // Philox normals -> global memory
 // ------------------------------------------------------------------------------------------
+template <bool FULL>
 __global__ void __launch_bounds__(256) philox_normal_kernel(float* __restrict__ out, int64_t n_local,
                                                             uint64_t elem_base, uint64_t seed,
                                                             uint64_t draw) {
@@ -22,7 +23,13 @@ __global__ void __launch_bounds__(256) philox_normal_kernel(float* __restrict__ 
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t q = q0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += stride) {
     float v[4];
-    philox_normal4(seed, draw, q, v);
+    if (FULL) {
+      const Philox4 p = philox4x32_10(q, draw, seed);
+      box_muller_full(p.x, p.y, v[0], v[1]);
+      box_muller_full(p.z, p.w, v[2], v[3]);
+    } else {
+      philox_normal4(seed, draw, q, v);
+    }
     const int64_t local = (int64_t)(q * 4) - (int64_t)elem_base;
     if (local >= 0 && local + 4 <= n_local &&
         ((reinterpret_cast<uintptr_t>(out + local) & 15) == 0)) {
@@ -821,9 +828,20 @@ extern "C" int ppi_philox_normal(float* out, int64_t rows, int64_t cols, uint64_
   if (rows == 0) return 0;
   const int64_t n = rows * cols;
   const int grid = grid_for(ceil_div(ceil_div(n, 4), 256 * 4), 8);
-  philox_normal_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(out, n, row_offset * (uint64_t)cols,
-                                                               seed, draw_id);
+  philox_normal_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(out, n, row_offset * (uint64_t)cols,
+                                                                      seed, draw_id);
   return check_launch("philox_normal_kernel");
+}
+
+extern "C" int ppi_philox_normal_full(float* out, int64_t rows, int64_t cols, uint64_t seed,
+                                      uint64_t draw_id, uint64_t row_offset, void* stream) {
+  PPI_REQUIRE(out && rows >= 0 && cols > 0, PPI_ERR_INVALID, "ppi_philox_normal_full: bad arguments");
+  if (rows == 0) return 0;
+  const int64_t n = rows * cols;
+  const int grid = grid_for(ceil_div(ceil_div(n, 4), 256 * 4), 8);
+  philox_normal_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(out, n, row_offset * (uint64_t)cols,
+                                                                     seed, draw_id);
+  return check_launch("philox_normal_kernel<full>");
 }
 
 extern "C" int ppi_kernel_gram_chol(const double* t1, int n1, const double* t2, int n2, int kind,

@@ -42,6 +42,7 @@ SIGNATURES = {
     "ppi_set_option": (_i, [_i, _i]),
     "ppi_get_option": (_i, [_i]),
     "ppi_philox_normal": (_i, [_p, _i64, _i64, _u64, _u64, _u64, _p]),
+    "ppi_philox_normal_full": (_i, [_p, _i64, _i64, _u64, _u64, _u64, _p]),
     "ppi_kernel_gram_chol": (_i, [_p, _i, _p, _i, _i, _d, _d, _d, _p, _p, _p, _p, _p, _p]),
     "ppi_cholesky_small": (_i, [_p, _i, _p, _p, _p, _p]),
     "ppi_sobol_normal": (_i, [_p, _i64, _i64, _p, _p, _i, _u64, _d, _p]),

@@ -16,7 +16,7 @@ import numpy as np
 import torch
 
 from . import _lib, ops, samplers
-from .device import DeviceArray, LazyStats, all_gather_rows, dist_info, f32
+from .device import DeviceArray, LazyStats, all_gather_rows, dist_info, f32, gather_global_rows, scope
 from .policies import DeviceWeights, _row, _samples
 
 __all__ = [
@@ -42,17 +42,31 @@ def null_callback(iteration, f, actions, costs, policy):
 
 
 def _global_costs(costs, samples):
-    """Costs of ALL K samples on every rank: K-sharded device costs are all-gathered (4K bytes) so
-    that each rank solves the temperature identically."""
+    """-> (costs of ALL K samples on every rank as an fp32 device tensor, fp64 offset).  K-sharded device
+    costs are all-gathered (4K bytes) so that each rank solves the temperature identically (SURVEY 8(e)
+    step 2).  Host (fp64) costs are centred on their smallest finite value before the fp32 cast, so that a
+    large common offset (1e6 +- 1) does not eat the fp32 mantissa; every weight the solver returns is
+    invariant under that shift and the offset is added back to the min / max / mean statistics."""
     if isinstance(costs, DeviceArray):
         c = costs.tensor.reshape(-1)
         if dist_info()[1] > 1 and c.shape[0] != costs.global_rows:
-            c = all_gather_rows(c, costs.global_rows)
-        return c
-    c = f32(np.asarray(costs, dtype=np.float64)).reshape(-1)
+            with scope("allgather_costs"):
+                c = all_gather_rows(c, costs.global_rows)
+        return c, 0.0
+    c64 = np.asarray(costs, dtype=np.float64).reshape(-1)
+    finite = c64[np.isfinite(c64)]
+    offset = float(finite.min()) if finite.size else 0.0
+    c = f32(c64 - offset).reshape(-1)
     if isinstance(samples, DeviceArray) and dist_info()[1] > 1 and c.shape[0] != samples.global_rows:
+        # every rank must subtract the same constant: agree on the global minimum first
+        import torch.distributed as dist
+
+        off = torch.tensor([offset], dtype=torch.float64, device=c.device)
+        dist.all_reduce(off, op=dist.ReduceOp.MIN)
+        c = f32(c64 - float(off.item())).reshape(-1)
+        offset = float(off.item())
         c = all_gather_rows(c, samples.global_rows)
-    return c
+    return c, offset
 
 
 class Base(object):
@@ -104,6 +118,11 @@ class Base(object):
                 c = c[~np.isnan(c)] if not np.isnan(c).all() else np.zeros_like(c)
                 self.trace["mean"].append(c.mean())
                 self.trace["std"].append(c.std())
+            if callback is not null_callback:
+                # the reference hands the callback the NaN-FILTERED costs (ppi/algorithms.py:87-91)
+                c = np.asarray(costs, dtype=np.float64).reshape(-1)
+                bad = np.isnan(c)
+                costs = np.zeros_like(c) if bad.all() else c[~bad]
             flag = callback(i, f, actions, costs, policy)
             if flag:
                 break
@@ -114,11 +133,11 @@ class Base(object):
 
     # -- device weights ---------------------------------------------------------------------------
     def _solve(self, costs, samples, mode, hyper):
-        c = _global_costs(costs, samples)
+        c, offset = _global_costs(costs, samples)
         # the statistics stay on the device until somebody reads one: a kernel / feature policy takes
         # them home together with its fitted moments (one synchronisation per update instead of two)
         nw, log_w, st = ops.solve_temperature(c, mode, hyper, sync=False)
-        self._stats = st = LazyStats(st)
+        self._stats = st = LazyStats(st, offset)
         return DeviceWeights(nw, log_w, st)
 
 
@@ -132,9 +151,9 @@ class _CemBase(Base):
         policy.reset_covariance()
 
     def _elite_update(self, costs, samples, policy):
-        c = _global_costs(costs, samples)
-        idx, nw, st = ops.cem_weights(c, self.n_elites)
-        self._stats = st
+        c, offset = _global_costs(costs, samples)
+        idx, nw, st = ops.cem_weights(c, self.n_elites, sync=False)
+        self._stats = st = LazyStats(st, offset)
         log_w = torch.where(nw > 0, torch.zeros_like(nw), torch.full_like(nw, -1e12))
         w = DeviceWeights(nw, log_w, st)
         ess, kl = policy.weighted_update(w, samples)
@@ -144,7 +163,7 @@ class _CemBase(Base):
         self.trace["kl"] += [kl]
         self.trace["ent"] += [policy.entropy]
         self.trace["weight_ent"] += [st.weight_entropy]
-        return idx, x, row_offset
+        return idx, x, row_offset, n_total, replicated
 
 
 class Cem(_CemBase):
@@ -171,10 +190,13 @@ class iCem(_CemBase):
         self.n_reuse = int(sample_reuse_pc * n_elites)
 
     def update(self, costs, samples, policy):
-        idx, x, row_offset = self._elite_update(costs, samples, policy)
+        idx, x, row_offset, n_total, replicated = self._elite_update(costs, samples, policy)
         if isinstance(policy.sampler, samplers.Particles):
-            reuse = idx[: self.n_reuse] - row_offset
-            policy.sampler.particles = x[reuse].cpu().numpy().astype(np.float64)
+            # idx holds GLOBAL sample numbers: under K-sharding the re-used elites are fetched from their
+            # owner ranks (every rank ends up with the same particles, as on one GPU)
+            reuse = idx[: self.n_reuse]
+            rows = x[reuse] if replicated else gather_global_rows(x, reuse, row_offset, n_total)
+            policy.sampler.particles = rows.cpu().numpy().astype(np.float64)
             assert policy.sampler.has_particles
         return policy
 

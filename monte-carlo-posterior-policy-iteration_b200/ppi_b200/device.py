@@ -50,16 +50,16 @@ _small_cache = {}
 
 def f32_cached(a, device=None):
     """f32() for small host arrays that are re-sent on every call (policy state: mean_fn, mean, factors,
-    limits): the device copy is reused while the SAME array object still holds the same numbers (shape,
-    sum and end points are re-checked, so in-place edits are seen)."""
+    limits): the device copy is reused while the SAME array object still holds the same numbers.  The
+    whole content is compared against a host snapshot taken at upload time (<= 64 K elements, a few
+    microseconds), so any in-place edit is seen -- the reference re-reads its arrays on every call."""
     if not isinstance(a, np.ndarray) or a.size == 0 or a.size > 1 << 16:
         return f32(a, device)
     device = device or require_cuda()
-    flat = a.reshape(-1)
-    sig = (a.shape, a.dtype.str, float(flat.sum()), float(flat[0]), float(flat[-1]), float(flat[a.size // 2]))
     key = (id(a), device.index)
     hit = _small_cache.get(key)
-    if hit is not None and hit[0] == sig and hit[2]() is a:   # the weak reference rules out a recycled id
+    if (hit is not None and hit[2]() is a and hit[0].shape == a.shape and hit[0].dtype == a.dtype
+            and np.array_equal(hit[0], a, equal_nan=True)):   # the weak reference rules out a recycled id
         return hit[1]
     if len(_small_cache) > 512:
         _small_cache.clear()
@@ -68,7 +68,7 @@ def f32_cached(a, device=None):
         ref = weakref.ref(a)
     except TypeError:      # array subclasses without weak-reference support: never cached
         return t
-    _small_cache[key] = (sig, t, ref)
+    _small_cache[key] = (a.copy(), t, ref)
     return t
 
 
@@ -79,14 +79,28 @@ def f64(a, device=None):
     return torch.as_tensor(np.ascontiguousarray(np.asarray(a, dtype=np.float64)), device=device)
 
 
+_pinned_staging = {}
+
+
+def _pinned(nbytes):
+    """One pinned staging buffer per process, grown on demand (a fresh cudaHostAlloc per read costs
+    ~1 ms for a 32 MB matrix and serialises the eight processes of a node on the driver lock)."""
+    buf = _pinned_staging.get("buf")
+    if buf is None or buf.numel() < nbytes:
+        buf = _pinned_staging["buf"] = torch.empty(max(int(nbytes), 1 << 16), dtype=torch.uint8, pin_memory=True)
+    return buf
+
+
 def to_host64(t):
-    """Device tensor -> host fp64 NumPy array through a pinned staging buffer (the conversion to
-    fp64 happens on the device; a pageable `.cpu()` of a 2048 x 2048 matrix costs ~15 ms)."""
+    """Device tensor -> host fp64 NumPy array through the pinned staging buffer (the conversion to
+    fp64 happens on the device; a pageable `.cpu()` of a 2048 x 2048 matrix costs ~15 ms).  The result
+    is a private copy (the staging buffer is reused by the next read)."""
     t64 = t.detach().to(torch.float64).contiguous()
-    host = torch.empty(t64.shape, dtype=torch.float64, pin_memory=True)
-    host.copy_(t64, non_blocking=True)
+    n = t64.numel()
+    stage = _pinned(8 * n)[: 8 * n].view(torch.float64)
+    stage.copy_(t64.reshape(-1), non_blocking=True)
     torch.cuda.current_stream().synchronize()
-    return host.numpy()
+    return stage.numpy().reshape(tuple(t64.shape)).copy()
 
 
 class DeviceArray:
@@ -165,10 +179,13 @@ class LazyStats:
     """struct ppi_weight_stats still on the device: read (with a synchronisation) on first attribute
     access, or filled from bytes that came home with another result (ppi_matnorm_update)."""
 
-    __slots__ = ("tensor", "_host")
+    __slots__ = ("tensor", "_host", "offset")
+    _SHIFTED = ("cost_min", "cost_max", "cost_mean")
 
-    def __init__(self, tensor):
-        self.tensor, self._host = tensor, None
+    def __init__(self, tensor, offset=0.0):
+        # offset: fp64 constant subtracted from host costs before the fp32 cast (algorithms._global_costs);
+        # added back to the statistics that are not shift-invariant
+        self.tensor, self._host, self.offset = tensor, None, float(offset)
 
     @property
     def resolved(self):
@@ -185,13 +202,55 @@ class LazyStats:
         self._host = _lib.WeightStats.from_buffer_copy(raw)
 
     def __getattr__(self, name):
-        return getattr(self.resolve(), name)
+        v = getattr(self.resolve(), name)
+        return v + self.offset if (name in LazyStats._SHIFTED and self.offset) else v
 
 
 def read_stats(stats_tensor):
     """One D2H copy (with sync) of struct ppi_weight_stats -> _lib.WeightStats."""
     host = stats_tensor.cpu().numpy().tobytes()
     return _lib.WeightStats.from_buffer_copy(host)
+
+
+# --------------------------------------------------------------------------------------------
+# host-level timing scopes (bench.py): CUDA-event brackets around the steps that are not one C call --
+# the collectives and the dense D x D tail.  Off unless profile_scopes(True); the C library keeps its own
+# per-kernel slots (ppi_profile_enable).
+# --------------------------------------------------------------------------------------------
+_scopes = {"on": False, "events": {}}
+
+
+def profile_scopes(on):
+    _scopes["on"] = bool(on)
+    _scopes["events"] = {}
+
+
+class scope:
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if _scopes["on"] and torch.cuda.is_available():
+            self.a = torch.cuda.Event(enable_timing=True)
+            self.a.record()
+        return self
+
+    def __exit__(self, *exc):
+        if _scopes["on"] and hasattr(self, "a"):
+            b = torch.cuda.Event(enable_timing=True)
+            b.record()
+            _scopes["events"].setdefault(self.name, []).append((self.a, b))
+        return False
+
+
+def profile_scopes_read():
+    """{name: (count, total device ms)} of the scopes recorded since profile_scopes(True)."""
+    out = {}
+    for name, evs in _scopes["events"].items():
+        if evs:
+            evs[-1][1].synchronize()
+            out[name] = (len(evs), float(sum(a.elapsed_time(b) for a, b in evs)))
+    return out
 
 
 # --------------------------------------------------------------------------------------------
@@ -216,19 +275,26 @@ def shard_rows(n_total, rank=None, world=None):
 
 
 def all_gather_rows(local, n_total):
-    """Concatenate per-rank row blocks of shard_rows() order into the global (n_total, ...) tensor."""
+    """Concatenate per-rank row blocks of shard_rows() order into the global (n_total, ...) tensor:
+    one all_gather_into_tensor when the split is even (the configured case), a padded gather + one
+    compaction otherwise."""
     import torch.distributed as dist
 
     rank, world = dist_info()
     if world == 1:
         return local
+    local = local.contiguous()
+    if n_total % world == 0:
+        out = torch.empty((n_total,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(out, local)
+        return out
     sizes = [shard_rows(n_total, r, world) for r in range(world)]
     maxn = max(e - b for b, e in sizes)
     pad = torch.zeros((maxn,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
     pad[: local.shape[0]] = local
-    out = [torch.empty_like(pad) for _ in range(world)]
-    dist.all_gather(out, pad)
-    return torch.cat([o[: e - b] for o, (b, e) in zip(out, sizes)], dim=0)
+    out = torch.empty((world * maxn,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, pad)
+    return torch.cat([out[r * maxn: r * maxn + (e - b)] for r, (b, e) in enumerate(sizes)], dim=0)
 
 
 def all_reduce_sum(t):
@@ -261,3 +327,19 @@ def broadcast_row(samples, global_index, n_total):
         row.copy_(samples[global_index - shard_rows(n_total, owner, world)[0]])
     dist.broadcast(row, src=owner)
     return row
+
+
+def gather_global_rows(samples, global_indices, row_offset, n_total):
+    """Rows `global_indices` (global sample numbers, any owners) of the K-sharded sample matrix on every
+    rank: each rank contributes the rows it owns, zeros elsewhere, and one all-reduce assembles them
+    (the index list is short: iCEM's re-used elites, ppi/algorithms.py:162-164)."""
+    idx = torch.as_tensor(global_indices, dtype=torch.int64, device=samples.device).reshape(-1)
+    rank, world = dist_info()
+    if world == 1:
+        return samples[idx - row_offset]
+    n_local = samples.shape[0]
+    mine = (idx >= row_offset) & (idx < row_offset + n_local)
+    out = torch.zeros((idx.numel(),) + tuple(samples.shape[1:]), dtype=samples.dtype, device=samples.device)
+    if bool(mine.any()):
+        out[mine] = samples[idx[mine] - row_offset]
+    return all_reduce_sum(out)

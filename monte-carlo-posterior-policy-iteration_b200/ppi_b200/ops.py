@@ -35,11 +35,12 @@ class _Keep:
 
 
 # ------------------------------------------------------------------ a3
-def philox_normal(rows, cols, seed, draw_id=0, row_offset=0):
+def philox_normal(rows, cols, seed, draw_id=0, row_offset=0, full_precision=False):
+    """full_precision: the same Philox / Box-Muller draw without the rounding to the fp16 grid."""
     dev = require_cuda()
     out = torch.empty((rows, cols), dtype=torch.float32, device=dev)
-    _lib.call("ppi_philox_normal", ptr(out), rows, cols, _u64(seed), _u64(draw_id), _u64(row_offset),
-              stream_ptr())
+    _lib.call("ppi_philox_normal_full" if full_precision else "ppi_philox_normal", ptr(out), rows, cols,
+              _u64(seed), _u64(draw_id), _u64(row_offset), stream_ptr())
     return out
 
 

@@ -17,7 +17,7 @@ import torch
 
 from . import _lib, ops, samplers
 from .device import (DeviceArray, LazyStats, all_reduce_max, all_reduce_sum, broadcast_row, dist_info, f32, f64, require_cuda,
-                     shard_rows, to_host64)
+                     scope, shard_rows, to_host64)
 
 __all__ = [
     "RbfFeatures",
@@ -284,7 +284,11 @@ def convolve(signal_samples, kernel):
 def _draw(sampler, n_total, d):
     """Base normals for this rank's rows: (z_local or None, seed, draw_id, row_offset, n_local)."""
     begin, end = shard_rows(n_total)
-    if hasattr(sampler, "device_normals"):
+    if getattr(sampler, "shard_aware", False):
+        z, seed, draw = sampler.device_normals(n_total, d, rows=(begin, end))
+        if z is not None:   # already this rank's rows
+            return z.reshape(end - begin, d), seed, draw, begin, end - begin, n_total
+    elif hasattr(sampler, "device_normals"):
         z, seed, draw = sampler.device_normals(n_total, d)
     else:  # foreign sampler obeying only the reference protocol
         z = f32(np.asarray(sampler(np.zeros((d,)), np.eye(1), n_total, standard_gaussian=True)))
@@ -303,6 +307,7 @@ class GaussianPolicy(object):
 
     name = "Gaussian"
     small_dim = 128  # at or below: SIMT kernels + host fp64 tail; above: tcgen05 + device tail
+    n_regularized = 0  # updates that took the non-PD branch of ppi/policies.py:263-268 (bench.py asserts 0)
 
     def __init__(self, mu, sigma, sampler, diagonal=False):
         self.sampler = sampler
@@ -438,8 +443,8 @@ class GaussianPolicy(object):
         d = self._dim
         begin, end = shard_rows(n_samples)
         n_local = end - begin
-        if (not isinstance(sampler, samplers.MonteCarlo) or n_local * d < self.prefetch_min_elements
-                or d <= self.small_dim):
+        if (not isinstance(sampler, samplers.MonteCarlo) or sampler.full_precision
+                or n_local * d < self.prefetch_min_elements or d <= self.small_dim):
             return
         dev = require_cuda()
         st = self.__dict__.setdefault("_pre_state", {})
@@ -511,6 +516,7 @@ class GaussianPolicy(object):
                 self._chol64_dev, self._chol_dev, self._logdet = chol64, None, None
             else:
                 logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
+                self.n_regularized += 1
                 self.sigma = sigma_old + SIGMA_MIN * np.eye(d)
         ess = float(w.stats.ess)
         self._version += 1
@@ -529,20 +535,25 @@ class GaussianPolicy(object):
         m, s = ops.wmoments_white(base, nw)
         if self.prefetch_normals == "update" and n_total is not None and not base.injected:
             self._prefetch_next(n_total)
-        all_reduce_sum(m)
-        all_reduce_sum(s)
-        c = s.double()
-        c.addr_(m, m, alpha=-1.0)
-        g, info = torch.linalg.cholesky_ex(c)
-        scal = torch.stack([info.double(), 2.0 * torch.log(torch.diagonal(g)).sum(), torch.trace(c), m @ m]).cpu()
-        self._mu_host, self._mu_dev = None, (mu_old_dev.double() + l_old @ m).float()
-        if int(scal[0]) == 0:
+        if dist_info()[1] > 1:
+            with scope("allreduce_moments"):
+                all_reduce_sum(m)
+                all_reduce_sum(s)
+        with scope("dense_tail"):
+            c = s.double()
+            c.addr_(m, m, alpha=-1.0)
+            g, info = torch.linalg.cholesky_ex(c)
+            scal = torch.stack([info.double(), 2.0 * torch.log(torch.diagonal(g)).sum(), torch.trace(c), m @ m]).cpu()
+            self._mu_host, self._mu_dev = None, (mu_old_dev.double() + l_old @ m).float()
+            l_new = l_old @ g if int(scal[0]) == 0 else None
+        if l_new is not None:
             logdet_c = float(scal[1])
             self._sigma_host = self._sigma_dev = self._chol_dev = self._sigma64_dev = None
-            self._chol64_dev, self._logdet = l_old @ g, old_logdet + logdet_c
+            self._chol64_dev, self._logdet = l_new, old_logdet + logdet_c
             kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(self._logdet) + float(scal[2]) + float(scal[3]) - d)
         else:  # ppi/policies.py:263-268: keep the old covariance, regularised
             logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
+            self.n_regularized += 1
             sigma_old = l_old @ l_old.T
             self._sigma_host, self._chol_dev, self._chol64_dev, self._logdet = None, None, None, None
             self._sigma64_dev = None
@@ -596,6 +607,7 @@ class GaussianPolicy(object):
                 self._logdet = float(2.0 * torch.log(torch.diagonal(chol64)).sum().item())
             else:
                 logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
+                self.n_regularized += 1
                 if sigma_old_host is not None:
                     self.sigma = sigma_old_host + SIGMA_MIN * np.eye(d)
                 else:
@@ -732,8 +744,8 @@ class BasePrimitive(object):
         """Device copies of the per-update constants (the centring shift in fp32 and fp64, 1 / diag(cov_out)),
         rebuilt only when the host arrays they come from were replaced or edited."""
         cov_out = np.asarray(self.covariance_out, np.float64)
-        key = (None if shift1 is None else (shift1.shape, np.ascontiguousarray(shift1[0]).tobytes(),
-                                            np.ascontiguousarray(shift1[-1]).tobytes(), float(shift1.sum())),
+        # the full content is the key (H x d fp64, a few KB): any in-place edit of mean_fn / cov_out is seen
+        key = (None if shift1 is None else (shift1.shape, np.ascontiguousarray(shift1).tobytes()),
                np.diagonal(cov_out).tobytes(), H, d)
         c = self.__dict__.get("_consts")
         if c is None or c[0] != key:
@@ -804,11 +816,12 @@ class BaseFeatures(BasePrimitive):
         return DeviceArray(ys, begin, n_total), DeviceArray(ws, begin, n_total)
 
     def _device_features(self):
-        """Phi(t) / Phi'(t) as device tensors, rebuilt only when the time grid (object, shape or end
-        points) or the feature parameters change: the reference recomputes them on every call
+        """Phi(t) / Phi'(t) as device tensors, rebuilt only when the time grid (its values) or the feature
+        parameters change: the reference recomputes them on every call
         (ppi/policies.py:406-408), 0.45 ms of host NumPy per draw at T = 1000."""
         t = self.t
-        key = (id(t), t.shape, float(t[0]), float(t[-1]), getattr(self, "ls", None),
+        # keyed on the whole time grid (T fp64 values): an edit of its interior rebuilds the features
+        key = (t.shape, np.ascontiguousarray(t).tobytes(), getattr(self, "ls", None),
                getattr(self, "order", None), self.dim_features, bool(self.use_derivatives))
         cache = getattr(self, "_feat_cache", None)
         if cache is None or cache[0] != key:
@@ -1002,13 +1015,13 @@ class BaseKernel(BasePrimitive):
         return t.shape == self.t.shape and bool((t == self.t).all())
 
     def _prior_device(self):
-        """(prior, prior_inv) as device fp64 tensors, re-uploaded when the host arrays were replaced."""
-        key = (id(self.covariance_in_prior), id(self.covariance_in_prior_inv))
+        """(prior, prior_inv) as device fp64 tensors, re-uploaded when the host arrays were replaced or edited."""
+        p, pi = np.asarray(self.covariance_in_prior), np.asarray(self.covariance_in_prior_inv)
         cache = getattr(self, "_prior_dev", None)
-        if cache is None or cache[0] != key:
-            self._prior_dev = cache = (key, f64(self.covariance_in_prior), f64(self.covariance_in_prior_inv),
-                                       self.covariance_in_prior, self.covariance_in_prior_inv)
-        return cache[1], cache[2]
+        if (cache is None or cache[2].shape != p.shape or not np.array_equal(cache[2], p)
+                or not np.array_equal(cache[3], pi)):
+            self._prior_dev = cache = (f64(p), f64(pi), p.copy(), pi.copy())   # host snapshots: edits are seen
+        return cache[0], cache[1]
 
     def update_timesteps(self, time_sequence, anneal=1.0, eps=1e-5):
         """GP shift of mean / covariance onto a new time window (ppi/policies.py:761-791)."""

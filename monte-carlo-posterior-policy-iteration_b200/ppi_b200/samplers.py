@@ -1,7 +1,7 @@
 """Base-normal samplers with the reference's sampler protocol (ppi/samplers.py:9-22):
 `Sampler(dimension)`, `sampler(mu, sigma, n_samples, standard_gaussian=False) -> (n, d)`.
 
-On top of the protocol, native samplers expose `device_normals(n, d, row_offset)` which the
+On top of the protocol, native samplers expose `device_normals(n, d)` which the
 ppi_b200 policies use to keep the draw on the GPU: MonteCarlo returns Philox parameters (the
 normals are generated inside the sampling kernel), InjectedNormals returns a device tensor.
 QuasiMonteCarlo generates its scrambled-Sobol points and the erfinv transform on the device from the
@@ -31,25 +31,37 @@ class MonteCarlo(BaseSampler):
     The non-standard path uses the Cholesky transform mu + z L^T (numpy's mvn factors by SVD: same
     distribution, different draws -- SURVEY 7.3 item 7)."""
 
-    def __init__(self, dimension, seed=None):
+    def __init__(self, dimension, seed=None, full_precision=False):
         self.d = dimension
         self.seed = int(np.random.randint(0, 2 ** 31 - 1)) if seed is None else int(seed)
         self.draw_id = 0
+        # full_precision: unrounded fp32 normals, materialised per draw and consumed like injected normals
+        # (fp16-pair operands, three partial products); the default keeps the normals on the fp16 grid, where
+        # each one is a single exact tensor-core operand (INTEGRATION.md section 3)
+        self.full_precision = bool(full_precision)
 
-    def device_normals(self, n_samples, d):
-        """-> (z or None, seed, draw_id): None means 'generate with Philox inside the kernel'."""
+    def device_normals(self, n_samples, d, rows=None):
+        """-> (z or None, seed, draw_id): None means 'generate with Philox inside the kernel'.
+        rows = (begin, end): the caller only needs those rows of the draw (K-sharding); z then holds them."""
         draw = self.draw_id
         self.draw_id += 1
+        if self.full_precision:
+            begin, end = rows if rows is not None else (0, n_samples)
+            return ops.philox_normal(end - begin, d, self.seed, draw, row_offset=begin, full_precision=True), self.seed, draw
         return None, self.seed, draw
 
+    shard_aware = True   # device_normals(..., rows=) returns only the requested rows
+
     def __call__(self, mu, sigma, n_samples, standard_gaussian=False):
-        _, seed, draw = self.device_normals(n_samples, self.d)
+        d = self.d if mu is None else np.asarray(mu).shape[0]
+        z, seed, draw = self.device_normals(n_samples, d)
         if standard_gaussian:
-            d = self.d if mu is None else np.asarray(mu).shape[0]
-            return ops.philox_normal(n_samples, d, seed, draw).cpu().numpy().astype(np.float64)
+            if z is None:
+                z = ops.philox_normal(n_samples, d, seed, draw)
+            return z.cpu().numpy().astype(np.float64)
         dev = require_cuda()
         L = torch.linalg.cholesky(torch.as_tensor(np.asarray(sigma, np.float64), device=dev))
-        x = ops.sample_gaussian(n_samples, mu, L.float(), seed=seed, draw_id=draw)
+        x = ops.sample_gaussian(n_samples, mu, L.float(), z=z, seed=seed, draw_id=draw)
         return x.cpu().numpy().astype(np.float64)
 
 
