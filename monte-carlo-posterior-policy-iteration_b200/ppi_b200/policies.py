@@ -556,8 +556,9 @@ class GaussianPolicy(object):
             self.n_regularized += 1
             sigma_old = l_old @ l_old.T
             self._sigma_host, self._chol_dev, self._chol64_dev, self._logdet = None, None, None, None
-            self._sigma64_dev = None
-            self._sigma_dev = (sigma_old + SIGMA_MIN * torch.eye(d, dtype=torch.float64, device=sigma_old.device)).float()
+            # kept in fp64: the 1e-6 regulariser is 17 ulps of an fp32 entry of size one
+            self._sigma_dev = None
+            self._sigma64_dev = sigma_old + SIGMA_MIN * torch.eye(d, dtype=torch.float64, device=sigma_old.device)
             self._factor()
             tr = torch.linalg.solve_triangular(l_old, self._chol64_dev, upper=False).square().sum()
             kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(self._logdet) + float(tr.item())
@@ -612,9 +613,8 @@ class GaussianPolicy(object):
                     self.sigma = sigma_old_host + SIGMA_MIN * np.eye(d)
                 else:
                     sigma_old = self._sigma64_d()  # device state still describes the old covariance
-                    self._sigma_host = self._sigma64_dev = None
-                    self._sigma_dev = (sigma_old + SIGMA_MIN * torch.eye(d, dtype=torch.float64,
-                                                                         device=x.device)).float()
+                    self._sigma_host = self._sigma_dev = None
+                    self._sigma64_dev = sigma_old + SIGMA_MIN * torch.eye(d, dtype=torch.float64, device=x.device)
                     self._chol_dev = self._chol64_dev = self._logdet = None
                 self._factor()
         # KL(new || old), ppi/policies.py:146-158,269, from the two Cholesky factors:

@@ -19,3 +19,26 @@ def golden():
     import numpy as np
 
     return dict(np.load(os.path.join(ROOT, "tests", "golden", "reference_golden.npz")))
+
+
+def record_errors(name, **values):
+    """Append the ACHIEVED errors of a parity test to gpurun_out/parity_errors.jsonl (and print them), so that
+    the measured margins -- not only pass / fail -- come home from the GPU box (profiles/ keeps a copy)."""
+    import json
+
+    line = {"test": name}
+    line.update({k: (float(v) if isinstance(v, (int, float)) or hasattr(v, "__float__") else v)
+                 for k, v in values.items()})
+    print("PARITY", json.dumps(line))
+    out = os.path.join(ROOT, "gpurun_out")
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "parity_errors.jsonl"), "a") as f:
+            f.write(json.dumps(line) + "\n")
+    except OSError:
+        pass
+
+
+@pytest.fixture(scope="session")
+def record():
+    return record_errors

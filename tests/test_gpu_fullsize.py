@@ -191,3 +191,215 @@ def test_feature_sampler_at_c4_size(env):
     cin = torch.einsum("bid,bjd->ij", dw, dw).cpu().numpy() / (K * d)
     ref_in = l_in @ l_in.T
     assert np.max(np.abs(cin - ref_in)) < 0.03 * np.max(np.abs(ref_in))
+
+
+# ------------------------------------------------------------------------------------------------
+# fp64 checkers AT the configured sizes ("What's weak" 1): C2 against the oracle's BLAS
+# restatement on the host, C5 against chunked fp64 algebra on the device (torch fp64 matmul is the CHECKER
+# here, never the product), C4 against the oracle on injected normals.
+# ------------------------------------------------------------------------------------------------
+def nerr(a, ref):
+    a, ref = np.asarray(a, np.float64), np.asarray(ref, np.float64)
+    assert a.shape == ref.shape, (a.shape, ref.shape)
+    return np.max(np.abs(a - ref)) / max(np.max(np.abs(ref)), 1e-300)
+
+
+@pytest.mark.parametrize("fn_name,solver_name,source", [
+    ("Rosenbrock", "Essps", "philox"), ("Rastrigin", "Lbps", "philox"),
+    ("Rosenbrock", "Lbps", "injected"), ("Rastrigin", "Essps", "injected")])
+def test_c2_three_iterations_against_fp64_oracle(env, record, fn_name, solver_name, source):
+    """Config C2 as SURVEY 8(d) states it: GaussianPolicy(ones(1024), 0.5 I) for iteration 1, the fitted full
+    covariance for iterations 2-3, K = 65536, Rosenbrock / Rastrigin, Essps(K/64) / Lbps(0.5).  Every
+    iteration: samples against the oracle's Cholesky transform of the SAME base normals, costs, temperature,
+    ESS, fitted mean / covariance / KL / entropy against the oracle's fp64 update of the same samples
+    (reference ppi/policies.py:78-93,251-269)."""
+    torch, _lib, ops = env
+    from ppi_b200 import algorithms as alg, functions as fn, policies as pol, samplers as smp
+
+    K, D = 65536, 1024
+    rng = np.random.default_rng(1024)
+    if source == "philox":
+        sampler = smp.MonteCarlo(D, seed=4242)
+    else:
+        zs = [np.asarray(rng.standard_normal((K, D)), np.float32) for _ in range(3)]
+        smp.InjectedNormals.queue = [z.copy() for z in zs]
+        sampler = smp.InjectedNormals(D)
+    policy = pol.GaussianPolicy(np.ones(D), 0.5 * np.eye(D), sampler)
+    solver = alg.Essps(n_elites=K // 64) if solver_name == "Essps" else alg.Lbps(delta=0.5)
+    solver.reset(policy)
+    f = getattr(fn, fn_name)(D)
+    f_ref = getattr(O, fn_name.lower())
+    worst = {}
+    for it in range(3):
+        mu_old, sigma_old = policy.mu.copy(), policy.sigma.copy()
+        z = (ops.philox_normal(K, D, 4242, draw_id=it).cpu().numpy().astype(np.float64) if source == "philox"
+             else zs[it].astype(np.float64))
+        samples, params = policy(K)
+        assert getattr(samples, "white", None) is not None          # the whitened route (the benchmarked one)
+        x = np.asarray(samples)
+        e = {"x": nerr(x, O.sample_gaussian(z, mu_old, sigma_old))}
+        costs = f(samples)
+        c = np.asarray(costs)
+        e["cost"] = nerr(c, f_ref(x))
+        solver.update(costs, params, policy)
+        log_w, alpha = (O.essps_log_w(c, K // 64) if solver_name == "Essps" else O.lbps_log_w(c, 0.5))
+        mu, sigma, ess, kl = O.gaussian_weighted_update(mu_old, sigma_old, log_w, x, naive=False)
+        e["alpha"] = abs(solver.trace["alpha"][-1] - alpha) / alpha
+        e["ess"] = abs(solver.trace["ess"][-1] - ess) / ess
+        e["mu"] = nerr(policy.mu, mu)
+        e["sigma"] = nerr(policy.sigma, sigma)
+        e["kl"] = abs(solver.trace["kl"][-1] - kl) / max(1.0, abs(kl))
+        ent = O.gaussian_entropy(sigma, D)
+        e["ent"] = abs(solver.trace["ent"][-1] - ent) / abs(ent)
+        record(f"c2_full[{fn_name}-{solver_name}-{source}] it{it}", **e)
+        for k, v in e.items():
+            worst[k] = max(worst.get(k, 0.0), v)
+    for k in ("x", "cost", "alpha", "ess", "mu", "sigma"):
+        assert worst[k] < TOL, (k, worst[k])
+    assert worst["kl"] < 1e-4 and worst["ent"] < 1e-4, worst
+    assert policy.n_regularized == 0
+
+
+def _fp64_moments(torch, x, nw64, chunk=1 << 16):
+    """Weighted mean and covariance about that mean in fp64, chunked over the samples (the checker)."""
+    K, D = x.shape
+    mu = torch.zeros(D, dtype=torch.float64, device=x.device)
+    for i in range(0, K, chunk):
+        mu += nw64[i:i + chunk] @ x[i:i + chunk].double()
+    cov = torch.zeros((D, D), dtype=torch.float64, device=x.device)
+    for i in range(0, K, chunk):
+        d = x[i:i + chunk].double() - mu
+        cov += (d * nw64[i:i + chunk, None]).T @ d
+    return mu, 0.5 * (cov + cov.T)
+
+
+def test_c5_update_against_fp64_checker(env, factor, record):
+    """Config C5 (K = 2^20, D = 2048, Rastrigin, Essps(K/64), Philox) through the public classes, every
+    stage against fp64 algebra on the device over ALL samples: the tensor-core sampler against
+    mu + z chol(sigma)^T, the cost kernel, the temperature root and weights, and the fitted mean /
+    covariance of BOTH moment-match routes (whitened: syrk_white_kernel on the stored base normals;
+    x-space: wmoments_diag + syrk_gemm_kernel) against (nw (x - mu'))^T (x - mu')."""
+    torch, _lib, ops = env
+    from ppi_b200 import algorithms as alg, functions as fn, policies as pol, samplers as smp
+
+    mu0, L = factor
+    dev = torch.device("cuda")
+    L64 = torch.as_tensor(L, device=dev).double()
+    sigma0 = (L64 @ L64.T).cpu().numpy()
+    policy = pol.GaussianPolicy(mu0.astype(np.float64), sigma0, smp.MonteCarlo(D5, seed=2048))
+    solver = alg.Essps(n_elites=K5 // 64)
+    solver.reset(policy)
+    ent0 = solver.trace["ent"]
+    samples, params = policy(K5)
+    x = samples.tensor
+    e = {}
+    # ---- sampler: x = mu + z chol(sigma)^T over all 2^31 elements -------------------------------------
+    chol = torch.linalg.cholesky(torch.as_tensor(sigma0, device=dev))
+    mu_t = torch.as_tensor(mu0, device=dev).double()
+    worst, scale = 0.0, 0.0
+    for i in range(0, K5, 1 << 16):
+        z = ops.philox_normal(1 << 16, D5, 2048, draw_id=0, row_offset=i).double()
+        ref = mu_t + z @ chol.T
+        worst = max(worst, float((x[i:i + (1 << 16)].double() - ref).abs().max()))
+        scale = max(scale, float(ref.abs().max()))
+        del z, ref
+    e["x"] = worst / scale
+    # ---- cost: every row ---------------------------------------------------------------------------------
+    costs = fn.Rastrigin(D5)(samples)
+    c = costs.tensor
+    c_ref = torch.empty(K5, dtype=torch.float64, device=dev)
+    for i in range(0, K5, 1 << 16):
+        xc = x[i:i + (1 << 16)].double()
+        c_ref[i:i + (1 << 16)] = 10.0 * D5 + (xc * xc - 10.0 * torch.cos(2.0 * np.pi * xc)).sum(1)
+        del xc
+    e["cost"] = float((c.double() - c_ref).abs().max() / c_ref.abs().max())
+    # ---- temperature and weights: fp64 softmax of the device costs at the device alpha; ESS root ------
+    nw, lw, st = ops.solve_temperature(c, _lib.TEMP_ESS_TARGET, K5 // 64)
+    cn = (c.double() - c.double().min()) / (c.double().max() - c.double().min())
+    lw64 = -st.alpha * cn
+    nw64 = torch.softmax(lw64, 0)
+    ess64 = 1.0 / float((nw64 * nw64).sum())
+    e["ess_root"] = abs(ess64 - K5 // 64) / (K5 // 64)
+    e["nw"] = float((nw.double() - nw64).abs().max() / nw64.max())
+    # ---- fitted moments: fp64 checker on x -------------------------------------------------------------
+    mu_ref, cov_ref = _fp64_moments(torch, x, nw64)
+    # route 2 first (x-space kernels; needs x, which route 1 does not)
+    mu_old = torch.as_tensor(mu0, device=dev)
+    s1 = ops.wmoments_diag(x, nw, shift1=mu_old)
+    mu_x = s1 + mu_old.double()
+    sig_x = ops.wmoments_dense(x, nw, shift=mu_x.float()).double()
+    sig_x = 0.5 * (sig_x + sig_x.T)
+    e["mu_xspace"] = float((mu_x - mu_ref).abs().max() / mu_ref.abs().max())
+    e["sigma_xspace"] = float((sig_x - cov_ref).abs().max() / cov_ref.abs().max())
+    del sig_x
+    # route 1: the policy's own update (whitened)
+    assert getattr(samples, "white", None) is not None
+    solver.update(costs, params, policy)
+    assert policy.n_regularized == 0
+    e["alpha"] = abs(solver.trace["alpha"][-1] - st.alpha) / st.alpha
+    mu_w = policy._mu_d().double()
+    sig_w = policy._sigma64_d()
+    e["mu_white"] = float((mu_w - mu_ref).abs().max() / mu_ref.abs().max())
+    e["sigma_white"] = float((sig_w - cov_ref).abs().max() / cov_ref.abs().max())
+    # KL(new || old) and entropy from fp64 factors of the CHECKER's moments (ppi/policies.py:146-158,213-216)
+    l_new = torch.linalg.cholesky(cov_ref)
+    ld_new, ld_old = (2.0 * torch.log(torch.diagonal(t)).sum().item() for t in (l_new, chol))
+    sol = torch.linalg.solve_triangular(chol, torch.cat([l_new, (mu_ref - mu_t)[:, None]], 1), upper=False)
+    clamp = lambda v: max(v, float(np.log(np.finfo(np.float64).tiny)))  # noqa: E731  log(max(EPS, det))
+    kl_ref = 0.5 * (clamp(ld_old) - clamp(ld_new) + float((sol * sol).sum()) - D5)
+    ent_ref = 0.5 * clamp(ld_new) + (D5 / 2) * (1 + np.log(2 * np.pi))
+    e["kl"] = abs(solver.trace["kl"][-1] - kl_ref) / max(1.0, abs(kl_ref))
+    e["ent"] = abs(solver.trace["ent"][-1] - ent_ref) / abs(ent_ref)
+    record("c5_full", **e)
+    for k in ("x", "cost", "ess_root", "nw", "mu_xspace", "sigma_xspace", "alpha", "mu_white", "sigma_white"):
+        assert e[k] < TOL, (k, e[k])
+    assert e["kl"] < 1e-4 and e["ent"] < 1e-4, e
+    assert len(ent0) >= 1
+
+
+def test_c4_feature_sampler_against_oracle_on_injected_normals(env, record):
+    """Config C4 at its own size (K = 2^16, T = 1000, F = 21, d = 2, value + derivative rows, RFF features of
+    ppi/policies.py:642-663) on INJECTED base normals: weights and limited trajectories of all samples against
+    the oracle (reference ppi/policies.py:404-421), then the ESSPS(10) update of the weights against the
+    oracle's matrix-normal update (reference :461-516)."""
+    torch, _lib, ops = env
+    K, T, F, d = 65536, 1000, 21, 2
+    rng = np.random.default_rng(44)
+    t = np.linspace(0, 2, T)
+    feat, dfeat = O.rff_features(t, np.sqrt(3e-2), 10, True)
+    mean_fn, mean = np.array([0.0, 1.5707]), 0.1 * rng.standard_normal((F, d))
+    a = rng.standard_normal((F, F + 2))
+    cin = 1e2 * (a @ a.T / F + 0.1 * np.eye(F))
+    l_in, l_out = np.linalg.cholesky(cin), np.sqrt(np.diag([1e-3, 1e-3]))
+    lo, hi = np.array([-1.5, -0.5, -60.0, -60.0]), np.array([1.5, 3.5, 60.0, 60.0])
+    z = np.asarray(rng.standard_normal((K, F, d)), np.float32)
+    y, w = ops.sample_features(K, mean_fn, mean, l_in, l_out, feat, dfeat, z=z, lower=lo, upper=hi)
+    err_y = err_w = 0.0
+    scale_y = scale_w = 0.0
+    for i in range(0, K, 8192):
+        ys, ws = O.sample_features(z[i:i + 8192].astype(np.float64), mean_fn, mean, l_in, l_out, feat, dfeat,
+                                   lower=lo, upper=hi, naive=False)
+        err_y = max(err_y, float(np.max(np.abs(y[i:i + 8192].cpu().numpy() - ys))))
+        err_w = max(err_w, float(np.max(np.abs(w[i:i + 8192].cpu().numpy() - ws))))
+        scale_y, scale_w = max(scale_y, float(np.max(np.abs(ys)))), max(scale_w, float(np.max(np.abs(ws))))
+    target = O.tracking_target(t, d)
+    cost = ops.cost_tracking(y, target)
+    yh = y.cpu().numpy().astype(np.float64)
+    c_ref = O.synthetic_return(yh, target)
+    del yh
+    e = {"y": err_y / scale_y, "w": err_w / scale_w, "cost": nerr(cost.cpu().numpy(), c_ref)}
+    c32 = cost.cpu().numpy().astype(np.float64)
+    nw, lw, st = ops.solve_temperature(cost, _lib.TEMP_ESS_TARGET, 10)
+    log_w, alpha = O.essps_log_w(c32, 10)
+    e["alpha"] = abs(st.alpha - alpha) / alpha
+    wh = w.cpu().numpy().astype(np.float64)
+    cout = np.diag([1e-3, 1e-3])
+    m_ref, cin_ref, _, ess_ref = O.m_projection_mavn(log_w, wh, cin, cout, naive=False)
+    s32 = None
+    res = ops.matnorm_update(w, nw, s32, torch.as_tensor(1.0 / np.diag(cout), dtype=torch.float32, device="cuda"),
+                             1e-12, -1)
+    e["mean"], e["cov_in"] = nerr(res[0], m_ref), nerr(res[1], cin_ref + 1e-12 * np.eye(F))
+    e["ess"] = abs(st.ess - ess_ref) / ess_ref
+    record("c4_full", **e)
+    for k, v in e.items():
+        assert v < TOL, (k, v)

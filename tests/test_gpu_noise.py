@@ -49,7 +49,7 @@ def test_smooth_noise_golden(pol, g, name, beta):
     ess, kl = policy.weighted_update(g["log_w"], params)
     assert abs(ess - float(g[tag + "_ess"])) < TOL * ess and kl == 0.0
     assert nerr(policy.mean, g[tag + "_mean"]) < TOL
-    assert nerr(policy.std, g[tag + "_std"]) < 2 * TOL
+    assert nerr(policy.std, g[tag + "_std"]) < TOL
     assert nerr(policy.map_sequence, g[tag + "_x"][np.argmax(g["log_w"])]) < TOL
 
 

@@ -252,3 +252,40 @@ def test_gaussian_policy_philox_statistics(mods):
     assert np.abs(np.cov(x.T) - sigma).max() < 0.03
     x2 = np.asarray(p(K)[0])
     assert not np.array_equal(x, x2)  # the draw counter advances
+
+
+def test_in_place_edits_of_policy_state_reach_the_device(mods):
+    """The reference re-reads its NumPy attributes on every call; the device copies are cached, so an in-place
+    edit of `policy.mean` (interior rows, zero-sum, end points untouched), of the time grid of a feature policy
+    or of `covariance_out` must be seen by the next draw / update (device.f32_cached)."""
+    alg, pol, smp, fn = mods
+    H, d, K = 12, 3, 64
+    rng = np.random.default_rng(3)
+    t = 0.05 * np.arange(H)
+    z = np.asarray(rng.standard_normal((K, H * d)), np.float32)
+    policy = pol.SquaredExponentialKernel(time_sequence=t, action_dimension=d, mean=np.zeros(d),
+                                          covariance_in=np.array([0.7]), covariance_out=np.eye(d), lengthscale=0.1,
+                                          sampler=smp.InjectedNormals)
+    smp.InjectedNormals.queue = [z.copy(), z.copy()]
+    x0 = np.asarray(policy(K)[0]).copy()
+    policy.mean[4] += 0.5              # interior rows, sum unchanged, first / middle / last rows untouched
+    policy.mean[7] -= 0.5
+    x1 = np.asarray(policy(K)[0])
+    delta = np.zeros((H, d))
+    delta[4], delta[7] = 0.5, -0.5
+    assert np.max(np.abs((x1 - x0) - delta[None])) < 1e-5
+    # feature policy: editing the interior of the time grid rebuilds Phi(t)
+    T = 40
+    tt = np.linspace(0, 1, T)
+    fp = pol.RbfFeatures(time_sequence=tt, action_dimension=d, mean=np.zeros(d), covariance_in=np.array([0.5]),
+                         covariance_out=np.eye(d), lengthscale=0.2, n_features=5, add_bias=True,
+                         use_derivatives=False, sampler=smp.InjectedNormals)
+    zf = np.asarray(rng.standard_normal((K, fp.dim_features * d)), np.float32)
+    smp.InjectedNormals.queue = [zf.copy(), zf.copy()]
+    y0, w0 = fp(K)
+    y0 = np.asarray(y0).copy()
+    tt[10:20] += 0.013                 # in place; shape, first and last entries unchanged
+    y1, w1 = fp(K)
+    w1, y1 = np.asarray(w1), np.asarray(y1)
+    assert np.max(np.abs(y1 - np.einsum("tf,bfd->btd", fp.feat(tt), w1))) < 1e-5
+    assert np.max(np.abs(y1[:, 10:20] - y0[:, 10:20])) > 1e-4 and np.array_equal(y1[:, :10], y0[:, :10])

@@ -65,7 +65,7 @@ def test_kernel_shift_sequence(mods, g, name):
     assert abs(np.linalg.cond(policy.covariance_in_prior) / float(g[f"{name}_cond"]) - 1.0) < 1e-6
     policy.weighted_update(g["log_w"], g[f"{name}_xs"])
     assert nerr(policy.mean, g[f"{name}_mean_0"]) < TOL
-    assert nerr(policy.covariance_in, g[f"{name}_cov_0"]) < 2 * TOL
+    assert nerr(policy.covariance_in, g[f"{name}_cov_0"]) < TOL
     # (the reference's trace over a (b, d, d) stack returns one value per actuator column, :729)
     assert nerr(policy.loglikelihood(g[f"{name}_xs"]), g[f"{name}_llh"]) < 1e-4
     # the whole control sequence, errors of the fp32 update included
@@ -140,7 +140,7 @@ def test_white_kernel_shift(mods, g):
     for i, t, _ in windows(g):
         policy.update_timesteps(t)
         assert nerr(policy.mean, g[f"white_mean_{i}"]) < TOL
-        assert nerr(policy.covariance_in, g[f"white_cov_{i}"]) < 2 * TOL
+        assert nerr(policy.covariance_in, g[f"white_cov_{i}"]) < TOL
 
 
 def test_iid_shift(mods, g):
@@ -150,7 +150,7 @@ def test_iid_shift(mods, g):
                                covariance_in=np.array([1.0]), covariance_out=g["cout"], sampler=None,
                                limiter=pol.Limiter(lower=g["lower"], upper=g["upper"]))
     policy.weighted_update(g["log_w"], g["iid_xs"])
-    assert nerr(policy.mean, g["iid_mean_0"]) < TOL and nerr(policy.std, g["iid_std_0"]) < 2 * TOL
+    assert nerr(policy.mean, g["iid_mean_0"]) < TOL and nerr(policy.std, g["iid_std_0"]) < TOL
     t_old = g["t0"]
     for i, t, anneal in windows(g):
         ref = O.iid_shift(t_old, t, g[f"iid_mean_{i - 1}"], g[f"iid_std_{i - 1}"],
@@ -158,7 +158,7 @@ def test_iid_shift(mods, g):
         assert nerr(ref[0], g[f"iid_mean_{i}"]) < 1e-14 and nerr(ref[1], g[f"iid_std_{i}"]) < 1e-14
         policy.update_timesteps(t, anneal)
         assert nerr(policy.mean, g[f"iid_mean_{i}"]) < TOL
-        assert nerr(policy.std, g[f"iid_std_{i}"]) < 2 * TOL
+        assert nerr(policy.std, g[f"iid_std_{i}"]) < TOL
         t_old = t
 
 
@@ -171,8 +171,8 @@ def test_features_anneal(mods, g):
                              limiter=pol.Limiter(lower=g["lower"], upper=g["upper"]))
     policy.weighted_update(g["log_w"], g["feat_ws"])
     policy.update_timesteps(float(g["dt"]) * np.arange(1, g["t0"].shape[0] + 1), 0.6)
-    assert nerr(policy.covariance_in, g["feat_cov_1"]) < 2 * TOL
-    assert nerr(policy.covariance_in_sqrt, g["feat_chol_1"]) < 2 * TOL
+    assert nerr(policy.covariance_in, g["feat_cov_1"]) < TOL
+    assert nerr(policy.covariance_in_sqrt, g["feat_chol_1"]) < TOL
 
 
 # ---------------------------------------------------------------------------------------------
@@ -199,8 +199,8 @@ def test_m_projection_mavn_iterated(mods, gm, iters, upd):
                                                  iterations=iters, update_out=upd)
     tag = f"mavn_{iters}_{int(upd)}"
     assert nerr(mean, gm[tag + "_mean"]) < TOL
-    assert nerr(cin, gm[tag + "_cin"]) < 2 * TOL
-    assert nerr(cout, gm[tag + "_cout"]) < 2 * TOL
+    assert nerr(cin, gm[tag + "_cin"]) < TOL
+    assert nerr(cout, gm[tag + "_cout"]) < TOL
     assert abs(ess - float(gm[tag + "_ess"])) < TOL * ess
 
 

