@@ -131,16 +131,31 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle port of the reference
 # ------------------------------------------------------------------------------------------------
-def set_blas_threads(n):
+def host_threads():
+    """Cores this process may run on (the cgroup / affinity mask, not the host's core count), at most 32."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    return max(1, min(32, n))
+
+
+def set_blas_threads(n=None):
     """Pin the BLAS / OpenMP pools explicitly (torchrun exports OMP_NUM_THREADS=1 to its workers, which
     silently changed the O(D^3) LAPACK share of the CPU arm between N = 1 and N > 1 in round 1)."""
+    n = host_threads() if n is None else int(n)
     try:
         from threadpoolctl import threadpool_limits
 
-        threadpool_limits(limits=int(n))
-        return int(n)
+        threadpool_limits(limits=n)
+        return n
     except Exception:
         return None
+
+
+def log(msg):
+    sys.stderr.write(f"[bench {time.strftime('%H:%M:%S')}] {msg}\n")
+    sys.stderr.flush()
 
 
 def cpu_step(wl, K, rng, naive=True):
@@ -206,20 +221,32 @@ def cpu_fit(wl, sizes, rng, naive=True, repeats=1):
 
 
 def cpu_sizes(wl, budget_s):
-    """Three sample sizes (k, 2k, 4k) whose naive updates together take about budget_s seconds."""
+    """Three sample sizes (k, 2k, 4k) whose naive updates together take about budget_s seconds.  The per-row
+    cost is timed on the K-proportional part alone (the moment-matching / sampling einsums); the
+    K-independent part (O(D^3) factorisations, ~1 s at D = 2048 and noisy) is what is left of a whole step."""
+    from oracle import ppi_oracle as O
+
     rng = np.random.default_rng(0)
     cpu_step(wl, 8, rng)  # warm caches / lazy imports
-    k = 32
+    k = 16
+    t0 = time.perf_counter()
+    if wl["kind"] == "gaussian":
+        O.m_projection(np.zeros(k), rng.standard_normal((k, wl["D"])))
+    elif wl["kind"] == "kernel":
+        x = rng.standard_normal((k, wl["H"], wl["d"]))
+        O.sample_matnorm(x, np.zeros(wl["d"]), np.zeros((wl["H"], wl["d"])), np.eye(wl["H"]), np.eye(wl["d"]))
+        O.m_projection_mavn(np.zeros(k), x, np.eye(wl["H"]), np.eye(wl["d"]))
+    else:
+        cpu_step(wl, k, rng)      # every part of the feature workload scales with K
+    per_row = max((time.perf_counter() - t0) / k, 1e-6)
     t0 = time.perf_counter()
     cpu_step(wl, k, rng)
-    t32 = time.perf_counter() - t0
-    t0 = time.perf_counter()
-    cpu_step(wl, 2 * k, rng)
-    t64 = time.perf_counter() - t0
-    per_row = max((t64 - t32) / k, 1e-7)
-    fixed = max(t32 - k * per_row, 0.0)
+    fixed = max(time.perf_counter() - t0 - k * per_row, 0.0)
     base = (budget_s - 3 * fixed) / (7 * per_row)          # k + 2k + 4k rows
     base = int(max(16, min(wl["K"] // 4, 1 << int(np.floor(np.log2(max(base, 16)))))))
+    # hard bound: never more than budget_s of per-row work, whatever the timings above said
+    while base > 16 and 7 * base * per_row > 1.5 * budget_s:
+        base //= 2
     return [base, 2 * base, 4 * base]
 
 
@@ -236,7 +263,7 @@ def run_reference(args, wl):
         return
     world = max(1, args.gpus)
     K_total = wl["K"] * (world if args.scaling == "weak" else 1)
-    threads = set_blas_threads(os.cpu_count() or 1)
+    threads = set_blas_threads()
     # every step = one bounded update at one of three sample sizes (k, 2k, 4k, cycling); the value is the
     # samples/s of the full-K update predicted by the linear fit t(K) = fixed + per_row K
     sizes = cpu_sizes(wl, max(6.0, 150.0 / max(1, args.steps + args.warmup) * 3))
@@ -407,6 +434,45 @@ def measure(hx, wl, K_total, steps, warmup, clock=None):
                 nominal_path=int(getattr(policy, "n_regularized", 0)) == 0)
 
 
+def measure_fresh(hx, wl, K_total, budget_s, chunk, clock):
+    """Side workloads: `chunk` timed steps at a time on a FRESH policy (hundreds of consecutive updates would
+    collapse the search distribution and time the revert branch), repeated until budget_s of device time
+    have been sampled.  -> same dict as measure()."""
+    from ppi_b200 import _lib, device
+
+    lib = _lib.load()
+    first = clock.mark() if clock is not None else 0
+    total_ms, steps, launches, nominal = 0.0, 0, 0, True
+    prof_acc, scope_acc = {}, {}
+    t_wall = time.perf_counter()
+    while total_ms < budget_s * 1e3 and steps < 20000 and time.perf_counter() - t_wall < 20.0 * budget_s + 10.0:
+        policy, solver, cost = build_workload(wl, K_total)
+        step = lambda: one_step(policy, solver, cost, K_total)  # noqa: E731
+        step()
+        launches0 = lib.ppi_launch_count()
+        lib.ppi_profile_enable(1)
+        device.profile_scopes(True)
+        total_ms += hx.timed(step, chunk)
+        for acc, src in ((prof_acc, _lib.profile_read()), (scope_acc, device.profile_scopes_read())):
+            for k, (n, t) in src.items():
+                a = acc.setdefault(k, [0, 0.0])
+                a[0] += n
+                a[1] += t
+        lib.ppi_profile_enable(0)
+        device.profile_scopes(False)
+        launches += lib.ppi_launch_count() - launches0
+        steps += chunk
+        nominal = nominal and int(getattr(policy, "n_regularized", 0)) == 0
+    clocks = clock.summary(first) if clock is not None else None
+    prof = {k: (n, t) for k, (n, t) in prof_acc.items()}
+    kernels = {k: {"launch_scopes": n, "ms_per_step": t / steps} for k, (n, t) in prof.items()}
+    kernels.update({k: {"launch_scopes": n, "ms_per_step": t / steps, "host_scope": True}
+                    for k, (n, t) in scope_acc.items()})
+    ms_per_step = total_ms / steps
+    return dict(ms_per_step=ms_per_step, value=K_total / (ms_per_step * 1e-3), launches=int(launches), prof=prof,
+                kernels=kernels, clocks=clocks, steps=steps, nominal_path=nominal)
+
+
 def small_roofline(wl, K_local, prof, steps, ms_per_step, pk):
     """Small-matrix workloads: every kernel but the (latency-bound) temperature solve streams the sample
     tensor once; report the scope that takes the largest share of the step against the HBM roofline with
@@ -459,7 +525,9 @@ def run_b200(args, wl):
     clock = ClockSampler(hx.local).start() if rank == 0 else None
 
     # ---- resident leg ----------------------------------------------------------------------------
+    log(f"resident leg: {wl['desc']}, K_total = {K_total}, world = {world}")
     res = measure(hx, wl, K_total, args.steps, args.warmup, clock)
+    log(f"resident leg done: {res['ms_per_step']:.3f} ms/step")
     ms_per_step, value, prof = res["ms_per_step"], res["value"], res["prof"]
 
     # ---- end-to-end leg: host buffers in, host results out, every step ------------------------------
@@ -494,6 +562,7 @@ def run_b200(args, wl):
     for _ in range(2):
         e2e_step()
     e2e_ms = hx.timed(e2e_step, args.steps) / args.steps
+    log(f"e2e leg done: {e2e_ms:.3f} ms/step")
     e2e_value = K_total / (e2e_ms * 1e-3)
 
     if rank != 0:
@@ -542,17 +611,15 @@ def run_b200(args, wl):
             if K:
                 w2["K"] = K
             try:
-                probe = measure(hx, w2, w2["K"], 3, 3)
-                probe.pop("policy")
-                n_steps = int(min(4000, max(5, 0.7 / (probe["ms_per_step"] * 1e-3))))   # >= 0.7 s: >= 20 clock samples
-                r2 = measure(hx, w2, w2["K"], n_steps, 3, clock)
-                r2.pop("policy")
-                rl = (small_roofline(w2, w2["K"], r2["prof"], n_steps, r2["ms_per_step"], pk)
+                log(f"extra {name}")
+                r2 = measure_fresh(hx, w2, w2["K"], 0.7, 4, clock)       # >= 0.7 s of device time: >= 20 clock samples
+                rl = (small_roofline(w2, w2["K"], r2["prof"], r2["steps"], r2["ms_per_step"], pk)
                       if w2["kind"] != "gaussian" else None)
-                extra[name] = {"workload": w2["desc"] + (f" [K = {K}]" if K else ""), "steps": n_steps,
+                extra[name] = {"workload": w2["desc"] + (f" [K = {K}]" if K else ""), "steps": r2["steps"],
                                "ms_per_step": r2["ms_per_step"], "value": r2["value"], "unit": "samples/s",
                                "kernels_ms_per_step": {k: round(v["ms_per_step"], 5) for k, v in r2["kernels"].items()},
-                               "roofline": rl, "clocks": r2["clocks"], "gpu_launches": r2["launches"]}
+                               "roofline": rl, "clocks": r2["clocks"], "gpu_launches": r2["launches"],
+                               "nominal_path": r2["nominal_path"]}
             except Exception as e:  # a side workload must never cost the headline line
                 extra[name] = {"error": repr(e)[:300]}
             torch.cuda.empty_cache()
@@ -563,8 +630,10 @@ def run_b200(args, wl):
     # ---- CPU baseline on a bounded sample ----------------------------------------------------------------
     cpu = None
     if world == 1 and not args.no_cpu:
-        threads = set_blas_threads(os.cpu_count() or 1)
+        threads = set_blas_threads()
+        log(f"cpu baseline: {threads} BLAS threads")
         sizes = cpu_sizes(wl, 14.0)
+        log(f"cpu baseline sizes {sizes}")
         fit = cpu_fit(wl, sizes, np.random.default_rng(0))
         cpu = {"value": fit["value_at_full_K"], "unit": "samples/s", "cores": 1, "kind": "port",
                "host_cores": os.cpu_count(), "blas_threads": threads, "fit": fit,
@@ -574,8 +643,9 @@ def run_b200(args, wl):
         if wl["kind"] == "gaussian":
             # the same math with BLAS contractions on every host core ("optimised CPU")
             rng = np.random.default_rng(0)
+            log("cpu baseline: BLAS restatement")
             cpu_step(wl, 512, rng, naive=False)
-            fb = cpu_fit(wl, [4096, 8192], rng, naive=False)
+            fb = cpu_fit(wl, [2048, 4096], rng, naive=False)
             cpu["blas"] = {"value": fb["value_at_full_K"], "unit": "samples/s", "cores": threads, "fit": fb,
                            "sample": "BLAS restatement of the einsums on every host core, linear fit in K"}
 

@@ -182,6 +182,18 @@ int ppi_sample_gaussian_keep(const float* z, uint64_t seed, uint64_t draw_id, ui
                              void* zstore, size_t zstore_bytes, void* workspace,
                              size_t workspace_bytes, void* stream);
 
+/* a7 + a9 fused: ppi_sample_gaussian_keep with a separable test function (PPI_FN_RASTRIGIN / PPI_FN_STYBLINSKI,
+ * optimization/functions.py:65-66,78-83) evaluated in the sampling epilogue -- the step `costs = f(actions)`
+ * of ppi/algorithms.py:85-86 without a second pass over the K x D samples.  cost (K) fp32.  x may be NULL: the
+ * samples are then never written (the whitened update reads the base-normal store; x is re-drawn from the same
+ * (seed, draw_id, row_offset) with ppi_sample_gaussian when a caller asks for it).
+ * workspace: ppi_sample_gaussian_cost_workspace_bytes(K, D). */
+size_t ppi_sample_gaussian_cost_workspace_bytes(int64_t K, int64_t D);
+int ppi_sample_gaussian_cost(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset, int64_t K,
+                             int64_t D, const float* mu, const float* L, float* x, void* zstore,
+                             size_t zstore_bytes, int fn, float* cost, void* workspace, size_t workspace_bytes,
+                             void* stream);
+
 /* Base normals of a Philox draw generated ahead of the sampling call (they depend on (seed, draw_id,
  * global row) only): zrows = sample-major exact-fp16 operand rows, round_up(K, 256) x round_up(D, 64),
  * zstore = the K-major store of ppi_sample_gaussian_keep; both 1 KB aligned, sizes from
@@ -303,12 +315,15 @@ int ppi_wmoments_dense(const float* x, const float* nw, int64_t K, int64_t D, co
  * so the K-long contraction runs on the stored base normals: operand A = nw z (fp16 pair), operand
  * B = z -- one exact fp16 for Philox normals, i.e. two partial products instead of three and no
  * pass over x.  s1 (D, fp64, zeroed by the caller) += m;  cov (D,D) receives S symmetrised (+= when
- * accumulate != 0).  K-sharded ranks all-reduce both.  `injected` must match the store.
+ * accumulate != 0).  s2 (D, fp64, zeroed by the caller; may be NULL) += diag(S) = sum_k nw_k z_k^2 with
+ * round-to-nearest products and fp64 sums: tcgen05's fp32 accumulation truncates, which biases sums of positive
+ * terms by ~2e-6, and tr C enters the KL as (tr C - D); ppi_white_finish takes the diagonal of C from s2.
+ * K-sharded ranks all-reduce all three.  `injected` must match the store.
  * The caller finishes with D x D algebra: chol(new sigma) = L chol(S - m m^T),
  * KL(new || old) = (tr(C) + |m|^2 - D - log det C) / 2 with C = S - m m^T.                   */
 size_t ppi_wmoments_white_workspace_bytes(int64_t K, int64_t D, int injected);
 int ppi_wmoments_white(const void* zstore, int injected, const float* nw, int64_t K, int64_t D,
-                       double* s1, float* cov, int accumulate, void* workspace,
+                       double* s1, double* s2, float* cov, int accumulate, void* workspace,
                        size_t workspace_bytes, void* stream);
 
 /* a17 tail: sigma = cov - delta delta^T (delta = new mean - shift), optional factorized() and
@@ -321,6 +336,35 @@ int ppi_finalize_gaussian(const double* s1, const float* cov_in, int64_t D, cons
 int ppi_finalize_matnorm(const double* s1, const double* acc, int H, int d, double jitter,
                          double* mean64, float* mean32, double* cov64, float* cov32,
                          double* chol64, float* chol32, int* status, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * f3  dense D x D fp64 tail of the Gaussian moment match, any D (blocked, fp64 tensor cores)
+ *     np.linalg.cholesky + PD check                  ppi/policies.py:259-268; ppi/samplers.py:38-39
+ *     log det / trace terms of KL and entropy        ppi/policies.py:146-158,213-216
+ * scalars (4 doubles, device): [0] status (0 = positive definite, else 1 + index of the first failing
+ * pivot -- np.linalg.LinAlgError), [1] log det of the factored matrix, [2] tr C, [3] |m|^2 (white finish).
+ * workspace: ppi_dense_workspace_bytes(D) (three padded D x D fp64 matrices).
+ *
+ * ppi_cholesky_blocked: chol64 / chol32 (D, D) = lower Cholesky factor of the symmetric a (D, D) fp64 (lower
+ *   triangle read), zero above the diagonal; either output may be NULL.
+ * ppi_white_finish: the whole tail of the whitened update (ppi_wmoments_white) in one call:
+ *   C = S - m m^T (its diagonal from `diag` = s2 of ppi_wmoments_white when non-NULL),  G = chol(C),
+ *   l_new = l_old G (fp64 + fp32 copy for the sampler),  mu_new = mu_old + l_old m,
+ *   log det C, tr C, |m|^2  ->  KL(new || old) = (tr C + |m|^2 - D - log det C) / 2 on the host.
+ *   Tiles above the block diagonal of l_new64 / l_new32 are not written: pass zeroed buffers.
+ *   On a failed factorisation l_new / mu_new are left untouched (the caller takes the reference's
+ *   regularisation branch).
+ * ppi_tri_gram: out = l l^T for a lower-triangular l (sigma from its factor; triangular tile skipping).
+ * ---------------------------------------------------------------------------------------- */
+size_t ppi_dense_workspace_bytes(int64_t D);
+int ppi_cholesky_blocked(const double* a, int64_t D, double* chol64, float* chol32, double* scalars,
+                         void* workspace, size_t workspace_bytes, void* stream);
+int ppi_white_finish(const float* S, const double* m, const double* diag, const double* l_old, const float* mu_old,
+                     int64_t D, double* l_new64, float* l_new32, float* mu_new32, double* scalars, void* workspace,
+                     size_t workspace_bytes, void* stream);
+int ppi_tri_gram(const double* l, int64_t D, double* out64, float* out32, void* stream);
+/* y32 = x0 + l v for a lower-triangular fp64 l (D, D); x0 may be NULL (the mean step mu + L m alone) */
+int ppi_tri_matvec(const double* l, int64_t D, const double* v, const float* x0, float* y32, void* stream);
 
 /* a18-a20 fused for one rank: ppi_wmoments_diag -> centre -> ppi_wmoments_matnorm -> ppi_finalize_matnorm
  * back to back, the result packed for a single device->host read (ppi/policies.py:96-143,804-848,461-516):
@@ -349,7 +393,7 @@ int ppi_matnorm_update(const float* x, const float* nw, int64_t K, int H, int d,
 enum { PPI_PROF_SYRK_GEMM = 0, PPI_PROF_SAMPLE_GEMM = 1, PPI_PROF_SYRK_OPERAND = 2,
        PPI_PROF_SAMPLE_OPERAND = 3, PPI_PROF_WMOMENTS_DIAG = 4, PPI_PROF_COST = 5,
        PPI_PROF_SOLVE = 6, PPI_PROF_SYRK_REDUCE = 7, PPI_PROF_SAMPLE_SMALL = 8,
-       PPI_PROF_WMOMENTS_MATNORM = 9, PPI_PROF_NUM_SLOTS = 10 };
+       PPI_PROF_WMOMENTS_MATNORM = 9, PPI_PROF_DENSE_TAIL = 10, PPI_PROF_NUM_SLOTS = 11 };
 int64_t ppi_launch_count(void);
 int ppi_profile_enable(int on);
 int ppi_profile_read(int slot, int64_t* count, double* total_ms);

@@ -14,7 +14,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "ppi_b200", "libppi_b200.so")
-SOURCES = ["capi.cu", "sample.cu", "cost.cu", "weights.cu", "moments.cu", "tc_gemm.cu", "mma_small.cu"]
+SOURCES = ["capi.cu", "sample.cu", "cost.cu", "weights.cu", "moments.cu", "tc_gemm.cu", "mma_small.cu", "dense64.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -454,7 +454,41 @@ struct SampleParams {
   const float* mu;
   const GemmScalars* scalars;  // inv_scale (FP16) or NULL
   int z_exact;          // TF32X3 only: z is exactly tf32 (Philox), its low-order operand is skipped
+  // fused separable cost (optimization/functions.py:65-66,78-83): per-(sample, j-tile) partial sums of the
+  // cost terms of the 128 columns of the tile, written to cost_part[(row0 + s) * tiles_j + tj]; x may then be
+  // NULL (nobody reads the samples: the whitened update contracts the stored base normals)
+  float* cost_part;
+  int cost_fn;          // PPI_FN_STYBLINSKI / PPI_FN_RASTRIGIN
+  int64_t row0;         // first sample row of this pass inside cost_part
 };
+
+// term of a separable test function at one coordinate (cost.cu has the same expressions)
+__device__ __forceinline__ float fused_cost_term(int fn, float x) {
+  if (fn == PPI_FN_STYBLINSKI) {
+    const float x2 = x * x;
+    return fmaf(x2, x2, fmaf(-16.f, x2, 5.f * x));
+  }
+  const float fr = x - rintf(x);   // Rastrigin: exact range reduction, one MUFU.COS
+  return fmaf(x, x, -10.f * __cosf(6.283185307179586f * fr));
+}
+
+// Transpose-reduce across the warp: every lane holds t[0..127] (one value per sample, its own column); on
+// return lane l holds in t[0..3] the sums over the 32 lanes for samples 4 l .. 4 l + 3.  124 shuffles.
+__device__ __forceinline__ void warp_transpose_reduce128(float (&t)[128]) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int w = 64, off = 16; w >= 4; w >>= 1, off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < 64; ++i) {
+      if (i < w) {
+        const float send = up ? t[i] : t[i + w];
+        const float keep = up ? t[i + w] : t[i];
+        t[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+      }
+    }
+  }
+}
 
 template <bool FP16, bool ZPAIR>
 __global__ void __launch_bounds__(kGemmThreads, 1)
@@ -469,6 +503,7 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
   static_assert(kStages * kStageBytes == kPipeBytes, "pipeline must fill the smem budget");
 
   extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(16) float cost_red[2][2][4][128];   // [tile parity][sample half][lane quarter][sample]
   GemmSmem gs;
   const uint32_t tmem_base = gemm_prologue(smem_raw, gs);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -557,7 +592,7 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
     const int q = warp & 3;   // TMEM lane quarter
     const int h = e >> 2;     // sample (column) half
     const float inv_scale = p.scalars ? p.scalars->inv_scale : 1.0f;
-    uint32_t ccount = 0;
+    uint32_t ccount = 0, tile_count = 0;
     for (int64_t u = blockIdx.x; u < p.n_units; u += gridDim.x) {
       const int nb = (int)(u / p.units_per_block), pr = (int)(u % p.units_per_block);
       for (int tt = 0; tt < tiles_in_unit(pr); ++tt) {
@@ -579,17 +614,46 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
         }
         const int64_t s_first = (int64_t)nb * BN + h * 128;
         const int64_t left = p.rows - s_first;
-        if (jok && left > 0) {
-          float* dst = p.x + s_first * p.D + j;
-          if (left >= 128) {
+        if (left > 0) {                      // uniform over the four quarter warps of this sample half
 #pragma unroll
-            for (int c = 0; c < 128; ++c) dst[(int64_t)c * p.D] = fmaf(acc[c], inv_scale, bias);
-          } else {
+          for (int c = 0; c < 128; ++c) acc[c] = fmaf(acc[c], inv_scale, bias);
+          if (jok && p.x != nullptr) {
+            float* dst = p.x + s_first * p.D + j;
+            if (left >= 128) {
 #pragma unroll
-            for (int c = 0; c < 128; ++c)
-              if (c < left) dst[(int64_t)c * p.D] = fmaf(acc[c], inv_scale, bias);
+              for (int c = 0; c < 128; ++c) dst[(int64_t)c * p.D] = acc[c];
+            } else {
+#pragma unroll
+              for (int c = 0; c < 128; ++c)
+                if (c < left) dst[(int64_t)c * p.D] = acc[c];
+            }
+          }
+          if (p.cost_part != nullptr) {
+            // cost terms of this thread's column for its 128 samples -> sums over the tile's 128 columns:
+            // across the 32 lanes by the transpose-reduce, across the four quarter warps through shared memory
+            // (double-buffered by tile parity: one named barrier per tile), in a FIXED order (deterministic)
+#pragma unroll
+            for (int c = 0; c < 128; ++c) acc[c] = jok ? fused_cost_term(p.cost_fn, acc[c]) : 0.f;
+            warp_transpose_reduce128(acc);
+            float* slot = &cost_red[tile_count & 1][h][q][4 * lane];
+            *reinterpret_cast<float4*>(slot) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            asm volatile("bar.sync %0, %1;" ::"r"(1 + h), "r"(128) : "memory");
+            if (q == 0) {
+              float4 r = *reinterpret_cast<const float4*>(&cost_red[tile_count & 1][h][0][4 * lane]);
+#pragma unroll
+              for (int qq = 1; qq < 4; ++qq) {
+                const float4 o = *reinterpret_cast<const float4*>(&cost_red[tile_count & 1][h][qq][4 * lane]);
+                r.x += o.x; r.y += o.y; r.z += o.z; r.w += o.w;
+              }
+              const float rv[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+              for (int u = 0; u < 4; ++u)
+                if (4 * lane + u < left)
+                  p.cost_part[(p.row0 + s_first + 4 * lane + u) * p.tiles_j + tj] = rv[u];
+            }
           }
         }
+        ++tile_count;
       }
     }
   }
@@ -1388,14 +1452,14 @@ __global__ void __launch_bounds__(256)
 white_operand_kernel(const uint16_t* __restrict__ zrows, const float* __restrict__ nw,
                      int64_t rows_valid, int64_t Dk, int64_t Kc, int64_t Dp, int tiles,
                      const GemmScalars* __restrict__ scalars, void* __restrict__ op_a,
-                     void* __restrict__ op_b, double* __restrict__ s1, int64_t D) {
+                     void* __restrict__ op_b, double* __restrict__ s1, double* __restrict__ s2, int64_t D) {
   __shared__ float tile[32][129];
   __shared__ float wsc[32];
   const float sa = scalars->scale_a;
   const float unz = 1.f / scalars->scale_b;         // undoes the scale of stored injected normals (1 for Philox)
   const int64_t it = (int64_t)blockIdx.y * 128;     // column offset
   const int64_t row_halfs = ZPAIR ? 2 * Dk : Dk;
-  double colsum = 0.0;
+  double colsum = 0.0, colsq = 0.0;
   for (int tl = 0; tl < tiles; ++tl) {
     const int64_t kt = ((int64_t)blockIdx.x * tiles + tl) * 32;  // local sample offset in the pass
     if (kt >= Kc) break;
@@ -1430,10 +1494,15 @@ white_operand_kernel(const uint16_t* __restrict__ zrows, const float* __restrict
     }
     __syncthreads();
     if (threadIdx.x < 128) {
-      float cs = 0.f;
+      float cs = 0.f, cq = 0.f;
 #pragma unroll 8
-      for (int r = 0; r < 32; ++r) cs = fmaf(wsc[r], tile[r][threadIdx.x], cs);
+      for (int r = 0; r < 32; ++r) {
+        const float t = tile[r][threadIdx.x], wt = wsc[r] * t;
+        cs += wt;
+        cq = fmaf(wt, t, cq);
+      }
       colsum += (double)cs;
+      colsq += (double)cq;
     }
     for (int e = threadIdx.x; e < 128 * 8; e += 256) {
       const int il = e / 8, k4 = (e % 8) * 4;
@@ -1452,6 +1521,9 @@ white_operand_kernel(const uint16_t* __restrict__ zrows, const float* __restrict
   }
   if (s1 && threadIdx.x < 128 && it + threadIdx.x < D)
     atomicAdd(s1 + it + threadIdx.x, colsum * (double)(1.f / sa));
+  // diagonal of S (see white_mean_kernel): the tile holds the STORED normals, z = tile / scale_b
+  if (s2 && threadIdx.x < 128 && it + threadIdx.x < D)
+    atomicAdd(s2 + it + threadIdx.x, colsq * (double)(1.f / sa) * (double)unz);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1484,14 +1556,18 @@ white_weights_kernel(const float* __restrict__ nw, int64_t K, int64_t kt, const 
 constexpr int kMeanRows = 8, kMeanChunk = 16384;
 __global__ void __launch_bounds__(256)
 white_mean_kernel(const uint16_t* __restrict__ zt, int64_t zt_rows, const float* __restrict__ nw, int64_t K,
-                  int64_t D, double* __restrict__ s1) {
+                  int64_t D, double* __restrict__ s1, double* __restrict__ s2) {
+  // s2[i] += sum_k nw_k zT[i][k]^2: the DIAGONAL of S with round-to-nearest fp32 products and fp64 sums.  The
+  // tensor-core accumulation truncates (a bias of ~2e-6 on sums of positive terms), and tr C = sum of D such
+  // entries enters the KL as (tr C - D): the finish takes the diagonal from here (same pass over the store).
   __shared__ double red[kMeanRows][8];
+  __shared__ double red2[kMeanRows][8];
   const int64_t i0 = (int64_t)blockIdx.x * kMeanRows;
   const int64_t kc0 = (int64_t)blockIdx.y * kMeanChunk;
   const bool w_vec = (reinterpret_cast<uintptr_t>(nw) & 15) == 0;
-  float acc[kMeanRows];
+  float acc[kMeanRows], acc2[kMeanRows];
 #pragma unroll
-  for (int r = 0; r < kMeanRows; ++r) acc[r] = 0.f;
+  for (int r = 0; r < kMeanRows; ++r) acc[r] = acc2[r] = 0.f;
   for (int it = 0; it < kMeanChunk / (256 * 8); ++it) {
     const int64_t k = kc0 + ((int64_t)it * 256 + threadIdx.x) * 8;
     if (k >= K) break;
@@ -1515,8 +1591,11 @@ white_mean_kernel(const uint16_t* __restrict__ zt, int64_t zt_rows, const float*
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const float2 zf = __half22float2(*reinterpret_cast<const __half2*>(&zw[u]));
-        acc[r] = fmaf(zf.x, w[2 * u], acc[r]);
-        acc[r] = fmaf(zf.y, w[2 * u + 1], acc[r]);
+        const float wx = zf.x * w[2 * u], wy = zf.y * w[2 * u + 1];
+        acc[r] += wx;
+        acc[r] += wy;
+        acc2[r] = fmaf(wx, zf.x, acc2[r]);
+        acc2[r] = fmaf(wy, zf.y, acc2[r]);
       }
     }
   }
@@ -1524,14 +1603,16 @@ white_mean_kernel(const uint16_t* __restrict__ zt, int64_t zt_rows, const float*
 #pragma unroll
   for (int r = 0; r < kMeanRows; ++r) {
     const double v = warp_sum((double)acc[r]);
-    if (lane == 0) red[r][wp] = v;
+    const double v2 = warp_sum((double)acc2[r]);
+    if (lane == 0) { red[r][wp] = v; red2[r][wp] = v2; }
   }
   __syncthreads();
   if (threadIdx.x < kMeanRows && i0 + threadIdx.x < D) {
-    double v = 0.0;
+    double v = 0.0, v2 = 0.0;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) v += red[threadIdx.x][q];
+    for (int q = 0; q < 8; ++q) { v += red[threadIdx.x][q]; v2 += red2[threadIdx.x][q]; }
     atomicAdd(s1 + i0 + threadIdx.x, v);
+    if (s2) atomicAdd(s2 + i0 + threadIdx.x, v2);
   }
 }
 
@@ -1769,7 +1850,7 @@ extern "C" size_t ppi_wmoments_white_workspace_bytes(int64_t K, int64_t D, int i
 }
 
 template <bool ZPAIR>
-static int wmoments_white_impl(const void* zstore, const float* nw, int64_t K, int64_t D, double* s1,
+static int wmoments_white_impl(const void* zstore, const float* nw, int64_t K, int64_t D, double* s1, double* s2,
                                float* cov, int accumulate, void* workspace, cudaStream_t st) {
   constexpr int MODE = ZPAIR ? SYRK_PAIR : SYRK_PAIR_SINGLE;
   const SyrkPlan pl = syrk_plan(K, D);
@@ -1821,7 +1902,7 @@ static int wmoments_white_impl(const void* zstore, const float* nw, int64_t K, i
       dim3 og((unsigned)ceil_div(pl.Kc / 32, kTilesPerBlock), (unsigned)ceil_div(pl.Dp, 128));
       white_operand_kernel<ZPAIR><<<og, 256, 0, st>>>(
           (const uint16_t*)(store_rows + (size_t)k0 * store_row_bytes), nw + k0, rows, Dk, pl.Kc, pl.Dp,
-          kTilesPerBlock, scalars, op_a, op_b, s1, D);
+          kTilesPerBlock, scalars, op_a, op_b, s1, s2, D);
       if (int rc = check_launch("white_operand_kernel")) return rc;
     }
     p.accumulate = pass > 0;
@@ -1840,7 +1921,7 @@ static int wmoments_white_impl(const void* zstore, const float* nw, int64_t K, i
 }
 
 // Philox store (K-major): one launch over all K samples, no operand pre-pass.
-static int wmoments_white_direct(const void* zstore, const float* nw, int64_t K, int64_t D, double* s1,
+static int wmoments_white_direct(const void* zstore, const float* nw, int64_t K, int64_t D, double* s1, double* s2,
                                  float* cov, int accumulate, void* workspace, cudaStream_t st) {
   const SyrkPlan pl = syrk_plan(K, D);
   const int64_t kt = zstore_kt(K);
@@ -1861,7 +1942,7 @@ static int wmoments_white_direct(const void* zstore, const float* nw, int64_t K,
   if (s1) {
     ProfileScope prof(PPI_PROF_WMOMENTS_DIAG, st);
     dim3 mg((unsigned)ceil_div(D, kMeanRows), (unsigned)ceil_div(K, kMeanChunk));
-    white_mean_kernel<<<mg, 256, 0, st>>>(zt, pl.Dp, nw, K, D, s1);
+    white_mean_kernel<<<mg, 256, 0, st>>>(zt, pl.Dp, nw, K, D, s1, s2);
     if (int rc = check_launch("white_mean_kernel")) return rc;
   }
   CUtensorMap a, b;
@@ -1900,15 +1981,15 @@ static int wmoments_white_direct(const void* zstore, const float* nw, int64_t K,
 }
 
 extern "C" int ppi_wmoments_white(const void* zstore, int injected, const float* nw, int64_t K,
-                                  int64_t D, double* s1, float* cov, int accumulate, void* workspace,
+                                  int64_t D, double* s1, double* s2, float* cov, int accumulate, void* workspace,
                                   size_t workspace_bytes, void* stream) {
   PPI_REQUIRE(zstore && nw && cov && K > 0 && D > 128 && workspace, PPI_ERR_INVALID,
               "ppi_wmoments_white: bad arguments");
   PPI_REQUIRE(workspace_bytes >= ppi_wmoments_white_workspace_bytes(K, D, injected), PPI_ERR_WORKSPACE,
               "ppi_wmoments_white: workspace too small");
   if (injected)
-    return wmoments_white_impl<true>(zstore, nw, K, D, s1, cov, accumulate, workspace, (cudaStream_t)stream);
-  return wmoments_white_direct(zstore, nw, K, D, s1, cov, accumulate, workspace, (cudaStream_t)stream);
+    return wmoments_white_impl<true>(zstore, nw, K, D, s1, s2, cov, accumulate, workspace, (cudaStream_t)stream);
+  return wmoments_white_direct(zstore, nw, K, D, s1, s2, cov, accumulate, workspace, (cudaStream_t)stream);
 }
 
 // sample.cu
@@ -1935,11 +2016,25 @@ extern "C" size_t ppi_sample_gaussian_workspace_bytes(int64_t K, int64_t D) {
 //   injected  round_up(K, 256) sample rows of round_up(D, 64) / 32 blocks [h1 x 32 | h2 x 32] fp16
 //             (4 B per value, scaled by scale_b)
 
+// sum of the per-tile partial costs in a fixed order + the function's affine part
+__global__ void __launch_bounds__(256)
+cost_finish_kernel(const float* __restrict__ part, int64_t K, int tiles, int fn, float D,
+                   float* __restrict__ cost) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < K; k += stride) {
+    float s = 0.f;
+    for (int t = 0; t < tiles; ++t) s += part[k * tiles + t];
+    if (fn == PPI_FN_STYBLINSKI) s = fmaf(0.5f, s, 39.16599f * D);
+    else s += 10.f * D;
+    cost[k] = s;
+  }
+}
+
 template <bool FP16, bool ZPAIR>
 static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
                                 int64_t K, int64_t D, const float* mu, const float* L, float* x,
                                 void* workspace, void* zstore, cudaStream_t st,
-                                const void* zrows_pre = nullptr) {
+                                const void* zrows_pre = nullptr, int cost_fn = -1, float* cost_out = nullptr) {
   // zrows_pre: the draw's sample-major fp16 operand rows AND its K-major store were generated ahead of
   // time (ppi_philox_prefetch): no staging passes, the GEMMs read the rows in place
   constexpr int LMODE = FP16 ? OP_F16_PAIR : OP_TF32X3;
@@ -2006,6 +2101,10 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
   p.mu = mu;
   p.scalars = scalars;
   p.z_exact = z_exact ? 1 : 0;
+  // fused cost: per-(sample, j-tile) partials behind the staging buffers of the workspace
+  p.cost_part = cost_out ? (float*)(wsp + kScalarBytes + 2 * l_bytes + 2 * z_bytes) : nullptr;
+  p.cost_fn = cost_fn;
+  p.row0 = 0;
 
   SideStream* ss = nullptr;
   cudaStream_t st_op = st;
@@ -2020,6 +2119,7 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
     const int bi = overlap ? (pass & 1) : 0;
     const int64_t rows = (K - k0) < Kc ? (K - k0) : Kc;
     const int64_t rows_p = round_up(rows, BN);
+    p.row0 = k0;
     if (store_pairs) {
       zbufs[0] = store_rows + (size_t)k0 * store_row_bytes;
       if (int rc = make_map(&mz[0], zbufs[0], rows_p, Dk, BN, ZMODE)) return rc;
@@ -2059,9 +2159,9 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
     }
     p.n_units = (rows_p / BN) * p.units_per_block;
     p.rows = rows;
-    p.x = x + k0 * D;
+    p.x = x ? x + k0 * D : nullptr;
     const unsigned g = (unsigned)(p.n_units < kNumSMs ? p.n_units : kNumSMs);
-    if (FP16 && !ZPAIR && gemm_pair()) {
+    if (FP16 && !ZPAIR && gemm_pair() && !cost_out && x) {
       // CTA pairs (cta_group::2): each CTA loads its own L rows and half of the z block
       static bool attr2_set = false;
       if (!attr2_set) {
@@ -2092,6 +2192,12 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
     }
     if (overlap) PPI_CUDA_TRY(cudaEventRecord(ss->gemm_done[bi], st));
   }
+  if (cost_out) {
+    ProfileScope prof(PPI_PROF_COST, st);
+    cost_finish_kernel<<<grid_cap(ceil_div(K, 256), 8), 256, 0, st>>>(p.cost_part, K, p.tiles_j, cost_fn, (float)D,
+                                                                      cost_out);
+    if (int rc = check_launch("cost_finish_kernel")) return rc;
+  }
   return 0;
 }
 
@@ -2110,6 +2216,11 @@ extern "C" int ppi_sample_gaussian(const float* z, uint64_t seed, uint64_t draw_
     return sample_gaussian_impl<true, false>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, nullptr, st);
   }
   return sample_gaussian_impl<false, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, nullptr, st);
+}
+
+extern "C" size_t ppi_sample_gaussian_cost_workspace_bytes(int64_t K, int64_t D) {
+  if (K <= 0 || D <= 128) return 0;
+  return ppi_sample_gaussian_workspace_bytes(K, D) + (size_t)K * ceil_div(D, BM) * sizeof(float) + 1024;
 }
 
 extern "C" size_t ppi_zstore_bytes(int64_t K, int64_t D, int injected) {
@@ -2181,4 +2292,30 @@ extern "C" int ppi_sample_gaussian_keep(const float* z, uint64_t seed, uint64_t 
   cudaStream_t st = (cudaStream_t)stream;
   if (z) return sample_gaussian_impl<true, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, zstore, st);
   return sample_gaussian_impl<true, false>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, zstore, st);
+}
+
+// ppi_sample_gaussian_keep with a separable test function evaluated in the sampling epilogue
+// (ppi/algorithms.py:85-86 fused: the samples are costed where they are produced).  x may be NULL: the
+// samples are then never written (the whitened update contracts the stored base normals; a caller that
+// wants x later re-draws it from the same (seed, draw_id, row_offset) with ppi_sample_gaussian).
+extern "C" int ppi_sample_gaussian_cost(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
+                                        int64_t K, int64_t D, const float* mu, const float* L, float* x,
+                                        void* zstore, size_t zstore_bytes, int fn, float* cost,
+                                        void* workspace, size_t workspace_bytes, void* stream) {
+  PPI_REQUIRE(mu && L && cost && K > 0 && D > 128 && zstore, PPI_ERR_INVALID,
+              "ppi_sample_gaussian_cost: bad arguments (needs K > 0, D > 128, a store, a cost buffer)");
+  PPI_REQUIRE(fn == PPI_FN_RASTRIGIN || fn == PPI_FN_STYBLINSKI, PPI_ERR_UNSUPPORTED,
+              "ppi_sample_gaussian_cost: only the separable test functions (Rastrigin, Styblinski) are fused");
+  PPI_REQUIRE(gemm_scheme() == PPI_GEMM_FP16X2, PPI_ERR_UNSUPPORTED,
+              "ppi_sample_gaussian_cost: the base-normal store exists under PPI_GEMM_FP16X2 only");
+  PPI_REQUIRE(((uintptr_t)zstore & 1023) == 0 && zstore_bytes >= ppi_zstore_bytes(K, D, z != nullptr),
+              PPI_ERR_WORKSPACE, "ppi_sample_gaussian_cost: store misaligned (1 KB) or too small");
+  PPI_REQUIRE(workspace && workspace_bytes >= ppi_sample_gaussian_cost_workspace_bytes(K, D), PPI_ERR_WORKSPACE,
+              "ppi_sample_gaussian_cost: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (z)
+    return sample_gaussian_impl<true, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, zstore, st,
+                                            nullptr, fn, cost);
+  return sample_gaussian_impl<true, false>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, zstore, st,
+                                           nullptr, fn, cost);
 }

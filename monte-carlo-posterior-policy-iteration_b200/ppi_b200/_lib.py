@@ -63,8 +63,10 @@ SIGNATURES = {
     "ppi_philox_prefetch": (_i, [_u64, _u64, _u64, _i64, _i64, _p, _sz, _p, _sz, _p]),
     "ppi_sample_gaussian_pre": (_i, [_i64, _i64, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "ppi_sample_gaussian_keep": (_i, [_p, _u64, _u64, _u64, _i64, _i64, _p, _p, _p, _p, _sz, _p, _sz, _p]),
+    "ppi_sample_gaussian_cost_workspace_bytes": (_sz, [_i64, _i64]),
+    "ppi_sample_gaussian_cost": (_i, [_p, _u64, _u64, _u64, _i64, _i64, _p, _p, _p, _p, _sz, _i, _p, _p, _sz, _p]),
     "ppi_wmoments_white_workspace_bytes": (_sz, [_i64, _i64, _i]),
-    "ppi_wmoments_white": (_i, [_p, _i, _p, _i64, _i64, _p, _p, _i, _p, _sz, _p]),
+    "ppi_wmoments_white": (_i, [_p, _i, _p, _i64, _i64, _p, _p, _p, _i, _p, _sz, _p]),
     "ppi_cost_function": (_i, [_i, _p, _i64, _i64, _p, _p, _p, _p]),
     "ppi_cost_tracking": (_i, [_p, _i64, _i, _i, _p, _i, _p, _p]),
     "ppi_solve_temperature_workspace_bytes": (_sz, [_i64]),
@@ -78,6 +80,11 @@ SIGNATURES = {
     "ppi_wmoments_dense": (_i, [_p, _p, _i64, _i64, _p, _p, _p, _i, _p, _sz, _p]),
     "ppi_finalize_gaussian": (_i, [_p, _p, _i64, _p, _i, _p, _p, _p]),
     "ppi_finalize_matnorm": (_i, [_p, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "ppi_dense_workspace_bytes": (_sz, [_i64]),
+    "ppi_cholesky_blocked": (_i, [_p, _i64, _p, _p, _p, _p, _sz, _p]),
+    "ppi_white_finish": (_i, [_p, _p, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _sz, _p]),
+    "ppi_tri_gram": (_i, [_p, _i64, _p, _p, _p]),
+    "ppi_tri_matvec": (_i, [_p, _i64, _p, _p, _p, _p]),
     "ppi_launch_count": (_i64, []),
     "ppi_profile_enable": (_i, [_i]),
     "ppi_profile_read": (_i, [_i, C.POINTER(_i64), C.POINTER(_d)]),
@@ -85,7 +92,7 @@ SIGNATURES = {
 
 PROFILE_SLOTS = {"syrk_gemm": 0, "sample_gemm": 1, "syrk_operand": 2, "sample_operand": 3,
                  "wmoments_diag": 4, "cost": 5, "solve": 6, "syrk_reduce": 7, "sample_small": 8,
-                 "wmoments_matnorm": 9}
+                 "wmoments_matnorm": 9, "dense_tail": 10}
 
 
 def profile_read():

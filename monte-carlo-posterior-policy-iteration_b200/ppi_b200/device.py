@@ -158,6 +158,85 @@ class DeviceArray:
         return f"DeviceArray(shape={self.shape}, device={self.tensor.device})"
 
 
+class DeferredGaussianSamples(DeviceArray):
+    """Handle on a Gaussian draw that has not been launched yet.  The draw is a pure function of
+    (seed, draw_id, global row) and of the policy state captured here, so WHEN it runs does not matter:
+
+      * `f(handle)` with a fusable device cost (functions.Rastrigin / Styblinski) launches the sampler with the
+        cost evaluated in its epilogue and never writes x (ppi_sample_gaussian_cost);
+      * anything that touches `.tensor` (a host cost, a callback, CEM's elite rows, the x-space update)
+        materialises x -- the same numbers, bit for bit, from the same Philox counters.
+
+    Either way the base normals end up in HBM (`white`) for the whitened moment match."""
+
+    def __init__(self, policy, version, mu_dev, chol_dev, n_local, dim, row_offset, global_rows, seed, draw_id,
+                 after=None):
+        self._x = None
+        self._shape = (int(n_local), int(dim))
+        self.row_offset, self.global_rows, self._host = int(row_offset), int(global_rows), None
+        self._launch = (policy, version, mu_dev, chol_dev, int(seed), int(draw_id))
+        self.white = None            # (policy, version, BaseNormals) once a kernel has produced the store
+        self._after = after          # called once after the first launch (prefetch hook)
+
+    def _done(self):
+        if self._after is not None:
+            after, self._after = self._after, None
+            after()
+
+    @property
+    def tensor(self):
+        if self._x is None:
+            from . import ops
+
+            policy, version, mu, chol, seed, draw = self._launch
+            n, _ = self._shape
+            if self.white is None:   # first launch: keep the base normals for the whitened update
+                self._x, base = ops.sample_gaussian_keep(n, mu, chol, seed=seed, draw_id=draw,
+                                                         row_offset=self.row_offset)
+                self.white = (policy, version, base)
+                self._done()
+            else:                    # the fused launch skipped x: re-draw it from the same counters
+                self._x = ops.sample_gaussian(n, mu, chol, seed=seed, draw_id=draw, row_offset=self.row_offset)
+        return self._x
+
+    @tensor.setter
+    def tensor(self, value):
+        self._x = value
+
+    @property
+    def materialised(self):
+        return self._x is not None
+
+    def fused_cost(self, fn_name):
+        """Costs of a separable test function from the sampling epilogue, or None when x already exists
+        (then the ordinary cost kernel reads it)."""
+        if self._x is not None or self.white is not None:
+            return None
+        from . import ops
+
+        policy, version, mu, chol, seed, draw = self._launch
+        n, _ = self._shape
+        _, base, cost = ops.sample_gaussian_cost(n, mu, chol, fn_name, seed=seed, draw_id=draw,
+                                                 row_offset=self.row_offset)
+        self.white = (policy, version, base)
+        self._done()
+        return cost
+
+    @property
+    def shape(self):
+        return self._shape
+
+    @property
+    def ndim(self):
+        return 2
+
+    def __len__(self):
+        return self._shape[0]
+
+    def __repr__(self):
+        return f"DeferredGaussianSamples(shape={self._shape}, launched={self.white is not None})"
+
+
 # --------------------------------------------------------------------------------------------
 # workspaces: one cached byte buffer per (tag, device), grown on demand
 # --------------------------------------------------------------------------------------------

@@ -239,6 +239,25 @@ def sample_gaussian_keep(K, mu, L, z=None, seed=0, draw_id=0, row_offset=0):
     return x, BaseNormals(store, K, D, zt is not None)
 
 
+def sample_gaussian_cost(K, mu, L, fn_name, z=None, seed=0, draw_id=0, row_offset=0, want_x=False):
+    """sample_gaussian_keep with a separable test function evaluated in the sampling epilogue
+    (ppi_sample_gaussian_cost): -> (x or None, BaseNormals, cost (K,) fp32).  want_x=False never writes x."""
+    dev = require_cuda()
+    kp = _Keep(dev)
+    mu = f32(mu, dev)
+    D = mu.numel()
+    x = torch.empty((K, D), dtype=torch.float32, device=dev) if want_x else None
+    zt = None if z is None else f32(z, dev).reshape(K, D)
+    nbytes = _lib.query("ppi_sample_gaussian_cost_workspace_bytes", K, D)
+    ws = workspace("sample_gaussian", nbytes)
+    sbytes = _lib.query("ppi_zstore_bytes", K, D, int(zt is not None))
+    store = _aligned_bytes(sbytes, dev)
+    cost = torch.empty((K,), dtype=torch.float32, device=dev)
+    _lib.call("ppi_sample_gaussian_cost", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, D, ptr(mu),
+              kp.p(L), ptr(x), ptr(store), sbytes, _lib.FN_IDS[fn_name], ptr(cost), ptr(ws), nbytes, stream_ptr())
+    return x, BaseNormals(store, K, D, zt is not None), cost
+
+
 def _aligned_bytes(nbytes, dev):
     raw = torch.empty(nbytes + 1024, dtype=torch.uint8, device=dev)
     off = (-raw.data_ptr()) % 1024
@@ -283,8 +302,9 @@ def sample_gaussian_pre(K, mu, L, pre):
     return x, BaseNormals(pre.store, K, D, False)
 
 
-def wmoments_white(base, nw, s1=None, cov=None, accumulate=False):
-    """Whitened moments of a BaseNormals store: s1 (D fp64) += sum nw z, cov (D, D) = sum nw z z^T."""
+def wmoments_white(base, nw, s1=None, cov=None, accumulate=False, s2=None):
+    """Whitened moments of a BaseNormals store: s1 (D fp64) += sum nw z, cov (D, D) = sum nw z z^T.
+    s2 (D fp64, optional) += diag of that sum with round-to-nearest products (the accurate trace)."""
     dev = require_cuda()
     kp = _Keep(dev)
     K, D = base.rows, base.dim
@@ -292,7 +312,7 @@ def wmoments_white(base, nw, s1=None, cov=None, accumulate=False):
     cov = torch.empty((D, D), dtype=torch.float32, device=dev) if cov is None else cov
     nbytes = _lib.query("ppi_wmoments_white_workspace_bytes", K, D, int(base.injected))
     ws = workspace("wmoments_dense", nbytes)
-    _lib.call("ppi_wmoments_white", ptr(base.store), int(base.injected), kp.p(nw), K, D, ptr(s1), ptr(cov),
+    _lib.call("ppi_wmoments_white", ptr(base.store), int(base.injected), kp.p(nw), K, D, ptr(s1), ptr(s2), ptr(cov),
               int(bool(accumulate)), ptr(ws), nbytes, stream_ptr())
     return s1, cov
 
@@ -462,4 +482,55 @@ def finalize_matnorm(s1, acc, H, d, jitter=0.0):
     _lib.call("ppi_finalize_matnorm", ptr(s1), ptr(acc), H, d, float(jitter), ptr(out["mean64"]),
               ptr(out["mean32"]), ptr(out.get("cov64")), ptr(out.get("cov32")), ptr(out.get("chol64")),
               ptr(out.get("chol32")), ptr(out.get("status")), stream_ptr())
+    return out
+
+
+# ------------------------------------------------------------------ f3: dense D x D fp64 tail
+def cholesky_blocked(a, want32=False):
+    """np.linalg.cholesky of a (D, D) fp64 device matrix, any D (blocked, fp64 tensor cores).
+    -> (L fp64, L fp32 or None, scalars): scalars = device tensor [status, log det, -, -]."""
+    dev = require_cuda()
+    a = f64(a, dev)
+    D = a.shape[0]
+    l64 = torch.empty_like(a)
+    l32 = torch.empty((D, D), dtype=torch.float32, device=dev) if want32 else None
+    scal = torch.empty(4, dtype=torch.float64, device=dev)
+    nbytes = _lib.query("ppi_dense_workspace_bytes", D)
+    ws = workspace("dense64", nbytes)
+    _lib.call("ppi_cholesky_blocked", ptr(a), D, ptr(l64), ptr(l32), ptr(scal), ptr(ws), nbytes, stream_ptr())
+    return l64, l32, scal
+
+
+def white_finish(s, m, l_old64, mu_old32, diag=None):
+    """Tail of the whitened update in one call (ppi_white_finish).
+    -> (l_new64, l_new32, mu_new32, scalars [status, log det C, tr C, |m|^2] on the device)."""
+    dev = require_cuda()
+    D = m.numel()
+    l_new64 = torch.zeros((D, D), dtype=torch.float64, device=dev)
+    l_new32 = torch.zeros((D, D), dtype=torch.float32, device=dev)
+    mu_new = torch.empty(D, dtype=torch.float32, device=dev)
+    scal = torch.empty(4, dtype=torch.float64, device=dev)
+    nbytes = _lib.query("ppi_dense_workspace_bytes", D)
+    ws = workspace("dense64", nbytes)
+    _lib.call("ppi_white_finish", ptr(s), ptr(m), ptr(diag), ptr(l_old64), ptr(mu_old32), D, ptr(l_new64), ptr(l_new32),
+              ptr(mu_new), ptr(scal), ptr(ws), nbytes, stream_ptr())
+    return l_new64, l_new32, mu_new, scal
+
+
+def tri_gram(l64, want32=False):
+    """sigma = L L^T from a lower-triangular fp64 factor (ppi_tri_gram)."""
+    dev = require_cuda()
+    D = l64.shape[0]
+    out64 = torch.empty((D, D), dtype=torch.float64, device=dev)
+    out32 = torch.empty((D, D), dtype=torch.float32, device=dev) if want32 else None
+    _lib.call("ppi_tri_gram", ptr(l64), D, ptr(out64), ptr(out32), stream_ptr())
+    return (out64, out32) if want32 else out64
+
+
+def tri_matvec(l64, v64, x0_32):
+    """x0 + L v (fp32 result) for a lower-triangular fp64 L: the mean step of the whitened update alone."""
+    dev = require_cuda()
+    D = v64.numel()
+    out = torch.empty(D, dtype=torch.float32, device=dev)
+    _lib.call("ppi_tri_matvec", ptr(l64), D, ptr(v64), ptr(x0_32), ptr(out), stream_ptr())
     return out

@@ -16,8 +16,8 @@ import numpy as np
 import torch
 
 from . import _lib, ops, samplers
-from .device import (DeviceArray, LazyStats, all_reduce_max, all_reduce_sum, broadcast_row, dist_info, f32, f64, require_cuda,
-                     scope, shard_rows, to_host64)
+from .device import (DeferredGaussianSamples, DeviceArray, LazyStats, all_reduce_max, all_reduce_sum, broadcast_row,
+                     dist_info, f32, f64, require_cuda, scope, shard_rows, to_host64)
 
 __all__ = [
     "RbfFeatures",
@@ -308,6 +308,7 @@ class GaussianPolicy(object):
     name = "Gaussian"
     small_dim = 128  # at or below: SIMT kernels + host fp64 tail; above: tcgen05 + device tail
     n_regularized = 0  # updates that took the non-PD branch of ppi/policies.py:263-268 (bench.py asserts 0)
+    defer_draws = True  # Philox draws (D > small_dim) are launched when first used: cost fused into the sampler
 
     def __init__(self, mu, sigma, sampler, diagonal=False):
         self.sampler = sampler
@@ -371,7 +372,7 @@ class GaussianPolicy(object):
         if self._sigma_dev is not None:
             return self._sigma_dev.double()
         if self._sigma_host is None:  # after a whitened update only the factor exists: sigma = L L^T
-            return self._chol64_dev @ self._chol64_dev.T
+            return ops.tri_gram(self._chol64_dev)
         return f64(self._sigma_host)
 
     def _factor(self):
@@ -382,13 +383,17 @@ class GaussianPolicy(object):
                 s64 = self._sigma64_d()
                 if s64.shape[0] <= 160:
                     l64, status = ops.cholesky_small(s64)
-                    if status != 0:
-                        raise np.linalg.LinAlgError("sigma is not positive definite")
-                else:
-                    l64 = torch.linalg.cholesky(s64)
-                self._chol64_dev = l64
-            self._chol_dev = self._chol64_dev.float().contiguous()
-            self._logdet = float(2.0 * torch.log(torch.diagonal(self._chol64_dev)).sum().item())
+                    l32 = logdet = None
+                else:  # blocked fp64 factorisation (dense64.cu), fp32 copy and log det in the same call
+                    l64, l32, scal = ops.cholesky_blocked(s64, want32=True)
+                    status, logdet = (float(v) for v in scal[:2].cpu())
+                if status != 0:
+                    raise np.linalg.LinAlgError("sigma is not positive definite")
+                self._chol64_dev, self._chol_dev, self._logdet = l64, l32, logdet
+            if self._chol_dev is None:
+                self._chol_dev = self._chol64_dev.float().contiguous()
+            if self._logdet is None:
+                self._logdet = float(2.0 * torch.log(torch.diagonal(self._chol64_dev)).sum().item())
         return self._chol_dev
 
     @property
@@ -414,6 +419,11 @@ class GaussianPolicy(object):
             if z is None and pre is not None and pre.key == (id(self.sampler), seed, draw, begin, n_local, d):
                 x, base = ops.sample_gaussian_pre(n_local, self._mu_d(), self._factor(), pre)
                 self._pre_owner[pre.slot] = base
+            elif z is None and self.defer_draws and self.prefetch_normals is None:
+                # Philox draw: nothing is launched yet -- the cost function decides whether x is ever written
+                handle = DeferredGaussianSamples(self, self._version, self._mu_d(), self._factor(), n_local, d,
+                                                 begin, n_total, seed, draw)
+                return handle, handle
             else:
                 x, base = ops.sample_gaussian_keep(n_local, self._mu_d(), self._factor(), z=z, seed=seed,
                                                    draw_id=draw, row_offset=begin)
@@ -466,13 +476,19 @@ class GaussianPolicy(object):
 
     def weighted_update(self, log_weights, samples, update_covariance_in=True):
         w = _weights(log_weights)
-        x, row_offset, n_total, replicated = _samples(samples)
-        nw = _local(w.nw, row_offset, x.shape[0])
-        d = x.shape[1]
+        if isinstance(samples, DeferredGaussianSamples) and samples.white is None:
+            samples.tensor    # never costed nor read: launch the draw now (keeps its base normals)
         white = getattr(samples, "white", None)
         if (white is not None and white[0] is self and white[1] == self._version and update_covariance_in
                 and not self.diagonal and white[2].valid):
-            return self._weighted_update_white(w, white[2], nw, n_total)
+            # the policy's own draw: contract the stored base normals -- x itself is not needed (and a
+            # deferred draw whose cost was fused never wrote it)
+            n_local = samples.shape[0]
+            nw = _local(w.nw, samples.row_offset, n_local)
+            return self._weighted_update_white(w, white[2], nw, samples.global_rows)
+        x, row_offset, n_total, replicated = _samples(samples)
+        nw = _local(w.nw, row_offset, x.shape[0])
+        d = x.shape[1]
         if d > self.small_dim:
             return self._weighted_update_large(w, x, nw, replicated, update_covariance_in)
         mu_old, sigma_old = self.mu.copy(), self.sigma.copy()
@@ -532,37 +548,43 @@ class GaussianPolicy(object):
         d = base.dim
         self._factor()
         l_old, mu_old_dev, old_logdet = self._chol64_dev, self._mu_d(), self._logdet
-        m, s = ops.wmoments_white(base, nw)
+        # first moments: row 0 = m = sum nw z, row 1 = diag(S) with round-to-nearest products (one tensor, so
+        # that K-sharded ranks reduce both in one collective)
+        m12 = torch.zeros((2, d), dtype=torch.float64, device=mu_old_dev.device)
+        m, diag = m12[0], m12[1]
+        _, s = ops.wmoments_white(base, nw, s1=m, s2=diag)
         if self.prefetch_normals == "update" and n_total is not None and not base.injected:
             self._prefetch_next(n_total)
         if dist_info()[1] > 1:
             with scope("allreduce_moments"):
-                all_reduce_sum(m)
+                all_reduce_sum(m12)
                 all_reduce_sum(s)
         with scope("dense_tail"):
-            c = s.double()
-            c.addr_(m, m, alpha=-1.0)
-            g, info = torch.linalg.cholesky_ex(c)
-            scal = torch.stack([info.double(), 2.0 * torch.log(torch.diagonal(g)).sum(), torch.trace(c), m @ m]).cpu()
-            self._mu_host, self._mu_dev = None, (mu_old_dev.double() + l_old @ m).float()
-            l_new = l_old @ g if int(scal[0]) == 0 else None
-        if l_new is not None:
-            logdet_c = float(scal[1])
-            self._sigma_host = self._sigma_dev = self._chol_dev = self._sigma64_dev = None
-            self._chol64_dev, self._logdet = l_new, old_logdet + logdet_c
-            kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(self._logdet) + float(scal[2]) + float(scal[3]) - d)
+            # C = S - m m^T, G = chol(C), L' = L G, mu' = mu + L m and the three scalars of the KL in ONE call of
+            # hand-written fp64 kernels (dense64.cu); one 32-byte device->host read decides the branch
+            l_new64, l_new32, mu_new, scal = ops.white_finish(s, m, l_old, mu_old_dev, diag=diag)
+            status, logdet_c, trace_c, msq = (float(v) for v in scal.cpu())
+        if status == 0:
+            self._mu_host, self._mu_dev = None, mu_new
+            self._sigma_host = self._sigma_dev = self._sigma64_dev = None
+            self._chol64_dev, self._chol_dev, self._logdet = l_new64, l_new32, old_logdet + logdet_c
+            kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(self._logdet) + trace_c + msq - d)
         else:  # ppi/policies.py:263-268: keep the old covariance, regularised
             logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
             self.n_regularized += 1
-            sigma_old = l_old @ l_old.T
+            self._mu_host, self._mu_dev = None, ops.tri_matvec(l_old, m, mu_old_dev)
+            sigma_old = ops.tri_gram(l_old)
             self._sigma_host, self._chol_dev, self._chol64_dev, self._logdet = None, None, None, None
             # kept in fp64: the 1e-6 regulariser is 17 ulps of an fp32 entry of size one
             self._sigma_dev = None
-            self._sigma64_dev = sigma_old + SIGMA_MIN * torch.eye(d, dtype=torch.float64, device=sigma_old.device)
+            sigma_old.diagonal().add_(SIGMA_MIN)
+            self._sigma64_dev = sigma_old
             self._factor()
-            tr = torch.linalg.solve_triangular(l_old, self._chol64_dev, upper=False).square().sum()
-            kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(self._logdet) + float(tr.item())
-                        + float(scal[3]) - d)  # (mu' - mu)^T sigma^-1 (mu' - mu) = |m|^2
+            # tr(sigma_old^-1 (sigma_old + eps I)) = D + eps |L_old^-1|_F^2  (rare branch: torch's triangular solve)
+            eye = torch.eye(d, dtype=torch.float64, device=l_old.device)
+            tr = d + SIGMA_MIN * float(torch.linalg.solve_triangular(l_old, eye, upper=False).square().sum().item())
+            kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(self._logdet) + tr + msq - d)
+            # (mu' - mu)^T sigma^-1 (mu' - mu) = |m|^2
         self._version += 1
         return float(w.stats.ess), kl
 
@@ -599,13 +621,16 @@ class GaussianPolicy(object):
                 cov = ops.wmoments_dense(x, nw, shift=mu_new_dev, dev_bound=dev_bound)
                 if not replicated:
                     all_reduce_sum(cov)
-                chol64, info = torch.linalg.cholesky_ex(cov.double())
-                pd = int(info.item()) == 0
+                chol64, chol32_new, scal = ops.cholesky_blocked(cov.double(), want32=True)
+                status, logdet_new = (float(v) for v in scal[:2].cpu())
+                pd = status == 0
             # accept / regularise exactly like ppi/policies.py:258-268
             if pd:
                 self._sigma_host, self._sigma_dev, self._sigma64_dev = None, cov, None
                 self._chol64_dev, self._chol_dev = chol64, None
                 self._logdet = float(2.0 * torch.log(torch.diagonal(chol64)).sum().item())
+                if not self.diagonal:
+                    self._chol_dev, self._logdet = chol32_new, logdet_new
             else:
                 logging.warning("Fitted multivariate normal not positive definite. Regularizing covariance.")
                 self.n_regularized += 1

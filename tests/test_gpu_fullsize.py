@@ -235,10 +235,10 @@ def test_c2_three_iterations_against_fp64_oracle(env, record, fn_name, solver_na
         z = (ops.philox_normal(K, D, 4242, draw_id=it).cpu().numpy().astype(np.float64) if source == "philox"
              else zs[it].astype(np.float64))
         samples, params = policy(K)
+        costs = f(samples)       # Philox + Rastrigin: cost fused into the sampler, x re-drawn below for the oracle
         assert getattr(samples, "white", None) is not None          # the whitened route (the benchmarked one)
         x = np.asarray(samples)
         e = {"x": nerr(x, O.sample_gaussian(z, mu_old, sigma_old))}
-        costs = f(samples)
         c = np.asarray(costs)
         e["cost"] = nerr(c, f_ref(x))
         solver.update(costs, params, policy)
@@ -291,7 +291,9 @@ def test_c5_update_against_fp64_checker(env, factor, record):
     solver.reset(policy)
     ent0 = solver.trace["ent"]
     samples, params = policy(K5)
-    x = samples.tensor
+    costs = fn.Rastrigin(D5)(samples)          # the benchmarked route: cost in the sampling epilogue, x not written
+    assert not samples.materialised
+    x = samples.tensor                         # re-drawn from the same Philox counters for the checkers
     e = {}
     # ---- sampler: x = mu + z chol(sigma)^T over all 2^31 elements -------------------------------------
     chol = torch.linalg.cholesky(torch.as_tensor(sigma0, device=dev))
@@ -305,14 +307,15 @@ def test_c5_update_against_fp64_checker(env, factor, record):
         del z, ref
     e["x"] = worst / scale
     # ---- cost: every row ---------------------------------------------------------------------------------
-    costs = fn.Rastrigin(D5)(samples)
     c = costs.tensor
+    c_kernel = ops.cost_function("Rastrigin", x)
     c_ref = torch.empty(K5, dtype=torch.float64, device=dev)
     for i in range(0, K5, 1 << 16):
         xc = x[i:i + (1 << 16)].double()
         c_ref[i:i + (1 << 16)] = 10.0 * D5 + (xc * xc - 10.0 * torch.cos(2.0 * np.pi * xc)).sum(1)
         del xc
     e["cost"] = float((c.double() - c_ref).abs().max() / c_ref.abs().max())
+    e["cost_kernel"] = float((c_kernel.double() - c_ref).abs().max() / c_ref.abs().max())
     # ---- temperature and weights: fp64 softmax of the device costs at the device alpha; ESS root ------
     nw, lw, st = ops.solve_temperature(c, _lib.TEMP_ESS_TARGET, K5 // 64)
     cn = (c.double() - c.double().min()) / (c.double().max() - c.double().min())
@@ -351,7 +354,8 @@ def test_c5_update_against_fp64_checker(env, factor, record):
     e["kl"] = abs(solver.trace["kl"][-1] - kl_ref) / max(1.0, abs(kl_ref))
     e["ent"] = abs(solver.trace["ent"][-1] - ent_ref) / abs(ent_ref)
     record("c5_full", **e)
-    for k in ("x", "cost", "ess_root", "nw", "mu_xspace", "sigma_xspace", "alpha", "mu_white", "sigma_white"):
+    for k in ("x", "cost", "cost_kernel", "ess_root", "nw", "mu_xspace", "sigma_xspace", "alpha", "mu_white",
+              "sigma_white"):
         assert e[k] < TOL, (k, e[k])
     assert e["kl"] < 1e-4 and e["ent"] < 1e-4, e
     assert len(ent0) >= 1

@@ -65,10 +65,14 @@ def test_wmoments_white_ops(ops, record, K, D, injected):
     import torch
 
     assert torch.equal(x, ref_x)                               # the store changes nothing in x
-    s1, s = ops.wmoments_white(base, nw)
+    import torch as _t
+
+    s2 = _t.zeros(D, dtype=_t.float64, device="cuda")
+    s1, s = ops.wmoments_white(base, nw, s2=s2)
     m_ref = nw @ z
     s_ref = (nw[:, None] * z).T @ z
     assert nerr(host(s1), m_ref) < TOL
+    assert nerr(host(s2), np.diag(s_ref)) < 2e-7        # the round-to-nearest diagonal (accurate trace for the KL)
     cov = host(s)
     assert nerr(cov, s_ref) < TOL
     assert np.array_equal(cov, cov.T)
@@ -125,8 +129,8 @@ def test_gaussian_policy_white_update(ops, record, philox):
     for it in range(2):
         mu_old, sigma_old = policy.mu.copy(), policy.sigma.copy()
         samples, params = policy(K)
+        costs = fn.Rastrigin(D)(samples)      # Philox: the draw is launched here, cost fused, x not written
         assert getattr(samples, "white", None) is not None
-        costs = fn.Rastrigin(D)(samples)
         x32, c32 = np.asarray(samples), np.asarray(costs)
         solver.update(costs, params, policy)
         log_w, alpha = O.essps_log_w(c32, K // 16)
@@ -227,3 +231,44 @@ def test_prefetch_c_abi_errors(ops):
         _lib.call("ppi_philox_prefetch", 1, 0, 0, 256, 256, p + 8, 1 << 19, p, 1 << 19, None)
     with pytest.raises(_lib.PpiError):     # D <= 128 has no tensor-core path
         _lib.call("ppi_philox_prefetch", 1, 0, 0, 256, 64, p, 1 << 19, p, 1 << 19, None)
+
+
+@pytest.mark.parametrize("name", ["Rastrigin", "Styblinski"])
+@pytest.mark.parametrize("K,D", [(3000, 384), (70001, 640), (4096, 2048), (600, 130)])
+def test_fused_cost_in_the_sampling_epilogue(ops, record, name, K, D):
+    """A Philox draw of a GaussianPolicy is deferred until its first use: `f(samples)` with a separable test
+    function launches the sampler with the cost in its epilogue and never writes x (ppi/algorithms.py:85-86
+    fused).  The costs equal the stand-alone cost kernel's on the re-drawn x, x equals the eager draw bit for
+    bit, and the whitened update that follows is bit-identical to the one of an eager draw."""
+    import torch
+    from ppi_b200 import functions as fn, policies as pol, samplers as smp
+    from ppi_b200.device import DeferredGaussianSamples
+
+    rng = np.random.default_rng(K + D)
+    a = rng.standard_normal((D, D + 8))
+    sigma = a @ a.T / D + 0.2 * np.eye(D)
+    mu = 0.5 * rng.standard_normal(D)
+    f = getattr(fn, name)(D)
+    lw_seed = f32r(-3.0 * rng.random(K))
+
+    def run(defer):
+        policy = pol.GaussianPolicy(mu.copy(), sigma.copy(), smp.MonteCarlo(D, seed=31))
+        policy.defer_draws = defer
+        samples, params = policy(K)
+        assert isinstance(samples, DeferredGaussianSamples) == defer
+        costs = f(samples)
+        launched_x = getattr(samples, "materialised", True)
+        c = costs.tensor.clone()
+        x = samples.tensor.clone()
+        policy.weighted_update(lw_seed, samples)
+        return c, x, policy.mu.copy(), policy.sigma.copy(), launched_x
+
+    c1, x1, mu1, sig1, mat1 = run(True)
+    c0, x0, mu0, sig0, mat0 = run(False)
+    assert mat1 is False and mat0 is True           # the fused launch did not write x
+    assert torch.equal(x1, x0)                      # the re-drawn samples are the eager ones
+    ref = {"Rastrigin": O.rastrigin, "Styblinski": O.styblinski}[name](host(x0))
+    e_fused, e_kernel = nerr(host(c1), ref), nerr(host(c0), ref)
+    record(f"fused_cost[{name}-{K}-{D}]", fused=e_fused, kernel=e_kernel)
+    assert e_fused < 2e-6 and e_kernel < 2e-6
+    assert np.array_equal(mu1, mu0) and np.array_equal(sig1, sig0)
