@@ -54,7 +54,7 @@ const char* ppi_last_error(void);
  * the call stays asynchronous and stream-ordered for the caller).  Default 0: measured gain on
  * B200 is ~1 % of a step because both kernels contend for L2 / HBM.
  * PPI_OPT_GEMM_PAIR != 0: kernels that have a CTA-pair form (tcgen05 cta_group::2, clusters of
- * two CTAs sharing the B operand) use it; 0 (default: measured faster) selects the single-CTA kernels.
+ * two CTAs sharing the B operand) use it; 0 (default) selects the single-CTA kernels.
  * Results are identical up to fp32 summation order.
  * PPI_OPT_PREFETCH_BLOCKS = resident CTAs per SM of ppi_philox_prefetch, 1..6 (default 6): fewer leave
  * room for the kernels of the stream it runs beside. */
@@ -195,17 +195,23 @@ int ppi_sample_gaussian_cost(const float* z, uint64_t seed, uint64_t draw_id, ui
                              void* stream);
 
 /* Base normals of a Philox draw generated ahead of the sampling call (they depend on (seed, draw_id,
- * global row) only): zrows = sample-major exact-fp16 operand rows, round_up(K, 256) x round_up(D, 64),
- * zstore = the K-major store of ppi_sample_gaussian_keep; both 1 KB aligned, sizes from
- * ppi_philox_rows_bytes / ppi_zstore_bytes(K, D, 0).  Issued on a side stream this hides the generator
- * (ppi/samplers.py:18-20, np.random.randn) under the HBM- and latency-bound part of the previous update.
+ * global row) only): zstore = the K-major store of ppi_sample_gaussian_keep, 1 KB aligned, size from
+ * ppi_zstore_bytes(K, D, 0).  Issued on a side stream this hides the generator (ppi/samplers.py:18-20,
+ * np.random.randn) under the HBM- and latency-bound part of the previous update.
  * ppi_sample_gaussian_pre is ppi_sample_gaussian_keep for such a draw: only the GEMM passes run. */
-size_t ppi_philox_rows_bytes(int64_t K, int64_t D);
 int ppi_philox_prefetch(uint64_t seed, uint64_t draw_id, uint64_t row_offset, int64_t K, int64_t D,
-                        void* zrows, size_t zrows_bytes, void* zstore, size_t zstore_bytes, void* stream);
-int ppi_sample_gaussian_pre(int64_t K, int64_t D, const float* mu, const float* L, float* x,
-                            const void* zrows, void* zstore, void* workspace, size_t workspace_bytes,
-                            void* stream);
+                        void* zstore, size_t zstore_bytes, void* stream);
+int ppi_sample_gaussian_pre(int64_t K, int64_t D, const float* mu, const float* L, float* x, void* zstore,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
+/* The base normals the dense Gaussian sampler (D > 128: ppi_sample_gaussian / _keep / _cost / _pre) draws for
+ * (seed, draw_id, row_offset), as a row-major fp32 matrix (rows, cols).  That sampler keeps its normals K-major
+ * (one store serves the sampling product and the whitened covariance), so its Philox counters run down the
+ * COLUMNS: one call = samples 4Q..4Q+3 of one column (counter (Q, draw_id << 32 | column), key seed ^ tag).
+ * ppi_philox_normal is the row-quad order of every other sampler.  Same fp16-grid values, same guarantees:
+ * element (r, c) is a pure function of (seed, draw_id, row_offset + r, c). */
+int ppi_philox_normal_cq(float* out, int64_t rows, int64_t cols, uint64_t seed, uint64_t draw_id,
+                         uint64_t row_offset, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * a9  cost evaluation                                     optimization/functions.py:21-104

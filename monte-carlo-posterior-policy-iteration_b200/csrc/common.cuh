@@ -194,6 +194,30 @@ __device__ __forceinline__ void philox_normal4_h2(const PhiloxKeys& ks, uint64_t
   hi = box_muller_h2(p.z, p.w);
 }
 
+// ---- column-quad order (the dense Gaussian sampler, D > 128) ------------------------------------------------
+// The tensor-core sampler keeps its base normals K-major (tc_gemm.cu: zT[column][sample]), so its Philox
+// counters run DOWN the columns: one call yields the normals of samples 4Q .. 4Q+3 of ONE column, i.e. 8 bytes
+// that are contiguous in that store (no transposition).  counter = (Q, draw << 32 | column), key = seed ^ tag
+// (the tag keeps the stream apart from the row-quad stream of the same seed).  Element (row, col) is still a
+// pure function of (seed, draw_id, global row, col): K-sharded ranks reproduce the 1-GPU matrix.
+constexpr uint64_t kPhiloxColTag = 0x9E3779B97F4A7C15ull;
+
+__device__ __forceinline__ void philox_cq_normal4_h2(const PhiloxKeys& ks_tagged, uint64_t draw_id, uint32_t col,
+                                                     uint64_t rowquad, __half2& lo, __half2& hi) {
+  const Philox4 p = philox4x32_10(rowquad, (draw_id << 32) | (uint64_t)col, ks_tagged);
+  lo = box_muller_h2(p.x, p.y);
+  hi = box_muller_h2(p.z, p.w);
+}
+
+// one element (slow path: unaligned shards, the TF32 scheme, host-visible copies)
+__device__ __forceinline__ float philox_cq_normal1(uint64_t seed, uint64_t draw_id, uint64_t row, uint32_t col) {
+  const Philox4 p = philox4x32_10(row >> 2, (draw_id << 32) | (uint64_t)col, seed ^ kPhiloxColTag);
+  float z0, z1;
+  if ((row & 2) == 0) box_muller(p.x, p.y, z0, z1);
+  else box_muller(p.z, p.w, z0, z1);
+  return (row & 1) ? z1 : z0;
+}
+
 // Single element e of the global matrix (slow path for unaligned access).
 __device__ __forceinline__ float philox_normal1(uint64_t seed, uint64_t draw_id, uint64_t elem) {
   float v[4];

@@ -9,12 +9,14 @@
 // and nothing else: every D^3 term is a product of (block-)triangular fp64 matrices.
 //
 // Layout.  All matrices row-major.  The factorisation works on 64 x 64 tiles of a padded copy (Dp =
-// round_up(D, 64), identity on the padded diagonal).  Right-looking blocked Cholesky, three kernels per block
-// column j (the chain  factor -> panel -> trailing update  is the critical path of the whole tail; the
-// trailing update is 64-deep rank updates spread over every SM):
-//   chol_diag_kernel   one CTA:  L_jj = chol(A_jj) in shared memory, W = L_jj^-1, log det, status
-//   chol_panel_kernel  CTA per row block i > j:  X_i = A_ij W^T        (fp64 tensor cores, mma.sync m8n8k4)
-//   chol_trail_kernel  CTA per lower tile (i, k), j < k <= i:  A_ik -= X_i X_k^T
+// round_up(D, 64), identity on the padded diagonal).  Right-looking blocked Cholesky with the look-ahead built
+// into the launch structure -- ONE launch per block column j (chol_step_kernel), whose CTAs never wait on one
+// another:
+//   A-role (CTA per row block i >= j): apply panel j-1's pending update to the own tiles of block column j
+//     (fp64 tensor cores, mma.sync m8n8k4), factor the diagonal tile in registers (4 x 4 blocks per thread; every
+//     CTA redundantly), solve the panel tile  X_i = A_ij L_jj^-T  by blocked forward substitution;
+//   B-role (CTA per lower tile (i, k), k > j): the rest of panel j-1's trailing update  A_ik -= X_i X_k^T.
+// The critical path is a chain of D / 64 launches of ~one tile factorisation + one tile solve each.
 // The factor is written twice, G and G^T, so that every product below is an "NT" contraction (both operands
 // read along their rows):
 //   dgemm_nt_kernel    C_tile(ti, tj) = sum_kt A(ti, kt) B(tj, kt)^T over the k-tiles where both triangular
@@ -105,118 +107,275 @@ struct CholScalars {      // device-side results of one factorisation (fp64, rea
   double msq;             // |m|^2 (white finish only)
 };
 
-// one CTA: factor the diagonal tile j, invert the factor, accumulate log det.
-__global__ void __launch_bounds__(kDenseThreads)
-chol_diag_kernel(double* __restrict__ a, int64_t Dp, int j, int64_t D, double* __restrict__ g,
-                 double* __restrict__ gt, double* __restrict__ winv, CholScalars* __restrict__ sc) {
-  extern __shared__ double smem[];
-  double* t = smem;                 // the tile, dense pitch (block_cholesky's layout)
-  double* w = smem + NB * NB;       // its inverse, pitch WP (odd: the 4 lanes of a column read 4 banks)
-  constexpr int WP = NB + 1;
-  __shared__ int fail;
-  __shared__ double red[32];
-  const int64_t base = (int64_t)j * NB;
-  if (sc->status != 0.0) return;    // an earlier block column already failed: nothing below is meaningful
-  for (int e = threadIdx.x; e < NB * NB; e += kDenseThreads) {
-    const int r = e >> 6, c = e & 63;
-    t[e] = a[(base + r) * Dp + base + c];
-  }
-  block_cholesky(t, NB, &fail);
-  if (fail != 0) {
-    if (threadIdx.x == 0) sc->status = (double)(base + fail);
-    return;
-  }
-  // W = L^-1, column c by 4 lanes: w_ic = -(sum_{k=c}^{i-1} l_ik w_kc) / l_ii, the dot product split in 4
-  {
-    const int c = threadIdx.x >> 2, q = threadIdx.x & 3;
-    for (int i = 0; i < NB; ++i) {
-      double s = 0.0;
-      if (i > c)
-        for (int k = c + q; k < i; k += 4) s = fma(t[i * NB + k], w[k * WP + c], s);
-      s += __shfl_xor_sync(0xffffffffu, s, 1);
-      s += __shfl_xor_sync(0xffffffffu, s, 2);
-      if (q == 0) w[i * WP + c] = i < c ? 0.0 : (i == c ? 1.0 / t[i * NB + i] : -s / t[i * NB + i]);
-      __syncwarp();
+// ---- SIMT part of a step: 256 threads = 16 x 16, thread (ty, tx) owns the 4 x 4 block (rows 4 ty.., columns
+// 4 tx..) of a 64 x 64 tile in registers.  Blocks of the factor are exchanged through shared memory in the layout
+//   Lt[kb][(a * 4 + c) * 16 + t]  =  element (a, c) of block (t, kb)          (t = block row, kb = block column)
+// so that the 16 threads of a block row / column read consecutive doubles (no bank conflicts) and the
+// threads that share a block read one address (broadcast).
+constexpr int kLtBlock = 256;     // doubles per block column of Lt: 16 entries x 16 block rows
+
+// Right-looking Cholesky of the 64 x 64 tile in Ds (pitch PITCH, lower part).  On return thread (ty >= tx) holds
+// block (ty, tx) of the factor in r, Lt holds every block column, dinv[kb] the inverse of diagonal block kb.
+// Returns false (uniformly) when a pivot fails; *fail_s = 1 + index of the first failing pivot in the tile.
+__device__ __forceinline__ bool tile_cholesky(const double* __restrict__ Ds, double* __restrict__ Lt,
+                                              double* __restrict__ dinv, int* fail_s, double (&r)[4][4]) {
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+  const bool lower = ty >= tx;
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) r[a][c] = lower ? Ds[(4 * ty + a) * PITCH + 4 * tx + c] : 0.0;
+  for (int kb = 0; kb < 16; ++kb) {
+    if (ty == kb && tx == kb) {
+      // 4 x 4 Cholesky of the diagonal block and the inverse of its factor, unrolled in registers
+      int bad = 0;
+      auto ok = [](double p) { return p > 0.0 && isfinite(p); };
+      // one reciprocal square root per pivot (l = p rsqrt(p), 1 / l = rsqrt(p)): fp64 sqrt and division are
+      // software sequences of ~200 dependent cycles each, and this chain is the serial spine of the whole tail
+      const double p0 = r[0][0];
+      if (!ok(p0)) bad = 1;
+      const double i0 = rsqrt(p0), l00 = p0 * i0;
+      const double l10 = r[1][0] * i0, l20 = r[2][0] * i0, l30 = r[3][0] * i0;
+      const double p1 = r[1][1] - l10 * l10;
+      if (!bad && !ok(p1)) bad = 2;
+      const double i1 = rsqrt(p1), l11 = p1 * i1;
+      const double l21 = (r[2][1] - l20 * l10) * i1, l31 = (r[3][1] - l30 * l10) * i1;
+      const double p2 = r[2][2] - l20 * l20 - l21 * l21;
+      if (!bad && !ok(p2)) bad = 3;
+      const double i2 = rsqrt(p2), l22 = p2 * i2;
+      const double l32 = (r[3][2] - l30 * l20 - l31 * l21) * i2;
+      const double p3 = r[3][3] - l30 * l30 - l31 * l31 - l32 * l32;
+      if (!bad && !ok(p3)) bad = 4;
+      const double i3 = rsqrt(p3), l33 = p3 * i3;
+      if (bad) *fail_s = 4 * kb + bad;
+      const double w10 = -l10 * i0 * i1, w21 = -l21 * i1 * i2, w32 = -l32 * i2 * i3;
+      const double w20 = -(l20 * i0 + l21 * w10) * i2, w31 = -(l31 * i1 + l32 * w21) * i3;
+      const double w30 = -(l30 * i0 + l31 * w10 + l32 * w20) * i3;
+      double* w = dinv + kb * 16;
+      w[0] = i0;  w[1] = 0.0; w[2] = 0.0;  w[3] = 0.0;
+      w[4] = w10; w[5] = i1;  w[6] = 0.0;  w[7] = 0.0;
+      w[8] = w20; w[9] = w21; w[10] = i2;  w[11] = 0.0;
+      w[12] = w30; w[13] = w31; w[14] = w32; w[15] = i3;
+      r[0][0] = l00; r[0][1] = 0.0; r[0][2] = 0.0; r[0][3] = 0.0;
+      r[1][0] = l10; r[1][1] = l11; r[1][2] = 0.0; r[1][3] = 0.0;
+      r[2][0] = l20; r[2][1] = l21; r[2][2] = l22; r[2][3] = 0.0;
+      r[3][0] = l30; r[3][1] = l31; r[3][2] = l32; r[3][3] = l33;
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) Lt[kb * kLtBlock + (a * 4 + c) * 16 + kb] = r[a][c];
+    }
+    __syncthreads();
+    if (*fail_s != 0) return false;
+    if (tx == kb && ty > kb) {
+      // X = A W^T with W = inverse of the diagonal factor: the final block (ty, kb) of the factor
+      const double* w = dinv + kb * 16;
+      double x[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b2 = 0; b2 < 4; ++b2) {
+          double acc = 0.0;
+#pragma unroll
+          for (int c = 0; c <= b2; ++c) acc = fma(r[a][c], w[b2 * 4 + c], acc);
+          x[a][b2] = acc;
+        }
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          r[a][c] = x[a][c];
+          Lt[kb * kLtBlock + (a * 4 + c) * 16 + ty] = x[a][c];
+        }
+    }
+    __syncthreads();
+    if (tx > kb && lower) {
+      const double* pl = Lt + kb * kLtBlock;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        double pa[4], pb[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { pa[a] = pl[(a * 4 + c) * 16 + ty]; pb[a] = pl[(a * 4 + c) * 16 + tx]; }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b2 = 0; b2 < 4; ++b2) r[a][b2] = fma(-pa[a], pb[b2], r[a][b2]);
+      }
     }
   }
-  __syncthreads();
-  double ld = 0.0;
-  for (int e = threadIdx.x; e < NB * NB; e += kDenseThreads) {
-    const int r = e >> 6, c = e & 63;
-    const double v = c <= r ? t[e] : 0.0;
-    g[(base + r) * Dp + base + c] = v;
-    gt[(base + c) * Dp + base + r] = v;
-    winv[e] = w[r * WP + c];
-    if (r == c && base + r < D) ld += log(v);
-  }
-  ld = block_sum(ld, red);
-  if (threadIdx.x == 0) sc->logdet += 2.0 * ld;
+  return true;
 }
 
-// CTA per row block i = j + 1 + blockIdx.x:  X = A_ij W^T  ->  G(i, j), G^T(j, i)
-__global__ void __launch_bounds__(kDenseThreads)
-chol_panel_kernel(const double* __restrict__ a, int64_t Dp, int j, const double* __restrict__ winv,
-                  double* __restrict__ g, double* __restrict__ gt, const CholScalars* __restrict__ sc) {
-  extern __shared__ double smem[];
-  double* As = smem;
-  double* Bs = smem + NB * PITCH;
-  if (sc->status != 0.0) return;
-  const int i = j + 1 + blockIdx.x;
-  load_tile<false>(As, a + ((int64_t)i * NB) * Dp + (int64_t)j * NB, Dp);
-  load_tile<false>(Bs, winv, NB);
-  __syncthreads();
-  TileAcc acc;
-  acc.zero();
-  tile_mma(As, Bs, acc);
-  __syncthreads();
-  // X -> G(i, j) straight from the fragments, and through shared memory (transposed) -> G^T(j, i)
-  double* gtile = g + ((int64_t)i * NB) * Dp + (int64_t)j * NB;
+// X = T L^-T for the 64 x 64 tile in Ts (pitch PITCH) and the factor held in Lt / dinv: blocked forward
+// substitution over the 16 block columns; on return thread (ty, tx) holds block (ty, tx) of X in r.
+// pn: 2 x 256 doubles of scratch (the solved block column, double-buffered: one barrier per step).
+__device__ __forceinline__ void tile_solve(const double* __restrict__ Ts, const double* __restrict__ Lt,
+                                           const double* __restrict__ dinv, double* __restrict__ pn,
+                                           double (&r)[4][4]) {
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) r[a][c] = Ts[(4 * ty + a) * PITCH + 4 * tx + c];
+  for (int kb = 0; kb < 16; ++kb) {
+    double* px = pn + (kb & 1) * kLtBlock;
+    if (tx == kb) {
+      const double* w = dinv + kb * 16;
+      double x[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b2 = 0; b2 < 4; ++b2) {
+          double acc = 0.0;
+#pragma unroll
+          for (int c = 0; c <= b2; ++c) acc = fma(r[a][c], w[b2 * 4 + c], acc);
+          x[a][b2] = acc;
+        }
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          r[a][c] = x[a][c];
+          px[(a * 4 + c) * 16 + ty] = x[a][c];
+        }
+    }
+    __syncthreads();
+    if (tx > kb) {
+      // r -= X(ty, kb) L(tx, kb)^T
+      const double* pl = Lt + kb * kLtBlock;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        double pa[4], pb[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { pa[a] = px[(a * 4 + c) * 16 + ty]; pb[a] = pl[(a * 4 + c) * 16 + tx]; }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b2 = 0; b2 < 4; ++b2) r[a][b2] = fma(-pa[a], pb[b2], r[a][b2]);
+      }
+    }
+  }
+}
+
+// subtract the DMMA accumulator from a tile in shared memory (each element has one owner)
+__device__ __forceinline__ void tile_sub(double* __restrict__ s, const TileAcc& acc) {
 #pragma unroll
   for (int ii = 0; ii < 4; ++ii)
 #pragma unroll
     for (int jj = 0; jj < 2; ++jj) {
-      const int r = acc_row(ii), c = acc_col(jj);
-      *reinterpret_cast<double2*>(gtile + (int64_t)r * Dp + c) = make_double2(acc.c[ii][jj][0], acc.c[ii][jj][1]);
-      As[c * PITCH + r] = acc.c[ii][jj][0];          // transposed staging: As[col][row]
-      As[(c + 1) * PITCH + r] = acc.c[ii][jj][1];
-    }
-  __syncthreads();
-  double* gttile = gt + ((int64_t)j * NB) * Dp + (int64_t)i * NB;
-  for (int e = threadIdx.x; e < NB * (NB / 2); e += kDenseThreads) {
-    const int r = e >> 5, c = (e & 31) * 2;
-    *reinterpret_cast<double2*>(gttile + (int64_t)r * Dp + c) = *reinterpret_cast<const double2*>(As + r * PITCH + c);
-  }
-}
-
-// CTA per lower tile (i, k) of the trailing matrix, j < k <= i:  A_ik -= X_i X_k^T
-__global__ void __launch_bounds__(kDenseThreads)
-chol_trail_kernel(double* __restrict__ a, int64_t Dp, int j, int T, const double* __restrict__ g,
-                  const CholScalars* __restrict__ sc) {
-  extern __shared__ double smem[];
-  double* As = smem;
-  double* Bs = smem + NB * PITCH;
-  if (sc->status != 0.0) return;
-  // blockIdx.x -> (i, k) with j < k <= i < T: row-major enumeration of the lower triangle of size n = T - j - 1
-  int rem = blockIdx.x, ri = 0;
-  while (rem > ri) { rem -= ri + 1; ++ri; }
-  const int i = j + 1 + ri, k = j + 1 + rem;
-  load_tile<false>(As, g + ((int64_t)i * NB) * Dp + (int64_t)j * NB, Dp);
-  load_tile<false>(Bs, g + ((int64_t)k * NB) * Dp + (int64_t)j * NB, Dp);
-  __syncthreads();
-  TileAcc acc;
-  acc.zero();
-  tile_mma(As, Bs, acc);
-  double* ct = a + ((int64_t)i * NB) * Dp + (int64_t)k * NB;
-#pragma unroll
-  for (int ii = 0; ii < 4; ++ii)
-#pragma unroll
-    for (int jj = 0; jj < 2; ++jj) {
-      double2* p = reinterpret_cast<double2*>(ct + (int64_t)acc_row(ii) * Dp + acc_col(jj));
+      double2* p = reinterpret_cast<double2*>(s + acc_row(ii) * PITCH + acc_col(jj));
       double2 v = *p;
       v.x -= acc.c[ii][jj][0];
       v.y -= acc.c[ii][jj][1];
       *p = v;
     }
+}
+
+// One launch per block column j (look-ahead built in: nothing inside a launch waits on another CTA).
+//   A-role, CTA per row block i = j .. T-1: applies the PENDING update of panel j-1 to its own tiles of block
+//     column j (A_jj -= X_j X_j^T, A_ij -= X_i X_j^T with X = G(., j-1): fp64 tensor cores), factors the
+//     diagonal tile (every CTA redundantly: the other SMs would idle), then either writes the diagonal factor
+//     (i == j) or solves its panel tile X_i = A_ij L_jj^-T and writes G(i, j), G^T(j, i);
+//   B-role, CTA per lower tile (i, k), j+1 <= k <= i: the rest of panel j-1's trailing update,
+//     A_ik -= X_i X_k^T -- independent of this step's factorisation, so it runs beside it.
+// The critical path of the factorisation is one launch per block column.
+__global__ void __launch_bounds__(kDenseThreads, 1)
+chol_step_kernel(double* __restrict__ a, int64_t Dp, int j, int T, int64_t D, double* __restrict__ g,
+                 double* __restrict__ gt, CholScalars* __restrict__ sc) {
+  extern __shared__ double smem[];
+  double* As = smem;                       // X_i           (MMA operand)
+  double* Bs = As + NB * PITCH;            // X_j / X_k     (MMA operand)
+  double* Ds = Bs + NB * PITCH;            // diagonal tile of block column j
+  double* Ts = Ds + NB * PITCH;            // this CTA's panel tile
+  double* Lt = Ts + NB * PITCH;            // factor blocks, 16 x 256
+  double* dinv = Lt + 16 * kLtBlock;       // 16 inverses of the diagonal 4 x 4 blocks
+  double* pn = dinv + 256;                 // 2 x 256 scratch of tile_solve
+  __shared__ int fail;
+  __shared__ double red[32];
+  if (sc->status != 0.0) return;           // an earlier block column failed
+  const int nA = T - j;
+  if ((int)blockIdx.x >= nA) {
+    // ---------------- B-role ----------------
+    int rem = blockIdx.x - nA, ri = 0;
+    while (rem > ri) { rem -= ri + 1; ++ri; }
+    const int i = j + 1 + ri, k = j + 1 + rem;
+    load_tile<false>(As, g + ((int64_t)i * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
+    load_tile<false>(Bs, g + ((int64_t)k * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
+    __syncthreads();
+    TileAcc acc;
+    acc.zero();
+    tile_mma(As, Bs, acc);
+    double* ct = a + ((int64_t)i * NB) * Dp + (int64_t)k * NB;
+#pragma unroll
+    for (int ii = 0; ii < 4; ++ii)
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj) {
+        double2* p = reinterpret_cast<double2*>(ct + (int64_t)acc_row(ii) * Dp + acc_col(jj));
+        double2 v = *p;
+        v.x -= acc.c[ii][jj][0];
+        v.y -= acc.c[ii][jj][1];
+        *p = v;
+      }
+    return;
+  }
+  // ---------------- A-role ----------------
+  const int i = j + blockIdx.x;
+  const bool diag_cta = i == j;
+  if (threadIdx.x == 0) fail = 0;
+  load_tile<false>(Ds, a + ((int64_t)j * NB) * Dp + (int64_t)j * NB, Dp);
+  if (!diag_cta) load_tile<false>(Ts, a + ((int64_t)i * NB) * Dp + (int64_t)j * NB, Dp);
+  if (j > 0) {
+    load_tile<false>(Bs, g + ((int64_t)j * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
+    if (!diag_cta) load_tile<false>(As, g + ((int64_t)i * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
+    __syncthreads();
+    TileAcc acc;
+    acc.zero();
+    tile_mma(Bs, Bs, acc);
+    tile_sub(Ds, acc);
+    if (!diag_cta) {
+      acc.zero();
+      tile_mma(As, Bs, acc);
+      tile_sub(Ts, acc);
+    }
+  }
+  __syncthreads();
+  double r[4][4];
+  if (!tile_cholesky(Ds, Lt, dinv, &fail, r)) {
+    if (diag_cta && threadIdx.x == 0) sc->status = (double)((int64_t)j * NB + fail);
+    return;
+  }
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+  if (diag_cta) {
+    // G(j, j) lower, zeros above; G^T(j, j); log det over the first D pivots
+    double* gtile = g + ((int64_t)j * NB) * Dp + (int64_t)j * NB;
+    double* gttile = gt + ((int64_t)j * NB) * Dp + (int64_t)j * NB;
+    double ld = 0.0;
+#pragma unroll
+    for (int aa = 0; aa < 4; ++aa)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const double v = ty >= tx ? r[aa][c] : 0.0;
+        gtile[(int64_t)(4 * ty + aa) * Dp + 4 * tx + c] = v;
+        gttile[(int64_t)(4 * tx + c) * Dp + 4 * ty + aa] = v;
+        if (ty == tx && aa == c && (int64_t)j * NB + 4 * ty + aa < D) ld += log(v);
+      }
+    ld = block_sum(ld, red);
+    if (threadIdx.x == 0) sc->logdet += 2.0 * ld;
+    return;
+  }
+  tile_solve(Ts, Lt, dinv, pn, r);
+  double* gtile = g + ((int64_t)i * NB) * Dp + (int64_t)j * NB;
+  double* gttile = gt + ((int64_t)j * NB) * Dp + (int64_t)i * NB;
+#pragma unroll
+  for (int aa = 0; aa < 4; ++aa) {
+    *reinterpret_cast<double2*>(gtile + (int64_t)(4 * ty + aa) * Dp + 4 * tx) = make_double2(r[aa][0], r[aa][1]);
+    *reinterpret_cast<double2*>(gtile + (int64_t)(4 * ty + aa) * Dp + 4 * tx + 2) = make_double2(r[aa][2], r[aa][3]);
+  }
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    *reinterpret_cast<double2*>(gttile + (int64_t)(4 * tx + c) * Dp + 4 * ty) = make_double2(r[0][c], r[1][c]);
+    *reinterpret_cast<double2*>(gttile + (int64_t)(4 * tx + c) * Dp + 4 * ty + 2) = make_double2(r[2][c], r[3][c]);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -348,30 +507,28 @@ tri_matvec_kernel(const double* __restrict__ L, int64_t D, const double* __restr
 }
 
 constexpr size_t kTileSmem = 2 * NB * PITCH * sizeof(double);   // 69 632 B: opt-in above 48 KB
-constexpr size_t kDiagSmem = (size_t)(NB * NB + NB * (NB + 1)) * sizeof(double);
+constexpr size_t kStepSmem = (size_t)(4 * NB * PITCH + 16 * kLtBlock + 256 + 2 * kLtBlock) * sizeof(double);  // 178 176 B
 
 static int64_t pad64(int64_t D) { return (D + NB - 1) / NB * NB; }
 
 static int set_dense_attrs() {
   static bool done = false;
   if (done) return 0;
-  PPI_CUDA_TRY(cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDiagSmem));
-  PPI_CUDA_TRY(cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileSmem));
-  PPI_CUDA_TRY(cudaFuncSetAttribute(chol_trail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileSmem));
+  PPI_CUDA_TRY(cudaFuncSetAttribute(chol_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStepSmem));
   PPI_CUDA_TRY(cudaFuncSetAttribute(dgemm_nt_kernel<MODE_LG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileSmem));
   PPI_CUDA_TRY(cudaFuncSetAttribute(dgemm_nt_kernel<MODE_LLT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileSmem));
   done = true;
   return 0;
 }
 
-// workspace: [scalars 1 KB][work Dp^2][G Dp^2][G^T Dp^2][W 64^2]
+// workspace: [scalars 1 KB][work Dp^2][G Dp^2][G^T Dp^2]
 struct DenseWs {
   CholScalars* sc;
-  double *work, *g, *gt, *winv;
+  double *work, *g, *gt;
 };
 static size_t dense_ws_bytes(int64_t D) {
   const int64_t Dp = pad64(D);
-  return 1024 + (size_t)(3 * Dp * Dp + NB * NB) * sizeof(double) + 256;
+  return 1024 + (size_t)(3 * Dp * Dp) * sizeof(double) + 256;
 }
 static DenseWs dense_ws(void* workspace, int64_t D) {
   const int64_t Dp = pad64(D);
@@ -381,23 +538,20 @@ static DenseWs dense_ws(void* workspace, int64_t D) {
   w.work = (double*)(p + 1024);
   w.g = w.work + Dp * Dp;
   w.gt = w.g + Dp * Dp;
-  w.winv = w.gt + Dp * Dp;
   return w;
 }
 
-// blocked factorisation of the padded matrix in ws.work -> ws.g / ws.gt, scalars in ws.sc
+// blocked factorisation of the padded matrix in ws.work -> ws.g / ws.gt, scalars in ws.sc: one launch per
+// block column
 static int chol_blocked(const DenseWs& ws, int64_t D, cudaStream_t st) {
   const int64_t Dp = pad64(D);
   const int T = (int)(Dp / NB);
   for (int j = 0; j < T; ++j) {
-    chol_diag_kernel<<<1, kDenseThreads, kDiagSmem, st>>>(ws.work, Dp, j, D, ws.g, ws.gt, ws.winv, ws.sc);
-    const int below = T - j - 1;
-    if (below > 0) {
-      chol_panel_kernel<<<below, kDenseThreads, kTileSmem, st>>>(ws.work, Dp, j, ws.winv, ws.g, ws.gt, ws.sc);
-      chol_trail_kernel<<<below * (below + 1) / 2, kDenseThreads, kTileSmem, st>>>(ws.work, Dp, j, T, ws.g, ws.sc);
-    }
+    const int nA = T - j, n = T - j - 1;
+    const int nB = j > 0 ? n * (n + 1) / 2 : 0;
+    chol_step_kernel<<<nA + nB, kDenseThreads, kStepSmem, st>>>(ws.work, Dp, j, T, D, ws.g, ws.gt, ws.sc);
   }
-  return check_launch("blocked Cholesky kernels", 3 * T - 2);
+  return check_launch("blocked Cholesky kernels", T);
 }
 
 }  // namespace ppi

@@ -213,6 +213,44 @@ __device__ __forceinline__ void issue_f16_pair_single(uint32_t tmem_d, uint32_t 
   }
 }
 
+// MN-major operand, 128-byte swizzle (cute::UMMA make_umma_desc<Major::MN>): rows of 128 B = 64 consecutive
+// MN-elements, one row per contraction index; 8 rows = one 1024-byte swizzle atom.  LBO = bytes between
+// 64-element chunks along MN, SBO = bytes between groups of 8 contraction rows.  This is how a TMA box
+// [64 columns i][64 samples] of the K-major base-normal store lands in shared memory when the SAMPLING GEMM
+// (contraction over i, N = samples) reads it: one such box per 64 samples, 8 KB apart.
+constexpr uint32_t kZBoxBytes = 64 * 128;   // [64 contraction rows][64 samples] fp16
+__device__ __forceinline__ uint64_t make_desc_mn(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)(kZBoxBytes >> 4) << 16;   // LBO: next 64 samples = next box
+  d |= (uint64_t)(1024 >> 4) << 32;         // SBO: next 8 contraction rows
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// kind::f16, fp32 accumulate, A K-major, B MN-major (b_major bit 16)
+constexpr uint32_t kIdescF16Bmn = kIdescF16 | (1u << 16);
+
+// FP16X2 pair x single with B = base normals straight from the K-major store (MN-major for this product):
+// A rows [h1 x 32 | h2 x 32] of the 32-deep k-block `half` of the stage; B = four boxes of 64 samples,
+// contraction rows 32 half .. 32 half + 31 of the stage (16 per MMA: two swizzle atoms, 2 KB).
+__device__ __forceinline__ void issue_f16_pair_store(uint32_t tmem_d, uint32_t a, uint32_t b, int half,
+                                                     uint32_t& accumulate) {
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const uint32_t off = (uint32_t)k * 32u;
+    const uint64_t bz = make_desc_mn(b + (uint32_t)(half * 2 + k) * 2048u);
+    tc_mma_f16(tmem_d, make_desc(a + off), bz, kIdescF16Bmn, accumulate);
+    accumulate = 1u;
+    tc_mma_f16(tmem_d, make_desc(a + 64u + off), bz, kIdescF16Bmn, 1u);
+  }
+}
+
+template <int N>
+__device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N>
+__device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+
 // ---- shared CTA prologue: barriers + TMEM allocation ----------------------------------------------
 struct GemmSmem {
   uint32_t base;      // 1024-aligned shared address of stage 0
@@ -223,7 +261,7 @@ struct GemmSmem {
   __device__ __forceinline__ uint32_t tempty_bar(int b) const { return bar_base + 8u * (2 * kMaxStages + 2 + b); }
 };
 
-__device__ __forceinline__ uint32_t gemm_prologue(uint8_t* smem_raw, GemmSmem& gs) {
+__device__ __forceinline__ uint32_t gemm_prologue(uint8_t* smem_raw, GemmSmem& gs, int epi_warps = 8) {
   const uint32_t raw = smem_u32(smem_raw);
   gs.base = (raw + 1023u) & ~1023u;
   gs.bar_base = gs.base + kPipeBytes;
@@ -233,7 +271,7 @@ __device__ __forceinline__ uint32_t gemm_prologue(uint8_t* smem_raw, GemmSmem& g
   const int warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) {
     for (int s = 0; s < kMaxStages; ++s) { mbar_init(gs.full_bar(s), 1); mbar_init(gs.empty_bar(s), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(gs.tfull_bar(b), 1); mbar_init(gs.tempty_bar(b), 8); }
+    for (int b = 0; b < 2; ++b) { mbar_init(gs.tfull_bar(b), 1); mbar_init(gs.tempty_bar(b), epi_warps); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -261,6 +299,18 @@ __device__ __forceinline__ void gemm_teardown(uint32_t tmem_base) {
 __device__ __forceinline__ void drain_add(uint32_t taddr, float (&acc)[128]) {
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
+    uint32_t v[32];
+    tc_ld32(taddr + j * 32, v);
+    tc_wait_ld();
+#pragma unroll
+    for (int i = 0; i < 32; ++i) acc[j * 32 + i] += __uint_as_float(v[i]);
+  }
+}
+
+// acc[64] += the 64 columns [col0, col0+64) of this warp's TMEM lane quarter
+__device__ __forceinline__ void drain_add64(uint32_t taddr, float (&acc)[64]) {
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
     uint32_t v[32];
     tc_ld32(taddr + j * 32, v);
     tc_wait_ld();
@@ -460,6 +510,9 @@ struct SampleParams {
   float* cost_part;
   int cost_fn;          // PPI_FN_STYBLINSKI / PPI_FN_RASTRIGIN
   int64_t row0;         // first sample row of this pass inside cost_part
+  // Philox normals (FP16, !ZPAIR): map_z is the blocked K-major store zT[k / 2048][i][k % 2048]
+  int64_t store_k0;     // store sample index of this pass' first sample (multiple of 256)
+  int store_rows;       // rows per 2048-sample block of the store (round_up(D, 128))
 };
 
 // term of a separable test function at one coordinate (cost.cu has the same expressions)
@@ -472,15 +525,15 @@ __device__ __forceinline__ float fused_cost_term(int fn, float x) {
   return fmaf(x, x, -10.f * __cosf(6.283185307179586f * fr));
 }
 
-// Transpose-reduce across the warp: every lane holds t[0..127] (one value per sample, its own column); on
-// return lane l holds in t[0..3] the sums over the 32 lanes for samples 4 l .. 4 l + 3.  124 shuffles.
-__device__ __forceinline__ void warp_transpose_reduce128(float (&t)[128]) {
+// Transpose-reduce across the warp: every lane holds t[0..63] (one value per sample, its own column); on
+// return lane l holds in t[0..1] the sums over the 32 lanes for samples 2 l, 2 l + 1.  62 shuffles.
+__device__ __forceinline__ void warp_transpose_reduce64(float (&t)[64]) {
   const int lane = threadIdx.x & 31;
 #pragma unroll
-  for (int w = 64, off = 16; w >= 4; w >>= 1, off >>= 1) {
+  for (int w = 32, off = 16; w >= 2; w >>= 1, off >>= 1) {
     const bool up = (lane & off) != 0;
 #pragma unroll
-    for (int i = 0; i < 64; ++i) {
+    for (int i = 0; i < 32; ++i) {
       if (i < w) {
         const float send = up ? t[i] : t[i + w];
         const float keep = up ? t[i + w] : t[i];
@@ -490,8 +543,14 @@ __device__ __forceinline__ void warp_transpose_reduce128(float (&t)[128]) {
   }
 }
 
+// CTA = 5 warpgroups: WG0 = warp 0 TMA producer, warp 1 MMA issuer (+ two idle warps), WG1-4 = sixteen warps
+// that drain TMEM: warp w owns its hardware lane quarter (w & 3) and one 64-column (sample) group -- sixteen
+// short epilogue tails instead of eight long ones, so that the per-tile tail (bias, optional store, optional
+// cost terms + their reduction over the tile's columns) stays inside the two accumulator chunks the MMA issuer
+// can run ahead.  The register file is re-divided with setmaxnreg (WG0 40, drain warps 112 per thread).
+constexpr int kSampleThreads = 640;
 template <bool FP16, bool ZPAIR>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(kSampleThreads, 1)
 sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_constant__ CUtensorMap map_l2,
                    const __grid_constant__ CUtensorMap map_z, const __grid_constant__ CUtensorMap map_z2,
                    const SampleParams p) {
@@ -503,9 +562,9 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
   static_assert(kStages * kStageBytes == kPipeBytes, "pipeline must fill the smem budget");
 
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(16) float cost_red[2][2][4][128];   // [tile parity][sample half][lane quarter][sample]
+  __shared__ __align__(16) float cost_red[2][4][4][64];   // [tile parity][sample group][lane quarter][sample]
   GemmSmem gs;
-  const uint32_t tmem_base = gemm_prologue(smem_raw, gs);
+  const uint32_t tmem_base = gemm_prologue(smem_raw, gs, 16);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool load_zlo = !FP16 && !p.z_exact;
 
@@ -514,6 +573,8 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
   auto tiles_in_unit = [&](int pr) { return (p.tiles_j - 1 - pr != pr) ? 2 : 1; };
   auto stages_of = [&](int tj) { return min(p.num_st, ((tj + 1) * BM + KS - 1) / KS); };  // L lower triangular
 
+  if (warp < 4) {
+  reg_dec<40>();
   if (warp == 0) {
     if (lane == 0) {
       // ================= TMA producer =================
@@ -533,7 +594,13 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
               mbar_expect_tx(fb, kStageBytes);
               tma_load_2d(sb, &map_l, fb, (2 * s) * 64, tj * BM);            // L pair, k-block 2s
               tma_load_2d(sb + kABytes, &map_l, fb, (2 * s + 1) * 64, tj * BM);  // k-block 2s+1
-              tma_load_2d(sb + 2 * kABytes, &map_z, fb, s * 64, nb * BN);    // 64 exact fp16 per row
+              // base normals of columns 64 s .. 64 s + 63 for the block's 256 samples: four boxes
+              // [64 store rows][64 samples] of the K-major store (MN-major operand of this product)
+              const int64_t smp = p.store_k0 + (int64_t)nb * BN;
+              const int c0 = (int)(smp % kZBlock), rb = (int)(smp / kZBlock) * p.store_rows + s * 64;
+#pragma unroll
+              for (int b = 0; b < 4; ++b)
+                tma_load_2d(sb + 2 * kABytes + b * kZBoxBytes, &map_z, fb, c0 + 64 * b, rb);
             } else if (FP16) {
               mbar_expect_tx(fb, kStageBytes);
               tma_load_2d(sb, &map_l, fb, s * 64, tj * BM);
@@ -571,8 +638,8 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
               tc_fence_after();
               const uint32_t sb = gs.base + stage * kStageBytes;
               if (kSingle) {
-                issue_f16_pair_single(tmem_d, sb, sb + 2 * kABytes, 0, accumulate);
-                issue_f16_pair_single(tmem_d, sb + kABytes, sb + 2 * kABytes, 1, accumulate);
+                issue_f16_pair_store(tmem_d, sb, sb + 2 * kABytes, 0, accumulate);
+                issue_f16_pair_store(tmem_d, sb + kABytes, sb + 2 * kABytes, 1, accumulate);
               } else if (FP16) {
                 issue_f16_pair_pair(tmem_d, sb, sb + kABytes, accumulate);
               } else {
@@ -586,11 +653,13 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
         }
       }
     }
+  }
   } else {
+    reg_inc<112>();
     // ================= epilogue: TMEM -> registers -> global, 128 B per warp store =================
-    const int e = warp - 2;
+    const int e = warp - 4;
     const int q = warp & 3;   // TMEM lane quarter
-    const int h = e >> 2;     // sample (column) half
+    const int h = e >> 2;     // sample (column) group of 64
     const float inv_scale = p.scalars ? p.scalars->inv_scale : 1.0f;
     uint32_t ccount = 0, tile_count = 0;
     for (int64_t u = blockIdx.x; u < p.n_units; u += gridDim.x) {
@@ -600,56 +669,52 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
         const int64_t j = (int64_t)tj * BM + q * 32 + lane;
         const bool jok = j < p.D;
         const float bias = jok ? __ldg(p.mu + j) : 0.f;
-        float acc[128];
+        float acc[64];
 #pragma unroll
-        for (int i = 0; i < 128; ++i) acc[i] = 0.f;
+        for (int i = 0; i < 64; ++i) acc[i] = 0.f;
         for (int s0 = 0; s0 < nst; s0 += p.chunk_st, ++ccount) {
           const uint32_t buf = ccount & 1u;
           mbar_wait(gs.tfull_bar(buf), (ccount >> 1) & 1u);
           tc_fence_after();
-          drain_add(tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + (uint32_t)(h * 128), acc);
+          drain_add64(tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + (uint32_t)(h * 64), acc);
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(gs.tempty_bar(buf));
         }
-        const int64_t s_first = (int64_t)nb * BN + h * 128;
+        const int64_t s_first = (int64_t)nb * BN + h * 64;
         const int64_t left = p.rows - s_first;
-        if (left > 0) {                      // uniform over the four quarter warps of this sample half
+        if (left > 0) {                      // uniform over the four quarter warps of this sample group
 #pragma unroll
-          for (int c = 0; c < 128; ++c) acc[c] = fmaf(acc[c], inv_scale, bias);
+          for (int c = 0; c < 64; ++c) acc[c] = fmaf(acc[c], inv_scale, bias);
           if (jok && p.x != nullptr) {
             float* dst = p.x + s_first * p.D + j;
-            if (left >= 128) {
+            if (left >= 64) {
 #pragma unroll
-              for (int c = 0; c < 128; ++c) dst[(int64_t)c * p.D] = acc[c];
+              for (int c = 0; c < 64; ++c) dst[(int64_t)c * p.D] = acc[c];
             } else {
 #pragma unroll
-              for (int c = 0; c < 128; ++c)
+              for (int c = 0; c < 64; ++c)
                 if (c < left) dst[(int64_t)c * p.D] = acc[c];
             }
           }
           if (p.cost_part != nullptr) {
-            // cost terms of this thread's column for its 128 samples -> sums over the tile's 128 columns:
+            // cost terms of this thread's column for its 64 samples -> sums over the tile's 128 columns:
             // across the 32 lanes by the transpose-reduce, across the four quarter warps through shared memory
             // (double-buffered by tile parity: one named barrier per tile), in a FIXED order (deterministic)
 #pragma unroll
-            for (int c = 0; c < 128; ++c) acc[c] = jok ? fused_cost_term(p.cost_fn, acc[c]) : 0.f;
-            warp_transpose_reduce128(acc);
-            float* slot = &cost_red[tile_count & 1][h][q][4 * lane];
-            *reinterpret_cast<float4*>(slot) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            for (int c = 0; c < 64; ++c) acc[c] = jok ? fused_cost_term(p.cost_fn, acc[c]) : 0.f;
+            warp_transpose_reduce64(acc);
+            *reinterpret_cast<float2*>(&cost_red[tile_count & 1][h][q][2 * lane]) = make_float2(acc[0], acc[1]);
             asm volatile("bar.sync %0, %1;" ::"r"(1 + h), "r"(128) : "memory");
             if (q == 0) {
-              float4 r = *reinterpret_cast<const float4*>(&cost_red[tile_count & 1][h][0][4 * lane]);
+              float2 r = *reinterpret_cast<const float2*>(&cost_red[tile_count & 1][h][0][2 * lane]);
 #pragma unroll
               for (int qq = 1; qq < 4; ++qq) {
-                const float4 o = *reinterpret_cast<const float4*>(&cost_red[tile_count & 1][h][qq][4 * lane]);
-                r.x += o.x; r.y += o.y; r.z += o.z; r.w += o.w;
+                const float2 o = *reinterpret_cast<const float2*>(&cost_red[tile_count & 1][h][qq][2 * lane]);
+                r.x += o.x; r.y += o.y;
               }
-              const float rv[4] = {r.x, r.y, r.z, r.w};
-#pragma unroll
-              for (int u = 0; u < 4; ++u)
-                if (4 * lane + u < left)
-                  p.cost_part[(p.row0 + s_first + 4 * lane + u) * p.tiles_j + tj] = rv[u];
+              if (2 * lane < left) p.cost_part[(p.row0 + s_first + 2 * lane) * p.tiles_j + tj] = r.x;
+              if (2 * lane + 1 < left) p.cost_part[(p.row0 + s_first + 2 * lane + 1) * p.tiles_j + tj] = r.y;
             }
           }
         }
@@ -733,171 +798,6 @@ __device__ __forceinline__ void issue_f16_pair_single_2sm(uint32_t tmem_d, uint3
     tc_mma_f16_2sm(tmem_d, make_desc(a + off), bz, kIdescF16Pair, accumulate);
     accumulate = 1u;
     tc_mma_f16_2sm(tmem_d, make_desc(a + 64u + off), bz, kIdescF16Pair, 1u);
-  }
-}
-
-// ---------------------------------------------------------------------------------------------
-// Sampling kernel, CTA pairs (Philox normals):  x[s, j] = mu[j] + sum_{k<=j} L[j,k] z[s,k]
-//   One UMMA = 256 output columns j (CTA r owns j-tile 2t + r) x 256 samples; CTA r loads its own L
-//   rows (pair, 2 x 16 KB per 64-step stage) and samples [128 r, 128 r + 128) of the z block (16 KB).
-//   Work unit = (sample block, p): double tiles t = T2-1-p then t = p (equal triangular cost).
-//   Barriers: full[s] lives in the leader (both CTAs' TMA bytes complete on it); empty[s] / tfull[b]
-//   are multicast commits to both CTAs; tempty[b] lives in the leader (8 drain warps per CTA arrive).
-// ---------------------------------------------------------------------------------------------
-constexpr int kS2Stages = 4;
-constexpr uint32_t kS2StageBytes = 2 * kABytes + kABytes;  // L pair x2 (32 KB) | z half (16 KB) = 48 KB
-static_assert(kS2Stages * kS2StageBytes == kPipeBytes, "pipeline must fill the smem budget");
-
-struct Sample2Params {
-  int tiles2;           // double j-tiles: ceil(D / 256)
-  int units_per_block;  // ceil(tiles2 / 2)
-  int num_st;           // 64-step stages covering the padded contraction length
-  int chunk_st;         // stages per TMEM accumulation chunk
-  int64_t n_units;      // sample blocks * units_per_block
-  int64_t rows;         // valid samples in this pass
-  int64_t D;
-  float* x;             // [rows][D]
-  const float* mu;
-  const GemmScalars* scalars;
-};
-
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
-sample_gemm2_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_constant__ CUtensorMap map_z,
-                    const Sample2Params p) {
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw = smem_u32(smem_raw);
-  GemmSmem gs;
-  gs.base = (raw + 1023u) & ~1023u;
-  gs.bar_base = gs.base + kPipeBytes;
-  uint8_t* smem = smem_raw + (gs.base - raw);
-  volatile uint32_t* tmem_ptr_smem =
-      reinterpret_cast<volatile uint32_t*>(smem + kPipeBytes + 8 * (2 * kMaxStages + 4));
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();
-  const bool leader = rank == 0;
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < kMaxStages; ++s) { mbar_init(gs.full_bar(s), 1); mbar_init(gs.empty_bar(s), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(gs.tfull_bar(b), 1); mbar_init(gs.tempty_bar(b), 16); }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;"
-                 ::"r"(smem_u32((const void*)tmem_ptr_smem)), "r"(512) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-  }
-  tc_fence_before();
-  cluster_sync_all();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr_smem;
-
-  const int64_t cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;   // cluster index / count
-  auto tile2 = [&](int pr, int tt) { return tt == 0 ? p.tiles2 - 1 - pr : pr; };
-  auto tiles_in_unit = [&](int pr) { return (p.tiles2 - 1 - pr != pr) ? 2 : 1; };
-  auto stages_of = [&](int t2) { return min(p.num_st, ((t2 + 1) * 256 + 63) / 64); };  // L lower triangular
-
-  if (warp == 0) {
-    if (lane == 0) {
-      // ================= TMA producer (both CTAs) =================
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_l) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_z) : "memory");
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int64_t u = cid; u < p.n_units; u += ncl) {
-        const int nb = (int)(u / p.units_per_block), pr = (int)(u % p.units_per_block);
-        for (int tt = 0; tt < tiles_in_unit(pr); ++tt) {
-          const int t2 = tile2(pr, tt), nst = stages_of(t2);
-          const int jrow = (2 * t2 + (int)rank) * BM;
-          for (int s = 0; s < nst; ++s) {
-            mbar_wait(gs.empty_bar(stage), phase ^ 1u);
-            const uint32_t sb = gs.base + stage * kS2StageBytes;
-            const uint32_t fb = gs.full_bar(stage);
-            if (leader) mbar_expect_tx(fb, 2 * kS2StageBytes);   // the bytes of both CTAs
-            tma_load_2d_2sm(sb, &map_l, fb, (2 * s) * 64, jrow);
-            tma_load_2d_2sm(sb + kABytes, &map_l, fb, (2 * s + 1) * 64, jrow);
-            tma_load_2d_2sm(sb + 2 * kABytes, &map_z, fb, s * 64, nb * BN + (int)rank * 128);
-            if (++stage == kS2Stages) { stage = 0; phase ^= 1u; }
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0 && leader) {
-      // ================= MMA issuer (leader CTA only) =================
-      int stage = 0;
-      uint32_t phase = 0, ccount = 0;
-      for (int64_t u = cid; u < p.n_units; u += ncl) {
-        const int pr = (int)(u % p.units_per_block);
-        for (int tt = 0; tt < tiles_in_unit(pr); ++tt) {
-          const int nst = stages_of(tile2(pr, tt));
-          for (int s0 = 0; s0 < nst; s0 += p.chunk_st, ++ccount) {
-            const uint32_t buf = ccount & 1u;
-            mbar_wait_cluster(gs.tempty_bar(buf), ((ccount >> 1) & 1u) ^ 1u);
-            tc_fence_after();
-            const uint32_t tmem_d = tmem_base + buf * BN;
-            uint32_t accumulate = 0;
-            const int s1 = min(nst, s0 + p.chunk_st);
-            for (int s = s0; s < s1; ++s) {
-              mbar_wait_cluster(gs.full_bar(stage), phase);
-              tc_fence_after();
-              const uint32_t sb = gs.base + stage * kS2StageBytes;
-              issue_f16_pair_single_2sm(tmem_d, sb, sb + 2 * kABytes, 0, accumulate);
-              issue_f16_pair_single_2sm(tmem_d, sb + kABytes, sb + 2 * kABytes, 1, accumulate);
-              tc_commit_2sm(gs.empty_bar(stage));
-              if (++stage == kS2Stages) { stage = 0; phase ^= 1u; }
-            }
-            tc_commit_2sm(gs.tfull_bar(buf));
-          }
-        }
-      }
-    }
-  } else {
-    // ================= epilogue (both CTAs): TMEM -> registers -> global =================
-    const int e = warp - 2;
-    const int q = warp & 3;   // TMEM lane quarter
-    const int h = e >> 2;     // sample (column) half
-    const float inv_scale = p.scalars ? p.scalars->inv_scale : 1.0f;
-    uint32_t ccount = 0;
-    for (int64_t u = cid; u < p.n_units; u += ncl) {
-      const int nb = (int)(u / p.units_per_block), pr = (int)(u % p.units_per_block);
-      for (int tt = 0; tt < tiles_in_unit(pr); ++tt) {
-        const int t2 = tile2(pr, tt), nst = stages_of(t2);
-        const int64_t j = (int64_t)(2 * t2 + (int)rank) * BM + q * 32 + lane;
-        const bool jok = j < p.D;
-        const float bias = jok ? __ldg(p.mu + j) : 0.f;
-        float acc[128];
-#pragma unroll
-        for (int i = 0; i < 128; ++i) acc[i] = 0.f;
-        for (int s0 = 0; s0 < nst; s0 += p.chunk_st, ++ccount) {
-          const uint32_t buf = ccount & 1u;
-          mbar_wait(gs.tfull_bar(buf), (ccount >> 1) & 1u);
-          tc_fence_after();
-          drain_add(tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + (uint32_t)(h * 128), acc);
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(mapa_rank(gs.tempty_bar(buf), 0));
-        }
-        const int64_t s_first = (int64_t)nb * BN + h * 128;
-        const int64_t left = p.rows - s_first;
-        if (jok && left > 0) {
-          float* dst = p.x + s_first * p.D + j;
-          if (left >= 128) {
-#pragma unroll
-            for (int c = 0; c < 128; ++c) dst[(int64_t)c * p.D] = fmaf(acc[c], inv_scale, bias);
-          } else {
-#pragma unroll
-            for (int c = 0; c < 128; ++c)
-              if (c < left) dst[(int64_t)c * p.D] = fmaf(acc[c], inv_scale, bias);
-          }
-        }
-      }
-    }
-  }
-  tc_fence_before();
-  cluster_sync_all();
-  if (warp == 1) {
-    __syncwarp();
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512)
-                 : "memory");
   }
 }
 
@@ -1074,10 +974,8 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
   const float scale = (src && scale_ptr) ? *scale_ptr : 1.f;
   const int nq_row = (int)(cols_p / 4);
   const bool quad_rng = (cols & 3) == 0;
-  const PhiloxKeys keys = philox_keys(seed);
   // one row per block iteration; threads stride over the row's quads (no 64-bit divisions)
   for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
-    const uint64_t e_row = (row_offset + (uint64_t)r) * (uint64_t)cols;
     for (int q = threadIdx.x; q < nq_row; q += blockDim.x) {
       const int64_t c = (int64_t)q * 4;
       float v[4] = {0.f, 0.f, 0.f, 0.f};
@@ -1091,73 +989,81 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
           for (int u = 0; u < 4; ++u)
             if (c + u < cols && (!lower_only || c + u <= r)) v[u] = scale * __ldg(src + r * cols + c + u);
         }
-      } else if (quad_rng) {
-        if (c < cols) philox_normal4(keys, draw, (e_row + (uint64_t)c) >> 2, v);
-      } else {
+      } else {   // Philox normals of the dense Gaussian sampler: column-quad order (element by element here;
+                 // the FP16X2 scheme generates its store with philox_store_kernel, this is the TF32X3 path)
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-          if (c + u < cols) v[u] = philox_normal1(seed, draw, e_row + (uint64_t)c + u);
+          if (c + u < cols) v[u] = philox_cq_normal1(seed, draw, row_offset + (uint64_t)r, (uint32_t)(c + u));
       }
       store_split4<MODE>(v, r, c, cols_p, op_a, op_b);
     }
   }
 }
 
-// Philox normals of `rows` sample rows (rows % 64 == 0) written twice: sample-major exact fp16
-// rows [rows][cols_p] (operand of the sampling GEMM, contraction over columns) and K-major into the
-// base-normal store zt[i][k0 + r] (operand of the whitened moment match, contraction over samples).
-// Tile = 64 samples x 128 columns through shared memory.
+// Base normals of the dense Gaussian sampler, generated straight into the blocked K-major store
+//   zT[k / 2048][i][k % 2048] = z[k][i]      (k = local sample, i = column, exact fp16)
+// with the column-quad Philox order (common.cuh): one call = samples 4Q .. 4Q+3 of one column = 8 contiguous
+// bytes of the store, so a thread writes 8 samples (two calls) as one 16-byte store and a warp 512 contiguous
+// bytes; one block = one whole 4 KB row of a store block.  No shared memory, no transposition.
+// Samples >= rows_valid and columns >= D are written as zeros (finite operands for the padded tiles).
 __global__ void __launch_bounds__(256)
-philox_dual_kernel(int64_t rows, int64_t cols, int64_t cols_p, uint64_t seed, uint64_t draw,
-                   uint64_t row_offset, uint16_t* __restrict__ op_rows, uint16_t* __restrict__ zt,
-                   int64_t zt_rows, int64_t k0) {
-  constexpr int kPitch = 130;  // halfs per tile row (65 words: the 8-sample column gathers spread over banks)
-  __shared__ __half tile[64 * kPitch];
-  const bool quad_rng = (cols & 3) == 0;
-  const PhiloxKeys keys = philox_keys(seed);
-  const int64_t tiles_c = ceil_div(zt_rows, 128);
-  const int64_t n_tiles = (rows / 64) * tiles_c;
-  for (int64_t tile_id = blockIdx.x; tile_id < n_tiles; tile_id += gridDim.x) {
-    const int64_t tr = tile_id / tiles_c, tc = tile_id % tiles_c;
-    for (int q = threadIdx.x; q < 64 * 32; q += 256) {
-      const int r = q >> 5, c4 = (q & 31) * 4;
-      const int64_t row = tr * 64 + r, col = tc * 128 + c4;
-      __half2 h01 = __floats2half2_rn(0.f, 0.f), h23 = h01;
-      const uint64_t e_row = (row_offset + (uint64_t)row) * (uint64_t)cols;
-      if (col < cols) {
-        if (quad_rng) {
-          philox_normal4_h2(keys, draw, (e_row + (uint64_t)col) >> 2, h01, h23);
-        } else {
-          float v[4] = {0.f, 0.f, 0.f, 0.f};
+philox_store_kernel(uint16_t* __restrict__ zt, int64_t store_rows, int64_t n_blocks, int64_t rows_valid,
+                    int64_t D, uint64_t seed, uint64_t draw, uint64_t row_offset) {
+  const PhiloxKeys keys = philox_keys(seed ^ kPhiloxColTag);
+  const bool aligned = (row_offset & 3) == 0;
+  const int64_t items = n_blocks * store_rows;
+  for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
+    const int64_t blk = it / store_rows, i = it % store_rows;
+    const int64_t k = blk * kZBlock + (int64_t)threadIdx.x * 8;       // first local sample of this thread
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (i < D && k < rows_valid) {
+      if (aligned && k + 8 <= rows_valid) {
+        __half2 a0, a1, b0, b1;
+        const uint64_t q = (row_offset + (uint64_t)k) >> 2;
+        philox_cq_normal4_h2(keys, draw, (uint32_t)i, q, a0, a1);
+        philox_cq_normal4_h2(keys, draw, (uint32_t)i, q + 1, b0, b1);
+        o.x = *reinterpret_cast<const uint32_t*>(&a0);
+        o.y = *reinterpret_cast<const uint32_t*>(&a1);
+        o.z = *reinterpret_cast<const uint32_t*>(&b0);
+        o.w = *reinterpret_cast<const uint32_t*>(&b1);
+      } else {   // unaligned shard offset or the ragged end: element by element
+        uint16_t h[8];
 #pragma unroll
-          for (int u = 0; u < 4; ++u)
-            if (col + u < cols) v[u] = philox_normal1(seed, draw, e_row + (uint64_t)col + u);
-          h01 = __floats2half2_rn(v[0], v[1]);
-          h23 = __floats2half2_rn(v[2], v[3]);
+        for (int u = 0; u < 8; ++u) {
+          const float v = (k + u < rows_valid) ? philox_cq_normal1(seed, draw, row_offset + (uint64_t)(k + u), (uint32_t)i)
+                                                : 0.f;
+          const __half hv = __float2half_rn(v);
+          h[u] = *reinterpret_cast<const uint16_t*>(&hv);
         }
-      }
-      if (col < cols_p)
-        *reinterpret_cast<uint2*>(op_rows + row * cols_p + col) =
-            make_uint2(*reinterpret_cast<const uint32_t*>(&h01), *reinterpret_cast<const uint32_t*>(&h23));
-      __half2* t2 = reinterpret_cast<__half2*>(tile + r * kPitch + c4);
-      t2[0] = h01;
-      t2[1] = h23;
-    }
-    __syncthreads();
-    for (int e = threadIdx.x; e < 128 * 8; e += 256) {
-      const int g = e & 7, cl = e >> 3;
-      const int64_t col = tc * 128 + cl;
-      if (col < zt_rows) {
-        const uint16_t* tp = reinterpret_cast<const uint16_t*>(tile) + (g * 8) * kPitch + cl;
-        uint4 o;
-        o.x = (uint32_t)tp[0] | ((uint32_t)tp[kPitch] << 16);
-        o.y = (uint32_t)tp[2 * kPitch] | ((uint32_t)tp[3 * kPitch] << 16);
-        o.z = (uint32_t)tp[4 * kPitch] | ((uint32_t)tp[5 * kPitch] << 16);
-        o.w = (uint32_t)tp[6 * kPitch] | ((uint32_t)tp[7 * kPitch] << 16);
-        *reinterpret_cast<uint4*>(zt + zt_index(k0 + tr * 64 + g * 8, col, zt_rows)) = o;
+        o.x = (uint32_t)h[0] | ((uint32_t)h[1] << 16);
+        o.y = (uint32_t)h[2] | ((uint32_t)h[3] << 16);
+        o.z = (uint32_t)h[4] | ((uint32_t)h[5] << 16);
+        o.w = (uint32_t)h[6] | ((uint32_t)h[7] << 16);
       }
     }
-    __syncthreads();
+    *reinterpret_cast<uint4*>(zt + (blk * store_rows + i) * kZBlock + (int64_t)threadIdx.x * 8) = o;
+  }
+}
+
+// The same draw as a row-major fp32 matrix (rows, cols): what the store holds, for callers that want to look at
+// the base normals (tests, ppi_philox_normal_cq).  Thread = (row quad, column), columns fastest.
+__global__ void __launch_bounds__(256)
+philox_cq_matrix_kernel(float* __restrict__ out, int64_t rows, int64_t cols, uint64_t seed, uint64_t draw,
+                        uint64_t row_offset) {
+  const int64_t nq = (rows + 3) / 4 + 1;    // row quads that can intersect [row_offset, row_offset + rows)
+  const uint64_t q0 = row_offset >> 2;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nq * cols; e += stride) {
+    const int64_t qi = e / cols, c = e % cols;
+    const Philox4 p = philox4x32_10(q0 + (uint64_t)qi, (draw << 32) | (uint64_t)c, seed ^ kPhiloxColTag);
+    float v[4];
+    box_muller(p.x, p.y, v[0], v[1]);
+    box_muller(p.z, p.w, v[2], v[3]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t r = (int64_t)((q0 + (uint64_t)qi) * 4 + u) - (int64_t)row_offset;
+      if (r >= 0 && r < rows) out[r * cols + c] = v[u];
+    }
   }
 }
 
@@ -1635,10 +1541,6 @@ struct WhiteParams {
   const uint16_t* wb;
 };
 
-template <int N>
-__device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
-template <int N>
-__device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 
 __global__ void __launch_bounds__(kWhiteThreads, 1)
 syrk_white_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
@@ -1998,23 +1900,19 @@ int ppi_sample_gaussian_small(const float* z, uint64_t seed, uint64_t draw_id, u
                               cudaStream_t st);
 
 static int64_t sample_kc(int64_t K) { return round_up(K < kSampleKc ? K : kSampleKc, BN); }
+// staging bytes of one pass: pair / tf32 rows (4 B per value) or, for Philox normals, a mini store of whole
+// 2048-sample blocks (2 B per value, round_up(D, 128) rows per block)
+static size_t sample_z_bytes(int64_t Kc, int64_t D) {
+  const size_t rows = (size_t)Kc * round_up(D, 64) * sizeof(float);
+  const size_t store = (size_t)round_up(Kc, kZBlock) * round_up(D, BM) * sizeof(uint16_t);
+  return rows > store ? rows : store;
+}
 
 extern "C" size_t ppi_sample_gaussian_workspace_bytes(int64_t K, int64_t D) {
   if (K <= 0 || D <= 128) return 0;
   const int64_t Dk = round_up(D, 64);
-  return kScalarBytes + 2 * (size_t)D * Dk * sizeof(float) +
-         2 * (size_t)sample_kc(K) * Dk * sizeof(float) + 1024;
+  return kScalarBytes + 2 * (size_t)D * Dk * sizeof(float) + 2 * sample_z_bytes(sample_kc(K), D) + 1024;
 }
-
-// FP16: L -> fp16 pair; z -> one exact fp16 (Philox, ZPAIR = false) or an fp16 pair (injected).
-// !FP16: TF32X3 (ZPAIR ignored; the low-order z operand is skipped for Philox normals).
-// Base-normal store kept for the whitened moment match (ppi_sample_gaussian_keep /
-// ppi_wmoments_white): a 1 KB header (GemmScalars of the sampling call: scale_b = power-of-two scale
-// of the stored injected normals, amax_b_bits = max |z|) followed by
-//   Philox    zT[k / 2048][i][k % 2048] = z[k][i]: blocks of 2048 samples x round_up(D, 128) rows of exact
-//             fp16, i.e. already K-major for the contraction over samples (2 B per value)
-//   injected  round_up(K, 256) sample rows of round_up(D, 64) / 32 blocks [h1 x 32 | h2 x 32] fp16
-//             (4 B per value, scaled by scale_b)
 
 // sum of the per-tile partial costs in a fixed order + the function's affine part
 __global__ void __launch_bounds__(256)
@@ -2030,26 +1928,47 @@ cost_finish_kernel(const float* __restrict__ part, int64_t K, int tiles, int fn,
   }
 }
 
+// Philox base normals of local samples [0, rows_valid) of a draw into a blocked K-major store of n_blocks
+// 2048-sample blocks (column-quad order; the rest of the last block and the padded rows are zero-filled).
+static int generate_store(uint16_t* zt, int64_t n_blocks, int64_t rows_valid, int64_t D, uint64_t seed,
+                          uint64_t draw_id, uint64_t row_offset, int blocks_per_sm, cudaStream_t st) {
+  const int64_t store_rows = round_up(D, BM);
+  ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st);
+  philox_store_kernel<<<grid_cap(n_blocks * store_rows, blocks_per_sm), 256, 0, st>>>(
+      zt, store_rows, n_blocks, rows_valid, D, seed, draw_id, row_offset);
+  return check_launch("philox_store_kernel");
+}
+
+// FP16: L -> fp16 pair; z -> one exact fp16 (Philox, ZPAIR = false) or an fp16 pair (injected).
+// !FP16: TF32X3 (ZPAIR ignored; the low-order z operand is skipped for Philox normals).
+// Base-normal store kept for the whitened moment match (ppi_sample_gaussian_keep /
+// ppi_wmoments_white): a 1 KB header (GemmScalars of the sampling call: scale_b = power-of-two scale
+// of the stored injected normals, amax_b_bits = max |z|) followed by
+//   Philox    zT[k / 2048][i][k % 2048] = z[k][i]: blocks of 2048 samples x round_up(D, 128) rows of exact
+//             fp16 (2 B per value).  K-major for the contraction over samples (covariance) and read as an
+//             MN-major operand by the contraction over columns (sampling): the ONLY copy of the base normals
+//   injected  round_up(K, 256) sample rows of round_up(D, 64) / 32 blocks [h1 x 32 | h2 x 32] fp16
+//             (4 B per value, scaled by scale_b)
 template <bool FP16, bool ZPAIR>
 static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
                                 int64_t K, int64_t D, const float* mu, const float* L, float* x,
                                 void* workspace, void* zstore, cudaStream_t st,
-                                const void* zrows_pre = nullptr, int cost_fn = -1, float* cost_out = nullptr) {
-  // zrows_pre: the draw's sample-major fp16 operand rows AND its K-major store were generated ahead of
-  // time (ppi_philox_prefetch): no staging passes, the GEMMs read the rows in place
+                                bool store_ready = false, int cost_fn = -1, float* cost_out = nullptr) {
+  // store_ready: the Philox store was generated ahead of time (ppi_philox_prefetch): only the GEMMs run
   constexpr int LMODE = FP16 ? OP_F16_PAIR : OP_TF32X3;
   constexpr int ZMODE = FP16 ? (ZPAIR ? OP_F16_PAIR : OP_F16_SINGLE) : OP_TF32X3;
-  constexpr int KS = (FP16 && !ZPAIR) ? 64 : 32;
-  const int64_t Dk = round_up(D, 64);
+  constexpr bool kStore = FP16 && !ZPAIR;       // Philox normals: the GEMM reads a blocked K-major store
+  constexpr int KS = kStore ? 64 : 32;
+  const int64_t Dk = round_up(D, 64), Dp = round_up(D, BM);
   const int64_t Kc = sample_kc(K);
   char* wsp = (char*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
-  const size_t l_bytes = (size_t)D * Dk * sizeof(float), z_bytes = (size_t)Kc * Dk * sizeof(float);
+  const size_t l_bytes = (size_t)D * Dk * sizeof(float), z_bytes = sample_z_bytes(Kc, D);
   GemmScalars* scalars = FP16 ? (GemmScalars*)wsp : nullptr;
   void* l_a = (void*)(wsp + kScalarBytes);
   void* l_b = (void*)(wsp + kScalarBytes + l_bytes);
   void* z_a = (void*)(wsp + kScalarBytes + 2 * l_bytes);
   void* z_b = (void*)(wsp + kScalarBytes + 2 * l_bytes + z_bytes);
-  const bool z_exact = (z == nullptr);  // Philox normals sit on the TF32 grid (common.cuh box_muller)
+  const bool z_exact = (z == nullptr);  // Philox normals sit on the fp16 (hence TF32) grid (common.cuh box_muller)
 
   if (FP16) {
     PPI_CUDA_TRY(cudaMemsetAsync(scalars, 0, sizeof(GemmScalars), st));
@@ -2067,18 +1986,36 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
   if (int rc = check_launch("split_rows_kernel(L)")) return rc;
 
   // injected normals + store: every pass stages its (pair) rows straight into the store (no ping-pong);
-  // Philox + store: the staging kernel writes the ping-pong rows AND the K-major store
+  // Philox + store: the whole store is generated up front, the passes read it in place;
+  // Philox without a store: every pass generates a mini store of its own samples in the workspace
   char* store_rows = zstore ? (char*)zstore + kScalarBytes : nullptr;
   const size_t store_row_bytes = zstore_row_bytes(D);
   const bool store_pairs = zstore && ZPAIR;
-  const bool overlap = FP16 && gemm_overlap() && K > Kc && !store_pairs && !zrows_pre;
+  const bool whole_store = zstore && kStore;
+  const bool overlap = FP16 && gemm_overlap() && K > Kc && !store_pairs && !whole_store;
   void* zbufs[2] = {z_a, FP16 ? z_b : z_a};
   CUtensorMap ml, ml2, mz[2], mz2[2];
   if (int rc = make_map(&ml, l_a, D, Dk, BM, LMODE)) return rc;
   ml2 = ml;
-  for (int i = 0; i < (FP16 ? 2 : 1) && !store_pairs; ++i) {
-    if (int rc = make_map(&mz[i], zbufs[i], Kc, Dk, BN, ZMODE)) return rc;
-    mz2[i] = mz[i];
+  if (kStore) {
+    if (whole_store) {
+      const int64_t n_blocks = zstore_kt(K) / kZBlock;
+      if (!store_ready)
+        if (int rc = generate_store((uint16_t*)store_rows, n_blocks, K, D, seed, draw_id, row_offset, 8, st)) return rc;
+      if (int rc = make_map(&mz[0], store_rows, n_blocks * Dp, kZBlock, 64, OP_F16_SINGLE)) return rc;
+      mz[1] = mz[0];
+    } else {
+      const int64_t n_blocks = round_up(Kc, kZBlock) / kZBlock;
+      for (int i = 0; i < 2; ++i)
+        if (int rc = make_map(&mz[i], zbufs[i], n_blocks * Dp, kZBlock, 64, OP_F16_SINGLE)) return rc;
+    }
+    mz2[0] = mz[0];
+    mz2[1] = mz[1];
+  } else {
+    for (int i = 0; i < (FP16 ? 2 : 1) && !store_pairs; ++i) {
+      if (int rc = make_map(&mz[i], zbufs[i], Kc, Dk, BN, ZMODE)) return rc;
+      mz2[i] = mz[i];
+    }
   }
   if (zstore && FP16)  // header: the scales of this call (read by ppi_wmoments_white)
     PPI_CUDA_TRY(cudaMemcpyAsync(zstore, scalars, sizeof(GemmScalars), cudaMemcpyDeviceToDevice, st));
@@ -2096,7 +2033,7 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
   p.tiles_j = (int)ceil_div(D, BM);
   p.units_per_block = (p.tiles_j + 1) / 2;
   p.num_st = (int)(Dk / KS);
-  p.chunk_st = (FP16 && !ZPAIR) ? gemm_chunk() / 2 : gemm_chunk();  // same 32-step boundaries in every variant
+  p.chunk_st = kStore ? gemm_chunk() / 2 : gemm_chunk();  // same 32-step boundaries in every variant
   p.D = D;
   p.mu = mu;
   p.scalars = scalars;
@@ -2105,6 +2042,8 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
   p.cost_part = cost_out ? (float*)(wsp + kScalarBytes + 2 * l_bytes + 2 * z_bytes) : nullptr;
   p.cost_fn = cost_fn;
   p.row0 = 0;
+  p.store_k0 = 0;
+  p.store_rows = (int)Dp;
 
   SideStream* ss = nullptr;
   cudaStream_t st_op = st;
@@ -2120,33 +2059,23 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
     const int64_t rows = (K - k0) < Kc ? (K - k0) : Kc;
     const int64_t rows_p = round_up(rows, BN);
     p.row0 = k0;
+    p.store_k0 = whole_store ? k0 : 0;
     if (store_pairs) {
       zbufs[0] = store_rows + (size_t)k0 * store_row_bytes;
       if (int rc = make_map(&mz[0], zbufs[0], rows_p, Dk, BN, ZMODE)) return rc;
       mz2[0] = mz[0];
     }
-    if (zrows_pre) {
-      zbufs[0] = (char*)zrows_pre + (size_t)k0 * Dk * sizeof(uint16_t);
-      if (int rc = make_map(&mz[0], zbufs[0], rows_p, Dk, BN, ZMODE)) return rc;
-      mz2[0] = mz[0];
-    }
-    // injected: rows beyond `rows` keep stale workspace values whose products are never stored;
-    // Philox: they are generated too (harmless)
-    if (!zrows_pre) {
+    if (!whole_store) {
+      // injected: rows beyond `rows` keep stale workspace values whose products are never stored;
+      // Philox: the mini store is zero-filled beyond `rows`
       if (overlap && pass >= 2) PPI_CUDA_TRY(cudaStreamWaitEvent(st_op, ss->gemm_done[bi], 0));
-      ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st_op);
-      const int64_t nrows = z ? rows : rows_p;
-      if (zstore && !ZPAIR) {
-        const int64_t zt_rows = round_up(D, BM);
-        philox_dual_kernel<<<grid_cap((nrows / 64) * ceil_div(zt_rows, 128), 6), 256, 0, st_op>>>(
-            nrows, D, Dk, seed, draw_id, row_offset + (uint64_t)k0, (uint16_t*)zbufs[bi],
-            (uint16_t*)store_rows, zt_rows, k0);
-        if (int rc = check_launch("philox_dual_kernel")) return rc;
-        const int64_t k_end = k0 + nrows, rem = k_end % kZBlock;
-        if (k_end >= K && rem)  // zero the unwritten tail of the last sample block (finite operands)
-          PPI_CUDA_TRY(cudaMemset2DAsync((uint16_t*)store_rows + zt_index(k_end, 0, zt_rows), kZBlock * 2, 0,
-                                         (kZBlock - rem) * 2, zt_rows, st_op));
+      if (kStore) {
+        if (int rc = generate_store((uint16_t*)zbufs[bi], round_up(rows_p, kZBlock) / kZBlock, rows, D, seed, draw_id,
+                                    row_offset + (uint64_t)k0, 8, st_op))
+          return rc;
       } else {
+        ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st_op);
+        const int64_t nrows = z ? rows : rows_p;
         split_rows_kernel<ZMODE><<<grid_cap(nrows, 8), 256, 0, st_op>>>(
             z ? z + k0 * D : nullptr, nrows, D, Dk, seed, draw_id, row_offset + (uint64_t)k0, 0,
             FP16 ? &scalars->scale_b : nullptr, zbufs[bi], (!FP16 && !z_exact) ? z_b : nullptr);
@@ -2161,33 +2090,9 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
     p.rows = rows;
     p.x = x ? x + k0 * D : nullptr;
     const unsigned g = (unsigned)(p.n_units < kNumSMs ? p.n_units : kNumSMs);
-    if (FP16 && !ZPAIR && gemm_pair() && !cost_out && x) {
-      // CTA pairs (cta_group::2): each CTA loads its own L rows and half of the z block
-      static bool attr2_set = false;
-      if (!attr2_set) {
-        if (int rc = set_gemm_smem(sample_gemm2_kernel)) return rc;
-        attr2_set = true;
-      }
-      CUtensorMap mzh;
-      if (int rc = make_map(&mzh, zbufs[bi], rows_p, Dk, BM, ZMODE)) return rc;
-      Sample2Params p2;
-      p2.tiles2 = (int)ceil_div(D, 2 * BM);
-      p2.units_per_block = (p2.tiles2 + 1) / 2;
-      p2.num_st = p.num_st;
-      p2.chunk_st = p.chunk_st;
-      p2.n_units = (rows_p / BN) * p2.units_per_block;
-      p2.rows = rows;
-      p2.D = D;
-      p2.x = p.x;
-      p2.mu = mu;
-      p2.scalars = scalars;
-      int64_t ncl = p2.n_units < kNumSMs / 2 ? p2.n_units : kNumSMs / 2;
+    {
       ProfileScope prof(PPI_PROF_SAMPLE_GEMM, st);
-      sample_gemm2_kernel<<<(unsigned)(2 * ncl), kGemmThreads, kGemmSmemBytes, st>>>(ml, mzh, p2);
-      if (int rc = check_launch("sample_gemm2_kernel")) return rc;
-    } else {
-      ProfileScope prof(PPI_PROF_SAMPLE_GEMM, st);
-      sample_gemm_kernel<FP16, ZPAIR><<<g, kGemmThreads, kGemmSmemBytes, st>>>(ml, ml2, mz[bi], mz2[bi], p);
+      sample_gemm_kernel<FP16, ZPAIR><<<g, kSampleThreads, kGemmSmemBytes, st>>>(ml, ml2, mz[bi], mz2[bi], p);
       if (int rc = check_launch("sample_gemm_kernel")) return rc;
     }
     if (overlap) PPI_CUDA_TRY(cudaEventRecord(ss->gemm_done[bi], st));
@@ -2229,52 +2134,45 @@ extern "C" size_t ppi_zstore_bytes(int64_t K, int64_t D, int injected) {
   return kScalarBytes + (size_t)round_up(D, BM) * zstore_kt(K) * 2 + 1024;
 }
 
-// Base normals of a whole Philox draw generated ahead of the sampling call (they depend on (seed, draw,
-// row) only, not on the policy): sample-major exact-fp16 operand rows for the sampling GEMMs + the K-major
-// store of the whitened moment match, one launch.  Issued on a side stream it runs under the HBM- and
-// latency-bound part of the previous update (cost, temperature solve, dense fp64 tail).
-extern "C" size_t ppi_philox_rows_bytes(int64_t K, int64_t D) {
-  if (K <= 0 || D <= 128) return 0;
-  return (size_t)round_up(K, BN) * round_up(D, 64) * sizeof(uint16_t) + 1024;
+// The base normals of the dense Gaussian sampler (D > 128) as a row-major fp32 matrix: what
+// ppi_sample_gaussian / _keep / _cost draw on the device for (seed, draw_id, row_offset) -- the column-quad
+// Philox order of their K-major store, not the row-quad order of ppi_philox_normal.
+extern "C" int ppi_philox_normal_cq(float* out, int64_t rows, int64_t cols, uint64_t seed, uint64_t draw_id,
+                                    uint64_t row_offset, void* stream) {
+  PPI_REQUIRE(out && rows >= 0 && cols > 0, PPI_ERR_INVALID, "ppi_philox_normal_cq: bad arguments");
+  if (rows == 0) return 0;
+  const int64_t work = ((rows + 3) / 4 + 1) * cols;
+  philox_cq_matrix_kernel<<<grid_cap(ceil_div(work, 256), 8), 256, 0, (cudaStream_t)stream>>>(out, rows, cols, seed,
+                                                                                              draw_id, row_offset);
+  return check_launch("philox_cq_matrix_kernel");
 }
 
+// Base normals of a whole Philox draw generated ahead of the sampling call (they depend on (seed, draw,
+// row) only, not on the policy): the K-major store, one launch.  Issued on a side stream it runs under the
+// HBM- and latency-bound part of the previous update (cost, temperature solve, dense fp64 tail).
 extern "C" int ppi_philox_prefetch(uint64_t seed, uint64_t draw_id, uint64_t row_offset, int64_t K,
-                                   int64_t D, void* zrows, size_t zrows_bytes, void* zstore,
-                                   size_t zstore_bytes, void* stream) {
-  PPI_REQUIRE(K > 0 && D > 128 && zrows && zstore, PPI_ERR_INVALID, "ppi_philox_prefetch: bad arguments");
-  PPI_REQUIRE(((uintptr_t)zrows & 1023) == 0 && zrows_bytes >= ppi_philox_rows_bytes(K, D), PPI_ERR_WORKSPACE,
-              "ppi_philox_prefetch: row buffer misaligned (1 KB) or too small");
+                                   int64_t D, void* zstore, size_t zstore_bytes, void* stream) {
+  PPI_REQUIRE(K > 0 && D > 128 && zstore, PPI_ERR_INVALID, "ppi_philox_prefetch: bad arguments");
   PPI_REQUIRE(((uintptr_t)zstore & 1023) == 0 && zstore_bytes >= ppi_zstore_bytes(K, D, 0), PPI_ERR_WORKSPACE,
               "ppi_philox_prefetch: store misaligned (1 KB) or too small");
-  cudaStream_t st = (cudaStream_t)stream;
-  const int64_t Dk = round_up(D, 64), zt_rows = round_up(D, BM), nrows = round_up(K, BN);
   uint16_t* store_rows = (uint16_t*)((char*)zstore + kScalarBytes);
-  ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st);
-  philox_dual_kernel<<<grid_cap((nrows / 64) * ceil_div(zt_rows, 128), prefetch_blocks()), 256, 0, st>>>(
-      nrows, D, Dk, seed, draw_id, row_offset, (uint16_t*)zrows, store_rows, zt_rows, 0);
-  if (int rc = check_launch("philox_dual_kernel")) return rc;
-  const int64_t rem = nrows % kZBlock;
-  if (rem)  // zero the unwritten tail of the last sample block (finite operands)
-    PPI_CUDA_TRY(cudaMemset2DAsync(store_rows + zt_index(nrows, 0, zt_rows), kZBlock * 2, 0, (kZBlock - rem) * 2,
-                                   zt_rows, st));
-  return 0;
+  return generate_store(store_rows, zstore_kt(K) / kZBlock, K, D, seed, draw_id, row_offset, prefetch_blocks(),
+                        (cudaStream_t)stream);
 }
 
-// ppi_sample_gaussian_keep for a draw whose base normals were prefetched: zrows / zstore as written by
+// ppi_sample_gaussian_keep for a draw whose base normals were prefetched: zstore as written by
 // ppi_philox_prefetch for the same (K, D); only the GEMM passes run.
 extern "C" int ppi_sample_gaussian_pre(int64_t K, int64_t D, const float* mu, const float* L, float* x,
-                                       const void* zrows, void* zstore, void* workspace,
-                                       size_t workspace_bytes, void* stream) {
-  PPI_REQUIRE(mu && L && x && K > 0 && D > 128 && zrows && zstore, PPI_ERR_INVALID,
-              "ppi_sample_gaussian_pre: bad arguments (needs K > 0, D > 128, prefetched rows and store)");
+                                       void* zstore, void* workspace, size_t workspace_bytes, void* stream) {
+  PPI_REQUIRE(mu && L && x && K > 0 && D > 128 && zstore, PPI_ERR_INVALID,
+              "ppi_sample_gaussian_pre: bad arguments (needs K > 0, D > 128, a prefetched store)");
   PPI_REQUIRE(gemm_scheme() == PPI_GEMM_FP16X2, PPI_ERR_UNSUPPORTED,
               "ppi_sample_gaussian_pre: the base-normal store exists under PPI_GEMM_FP16X2 only");
-  PPI_REQUIRE(((uintptr_t)zrows & 1023) == 0 && ((uintptr_t)zstore & 1023) == 0, PPI_ERR_WORKSPACE,
-              "ppi_sample_gaussian_pre: rows / store misaligned (1 KB)");
+  PPI_REQUIRE(((uintptr_t)zstore & 1023) == 0, PPI_ERR_WORKSPACE, "ppi_sample_gaussian_pre: store misaligned (1 KB)");
   PPI_REQUIRE(workspace && workspace_bytes >= ppi_sample_gaussian_workspace_bytes(K, D),
               PPI_ERR_WORKSPACE, "ppi_sample_gaussian_pre: workspace too small");
   return sample_gaussian_impl<true, false>(nullptr, 0, 0, 0, K, D, mu, L, x, workspace, zstore,
-                                           (cudaStream_t)stream, zrows);
+                                           (cudaStream_t)stream, true);
 }
 
 extern "C" int ppi_sample_gaussian_keep(const float* z, uint64_t seed, uint64_t draw_id,
@@ -2315,7 +2213,7 @@ extern "C" int ppi_sample_gaussian_cost(const float* z, uint64_t seed, uint64_t 
   cudaStream_t st = (cudaStream_t)stream;
   if (z)
     return sample_gaussian_impl<true, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, zstore, st,
-                                            nullptr, fn, cost);
+                                            false, fn, cost);
   return sample_gaussian_impl<true, false>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, zstore, st,
-                                           nullptr, fn, cost);
+                                           false, fn, cost);
 }

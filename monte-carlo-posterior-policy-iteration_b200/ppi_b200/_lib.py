@@ -59,9 +59,9 @@ SIGNATURES = {
     "ppi_sample_gaussian_workspace_bytes": (_sz, [_i64, _i64]),
     "ppi_sample_gaussian": (_i, [_p, _u64, _u64, _u64, _i64, _i64, _p, _p, _p, _p, _sz, _p]),
     "ppi_zstore_bytes": (_sz, [_i64, _i64, _i]),
-    "ppi_philox_rows_bytes": (_sz, [_i64, _i64]),
-    "ppi_philox_prefetch": (_i, [_u64, _u64, _u64, _i64, _i64, _p, _sz, _p, _sz, _p]),
-    "ppi_sample_gaussian_pre": (_i, [_i64, _i64, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "ppi_philox_prefetch": (_i, [_u64, _u64, _u64, _i64, _i64, _p, _sz, _p]),
+    "ppi_sample_gaussian_pre": (_i, [_i64, _i64, _p, _p, _p, _p, _p, _sz, _p]),
+    "ppi_philox_normal_cq": (_i, [_p, _i64, _i64, _u64, _u64, _u64, _p]),
     "ppi_sample_gaussian_keep": (_i, [_p, _u64, _u64, _u64, _i64, _i64, _p, _p, _p, _p, _sz, _p, _sz, _p]),
     "ppi_sample_gaussian_cost_workspace_bytes": (_sz, [_i64, _i64]),
     "ppi_sample_gaussian_cost": (_i, [_p, _u64, _u64, _u64, _i64, _i64, _p, _p, _p, _p, _sz, _i, _p, _p, _sz, _p]),

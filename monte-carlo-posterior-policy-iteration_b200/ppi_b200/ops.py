@@ -35,12 +35,18 @@ class _Keep:
 
 
 # ------------------------------------------------------------------ a3
-def philox_normal(rows, cols, seed, draw_id=0, row_offset=0, full_precision=False):
-    """full_precision: the same Philox / Box-Muller draw without the rounding to the fp16 grid."""
+def philox_normal(rows, cols, seed, draw_id=0, row_offset=0, full_precision=False, order="row"):
+    """Base normals of a Philox draw as a (rows, cols) fp32 matrix.
+    order="row": the row-quad counters of ppi_philox_normal (every sampler but the dense Gaussian one);
+    order="col": the column-quad counters of the dense Gaussian sampler (D > 128), i.e. what
+    sample_gaussian / _keep / _cost draw for the same (seed, draw_id, row_offset).
+    full_precision (row order only): the same draw without the rounding to the fp16 grid."""
     dev = require_cuda()
     out = torch.empty((rows, cols), dtype=torch.float32, device=dev)
-    _lib.call("ppi_philox_normal_full" if full_precision else "ppi_philox_normal", ptr(out), rows, cols,
-              _u64(seed), _u64(draw_id), _u64(row_offset), stream_ptr())
+    assert order in ("row", "col") and not (full_precision and order == "col")
+    name = "ppi_philox_normal_cq" if order == "col" else ("ppi_philox_normal_full" if full_precision
+                                                          else "ppi_philox_normal")
+    _lib.call(name, ptr(out), rows, cols, _u64(seed), _u64(draw_id), _u64(row_offset), stream_ptr())
     return out
 
 
@@ -266,25 +272,24 @@ def _aligned_bytes(nbytes, dev):
 
 class PrefetchedNormals:
     """Base normals of one Philox draw generated ahead of the sampling call (ppi_philox_prefetch) on a
-    side stream: operand rows for the sampling GEMMs + the K-major store, and the event that marks them
-    complete.  `key` identifies the draw; `base` is the BaseNormals the consuming call hands out."""
+    side stream: the K-major store and the event that marks it complete.  `key` identifies the draw."""
 
-    def __init__(self, key, rows, store, done):
-        self.key, self.rows, self.store, self.done = key, rows, store, done
+    def __init__(self, key, store, done):
+        self.key, self.store, self.done = key, store, done
 
 
-def philox_prefetch(K, D, seed, draw_id, row_offset, rows, store, side, key):
+def philox_prefetch(K, D, seed, draw_id, row_offset, store, side, key):
     """Enqueue the generation of draw (seed, draw_id) rows [row_offset, row_offset + K) on `side` after
-    everything already enqueued on the current stream.  rows / store: persistent 1 KB-aligned buffers."""
+    everything already enqueued on the current stream.  store: persistent 1 KB-aligned buffer."""
     main = torch.cuda.current_stream()
     fork = torch.cuda.Event()
     fork.record(main)
     side.wait_event(fork)
-    _lib.call("ppi_philox_prefetch", _u64(seed), _u64(draw_id), _u64(row_offset), K, D, ptr(rows), rows.numel(),
-              ptr(store), store.numel(), C.c_void_p(side.cuda_stream))
+    _lib.call("ppi_philox_prefetch", _u64(seed), _u64(draw_id), _u64(row_offset), K, D, ptr(store), store.numel(),
+              C.c_void_p(side.cuda_stream))
     done = torch.cuda.Event()
     done.record(side)
-    return PrefetchedNormals(key, rows, store, done)
+    return PrefetchedNormals(key, store, done)
 
 
 def sample_gaussian_pre(K, mu, L, pre):
@@ -297,8 +302,8 @@ def sample_gaussian_pre(K, mu, L, pre):
     nbytes = _lib.query("ppi_sample_gaussian_workspace_bytes", K, D)
     ws = workspace("sample_gaussian", nbytes)
     torch.cuda.current_stream().wait_event(pre.done)
-    _lib.call("ppi_sample_gaussian_pre", K, D, ptr(mu), kp.p(L), ptr(x), ptr(pre.rows), ptr(pre.store), ptr(ws),
-              nbytes, stream_ptr())
+    _lib.call("ppi_sample_gaussian_pre", K, D, ptr(mu), kp.p(L), ptr(x), ptr(pre.store), ptr(ws), nbytes,
+              stream_ptr())
     return x, BaseNormals(pre.store, K, D, False)
 
 

@@ -459,9 +459,8 @@ class GaussianPolicy(object):
         dev = require_cuda()
         st = self.__dict__.setdefault("_pre_state", {})
         if st.get("shape") != (n_local, d):
-            rows = ops._aligned_bytes(_lib.query("ppi_philox_rows_bytes", n_local, d), dev)
             sbytes = _lib.query("ppi_zstore_bytes", n_local, d, 0)
-            st.update(shape=(n_local, d), rows=rows, stores=[ops._aligned_bytes(sbytes, dev) for _ in range(2)],
+            st.update(shape=(n_local, d), stores=[ops._aligned_bytes(sbytes, dev) for _ in range(2)],
                       side=torch.cuda.Stream(), slot=0)
             self._pre_owner = [None, None]
         slot = st["slot"] = 1 - st["slot"]
@@ -470,8 +469,8 @@ class GaussianPolicy(object):
             owner.valid = False     # a handle that still holds this store falls back to the x-space update
             self._pre_owner[slot] = None
         key = (id(sampler), sampler.seed, sampler.draw_id, begin, n_local, d)
-        self._pre = ops.philox_prefetch(n_local, d, sampler.seed, sampler.draw_id, begin, st["rows"],
-                                        st["stores"][slot], st["side"], key)
+        self._pre = ops.philox_prefetch(n_local, d, sampler.seed, sampler.draw_id, begin, st["stores"][slot],
+                                        st["side"], key)
         self._pre.slot = slot
 
     def weighted_update(self, log_weights, samples, update_covariance_in=True):

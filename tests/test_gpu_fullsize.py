@@ -104,7 +104,7 @@ def test_white_moments_uniform_and_one_hot(env, factor):
     nw = torch.zeros(K5, dtype=torch.float32, device="cuda")
     nw[k] = 1.0
     m, s = ops.wmoments_white(base, nw)
-    z = ops.philox_normal(1, D5, seed=5, draw_id=1, row_offset=k)[0].double()
+    z = ops.philox_normal(1, D5, seed=5, draw_id=1, row_offset=k, order="col")[0].double()
     assert float((m - z).abs().max()) < 1e-6
     assert float((s.double() - torch.outer(z, z)).abs().max()) < TOL * float(z.abs().max()) ** 2
 
@@ -232,7 +232,7 @@ def test_c2_three_iterations_against_fp64_oracle(env, record, fn_name, solver_na
     worst = {}
     for it in range(3):
         mu_old, sigma_old = policy.mu.copy(), policy.sigma.copy()
-        z = (ops.philox_normal(K, D, 4242, draw_id=it).cpu().numpy().astype(np.float64) if source == "philox"
+        z = (ops.philox_normal(K, D, 4242, draw_id=it, order="col").cpu().numpy().astype(np.float64) if source == "philox"
              else zs[it].astype(np.float64))
         samples, params = policy(K)
         costs = f(samples)       # Philox + Rastrigin: cost fused into the sampler, x re-drawn below for the oracle
@@ -300,7 +300,7 @@ def test_c5_update_against_fp64_checker(env, factor, record):
     mu_t = torch.as_tensor(mu0, device=dev).double()
     worst, scale = 0.0, 0.0
     for i in range(0, K5, 1 << 16):
-        z = ops.philox_normal(1 << 16, D5, 2048, draw_id=0, row_offset=i).double()
+        z = ops.philox_normal(1 << 16, D5, 2048, draw_id=0, row_offset=i, order="col").double()
         ref = mu_t + z @ chol.T
         worst = max(worst, float((x[i:i + (1 << 16)].double() - ref).abs().max()))
         scale = max(scale, float(ref.abs().max()))

@@ -64,6 +64,23 @@ def test_philox_sharding_invariance(ops, cols):
         assert (part == full[a:b]).all()
 
 
+@pytest.mark.parametrize("cols", [640, 130, 7])
+def test_philox_column_order_sharding_invariance_and_law(ops, cols):
+    """The dense Gaussian sampler's column-quad order (ppi_philox_normal_cq): shards at aligned and unaligned
+    row offsets equal the rows of the full matrix bit for bit; the values are another stream than the row-quad
+    order of the same (seed, draw) and follow the same law."""
+    full = host(ops.philox_normal(1000, cols, seed=11, draw_id=2, order="col"))
+    for a, b in [(0, 252), (252, 501), (501, 1000), (3, 9), (997, 1000)]:
+        part = host(ops.philox_normal(b - a, cols, seed=11, draw_id=2, row_offset=a, order="col"))
+        assert (part == full[a:b]).all(), (a, b)
+    row = host(ops.philox_normal(1000, cols, seed=11, draw_id=2))
+    assert np.mean(row == full) < 0.01
+    big = host(ops.philox_normal(4096, 640, seed=3, draw_id=1, order="col"))
+    assert abs(big.mean()) < 5e-3 and abs(big.var() - 1.0) < 5e-3
+    assert abs(np.mean(big[1:] * big[:-1])) < 5e-3 and abs(np.mean(big[:, 1:] * big[:, :-1])) < 5e-3
+    assert (big.astype(np.float16).astype(np.float64) == big).all()       # on the fp16 grid too
+
+
 # ------------------------------------------------------------------ a22 Gram + Cholesky
 def test_gram_matrices(ops, golden):
     g = golden

@@ -59,7 +59,7 @@ def test_wmoments_white_ops(ops, record, K, D, injected):
         x, base = ops.sample_gaussian_keep(K, mu, L, z=z)
         ref_x = ops.sample_gaussian(K, mu, L, z=z)
     else:
-        z = host(ops.philox_normal(K, D, seed=5, draw_id=3, row_offset=11))
+        z = host(ops.philox_normal(K, D, seed=5, draw_id=3, row_offset=11, order="col"))
         x, base = ops.sample_gaussian_keep(K, mu, L, seed=5, draw_id=3, row_offset=11)
         ref_x = ops.sample_gaussian(K, mu, L, seed=5, draw_id=3, row_offset=11)
     import torch
@@ -96,7 +96,7 @@ def test_wmoments_white_zero_and_one_hot(ops):
     K, D = 4096, 256
     rng = np.random.default_rng(2)
     L, mu = _factor(D, rng)
-    z = host(ops.philox_normal(K, D, seed=1))
+    z = host(ops.philox_normal(K, D, seed=1, order="col"))
     _, base = ops.sample_gaussian_keep(K, mu, L, seed=1)
     _, nw = _weights(K, rng, spread=30.0)   # 13 decades of dynamic range
     nw[::3] = 0.0
@@ -225,12 +225,12 @@ def test_prefetch_c_abi_errors(ops):
 
     buf = torch.zeros(1 << 20, dtype=torch.uint8, device="cuda")
     p = buf.data_ptr() + (-buf.data_ptr()) % 1024
-    with pytest.raises(_lib.PpiError):     # buffers far too small for K x D
-        _lib.call("ppi_philox_prefetch", 1, 0, 0, 65536, 2048, p, 1 << 19, p, 1 << 19, None)
-    with pytest.raises(_lib.PpiError):     # misaligned rows
-        _lib.call("ppi_philox_prefetch", 1, 0, 0, 256, 256, p + 8, 1 << 19, p, 1 << 19, None)
+    with pytest.raises(_lib.PpiError):     # store far too small for K x D
+        _lib.call("ppi_philox_prefetch", 1, 0, 0, 65536, 2048, p, 1 << 19, None)
+    with pytest.raises(_lib.PpiError):     # misaligned store
+        _lib.call("ppi_philox_prefetch", 1, 0, 0, 256, 256, p + 8, 1 << 19, None)
     with pytest.raises(_lib.PpiError):     # D <= 128 has no tensor-core path
-        _lib.call("ppi_philox_prefetch", 1, 0, 0, 256, 64, p, 1 << 19, p, 1 << 19, None)
+        _lib.call("ppi_philox_prefetch", 1, 0, 0, 256, 64, p, 1 << 19, None)
 
 
 @pytest.mark.parametrize("name", ["Rastrigin", "Styblinski"])
