@@ -114,9 +114,53 @@ struct CholScalars {      // device-side results of one factorisation (fp64, rea
 // threads that share a block read one address (broadcast).
 constexpr int kLtBlock = 256;     // doubles per block column of Lt: 16 entries x 16 block rows
 
+// 4 x 4 Cholesky of diagonal block kb (held in r by its owner thread) and the inverse of its factor, unrolled in
+// registers; publishes the factor (Lt) and its inverse (dinv).  One reciprocal square root per pivot
+// (l = p rsqrt(p), 1 / l = rsqrt(p)): fp64 sqrt and division are long dependent software sequences, and this
+// chain is the serial spine of the whole tail.
+__device__ __forceinline__ void factor_diag_block(double (&r)[4][4], int kb, double* __restrict__ Lt,
+                                                  double* __restrict__ dinv, int* fail_s) {
+  int bad = 0;
+  auto ok = [](double p) { return p > 0.0 && isfinite(p); };
+  const double p0 = r[0][0];
+  if (!ok(p0)) bad = 1;
+  const double i0 = rsqrt(p0), l00 = p0 * i0;
+  const double l10 = r[1][0] * i0, l20 = r[2][0] * i0, l30 = r[3][0] * i0;
+  const double p1 = r[1][1] - l10 * l10;
+  if (!bad && !ok(p1)) bad = 2;
+  const double i1 = rsqrt(p1), l11 = p1 * i1;
+  const double l21 = (r[2][1] - l20 * l10) * i1, l31 = (r[3][1] - l30 * l10) * i1;
+  const double p2 = r[2][2] - l20 * l20 - l21 * l21;
+  if (!bad && !ok(p2)) bad = 3;
+  const double i2 = rsqrt(p2), l22 = p2 * i2;
+  const double l32 = (r[3][2] - l30 * l20 - l31 * l21) * i2;
+  const double p3 = r[3][3] - l30 * l30 - l31 * l31 - l32 * l32;
+  if (!bad && !ok(p3)) bad = 4;
+  const double i3 = rsqrt(p3), l33 = p3 * i3;
+  if (bad) *fail_s = 4 * kb + bad;
+  const double w10 = -l10 * i0 * i1, w21 = -l21 * i1 * i2, w32 = -l32 * i2 * i3;
+  const double w20 = -(l20 * i0 + l21 * w10) * i2, w31 = -(l31 * i1 + l32 * w21) * i3;
+  const double w30 = -(l30 * i0 + l31 * w10 + l32 * w20) * i3;
+  double* w = dinv + kb * 16;
+  w[0] = i0;  w[1] = 0.0; w[2] = 0.0;  w[3] = 0.0;
+  w[4] = w10; w[5] = i1;  w[6] = 0.0;  w[7] = 0.0;
+  w[8] = w20; w[9] = w21; w[10] = i2;  w[11] = 0.0;
+  w[12] = w30; w[13] = w31; w[14] = w32; w[15] = i3;
+  r[0][0] = l00; r[0][1] = 0.0; r[0][2] = 0.0; r[0][3] = 0.0;
+  r[1][0] = l10; r[1][1] = l11; r[1][2] = 0.0; r[1][3] = 0.0;
+  r[2][0] = l20; r[2][1] = l21; r[2][2] = l22; r[2][3] = 0.0;
+  r[3][0] = l30; r[3][1] = l31; r[3][2] = l32; r[3][3] = l33;
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) Lt[kb * kLtBlock + (a * 4 + c) * 16 + kb] = r[a][c];
+}
+
 // Right-looking Cholesky of the 64 x 64 tile in Ds (pitch PITCH, lower part).  On return thread (ty >= tx) holds
 // block (ty, tx) of the factor in r, Lt holds every block column, dinv[kb] the inverse of diagonal block kb.
 // Returns false (uniformly) when a pivot fails; *fail_s = 1 + index of the first failing pivot in the tile.
+// Two barriers per block column; the owner of the NEXT diagonal block factors it right after its own trailing
+// update, while the other threads are still updating theirs (the scalar chain hides behind the rank-4 update).
 __device__ __forceinline__ bool tile_cholesky(const double* __restrict__ Ds, double* __restrict__ Lt,
                                               double* __restrict__ dinv, int* fail_s, double (&r)[4][4]) {
   const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
@@ -125,47 +169,9 @@ __device__ __forceinline__ bool tile_cholesky(const double* __restrict__ Ds, dou
   for (int a = 0; a < 4; ++a)
 #pragma unroll
     for (int c = 0; c < 4; ++c) r[a][c] = lower ? Ds[(4 * ty + a) * PITCH + 4 * tx + c] : 0.0;
+  if (ty == 0 && tx == 0) factor_diag_block(r, 0, Lt, dinv, fail_s);
   for (int kb = 0; kb < 16; ++kb) {
-    if (ty == kb && tx == kb) {
-      // 4 x 4 Cholesky of the diagonal block and the inverse of its factor, unrolled in registers
-      int bad = 0;
-      auto ok = [](double p) { return p > 0.0 && isfinite(p); };
-      // one reciprocal square root per pivot (l = p rsqrt(p), 1 / l = rsqrt(p)): fp64 sqrt and division are
-      // software sequences of ~200 dependent cycles each, and this chain is the serial spine of the whole tail
-      const double p0 = r[0][0];
-      if (!ok(p0)) bad = 1;
-      const double i0 = rsqrt(p0), l00 = p0 * i0;
-      const double l10 = r[1][0] * i0, l20 = r[2][0] * i0, l30 = r[3][0] * i0;
-      const double p1 = r[1][1] - l10 * l10;
-      if (!bad && !ok(p1)) bad = 2;
-      const double i1 = rsqrt(p1), l11 = p1 * i1;
-      const double l21 = (r[2][1] - l20 * l10) * i1, l31 = (r[3][1] - l30 * l10) * i1;
-      const double p2 = r[2][2] - l20 * l20 - l21 * l21;
-      if (!bad && !ok(p2)) bad = 3;
-      const double i2 = rsqrt(p2), l22 = p2 * i2;
-      const double l32 = (r[3][2] - l30 * l20 - l31 * l21) * i2;
-      const double p3 = r[3][3] - l30 * l30 - l31 * l31 - l32 * l32;
-      if (!bad && !ok(p3)) bad = 4;
-      const double i3 = rsqrt(p3), l33 = p3 * i3;
-      if (bad) *fail_s = 4 * kb + bad;
-      const double w10 = -l10 * i0 * i1, w21 = -l21 * i1 * i2, w32 = -l32 * i2 * i3;
-      const double w20 = -(l20 * i0 + l21 * w10) * i2, w31 = -(l31 * i1 + l32 * w21) * i3;
-      const double w30 = -(l30 * i0 + l31 * w10 + l32 * w20) * i3;
-      double* w = dinv + kb * 16;
-      w[0] = i0;  w[1] = 0.0; w[2] = 0.0;  w[3] = 0.0;
-      w[4] = w10; w[5] = i1;  w[6] = 0.0;  w[7] = 0.0;
-      w[8] = w20; w[9] = w21; w[10] = i2;  w[11] = 0.0;
-      w[12] = w30; w[13] = w31; w[14] = w32; w[15] = i3;
-      r[0][0] = l00; r[0][1] = 0.0; r[0][2] = 0.0; r[0][3] = 0.0;
-      r[1][0] = l10; r[1][1] = l11; r[1][2] = 0.0; r[1][3] = 0.0;
-      r[2][0] = l20; r[2][1] = l21; r[2][2] = l22; r[2][3] = 0.0;
-      r[3][0] = l30; r[3][1] = l31; r[3][2] = l32; r[3][3] = l33;
-#pragma unroll
-      for (int a = 0; a < 4; ++a)
-#pragma unroll
-        for (int c = 0; c < 4; ++c) Lt[kb * kLtBlock + (a * 4 + c) * 16 + kb] = r[a][c];
-    }
-    __syncthreads();
+    __syncthreads();                        // diagonal block kb factored, its inverse published
     if (*fail_s != 0) return false;
     if (tx == kb && ty > kb) {
       // X = A W^T with W = inverse of the diagonal factor: the final block (ty, kb) of the factor
@@ -188,7 +194,7 @@ __device__ __forceinline__ bool tile_cholesky(const double* __restrict__ Ds, dou
           Lt[kb * kLtBlock + (a * 4 + c) * 16 + ty] = x[a][c];
         }
     }
-    __syncthreads();
+    __syncthreads();                        // block column kb published
     if (tx > kb && lower) {
       const double* pl = Lt + kb * kLtBlock;
 #pragma unroll
@@ -201,9 +207,11 @@ __device__ __forceinline__ bool tile_cholesky(const double* __restrict__ Ds, dou
 #pragma unroll
           for (int b2 = 0; b2 < 4; ++b2) r[a][b2] = fma(-pa[a], pb[b2], r[a][b2]);
       }
+      if (ty == kb + 1 && tx == kb + 1) factor_diag_block(r, kb + 1, Lt, dinv, fail_s);
     }
   }
-  return true;
+  __syncthreads();
+  return *fail_s == 0;
 }
 
 // X = T L^-T for the 64 x 64 tile in Ts (pitch PITCH) and the factor held in Lt / dinv: blocked forward

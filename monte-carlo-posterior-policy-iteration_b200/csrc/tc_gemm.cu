@@ -547,7 +547,7 @@ __device__ __forceinline__ void warp_transpose_reduce64(float (&t)[64]) {
 // that drain TMEM: warp w owns its hardware lane quarter (w & 3) and one 64-column (sample) group -- sixteen
 // short epilogue tails instead of eight long ones, so that the per-tile tail (bias, optional store, optional
 // cost terms + their reduction over the tile's columns) stays inside the two accumulator chunks the MMA issuer
-// can run ahead.  The register file is re-divided with setmaxnreg (WG0 40, drain warps 112 per thread).
+// can run ahead.  The CTA's registers are re-divided with setmaxnreg (WG0 40, drain warps 104 per thread).
 constexpr int kSampleThreads = 640;
 template <bool FP16, bool ZPAIR>
 __global__ void __launch_bounds__(kSampleThreads, 1)
@@ -655,7 +655,8 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
     }
   }
   } else {
-    reg_inc<112>();
+    // setmaxnreg moves registers inside the CTA's own allocation (96 x 640 at launch): 40 x 128 + 104 x 512 fits
+    reg_inc<104>();
     // ================= epilogue: TMEM -> registers -> global, 128 B per warp store =================
     const int e = warp - 4;
     const int q = warp & 3;   // TMEM lane quarter

@@ -92,11 +92,18 @@ def _pinned(nbytes):
 
 
 def to_host64(t):
-    """Device tensor -> host fp64 NumPy array through the pinned staging buffer (the conversion to
-    fp64 happens on the device; a pageable `.cpu()` of a 2048 x 2048 matrix costs ~15 ms).  The result
-    is a private copy (the staging buffer is reused by the next read)."""
+    """Device tensor -> host fp64 NumPy array (the conversion to fp64 happens on the device; a pageable
+    `.cpu()` of a 2048 x 2048 matrix costs ~15 ms).  Small results go through the process-wide pinned staging
+    buffer and are copied out of it; large ones (>= 1 MB) land in a pinned tensor of their own, which torch's
+    caching host allocator recycles once the previous result of that size has been dropped -- no cudaHostAlloc
+    and no second host copy in a steady loop."""
     t64 = t.detach().to(torch.float64).contiguous()
     n = t64.numel()
+    if 8 * n >= 1 << 20:
+        host = torch.empty(t64.shape, dtype=torch.float64, pin_memory=True)
+        host.copy_(t64, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return host.numpy()
     stage = _pinned(8 * n)[: 8 * n].view(torch.float64)
     stage.copy_(t64.reshape(-1), non_blocking=True)
     torch.cuda.current_stream().synchronize()
