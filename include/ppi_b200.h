@@ -187,12 +187,13 @@ int ppi_sample_gaussian_keep(const float* z, uint64_t seed, uint64_t draw_id, ui
  * of ppi/algorithms.py:85-86 without a second pass over the K x D samples.  cost (K) fp32.  x may be NULL: the
  * samples are then never written (the whitened update reads the base-normal store; x is re-drawn from the same
  * (seed, draw_id, row_offset) with ppi_sample_gaussian when a caller asks for it).
+ * store_ready != 0 (Philox only): zstore already holds this draw (ppi_philox_prefetch), only the GEMMs run.
  * workspace: ppi_sample_gaussian_cost_workspace_bytes(K, D). */
 size_t ppi_sample_gaussian_cost_workspace_bytes(int64_t K, int64_t D);
 int ppi_sample_gaussian_cost(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset, int64_t K,
                              int64_t D, const float* mu, const float* L, float* x, void* zstore,
-                             size_t zstore_bytes, int fn, float* cost, void* workspace, size_t workspace_bytes,
-                             void* stream);
+                             size_t zstore_bytes, int store_ready, int fn, float* cost, void* workspace,
+                             size_t workspace_bytes, void* stream);
 
 /* Base normals of a Philox draw generated ahead of the sampling call (they depend on (seed, draw_id,
  * global row) only): zstore = the K-major store of ppi_sample_gaussian_keep, 1 KB aligned, size from

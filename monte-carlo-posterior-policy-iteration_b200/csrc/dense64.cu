@@ -96,6 +96,22 @@ __device__ __forceinline__ void load_tile(double* __restrict__ s, const double* 
   }
 }
 
+// The same tile through cp.async (LDGSTS, 16 bytes per request, no registers in between): every thread has its
+// eight requests per tile in flight at once, and several tiles can be queued before one wait -- a plain
+// load / store loop exposes one L2 round trip per iteration (measured: 14 k cycles for the four tiles of a step).
+__device__ __forceinline__ void load_tile_async(double* __restrict__ s, const double* __restrict__ g, int64_t ld) {
+#pragma unroll
+  for (int it = 0; it < NB * (NB / 2) / kDenseThreads; ++it) {
+    const int e = threadIdx.x + it * kDenseThreads;
+    const int r = e >> 5, c = (e & 31) * 2;
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(s + r * PITCH + c);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(g + (int64_t)r * ld + c) : "memory");
+  }
+}
+__device__ __forceinline__ void async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 // ---------------------------------------------------------------------------------------------
 // Cholesky of a padded Dp x Dp matrix held (lower tiles) in `a`; G (lower, zero above the diagonal inside
 // the diagonal tiles) and G^T (upper) are written tile by tile.
@@ -225,31 +241,35 @@ __device__ __forceinline__ void tile_solve(const double* __restrict__ Ts, const 
   for (int a = 0; a < 4; ++a)
 #pragma unroll
     for (int c = 0; c < 4; ++c) r[a][c] = Ts[(4 * ty + a) * PITCH + 4 * tx + c];
-  for (int kb = 0; kb < 16; ++kb) {
+  // block column kb is solved (X = R W_kb^T) and published by the threads that own it right after THEIR part of
+  // the rank-4 update of step kb - 1, while the other columns are still being updated: one barrier per step
+  auto solve_column = [&](int kb) {
     double* px = pn + (kb & 1) * kLtBlock;
-    if (tx == kb) {
-      const double* w = dinv + kb * 16;
-      double x[4][4];
+    const double* w = dinv + kb * 16;
+    double x[4][4];
 #pragma unroll
-      for (int a = 0; a < 4; ++a)
+    for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int b2 = 0; b2 < 4; ++b2) {
-          double acc = 0.0;
+      for (int b2 = 0; b2 < 4; ++b2) {
+        double acc = 0.0;
 #pragma unroll
-          for (int c = 0; c <= b2; ++c) acc = fma(r[a][c], w[b2 * 4 + c], acc);
-          x[a][b2] = acc;
-        }
+        for (int c = 0; c <= b2; ++c) acc = fma(r[a][c], w[b2 * 4 + c], acc);
+        x[a][b2] = acc;
+      }
 #pragma unroll
-      for (int a = 0; a < 4; ++a)
+    for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          r[a][c] = x[a][c];
-          px[(a * 4 + c) * 16 + ty] = x[a][c];
-        }
-    }
-    __syncthreads();
+      for (int c = 0; c < 4; ++c) {
+        r[a][c] = x[a][c];
+        px[(a * 4 + c) * 16 + ty] = x[a][c];
+      }
+  };
+  if (tx == 0) solve_column(0);
+  for (int kb = 0; kb < 15; ++kb) {
+    __syncthreads();                          // X(:, kb) published (buffer kb & 1)
     if (tx > kb) {
       // r -= X(ty, kb) L(tx, kb)^T
+      const double* px = pn + (kb & 1) * kLtBlock;
       const double* pl = Lt + kb * kLtBlock;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
@@ -261,6 +281,7 @@ __device__ __forceinline__ void tile_solve(const double* __restrict__ Ts, const 
 #pragma unroll
           for (int b2 = 0; b2 < 4; ++b2) r[a][b2] = fma(-pa[a], pb[b2], r[a][b2]);
       }
+      if (tx == kb + 1) solve_column(kb + 1);  // writes buffer (kb + 1) & 1: nobody reads it before the barrier
     }
   }
 }
@@ -278,6 +299,11 @@ __device__ __forceinline__ void tile_sub(double* __restrict__ s, const TileAcc& 
       *p = v;
     }
 }
+
+// Phase clocks of the critical path (A-role CTAs i = j and i = j + 1 of every step), read by tools/dense_tail_timing.py
+// through ppi_debug_chol_trace: [step][cta 0/1][phase] SM clock at start / loaded / updated / factored / done.
+__device__ long long g_chol_trace[64 * 2 * 8];
+#define CHOL_TRACE(slot) do { if (trace_me && threadIdx.x == 0) g_chol_trace[((j & 63) * 2 + (int)blockIdx.x) * 8 + (slot)] = clock64(); } while (0)
 
 // One launch per block column j (look-ahead built in: nothing inside a launch waits on another CTA).
 //   A-role, CTA per row block i = j .. T-1: applies the PENDING update of panel j-1 to its own tiles of block
@@ -307,8 +333,10 @@ chol_step_kernel(double* __restrict__ a, int64_t Dp, int j, int T, int64_t D, do
     int rem = blockIdx.x - nA, ri = 0;
     while (rem > ri) { rem -= ri + 1; ++ri; }
     const int i = j + 1 + ri, k = j + 1 + rem;
-    load_tile<false>(As, g + ((int64_t)i * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
-    load_tile<false>(Bs, g + ((int64_t)k * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
+    load_tile_async(As, g + ((int64_t)i * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
+    load_tile_async(Bs, g + ((int64_t)k * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
+    async_commit();
+    async_wait<0>();
     __syncthreads();
     TileAcc acc;
     acc.zero();
@@ -329,29 +357,43 @@ chol_step_kernel(double* __restrict__ a, int64_t Dp, int j, int T, int64_t D, do
   // ---------------- A-role ----------------
   const int i = j + blockIdx.x;
   const bool diag_cta = i == j;
+  const bool trace_me = blockIdx.x < 2;
+  CHOL_TRACE(0);
   if (threadIdx.x == 0) fail = 0;
-  load_tile<false>(Ds, a + ((int64_t)j * NB) * Dp + (int64_t)j * NB, Dp);
-  if (!diag_cta) load_tile<false>(Ts, a + ((int64_t)i * NB) * Dp + (int64_t)j * NB, Dp);
+  // two request groups: what the diagonal tile needs first, the panel tile's operands behind it
+  load_tile_async(Ds, a + ((int64_t)j * NB) * Dp + (int64_t)j * NB, Dp);
+  if (j > 0) load_tile_async(Bs, g + ((int64_t)j * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
+  async_commit();
+  if (!diag_cta) {
+    load_tile_async(Ts, a + ((int64_t)i * NB) * Dp + (int64_t)j * NB, Dp);
+    if (j > 0) load_tile_async(As, g + ((int64_t)i * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
+  }
+  async_commit();
   if (j > 0) {
-    load_tile<false>(Bs, g + ((int64_t)j * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
-    if (!diag_cta) load_tile<false>(As, g + ((int64_t)i * NB) * Dp + (int64_t)(j - 1) * NB, Dp);
+    async_wait<1>();
     __syncthreads();
+    CHOL_TRACE(1);
     TileAcc acc;
     acc.zero();
     tile_mma(Bs, Bs, acc);
     tile_sub(Ds, acc);
     if (!diag_cta) {
+      async_wait<0>();
+      __syncthreads();
       acc.zero();
       tile_mma(As, Bs, acc);
       tile_sub(Ts, acc);
     }
   }
+  async_wait<0>();
   __syncthreads();
+  CHOL_TRACE(2);
   double r[4][4];
   if (!tile_cholesky(Ds, Lt, dinv, &fail, r)) {
     if (diag_cta && threadIdx.x == 0) sc->status = (double)((int64_t)j * NB + fail);
     return;
   }
+  CHOL_TRACE(3);
   const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
   if (diag_cta) {
     // G(j, j) lower, zeros above; G^T(j, j); log det over the first D pivots
@@ -369,9 +411,11 @@ chol_step_kernel(double* __restrict__ a, int64_t Dp, int j, int T, int64_t D, do
       }
     ld = block_sum(ld, red);
     if (threadIdx.x == 0) sc->logdet += 2.0 * ld;
+    CHOL_TRACE(5);
     return;
   }
   tile_solve(Ts, Lt, dinv, pn, r);
+  CHOL_TRACE(4);
   double* gtile = g + ((int64_t)i * NB) * Dp + (int64_t)j * NB;
   double* gttile = gt + ((int64_t)j * NB) * Dp + (int64_t)i * NB;
 #pragma unroll
@@ -384,6 +428,7 @@ chol_step_kernel(double* __restrict__ a, int64_t Dp, int j, int T, int64_t D, do
     *reinterpret_cast<double2*>(gttile + (int64_t)(4 * tx + c) * Dp + 4 * ty) = make_double2(r[0][c], r[1][c]);
     *reinterpret_cast<double2*>(gttile + (int64_t)(4 * tx + c) * Dp + 4 * ty + 2) = make_double2(r[2][c], r[3][c]);
   }
+  CHOL_TRACE(5);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -627,4 +672,10 @@ extern "C" int ppi_tri_matvec(const double* l, int64_t D, const double* v, const
   PPI_REQUIRE(l && v && y32 && D > 0, PPI_ERR_INVALID, "ppi_tri_matvec: bad arguments");
   tri_matvec_kernel<<<(unsigned)ceil_div(D * 32, 256), 256, 0, (cudaStream_t)stream>>>(l, D, v, x0, y32, nullptr);
   return check_launch("tri_matvec_kernel");
+}
+
+// debug: the phase clocks of the last factorisation (64 steps x 2 CTAs x 8 slots), see g_chol_trace
+extern "C" int ppi_debug_chol_trace(long long* host_out) {
+  PPI_CUDA_TRY(cudaMemcpyFromSymbol(host_out, g_chol_trace, sizeof(long long) * 64 * 2 * 8));
+  return 0;
 }

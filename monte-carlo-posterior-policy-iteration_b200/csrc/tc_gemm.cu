@@ -2199,7 +2199,7 @@ extern "C" int ppi_sample_gaussian_keep(const float* z, uint64_t seed, uint64_t 
 // wants x later re-draws it from the same (seed, draw_id, row_offset) with ppi_sample_gaussian).
 extern "C" int ppi_sample_gaussian_cost(const float* z, uint64_t seed, uint64_t draw_id, uint64_t row_offset,
                                         int64_t K, int64_t D, const float* mu, const float* L, float* x,
-                                        void* zstore, size_t zstore_bytes, int fn, float* cost,
+                                        void* zstore, size_t zstore_bytes, int store_ready, int fn, float* cost,
                                         void* workspace, size_t workspace_bytes, void* stream) {
   PPI_REQUIRE(mu && L && cost && K > 0 && D > 128 && zstore, PPI_ERR_INVALID,
               "ppi_sample_gaussian_cost: bad arguments (needs K > 0, D > 128, a store, a cost buffer)");
@@ -2216,5 +2216,5 @@ extern "C" int ppi_sample_gaussian_cost(const float* z, uint64_t seed, uint64_t 
     return sample_gaussian_impl<true, true>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, zstore, st,
                                             false, fn, cost);
   return sample_gaussian_impl<true, false>(z, seed, draw_id, row_offset, K, D, mu, L, x, workspace, zstore, st,
-                                           false, fn, cost);
+                                           store_ready != 0, fn, cost);
 }

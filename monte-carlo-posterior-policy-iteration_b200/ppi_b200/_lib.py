@@ -64,7 +64,7 @@ SIGNATURES = {
     "ppi_philox_normal_cq": (_i, [_p, _i64, _i64, _u64, _u64, _u64, _p]),
     "ppi_sample_gaussian_keep": (_i, [_p, _u64, _u64, _u64, _i64, _i64, _p, _p, _p, _p, _sz, _p, _sz, _p]),
     "ppi_sample_gaussian_cost_workspace_bytes": (_sz, [_i64, _i64]),
-    "ppi_sample_gaussian_cost": (_i, [_p, _u64, _u64, _u64, _i64, _i64, _p, _p, _p, _p, _sz, _i, _p, _p, _sz, _p]),
+    "ppi_sample_gaussian_cost": (_i, [_p, _u64, _u64, _u64, _i64, _i64, _p, _p, _p, _p, _sz, _i, _i, _p, _p, _sz, _p]),
     "ppi_wmoments_white_workspace_bytes": (_sz, [_i64, _i64, _i]),
     "ppi_wmoments_white": (_i, [_p, _i, _p, _i64, _i64, _p, _p, _p, _i, _p, _sz, _p]),
     "ppi_cost_function": (_i, [_i, _p, _i64, _i64, _p, _p, _p, _p]),

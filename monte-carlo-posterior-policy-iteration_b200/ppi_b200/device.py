@@ -177,18 +177,19 @@ class DeferredGaussianSamples(DeviceArray):
     Either way the base normals end up in HBM (`white`) for the whitened moment match."""
 
     def __init__(self, policy, version, mu_dev, chol_dev, n_local, dim, row_offset, global_rows, seed, draw_id,
-                 after=None):
+                 after=None, pre=None):
         self._x = None
+        self._pre = pre              # PrefetchedNormals: the store of this draw was generated ahead of time
         self._shape = (int(n_local), int(dim))
         self.row_offset, self.global_rows, self._host = int(row_offset), int(global_rows), None
         self._launch = (policy, version, mu_dev, chol_dev, int(seed), int(draw_id))
         self.white = None            # (policy, version, BaseNormals) once a kernel has produced the store
         self._after = after          # called once after the first launch (prefetch hook)
 
-    def _done(self):
+    def _done(self, base):
         if self._after is not None:
             after, self._after = self._after, None
-            after()
+            after(base)
 
     @property
     def tensor(self):
@@ -198,10 +199,13 @@ class DeferredGaussianSamples(DeviceArray):
             policy, version, mu, chol, seed, draw = self._launch
             n, _ = self._shape
             if self.white is None:   # first launch: keep the base normals for the whitened update
-                self._x, base = ops.sample_gaussian_keep(n, mu, chol, seed=seed, draw_id=draw,
-                                                         row_offset=self.row_offset)
+                if self._pre is not None:
+                    self._x, base = ops.sample_gaussian_pre(n, mu, chol, self._pre)
+                else:
+                    self._x, base = ops.sample_gaussian_keep(n, mu, chol, seed=seed, draw_id=draw,
+                                                             row_offset=self.row_offset)
                 self.white = (policy, version, base)
-                self._done()
+                self._done(base)
             else:                    # the fused launch skipped x: re-draw it from the same counters
                 self._x = ops.sample_gaussian(n, mu, chol, seed=seed, draw_id=draw, row_offset=self.row_offset)
         return self._x
@@ -224,9 +228,9 @@ class DeferredGaussianSamples(DeviceArray):
         policy, version, mu, chol, seed, draw = self._launch
         n, _ = self._shape
         _, base, cost = ops.sample_gaussian_cost(n, mu, chol, fn_name, seed=seed, draw_id=draw,
-                                                 row_offset=self.row_offset)
+                                                 row_offset=self.row_offset, pre=self._pre)
         self.white = (policy, version, base)
-        self._done()
+        self._done(base)
         return cost
 
     @property

@@ -245,9 +245,10 @@ def sample_gaussian_keep(K, mu, L, z=None, seed=0, draw_id=0, row_offset=0):
     return x, BaseNormals(store, K, D, zt is not None)
 
 
-def sample_gaussian_cost(K, mu, L, fn_name, z=None, seed=0, draw_id=0, row_offset=0, want_x=False):
+def sample_gaussian_cost(K, mu, L, fn_name, z=None, seed=0, draw_id=0, row_offset=0, want_x=False, pre=None):
     """sample_gaussian_keep with a separable test function evaluated in the sampling epilogue
-    (ppi_sample_gaussian_cost): -> (x or None, BaseNormals, cost (K,) fp32).  want_x=False never writes x."""
+    (ppi_sample_gaussian_cost): -> (x or None, BaseNormals, cost (K,) fp32).  want_x=False never writes x.
+    pre: a PrefetchedNormals whose store already holds this draw (only the GEMMs run)."""
     dev = require_cuda()
     kp = _Keep(dev)
     mu = f32(mu, dev)
@@ -256,11 +257,17 @@ def sample_gaussian_cost(K, mu, L, fn_name, z=None, seed=0, draw_id=0, row_offse
     zt = None if z is None else f32(z, dev).reshape(K, D)
     nbytes = _lib.query("ppi_sample_gaussian_cost_workspace_bytes", K, D)
     ws = workspace("sample_gaussian", nbytes)
-    sbytes = _lib.query("ppi_zstore_bytes", K, D, int(zt is not None))
-    store = _aligned_bytes(sbytes, dev)
+    if pre is not None:
+        assert zt is None
+        torch.cuda.current_stream().wait_event(pre.done)
+        store, sbytes = pre.store, pre.store.numel()
+    else:
+        sbytes = _lib.query("ppi_zstore_bytes", K, D, int(zt is not None))
+        store = _aligned_bytes(sbytes, dev)
     cost = torch.empty((K,), dtype=torch.float32, device=dev)
     _lib.call("ppi_sample_gaussian_cost", ptr(zt), _u64(seed), _u64(draw_id), _u64(row_offset), K, D, ptr(mu),
-              kp.p(L), ptr(x), ptr(store), sbytes, _lib.FN_IDS[fn_name], ptr(cost), ptr(ws), nbytes, stream_ptr())
+              kp.p(L), ptr(x), ptr(store), sbytes, int(pre is not None), _lib.FN_IDS[fn_name], ptr(cost), ptr(ws),
+              nbytes, stream_ptr())
     return x, BaseNormals(store, K, D, zt is not None), cost
 
 

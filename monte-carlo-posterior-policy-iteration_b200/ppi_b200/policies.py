@@ -11,6 +11,7 @@ reference keeps its attributes.  The host-side bookkeeping the reference does be
 from __future__ import annotations
 
 import logging
+import weakref
 
 import numpy as np
 import torch
@@ -416,14 +417,27 @@ class GaussianPolicy(object):
         if d > self.small_dim and not self.diagonal and _lib.load().ppi_get_option(_lib.OPT_GEMM_SCHEME) == _lib.GEMM_FP16X2:
             # keep the base normals in HBM: weighted_update on this very handle contracts z, not x
             pre, self._pre = self._pre, None
-            if z is None and pre is not None and pre.key == (id(self.sampler), seed, draw, begin, n_local, d):
+            if pre is not None and not (z is None and pre.key == (id(self.sampler), seed, draw, begin, n_local, d)):
+                pre = None          # a prefetched store of another draw: not ours
+            if z is None and self.defer_draws:
+                # Philox draw: nothing is launched yet -- the cost function decides whether x is ever written
+                slot = None if pre is None else pre.slot
+
+                def after(base, slot=slot, n_samples=n_samples):
+                    if slot is not None:
+                        self._pre_owner[slot] = base              # this store now backs a launched draw
+                        self._pre_pending[slot] = None
+                    if self.prefetch_normals == "sample":
+                        self._prefetch_next(n_samples)            # right behind the sampling GEMMs
+
+                handle = DeferredGaussianSamples(self, self._version, self._mu_d(), self._factor(), n_local, d,
+                                                 begin, n_total, seed, draw, after=after, pre=pre)
+                if slot is not None:
+                    self._pre_pending[slot] = weakref.ref(handle)
+                return handle, handle
+            if pre is not None:
                 x, base = ops.sample_gaussian_pre(n_local, self._mu_d(), self._factor(), pre)
                 self._pre_owner[pre.slot] = base
-            elif z is None and self.defer_draws and self.prefetch_normals is None:
-                # Philox draw: nothing is launched yet -- the cost function decides whether x is ever written
-                handle = DeferredGaussianSamples(self, self._version, self._mu_d(), self._factor(), n_local, d,
-                                                 begin, n_total, seed, draw)
-                return handle, handle
             else:
                 x, base = ops.sample_gaussian_keep(n_local, self._mu_d(), self._factor(), z=z, seed=seed,
                                                    draw_id=draw, row_offset=begin)
@@ -447,6 +461,8 @@ class GaussianPolicy(object):
     prefetch_normals = None
     prefetch_min_elements = 1 << 26
     _pre = None
+    _pre_owner = [None, None]
+    _pre_pending = [None, None]
 
     def _prefetch_next(self, n_samples):
         sampler = self.sampler
@@ -463,11 +479,16 @@ class GaussianPolicy(object):
             st.update(shape=(n_local, d), stores=[ops._aligned_bytes(sbytes, dev) for _ in range(2)],
                       side=torch.cuda.Stream(), slot=0)
             self._pre_owner = [None, None]
+            self._pre_pending = [None, None]
         slot = st["slot"] = 1 - st["slot"]
         owner = self._pre_owner[slot]
         if owner is not None:
             owner.valid = False     # a handle that still holds this store falls back to the x-space update
             self._pre_owner[slot] = None
+        pending = self._pre_pending[slot]
+        if pending is not None and pending() is not None:
+            pending()._pre = None   # a deferred draw that has not run yet: it will generate its own store
+        self._pre_pending[slot] = None
         key = (id(sampler), sampler.seed, sampler.draw_id, begin, n_local, d)
         self._pre = ops.philox_prefetch(n_local, d, sampler.seed, sampler.draw_id, begin, st["stores"][slot],
                                         st["side"], key)

@@ -210,6 +210,7 @@ def test_prefetch_recycles_a_store_only_after_invalidating_its_handle(ops):
     policy = pol.GaussianPolicy(np.zeros(D), np.eye(D), smp.MonteCarlo(D, seed=5))
     policy.prefetch_normals = "sample"
     policy.prefetch_min_elements = 0
+    policy.defer_draws = False                          # eager draws: every call launches and prefetches the next
     handles = [policy(K)[0] for _ in range(4)]          # draws 1.. come from prefetched stores
     assert not handles[1].white[2].valid and handles[3].white[2].valid
     lw = f32r(-4.0 * rng.random(K))
@@ -272,3 +273,40 @@ def test_fused_cost_in_the_sampling_epilogue(ops, record, name, K, D):
     record(f"fused_cost[{name}-{K}-{D}]", fused=e_fused, kernel=e_kernel)
     assert e_fused < 2e-6 and e_kernel < 2e-6
     assert np.array_equal(mu1, mu0) and np.array_equal(sig1, sig0)
+
+
+def test_deferred_draws_with_prefetched_stores(ops):
+    """Deferred draws + prefetch: the store of draw t+1 is generated on a side stream behind update t; the deferred
+    handle of draw t+1 consumes it (fused cost, no x), a handle whose store slot is recycled before it ran
+    generates its own.  Everything bit-identical to the run without prefetch."""
+    from ppi_b200 import functions as fn, policies as pol, samplers as smp
+
+    K, D = 3000, 384
+    rng = np.random.default_rng(12)
+    lws = [f32r(-3.0 * rng.random(K)) for _ in range(4)]
+    f = fn.Rastrigin(D)
+
+    def run(prefetch):
+        policy = pol.GaussianPolicy(0.3 * np.ones(D), 0.5 * np.eye(D) + 0.01, smp.MonteCarlo(D, seed=21))
+        policy.prefetch_normals = prefetch
+        policy.prefetch_min_elements = 0
+        costs, used = [], []
+        for lw in lws:
+            samples, _ = policy(K)
+            used.append(getattr(samples, "_pre", None) is not None)
+            costs.append(host(f(samples).tensor))
+            assert not samples.materialised
+            policy.weighted_update(lw, samples)
+        # two draws without an update: the first one's prefetched store may be recycled before it runs
+        h1, h2 = policy(K)[0], policy(K)[0]
+        x1, x2 = host(h1.tensor), host(h2.tensor)
+        return costs, policy.mu.copy(), policy.sigma.copy(), used, x1, x2
+
+    c0, mu0, sig0, used0, xa0, xb0 = run(None)
+    for mode in ("update", "sample"):
+        c1, mu1, sig1, used1, xa1, xb1 = run(mode)
+        assert not any(used0) and any(used1), (mode, used1)
+        for a, b in zip(c0, c1):
+            assert np.array_equal(a, b)
+        assert np.array_equal(mu0, mu1) and np.array_equal(sig0, sig1)
+        assert np.array_equal(xa0, xa1) and np.array_equal(xb0, xb1)

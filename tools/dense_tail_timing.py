@@ -58,6 +58,26 @@ def main():
             "torch_cholesky_ex_plus_LG_ms": timed(torch_tail, args.reps),
             "torch_cholesky_ms": timed(lambda: torch.linalg.cholesky_ex(a64), args.reps),
         }
+    # phase clocks of the critical-path CTAs of the last factorisation (debug export of dense64.cu)
+    import ctypes as C
+
+    from ppi_b200 import _lib
+
+    lib = _lib.load()
+    buf = (C.c_longlong * (64 * 2 * 8))()
+    torch.cuda.synchronize()
+    lib.ppi_debug_chol_trace.argtypes = [C.c_void_p]
+    lib.ppi_debug_chol_trace(buf)
+    tr = np.array(buf, dtype=np.int64).reshape(64, 2, 8)
+    T = args.dims[-1] // 64
+    ph = {}
+    for cta, names in ((0, ("load", "update", "factor", None, "store_diag")), (1, ("load", "update", "factor", "solve", "store"))):
+        d = np.diff(tr[1:T - 1, cta, :6].astype(np.float64), axis=1)      # steps 1 .. T-2: all phases present
+        for k, nm in enumerate(names):
+            if nm:
+                ph[f"cta{cta}_{nm}_cycles"] = float(np.median(d[:, k]))
+    ph["cta1_total_cycles"] = float(np.median(tr[1:T - 1, 1, 5] - tr[1:T - 1, 1, 0]))
+    out["phase_clocks_last_dim"] = ph
     print(json.dumps(out))
 
 
