@@ -286,6 +286,120 @@ __device__ __forceinline__ void tile_solve(const double* __restrict__ Ts, const 
   }
 }
 
+// ---- panel solve on fp64 tensor cores ------------------------------------------------------------------------
+// X = T L^-T row by row is independent across rows, so every warp solves ITS 8 rows of the tile alone (no block
+// barrier): four 16-column blocks,  R_b = T_b - sum_{p<b} X_p L_bp^T  (m8n8k4 chain of 4 b k-steps),
+// X_b = R_b W_b^T with W_b the inverse of the b-th 16 x 16 diagonal block of L.  ~80 DMMA per warp instead of
+// sixteen block-wide SIMT phases (measured 16 k cycles).
+constexpr int WP16 = 20;   // pitch of the 16 x 16 inverses and of the per-warp R scratch (20 mod 16 = 4: conflict-free)
+
+// Inverses of the four 16 x 16 diagonal blocks of the factor from its 4 x 4 blocks (Lt) and their inverses (dinv):
+// W_aa = dinv,  W_ab = -W_aa sum_{k=b}^{a-1} L_ak W_kb  (a > b), three dependency levels inside warp 0.
+__device__ __forceinline__ void build_w16(const double* __restrict__ Lt, const double* __restrict__ dinv,
+                                          double* __restrict__ w16) {
+  const int tid = threadIdx.x;
+  // diagonal 4 x 4 blocks and zeros everywhere else: 4 blocks x 16 x 16 entries
+  for (int e = tid; e < 4 * 16 * 16; e += kDenseThreads) {
+    const int blk = e >> 8, rr = (e >> 4) & 15, cc = e & 15;
+    double v = 0.0;
+    if ((rr >> 2) == (cc >> 2)) v = dinv[(4 * blk + (rr >> 2)) * 16 + (rr & 3) * 4 + (cc & 3)];
+    w16[blk * 16 * WP16 + rr * WP16 + cc] = v;
+  }
+  __syncthreads();
+  if (tid < 32) {
+    const int blk = tid / 6, e = tid % 6;   // (a, b) = (1,0) (2,1) (3,2) | (2,0) (3,1) | (3,0)
+    const int a = e < 3 ? e + 1 : (e < 5 ? e - 1 : 3), b = e < 3 ? e : (e < 5 ? e - 3 : 0);
+    double* wb = w16 + blk * 16 * WP16;
+#pragma unroll
+    for (int d = 1; d <= 3; ++d) {
+      if (tid < 24 && a - b == d) {
+        double sacc[4][4];
+#pragma unroll
+        for (int x = 0; x < 4; ++x)
+#pragma unroll
+          for (int y = 0; y < 4; ++y) sacc[x][y] = 0.0;
+        for (int k = b; k < a; ++k) {
+          // L block (row 4 blk + a, column 4 blk + k) times W block (k, b)
+          const double* lb = Lt + (4 * blk + k) * kLtBlock + (4 * blk + a);
+#pragma unroll
+          for (int x = 0; x < 4; ++x)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const double l = lb[(x * 4 + c) * 16];
+#pragma unroll
+              for (int y = 0; y < 4; ++y) sacc[x][y] = fma(l, wb[(4 * k + c) * WP16 + 4 * b + y], sacc[x][y]);
+            }
+        }
+        const double* waa = dinv + (4 * blk + a) * 16;
+#pragma unroll
+        for (int x = 0; x < 4; ++x)
+#pragma unroll
+          for (int y = 0; y < 4; ++y) {
+            double v = 0.0;
+#pragma unroll
+            for (int c = 0; c <= x; ++c) v = fma(waa[x * 4 + c], sacc[c][y], v);
+            wb[(4 * a + x) * WP16 + 4 * b + y] = -v;
+          }
+      }
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+}
+
+// In place: Ts (64 x 64, pitch PITCH) <- Ts L^-T, with L row-major in Ls (pitch PITCH, zero above the diagonal),
+// the 16 x 16 inverses in w16 and 8 x (8 x WP16) doubles of per-warp scratch in rs.
+__device__ __forceinline__ void tile_solve_mma(double* __restrict__ Ts, const double* __restrict__ Ls,
+                                               const double* __restrict__ w16, double* __restrict__ rs,
+                                               double* __restrict__ gtile, double* __restrict__ gttile, int64_t Dp) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int fr = lane >> 2, fk = lane & 3;           // fragment row / contraction index
+  double* trow = Ts + (8 * warp) * PITCH;            // this warp's 8 rows
+  double* rw = rs + warp * 8 * WP16;
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    double acc[2][2];
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+      acc[nt][0] = trow[fr * PITCH + 16 * b + 8 * nt + 2 * fk];
+      acc[nt][1] = trow[fr * PITCH + 16 * b + 8 * nt + 2 * fk + 1];
+    }
+    // R_b = T_b - X[:, 0 : 16 b] L[16 b .. 16 b + 15, 0 : 16 b]^T
+    for (int k0 = 0; k0 < 16 * b; k0 += 4) {
+      const double av = -trow[fr * PITCH + k0 + fk];
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) dmma884(acc[nt], av, Ls[(16 * b + 8 * nt + fr) * PITCH + k0 + fk]);
+    }
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+      rw[fr * WP16 + 8 * nt + 2 * fk] = acc[nt][0];
+      rw[fr * WP16 + 8 * nt + 2 * fk + 1] = acc[nt][1];
+    }
+    __syncwarp();
+    // X_b = R_b W_b^T
+    double xacc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+    const double* wb = w16 + b * 16 * WP16;
+#pragma unroll
+    for (int k0 = 0; k0 < 16; k0 += 4) {
+      const double av = rw[fr * WP16 + k0 + fk];
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) dmma884(xacc[nt], av, wb[(8 * nt + fr) * WP16 + k0 + fk]);
+    }
+    // X_b: back into the tile (operand of the later blocks) and straight from the fragments to G(i, j) (16 bytes
+    // per lane, 64 contiguous bytes per row) and G^T(j, i) (8 consecutive rows = 64 contiguous bytes per column)
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+      const int col = 16 * b + 8 * nt + 2 * fk, row = 8 * warp + fr;
+      trow[fr * PITCH + col] = xacc[nt][0];
+      trow[fr * PITCH + col + 1] = xacc[nt][1];
+      *reinterpret_cast<double2*>(gtile + (int64_t)row * Dp + col) = make_double2(xacc[nt][0], xacc[nt][1]);
+      gttile[(int64_t)col * Dp + row] = xacc[nt][0];
+      gttile[(int64_t)(col + 1) * Dp + row] = xacc[nt][1];
+    }
+    __syncwarp();
+  }
+}
+
 // subtract the DMMA accumulator from a tile in shared memory (each element has one owner)
 __device__ __forceinline__ void tile_sub(double* __restrict__ s, const TileAcc& acc) {
 #pragma unroll
@@ -323,7 +437,8 @@ chol_step_kernel(double* __restrict__ a, int64_t Dp, int j, int T, int64_t D, do
   double* Ts = Ds + NB * PITCH;            // this CTA's panel tile
   double* Lt = Ts + NB * PITCH;            // factor blocks, 16 x 256
   double* dinv = Lt + 16 * kLtBlock;       // 16 inverses of the diagonal 4 x 4 blocks
-  double* pn = dinv + 256;                 // 2 x 256 scratch of tile_solve
+  double* w16 = dinv + 256;                // inverses of the four 16 x 16 diagonal blocks, pitch WP16
+  double* rs = w16 + 4 * 16 * WP16;        // per-warp 8 x 16 scratch of tile_solve_mma
   __shared__ int fail;
   __shared__ double red[32];
   if (sc->status != 0.0) return;           // an earlier block column failed
@@ -414,20 +529,15 @@ chol_step_kernel(double* __restrict__ a, int64_t Dp, int j, int T, int64_t D, do
     CHOL_TRACE(5);
     return;
   }
-  tile_solve(Ts, Lt, dinv, pn, r);
+  // the factor, row-major (zero above the diagonal), into the diagonal tile's buffer: the DMMA solve reads it
+#pragma unroll
+  for (int aa = 0; aa < 4; ++aa)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) Ds[(4 * ty + aa) * PITCH + 4 * tx + c] = ty >= tx ? r[aa][c] : 0.0;
+  build_w16(Lt, dinv, w16);                  // ends with a block barrier: Ds and w16 visible to every warp
+  tile_solve_mma(Ts, Ds, w16, rs, g + ((int64_t)i * NB) * Dp + (int64_t)j * NB,
+                 gt + ((int64_t)j * NB) * Dp + (int64_t)i * NB, Dp);
   CHOL_TRACE(4);
-  double* gtile = g + ((int64_t)i * NB) * Dp + (int64_t)j * NB;
-  double* gttile = gt + ((int64_t)j * NB) * Dp + (int64_t)i * NB;
-#pragma unroll
-  for (int aa = 0; aa < 4; ++aa) {
-    *reinterpret_cast<double2*>(gtile + (int64_t)(4 * ty + aa) * Dp + 4 * tx) = make_double2(r[aa][0], r[aa][1]);
-    *reinterpret_cast<double2*>(gtile + (int64_t)(4 * ty + aa) * Dp + 4 * tx + 2) = make_double2(r[aa][2], r[aa][3]);
-  }
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    *reinterpret_cast<double2*>(gttile + (int64_t)(4 * tx + c) * Dp + 4 * ty) = make_double2(r[0][c], r[1][c]);
-    *reinterpret_cast<double2*>(gttile + (int64_t)(4 * tx + c) * Dp + 4 * ty + 2) = make_double2(r[2][c], r[3][c]);
-  }
   CHOL_TRACE(5);
 }
 
@@ -560,7 +670,7 @@ tri_matvec_kernel(const double* __restrict__ L, int64_t D, const double* __restr
 }
 
 constexpr size_t kTileSmem = 2 * NB * PITCH * sizeof(double);   // 69 632 B: opt-in above 48 KB
-constexpr size_t kStepSmem = (size_t)(4 * NB * PITCH + 16 * kLtBlock + 256 + 2 * kLtBlock) * sizeof(double);  // 178 176 B
+constexpr size_t kStepSmem = (size_t)(4 * NB * PITCH + 16 * kLtBlock + 256 + 4 * 16 * WP16 + 8 * 8 * WP16) * sizeof(double);
 
 static int64_t pad64(int64_t D) { return (D + NB - 1) / NB * NB; }
 
