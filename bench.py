@@ -516,7 +516,8 @@ def run_b200(args, wl):
     torch, world, rank = hx.torch, hx.world, hx.rank
     lib = _lib.load()
     for key, val in ((_lib.OPT_GEMM_OVERLAP, args.overlap), (_lib.OPT_GEMM_CHUNK, args.chunk),
-                     (_lib.OPT_GEMM_PAIR, args.pair), (_lib.OPT_PREFETCH_BLOCKS, args.prefetch_blocks)):
+                     (_lib.OPT_GEMM_PAIR, args.pair), (_lib.OPT_PREFETCH_BLOCKS, args.prefetch_blocks),
+                     (_lib.OPT_SAMPLE_CHUNK, args.sample_chunk)):
         if val is not None:
             _lib.call("ppi_set_option", key, val)
 
@@ -715,6 +716,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-extras", action="store_true", help="skip the C2 / C3 / C4 side records")
     ap.add_argument("--chunk", type=int, default=None, help="override PPI_OPT_GEMM_CHUNK")
+    ap.add_argument("--sample-chunk", type=int, default=None, help="override PPI_OPT_SAMPLE_CHUNK")
     ap.add_argument("--pair", type=int, default=None, choices=[0, 1], help="override PPI_OPT_GEMM_PAIR")
     ap.add_argument("--overlap", type=int, default=None, choices=[0, 1],
                     help="override PPI_OPT_GEMM_OVERLAP (operand staging on a side stream)")

@@ -47,8 +47,13 @@ const char* ppi_last_error(void);
  *   PPI_GEMM_TF32X3  hi = tf32(v), lo = tf32(v - hi); hi hi + hi lo + lo hi as kind::tf32 MMAs
  *                    (error ~2^-21 |a||b| at any magnitude; 8 bytes per value, twice the MMA time).
  * PPI_OPT_GEMM_CHUNK = 32-deep k-blocks accumulated inside the tensor core before the partial sum is
- * promoted to fp32 registers (tcgen05 accumulation truncates: ~3e-8 relative per MMA instruction).
- * Even, default 8.
+ * promoted to fp32 registers (tcgen05 accumulation truncates: ~3e-8 relative per MMA instruction) in the
+ * moment kernels.  Even, default 16: every promotion drains 128 KB of TMEM, as long as the chunk's own
+ * MMAs at 8 k-blocks; measured on B200 (K = 65536, D = 2048, error relative to the largest entry):
+ *   chunk 8: S 2.0e-6 | 16: 3.5e-6 | 32: 7.0e-6 | 64: 1.4e-5   (the diagonal, where the truncation is a
+ *   coherent bias, is replaced by the fp64-folded ppi_wmoments_white s2 before the dense tail).
+ * PPI_OPT_SAMPLE_CHUNK: the same for the sampling kernels (x = mu + L z).  Even, default 32:
+ *   chunk 8: x 3.9e-7 | 16: 7.7e-7 | 32: 1.5e-6 | 64: 2.9e-6.
  * PPI_OPT_GEMM_OVERLAP != 0: the FP16X2 kernels stage the operands of pass p+1 on an internal side
  * stream while pass p multiplies (two staging buffers, event-ordered against the caller's stream;
  * the call stays asynchronous and stream-ordered for the caller).  Default 0: measured gain on
@@ -59,7 +64,7 @@ const char* ppi_last_error(void);
  * PPI_OPT_PREFETCH_BLOCKS = resident CTAs per SM of ppi_philox_prefetch, 1..6 (default 6): fewer leave
  * room for the kernels of the stream it runs beside. */
 enum { PPI_OPT_GEMM_SCHEME = 0, PPI_OPT_GEMM_CHUNK = 1, PPI_OPT_GEMM_OVERLAP = 2, PPI_OPT_GEMM_PAIR = 3,
-       PPI_OPT_PREFETCH_BLOCKS = 4 };
+       PPI_OPT_PREFETCH_BLOCKS = 4, PPI_OPT_SAMPLE_CHUNK = 5 };
 enum { PPI_GEMM_TF32X3 = 0, PPI_GEMM_FP16X2 = 1 };
 int ppi_set_option(int key, int value);
 int ppi_get_option(int key);
@@ -382,13 +387,15 @@ int ppi_tri_matvec(const double* l, int64_t D, const double* v, const float* x0,
  * x[stats->argmax] and the statistics travel home in the same read (no synchronisation between the
  * temperature solve and the match).
  * shift1 (H, d) may be NULL (feature weights are matched without a mean function); inv_cov_out (d).
+ * mean32 (H, d) / chol32 (H, H), optional: fp32 device copies of the fitted mean and factor -- what the next
+ * ppi_sample_matnorm / ppi_sample_features call consumes, so the policy state never has to be uploaded again.
  * workspace: ppi_matnorm_update_workspace_bytes(H, d).  K-sharded ranks use the three separate entry
  * points with their all-reduces in between. */
 size_t ppi_matnorm_update_workspace_bytes(int H, int d);
 int ppi_matnorm_update(const float* x, const float* nw, int64_t K, int H, int d, const float* shift1,
                        const float* inv_cov_out, double jitter, int64_t map_index,
-                       const ppi_weight_stats* stats, double* packed, void* workspace,
-                       size_t workspace_bytes, void* stream);
+                       const ppi_weight_stats* stats, double* packed, float* mean32, float* chol32,
+                       void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Measurement hooks (new; the reference has no instrumentation beyond profile_mpc.py:96-108).

@@ -48,8 +48,10 @@ ProfileScope::~ProfileScope() {
 namespace ppi {
 static std::atomic<int> g_gemm_scheme{PPI_GEMM_FP16X2};
 int gemm_scheme() { return g_gemm_scheme.load(std::memory_order_relaxed); }
-static std::atomic<int> g_gemm_chunk{8};
+static std::atomic<int> g_gemm_chunk{16};
 int gemm_chunk() { return g_gemm_chunk.load(std::memory_order_relaxed); }
+static std::atomic<int> g_sample_chunk{32};
+int sample_chunk() { return g_sample_chunk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_gemm_overlap{0};
 int gemm_overlap() { return g_gemm_overlap.load(std::memory_order_relaxed); }
 static std::atomic<int> g_gemm_pair{0};
@@ -71,6 +73,12 @@ extern "C" int ppi_set_option(int key, int value) {
     ppi::g_gemm_chunk.store(value);
     return 0;
   }
+  if (key == PPI_OPT_SAMPLE_CHUNK) {
+    PPI_REQUIRE(value >= 2 && value <= 4096 && value % 2 == 0, PPI_ERR_INVALID,
+                "ppi_set_option: sampling chunk must be an even number of k-blocks in [2, 4096]");
+    ppi::g_sample_chunk.store(value);
+    return 0;
+  }
   if (key == PPI_OPT_GEMM_OVERLAP) { ppi::g_gemm_overlap.store(value != 0); return 0; }
   if (key == PPI_OPT_GEMM_PAIR) { ppi::g_gemm_pair.store(value != 0); return 0; }
   if (key == PPI_OPT_PREFETCH_BLOCKS) {
@@ -86,7 +94,8 @@ extern "C" int ppi_get_option(int key) {
        : key == PPI_OPT_GEMM_CHUNK ? ppi::gemm_chunk()
        : key == PPI_OPT_GEMM_OVERLAP ? ppi::gemm_overlap()
        : key == PPI_OPT_GEMM_PAIR ? ppi::gemm_pair()
-       : key == PPI_OPT_PREFETCH_BLOCKS ? ppi::prefetch_blocks() : -1;
+       : key == PPI_OPT_PREFETCH_BLOCKS ? ppi::prefetch_blocks()
+       : key == PPI_OPT_SAMPLE_CHUNK ? ppi::sample_chunk() : -1;
 }
 
 extern "C" int64_t ppi_launch_count(void) { return ppi::g_launches.load(); }

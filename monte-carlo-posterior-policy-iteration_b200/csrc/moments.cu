@@ -417,7 +417,8 @@ extern "C" size_t ppi_matnorm_update_workspace_bytes(int H, int d) {
 extern "C" int ppi_matnorm_update(const float* x, const float* nw, int64_t K, int H, int d,
                                   const float* shift1, const float* inv_cov_out, double jitter,
                                   int64_t map_index, const ppi_weight_stats* stats, double* packed,
-                                  void* workspace, size_t workspace_bytes, void* stream) {
+                                  float* mean32, float* chol32, void* workspace, size_t workspace_bytes,
+                                  void* stream) {
   static_assert(sizeof(ppi_weight_stats) % 8 == 0, "statistics are copied as 8-byte words");
   PPI_REQUIRE(x && nw && packed && workspace && K > 0 && H > 0 && d > 0, PPI_ERR_INVALID,
               "ppi_matnorm_update: bad arguments");
@@ -438,7 +439,7 @@ extern "C" int ppi_matnorm_update(const float* x, const float* nw, int64_t K, in
   if (int rc = ppi_wmoments_matnorm(x, nw, K, H, d, shift, inv_cov_out, acc, stream)) return rc;
   double* cov = packed + HD;
   double* chol = cov + (size_t)H * H;
-  if (int rc = ppi_finalize_matnorm(s1, acc, H, d, jitter, packed, nullptr, cov, nullptr, chol, nullptr, status,
+  if (int rc = ppi_finalize_matnorm(s1, acc, H, d, jitter, packed, mean32, cov, nullptr, chol, chol32, status,
                                     stream))
     return rc;
   matnorm_pack_tail_kernel<<<(HD + 255) / 256, 256, 0, st>>>(status, x, K, HD, map_index, stats,

@@ -1007,14 +1007,20 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
 // bytes of the store, so a thread writes 8 samples (two calls) as one 16-byte store and a warp 512 contiguous
 // bytes; one block = one whole 4 KB row of a store block.  No shared memory, no transposition.
 // Samples >= rows_valid and columns >= D are written as zeros (finite operands for the padded tiles).
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 8)
 philox_store_kernel(uint16_t* __restrict__ zt, int64_t store_rows, int64_t n_blocks, int64_t rows_valid,
                     int64_t D, uint64_t seed, uint64_t draw, uint64_t row_offset) {
   const PhiloxKeys keys = philox_keys(seed ^ kPhiloxColTag);
   const bool aligned = (row_offset & 3) == 0;
-  const int64_t items = n_blocks * store_rows;
-  for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
-    const int64_t blk = it / store_rows, i = it % store_rows;
+  // items (sample block, column) are dealt round-robin to the CTAs (equal shares); the pair is advanced
+  // incrementally -- a 64-bit division per item cost a quarter of the instructions of the first version
+  // (28 per normal in the ncu capture)
+  const uint32_t rows32 = (uint32_t)store_rows;
+  const uint32_t d_blk = gridDim.x / rows32, d_i = gridDim.x % rows32;
+  uint32_t blk32 = blockIdx.x / rows32, i32 = blockIdx.x % rows32;
+  for (; blk32 < (uint32_t)n_blocks; blk32 += d_blk, i32 += d_i) {
+    if (i32 >= rows32) { i32 -= rows32; ++blk32; if (blk32 >= (uint32_t)n_blocks) break; }
+    const int64_t blk = blk32, i = i32;
     const int64_t k = blk * kZBlock + (int64_t)threadIdx.x * 8;       // first local sample of this thread
     uint4 o = make_uint4(0u, 0u, 0u, 0u);
     if (i < D && k < rows_valid) {
@@ -1089,6 +1095,7 @@ __global__ void syrk_reduce_kernel(const float* __restrict__ partials, int split
 // ---------------------------------------------------------------------------------------------
 int gemm_scheme();     // capi.cu: PPI_GEMM_TF32X3 / PPI_GEMM_FP16X2 (ppi_set_option)
 int gemm_chunk();      // capi.cu: pipeline stages per TMEM accumulation chunk
+int sample_chunk();    // capi.cu: the same for the sampling kernels
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -1460,24 +1467,32 @@ white_weights_kernel(const float* __restrict__ nw, int64_t K, int64_t kt, const 
 }
 
 // s1[i] += sum_k nw_k zT[i][k]: block = 8 store rows x 16384 samples, weights loaded once per 8 rows.
-constexpr int kMeanRows = 8, kMeanChunk = 16384;
+constexpr int kMeanRows = 8;
 __global__ void __launch_bounds__(256)
 white_mean_kernel(const uint16_t* __restrict__ zt, int64_t zt_rows, const float* __restrict__ nw, int64_t K,
-                  int64_t D, double* __restrict__ s1, double* __restrict__ s2) {
+                  int64_t D, double* __restrict__ s1, double* __restrict__ s2, int chunk) {
   // s2[i] += sum_k nw_k zT[i][k]^2: the DIAGONAL of S with round-to-nearest fp32 products and fp64 sums.  The
   // tensor-core accumulation truncates (a bias of ~2e-6 on sums of positive terms), and tr C = sum of D such
   // entries enters the KL as (tr C - D): the finish takes the diagonal from here (same pass over the store).
   __shared__ double red[kMeanRows][8];
   __shared__ double red2[kMeanRows][8];
   const int64_t i0 = (int64_t)blockIdx.x * kMeanRows;
-  const int64_t kc0 = (int64_t)blockIdx.y * kMeanChunk;
+  const int64_t kc0 = (int64_t)blockIdx.y * chunk;
   const bool w_vec = (reinterpret_cast<uintptr_t>(nw) & 15) == 0;
   float acc[kMeanRows], acc2[kMeanRows];
+  double accd[kMeanRows], accd2[kMeanRows];     // fp32 partials are folded into fp64 every 8 iterations (64 terms)
 #pragma unroll
-  for (int r = 0; r < kMeanRows; ++r) acc[r] = acc2[r] = 0.f;
-  for (int it = 0; it < kMeanChunk / (256 * 8); ++it) {
+  for (int r = 0; r < kMeanRows; ++r) { acc[r] = acc2[r] = 0.f; accd[r] = accd2[r] = 0.0; }
+  for (int it = 0; it < chunk / (256 * 8); ++it) {
     const int64_t k = kc0 + ((int64_t)it * 256 + threadIdx.x) * 8;
     if (k >= K) break;
+    if ((it & 7) == 7) {
+#pragma unroll
+      for (int r = 0; r < kMeanRows; ++r) {
+        accd[r] += (double)acc[r]; accd2[r] += (double)acc2[r];
+        acc[r] = acc2[r] = 0.f;
+      }
+    }
     float w[8];
     if (k + 8 <= K && w_vec) {
       const float4 w0 = __ldg(reinterpret_cast<const float4*>(nw + k));
@@ -1509,8 +1524,8 @@ white_mean_kernel(const uint16_t* __restrict__ zt, int64_t zt_rows, const float*
   const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
 #pragma unroll
   for (int r = 0; r < kMeanRows; ++r) {
-    const double v = warp_sum((double)acc[r]);
-    const double v2 = warp_sum((double)acc2[r]);
+    const double v = warp_sum(accd[r] + (double)acc[r]);
+    const double v2 = warp_sum(accd2[r] + (double)acc2[r]);
     if (lane == 0) { red[r][wp] = v; red2[r][wp] = v2; }
   }
   __syncthreads();
@@ -1844,8 +1859,12 @@ static int wmoments_white_direct(const void* zstore, const float* nw, int64_t K,
   }
   if (s1) {
     ProfileScope prof(PPI_PROF_WMOMENTS_DIAG, st);
-    dim3 mg((unsigned)ceil_div(D, kMeanRows), (unsigned)ceil_div(K, kMeanChunk));
-    white_mean_kernel<<<mg, 256, 0, st>>>(zt, pl.Dp, nw, K, D, s1, s2);
+    // samples per CTA: as long as the grid still holds ~8 CTAs per SM (a 16 384-sample CTA lives 6 us: launch and
+    // reduction tails cost a quarter of the kernel, ncu: 57 % of the DRAM peak)
+    int64_t chunk = 131072;
+    while (chunk > 16384 && ceil_div(D, kMeanRows) * ceil_div(K, chunk) < (int64_t)kNumSMs * 8) chunk >>= 1;
+    dim3 mg((unsigned)ceil_div(D, kMeanRows), (unsigned)ceil_div(K, chunk));
+    white_mean_kernel<<<mg, 256, 0, st>>>(zt, pl.Dp, nw, K, D, s1, s2, (int)chunk);
     if (int rc = check_launch("white_mean_kernel")) return rc;
   }
   CUtensorMap a, b;
@@ -2034,7 +2053,7 @@ static int sample_gaussian_impl(const float* z, uint64_t seed, uint64_t draw_id,
   p.tiles_j = (int)ceil_div(D, BM);
   p.units_per_block = (p.tiles_j + 1) / 2;
   p.num_st = (int)(Dk / KS);
-  p.chunk_st = kStore ? gemm_chunk() / 2 : gemm_chunk();  // same 32-step boundaries in every variant
+  p.chunk_st = kStore ? sample_chunk() / 2 : sample_chunk();  // same 32-step boundaries in every variant
   p.D = D;
   p.mu = mu;
   p.scalars = scalars;

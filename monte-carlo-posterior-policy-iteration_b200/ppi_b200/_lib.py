@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libppi_b200.so")
 KERNEL_KINDS = {"se": 0, "matern12": 1, "matern32": 2, "matern52": 3, "periodic": 4, "white": 5}
 FN_IDS = {"Himmelblau": 0, "Rosenbrock": 1, "Styblinski": 2, "Rastrigin": 3, "NoisySphere": 4}
 OPT_GEMM_SCHEME, OPT_GEMM_CHUNK, OPT_GEMM_OVERLAP, OPT_GEMM_PAIR, OPT_PREFETCH_BLOCKS = 0, 1, 2, 3, 4
+OPT_SAMPLE_CHUNK = 5
 GEMM_TF32X3, GEMM_FP16X2 = 0, 1
 TEMP_FIXED_NORMALISED, TEMP_FIXED_SHIFTED, TEMP_REPS_KL, TEMP_ESS_TARGET, TEMP_LOWER_BOUND = range(5)
 
@@ -48,7 +49,7 @@ SIGNATURES = {
     "ppi_sobol_normal": (_i, [_p, _i64, _i64, _p, _p, _i, _u64, _d, _p]),
     "ppi_cubature_points": (_i, [_p, _i, _p]),
     "ppi_matnorm_update_workspace_bytes": (_sz, [_i, _i]),
-    "ppi_matnorm_update": (_i, [_p, _p, _i64, _i, _i, _p, _p, _d, _i64, _p, _p, _p, _sz, _p]),
+    "ppi_matnorm_update": (_i, [_p, _p, _i64, _i, _i, _p, _p, _d, _i64, _p, _p, _p, _p, _p, _sz, _p]),
     "ppi_kernel_shift_workspace_bytes": (_sz, [_i, _i]),
     "ppi_kernel_shift": (_i, [_i, _d, _d, _d, _p, _i, _p, _i, _p, _p, _p, _p, _i, _p, _p, _p, _d, _d, _p, _p,
                               _p, _p, _p, _p]),

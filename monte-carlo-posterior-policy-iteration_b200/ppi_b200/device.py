@@ -16,15 +16,23 @@ import torch
 from . import _lib
 
 
+_cuda_ok = False
+
+
 def require_cuda():
-    if not torch.cuda.is_available():
-        raise _lib.PpiError("ppi_b200 needs a CUDA device (B200); there is no CPU fallback")
-    _lib.load()
+    global _cuda_ok
+    if not _cuda_ok:     # checked once: torch.cuda.is_available() costs ~5 us per call on the latency-bound paths
+        if not torch.cuda.is_available():
+            raise _lib.PpiError("ppi_b200 needs a CUDA device (B200); there is no CPU fallback")
+        _lib.load()
+        _cuda_ok = True
     return torch.device("cuda", torch.cuda.current_device())
 
 
 def stream_ptr():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    """Raw cudaStream_t of torch's current stream on the current device (the C getter: building a
+    torch.cuda.Stream object per kernel launch cost more than the launch)."""
+    return C.c_void_p(torch._C._cuda_getCurrentRawStream(torch.cuda.current_device()))
 
 
 def ptr(t):
@@ -70,6 +78,21 @@ def f32_cached(a, device=None):
         return t
     _small_cache[key] = (a.copy(), t, ref)
     return t
+
+
+def seed_f32_cache(a, t):
+    """Tell f32_cached that the device tensor t already holds float32(a) -- for host mirrors that were READ from
+    the device (a policy's fitted mean / factor): the next sampling call then re-uses the device copy instead of
+    uploading what it just downloaded.  In-place edits of `a` are still seen (content compare)."""
+    if not isinstance(a, np.ndarray) or a.size == 0 or a.size > 1 << 16 or not t.is_cuda:
+        return
+    try:
+        ref = weakref.ref(a)
+    except TypeError:
+        return
+    if len(_small_cache) > 512:
+        _small_cache.clear()
+    _small_cache[(id(a), t.device.index)] = (a.copy(), t, ref)
 
 
 def f64(a, device=None):

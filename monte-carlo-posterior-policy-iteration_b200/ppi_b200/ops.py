@@ -452,11 +452,17 @@ def finalize_gaussian(s1=None, cov=None, shift=None, diagonal_only=False, want_m
     return mu, sigma
 
 
+_matnorm_ws_bytes = {}
+
+
 def matnorm_update(x, nw, shift1, inv_cov_out, jitter=0.0, map_index=-1, stats=None):
-    """One-rank matrix-normal moment match in a single call (ppi_matnorm_update): -> host fp64
-    (mean, cov_in, chol, status[, x[map_index]]) after ONE device->host read.
+    """One-rank matrix-normal moment match in a single call (ppi_matnorm_update): -> (host, dev) with
+    host = fp64 (mean, cov_in, chol, status[, x[map_index]]) after ONE device->host read through pinned staging,
+    dev = (mean32, chol32) fp32 device copies of the fit for the next sampling call.
     stats: a LazyStats whose struct is still on the device -- the sample row is then x[stats.argmax] and
     the statistics are filled from the same read (no synchronisation since the temperature solve)."""
+    from .device import _pinned
+
     dev = require_cuda()
     K, H, d = x.shape
     on_dev = stats is not None and not stats.resolved
@@ -464,16 +470,24 @@ def matnorm_update(x, nw, shift1, inv_cov_out, jitter=0.0, map_index=-1, stats=N
     n_stats = _lib.STATS_BYTES // 8 if on_dev else 0
     n = H * d + 2 * H * H + 1 + (H * d if want_row else 0) + n_stats
     packed = torch.empty(n, dtype=torch.float64, device=dev)
-    nbytes = _lib.query("ppi_matnorm_update_workspace_bytes", H, d)
+    mean32 = torch.empty((H, d), dtype=torch.float32, device=dev)
+    chol32 = torch.empty((H, H), dtype=torch.float32, device=dev)
+    nbytes = _matnorm_ws_bytes.get((H, d))
+    if nbytes is None:
+        nbytes = _matnorm_ws_bytes[(H, d)] = _lib.query("ppi_matnorm_update_workspace_bytes", H, d)
     ws = workspace("matnorm_update", nbytes)
     _lib.call("ppi_matnorm_update", ptr(x), ptr(nw), K, H, d, ptr(shift1), ptr(inv_cov_out), float(jitter),
-              int(map_index), ptr(stats.tensor) if on_dev else None, ptr(packed), ptr(ws), nbytes, stream_ptr())
-    host = packed.cpu().numpy()
+              int(map_index), ptr(stats.tensor) if on_dev else None, ptr(packed), ptr(mean32), ptr(chol32), ptr(ws),
+              nbytes, stream_ptr())
+    stage = _pinned(8 * n)[: 8 * n].view(torch.float64)
+    stage.copy_(packed, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    host = stage.numpy().copy()
     if on_dev:
         stats.fill(host[n - n_stats:].tobytes())
     a, b, c = H * d, H * d + H * H, H * d + 2 * H * H
     out = (host[:a].reshape(H, d), host[a:b].reshape(H, H), host[b:c].reshape(H, H), int(host[c]))
-    return out + ((host[c + 1:c + 1 + H * d].reshape(H, d),) if want_row else ())
+    return out + ((host[c + 1:c + 1 + H * d].reshape(H, d),) if want_row else ()), (mean32, chol32)
 
 
 def finalize_matnorm(s1, acc, H, d, jitter=0.0):

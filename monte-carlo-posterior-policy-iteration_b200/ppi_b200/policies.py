@@ -783,7 +783,10 @@ class BasePrimitive(object):
     # -- shared device pieces ---------------------------------------------------------------------
     def _l_out_is_diag(self):
         c = np.asarray(self.cov_out_sqrt)
-        return bool(np.count_nonzero(c - np.diag(np.diag(c))) == 0)
+        hit = self.__dict__.get("_diag_flag")
+        if hit is None or hit[0] is not c or not np.array_equal(hit[1], c):
+            hit = self._diag_flag = (c, c.copy(), bool(np.count_nonzero(c - np.diag(np.diag(c))) == 0))
+        return hit[2]
 
     def _update_consts(self, shift1, H, d):
         """Device copies of the per-update constants (the centring shift in fp32 and fp64, 1 / diag(cov_out)),
@@ -799,6 +802,20 @@ class BasePrimitive(object):
             c = self._consts = (key, s32, s64, f32(1.0 / np.diag(cov_out)))
         return c[1], c[2], c[3]
 
+    _fit_dev = None
+
+    def _seed_fit(self, with_factor):
+        """The fp32 device copies the fused update left behind are what the next draw needs: register them
+        against the fresh host mirrors so that the sampler does not upload what was just downloaded."""
+        from .device import seed_f32_cache
+
+        if self._fit_dev is not None:
+            mean32, chol32 = self._fit_dev
+            seed_f32_cache(self.mean, mean32)
+            if with_factor:
+                seed_f32_cache(self.covariance_in_sqrt, chol32)
+            self._fit_dev = None
+
     def _mavn_update(self, w, x, row_offset, replicated, shift1, jitter, extra=None):
         """m_projection_mavn (ppi/policies.py:96-143, iterations=1, update_out=False) on the
         device: returns host fp64 (mean, cov_in, chol or None, pd[, map row]).  extra="argmax": the most
@@ -812,11 +829,12 @@ class BasePrimitive(object):
             lazy = w.stats if isinstance(w.stats, LazyStats) and not w.stats.resolved else None
             if extra == "argmax":
                 idx = -1 if lazy is not None else int(w.stats.argmax) - row_offset
-                res = ops.matnorm_update(x, nw, s32, inv_out, jitter, idx, stats=lazy)
+                res, self._fit_dev = ops.matnorm_update(x, nw, s32, inv_out, jitter, idx, stats=lazy)
             else:
-                res = ops.matnorm_update(x, nw, s32, inv_out, jitter, -1, stats=lazy)
+                res, self._fit_dev = ops.matnorm_update(x, nw, s32, inv_out, jitter, -1, stats=lazy)
                 res = res[:4]
             return res[:3] + (res[3] == 0,) + res[4:]
+        self._fit_dev = None
         if extra is not None:
             extra = x[int(w.stats.argmax) - row_offset]
         s1 = ops.wmoments_diag(x, nw, shift1=s32)
@@ -910,6 +928,7 @@ class BaseFeatures(BasePrimitive):
             self.mean = mean_
             if update_covariance_in:
                 self.covariance_in, self.covariance_in_sqrt = cov_in_, chol_
+            self._seed_fit(update_covariance_in)
         else:
             logging.warning(f"Update error, ESS={ess}")
             logging.warning("Weighted update error, reverting")
@@ -1127,10 +1146,11 @@ class BaseKernel(BasePrimitive):
             mean_, cov_in_, chol_, pd = self._mavn_update(w, x, row_offset, replicated, shift1, 0.0)
         self.mean = mean_
         ess = float(w.stats.ess)
+        if update_covariance_in and pd:
+            self.covariance_in, self.covariance_in_sqrt = cov_in_, chol_
+        self._seed_fit(update_covariance_in and pd)
         if update_covariance_in:
-            if pd:
-                self.covariance_in, self.covariance_in_sqrt = cov_in_, chol_
-            else:
+            if not pd:
                 logging.warning(f"Update error, ESS={ess}")
                 logging.warning("Weighted update error, reverting")
                 jitter = SIGMA_MIN * np.eye(self.dim_features)

@@ -400,8 +400,9 @@ def test_c4_feature_sampler_against_oracle_on_injected_normals(env, record):
     cout = np.diag([1e-3, 1e-3])
     m_ref, cin_ref, _, ess_ref = O.m_projection_mavn(log_w, wh, cin, cout, naive=False)
     s32 = None
-    res = ops.matnorm_update(w, nw, s32, torch.as_tensor(1.0 / np.diag(cout), dtype=torch.float32, device="cuda"),
-                             1e-12, -1)
+    res, (mean32, chol32) = ops.matnorm_update(
+        w, nw, s32, torch.as_tensor(1.0 / np.diag(cout), dtype=torch.float32, device="cuda"), 1e-12, -1)
+    assert nerr(mean32.cpu().numpy(), res[0]) < 1e-6 and nerr(chol32.cpu().numpy(), res[2]) < 1e-6
     e["mean"], e["cov_in"] = nerr(res[0], m_ref), nerr(res[1], cin_ref + 1e-12 * np.eye(F))
     e["ess"] = abs(st.ess - ess_ref) / ess_ref
     record("c4_full", **e)
