@@ -720,7 +720,7 @@ def main():
     ap.add_argument("--pair", type=int, default=None, choices=[0, 1], help="override PPI_OPT_GEMM_PAIR")
     ap.add_argument("--overlap", type=int, default=None, choices=[0, 1],
                     help="override PPI_OPT_GEMM_OVERLAP (operand staging on a side stream)")
-    ap.add_argument("--prefetch", default=None, choices=["none", "sample", "update"],
+    ap.add_argument("--prefetch", default=None, choices=["none", "sample", "moments", "update"],
                     help="override GaussianPolicy.prefetch_normals (base normals of the next draw generated "
                          "ahead on a side stream)")
     ap.add_argument("--prefetch-blocks", type=int, default=None, help="override PPI_OPT_PREFETCH_BLOCKS")

@@ -138,28 +138,40 @@ __device__ __forceinline__ float round_half(float v) { return __half2float(__flo
 // with the MUFU transcendentals, which is what bounds the generator): the angle needs no more.
 __device__ __forceinline__ float u01_23(uint32_t r) { return __uint_as_float(0x3F800000u | (r >> 9)) - 1.0f; }
 
-// One Box-Muller pair as a packed half2 (z0 low, z1 high) -- the form the tensor-core operand
-// stores want; box_muller() below widens exactly these values.
-__device__ __forceinline__ __half2 box_muller_h2(uint32_t a, uint32_t b) {
-  const float u = u01(a), v = u01_23(b);
-  // every transcendental is a single MUFU instruction (lg2 / sqrt / sin / cos, no slow paths): the
-  // result is rounded to 11 bits anyway
+// Radius and direction of one Box-Muller pair: r = sqrt(-2 ln u), (c, s) = (cos, sin)(2 pi v), v the top 23 bits
+// of b.  Written as the bare MUFU forms: lg2.approx.ftz (u >= 2^-33 is never subnormal -- the non-ftz form
+// costs a compare and two predicated fix-ups per call), and the angle as 2 pi t with t in [1, 2) read straight
+// off the bit pattern (sine and cosine have period one in t; the range reduction inside MUFU keeps the
+// fractional part, 23 bits either way).
+__device__ __forceinline__ void box_muller_polar(uint32_t a, uint32_t b, float& r, float& s, float& c) {
+  const float u = u01(a);
+  const float t = __uint_as_float(0x3F800000u | (b >> 9));
+  float lg;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(u));
   // the radicand is clamped from below: MUFU.LG2 carries an absolute error of 2^-22, so for u in the top
   // float bins below 1 nothing guarantees a non-positive logarithm (sqrt of a negative number would be a NaN
   // that poisons a whole D x D moment), and u01() returns exactly 1 for r >= 2^32 - 128 (an atom at z = 0)
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaxf(-1.3862943611198906f * lg, 1e-12f)));  // sqrt(-2 ln u)
+  const float x = 6.283185307179586f * t;
+  asm("sin.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(x));
+  asm("cos.approx.ftz.f32 %0, %1;" : "=f"(c) : "f"(x));
+}
+
+// One Box-Muller pair as a packed half2 (z0 low, z1 high) -- the form the tensor-core operand
+// stores want; box_muller() below widens exactly these values.
+__device__ __forceinline__ __half2 box_muller_h2(uint32_t a, uint32_t b) {
+  // every transcendental is a single MUFU instruction (lg2 / sqrt / sin / cos, no slow paths): the
+  // result is rounded to 11 bits anyway
   float r, s, c;
-  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaxf(-1.3862943611198906f * __log2f(u), 1e-12f)));  // sqrt(-2 ln u)
-  __sincosf(6.283185307179586f * v, &s, &c);
+  box_muller_polar(a, b, r, s, c);
   return __floats2half2_rn(r * c, r * s);
 }
 
 // The same pair WITHOUT the rounding to the fp16 grid (ppi_philox_normal_full): what the generator
 // would emit if the normals were not made exact tensor-core operands.  Same Philox words, same angles.
 __device__ __forceinline__ void box_muller_full(uint32_t a, uint32_t b, float& z0, float& z1) {
-  const float u = u01(a), v = u01_23(b);
   float r, s, c;
-  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaxf(-1.3862943611198906f * __log2f(u), 1e-12f)));
-  __sincosf(6.283185307179586f * v, &s, &c);
+  box_muller_polar(a, b, r, s, c);
   z0 = r * c;
   z1 = r * s;
 }

@@ -1954,6 +1954,12 @@ static int generate_store(uint16_t* zt, int64_t n_blocks, int64_t rows_valid, in
                           uint64_t draw_id, uint64_t row_offset, int blocks_per_sm, cudaStream_t st) {
   const int64_t store_rows = round_up(D, BM);
   ProfileScope prof(PPI_PROF_SAMPLE_OPERAND, st);
+  // an SM changes its L1 / shared-memory split only when it is empty: ask for the largest shared-memory
+  // carve-out although the generator uses none, so that kernels with 100+ KB of dynamic shared memory
+  // (dense64.cu chol_step_kernel, the tcgen05 GEMMs) can become resident BESIDE it on another stream
+  static const cudaError_t carve = cudaFuncSetAttribute(
+      philox_store_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+  (void)carve;
   philox_store_kernel<<<grid_cap(n_blocks * store_rows, blocks_per_sm), 256, 0, st>>>(
       zt, store_rows, n_blocks, rows_valid, D, seed, draw_id, row_offset);
   return check_launch("philox_store_kernel");

@@ -572,6 +572,8 @@ class GaussianPolicy(object):
         # that K-sharded ranks reduce both in one collective)
         m12 = torch.zeros((2, d), dtype=torch.float64, device=mu_old_dev.device)
         m, diag = m12[0], m12[1]
+        if self.prefetch_normals == "moments" and n_total is not None and not base.injected:
+            self._prefetch_next(n_total)        # under the moment kernels and the tail
         _, s = ops.wmoments_white(base, nw, s1=m, s2=diag)
         if self.prefetch_normals == "update" and n_total is not None and not base.injected:
             self._prefetch_next(n_total)
