@@ -48,12 +48,14 @@ const char* ppi_last_error(void);
  *                    (error ~2^-21 |a||b| at any magnitude; 8 bytes per value, twice the MMA time).
  * PPI_OPT_GEMM_CHUNK = 32-deep k-blocks accumulated inside the tensor core before the partial sum is
  * promoted to fp32 registers (tcgen05 accumulation truncates: ~3e-8 relative per MMA instruction) in the
- * moment kernels.  Even, default 16: every promotion drains 128 KB of TMEM, as long as the chunk's own
- * MMAs at 8 k-blocks; measured on B200 (K = 65536, D = 2048, error relative to the largest entry):
+ * moment kernels.  Even, default 8.  Every promotion drains 128 KB of TMEM, which takes as long as the MMAs of
+ * an 8-block chunk; measured on B200 (K = 65536, D = 2048, error relative to the largest entry):
  *   chunk 8: S 2.0e-6 | 16: 3.5e-6 | 32: 7.0e-6 | 64: 1.4e-5   (the diagonal, where the truncation is a
  *   coherent bias, is replaced by the fp64-folded ppi_wmoments_white s2 before the dense tail).
- * PPI_OPT_SAMPLE_CHUNK: the same for the sampling kernels (x = mu + L z).  Even, default 32:
- *   chunk 8: x 3.9e-7 | 16: 7.7e-7 | 32: 1.5e-6 | 64: 2.9e-6.
+ * PPI_OPT_SAMPLE_CHUNK: the same for the sampling kernels (x = mu + L z).  Even, default 16:
+ *   chunk 8: x 3.9e-7, 7.8 ms per 2^20 x 2048 draw | 16: 7.7e-7, 6.9 ms | 32: 1.5e-6, 6.7 ms | 64: 2.9e-6.
+ *   The error of x feeds every later quantity (covariance at C2 after three updates: 1.8e-6 / 5.5e-6 with
+ *   chunks 8 / 32), so the default keeps a factor of four to the 1e-5 parity bound.
  * PPI_OPT_GEMM_OVERLAP != 0: the FP16X2 kernels stage the operands of pass p+1 on an internal side
  * stream while pass p multiplies (two staging buffers, event-ordered against the caller's stream;
  * the call stays asynchronous and stream-ordered for the caller).  Default 0: measured gain on

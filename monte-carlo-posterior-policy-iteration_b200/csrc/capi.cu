@@ -48,9 +48,9 @@ ProfileScope::~ProfileScope() {
 namespace ppi {
 static std::atomic<int> g_gemm_scheme{PPI_GEMM_FP16X2};
 int gemm_scheme() { return g_gemm_scheme.load(std::memory_order_relaxed); }
-static std::atomic<int> g_gemm_chunk{16};
+static std::atomic<int> g_gemm_chunk{8};
 int gemm_chunk() { return g_gemm_chunk.load(std::memory_order_relaxed); }
-static std::atomic<int> g_sample_chunk{32};
+static std::atomic<int> g_sample_chunk{16};
 int sample_chunk() { return g_sample_chunk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_gemm_overlap{0};
 int gemm_overlap() { return g_gemm_overlap.load(std::memory_order_relaxed); }

@@ -60,8 +60,16 @@ class MonteCarlo(BaseSampler):
                 z = ops.philox_normal(n_samples, d, seed, draw)
             return z.cpu().numpy().astype(np.float64)
         dev = require_cuda()
-        L = torch.linalg.cholesky(torch.as_tensor(np.asarray(sigma, np.float64), device=dev))
-        x = ops.sample_gaussian(n_samples, mu, L.float(), z=z, seed=seed, draw_id=draw)
+        s64 = torch.as_tensor(np.ascontiguousarray(sigma, np.float64), device=dev)
+        if s64.shape[0] <= 160:      # np.linalg.cholesky(sigma), ppi/samplers.py:39 -- the library's own factorisations
+            l64, status = ops.cholesky_small(s64)
+            status = float(status)
+        else:
+            l64, _, scal = ops.cholesky_blocked(s64)
+            status = float(scal[0].item())
+        if status != 0:
+            raise np.linalg.LinAlgError("Matrix is not positive definite")
+        x = ops.sample_gaussian(n_samples, mu, l64.float(), z=z, seed=seed, draw_id=draw)
         return x.cpu().numpy().astype(np.float64)
 
 
