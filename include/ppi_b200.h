@@ -379,6 +379,14 @@ int ppi_white_finish(const float* S, const double* m, const double* diag, const 
 int ppi_tri_gram(const double* l, int64_t D, double* out64, float* out32, void* stream);
 /* y32 = x0 + l v for a lower-triangular fp64 l (D, D); x0 may be NULL (the mean step mu + L m alone) */
 int ppi_tri_matvec(const double* l, int64_t D, const double* v, const float* x0, float* y32, void* stream);
+/* The two solve-dependent terms of the Gaussian KL (ppi/policies.py:146-158: np.linalg.solve(sigma_2, .)) from
+ * the Cholesky factors, by blocked forward substitution on the fp64 tensor cores:
+ *   out[0] = |l^-1 b_lower|_F^2   (= tr(Sigma_old^-1 Sigma_new) for l = chol(Sigma_old), b_lower = chol(Sigma_new))
+ *   out[1] = |l^-1 v|^2           (= (mu_1 - mu_2)^T Sigma_old^-1 (mu_1 - mu_2))
+ * l, b_lower: (D, D) fp64 lower triangular with zeros above the diagonal; v: (D) fp64; b_lower or v may be NULL.
+ * out: 2 doubles on the device.  workspace: ppi_dense_workspace_bytes(D). */
+int ppi_tri_solve_sumsq(const double* l, int64_t D, const double* b_lower, const double* v, double* out,
+                        void* workspace, size_t workspace_bytes, void* stream);
 
 /* a18-a20 fused for one rank: ppi_wmoments_diag -> centre -> ppi_wmoments_matnorm -> ppi_finalize_matnorm
  * back to back, the result packed for a single device->host read (ppi/policies.py:96-143,804-848,461-516):

@@ -669,6 +669,103 @@ tri_matvec_kernel(const double* __restrict__ L, int64_t D, const double* __restr
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Forward substitution with many right-hand sides, reduced to what the KL needs (ppi/policies.py:146-158):
+//   out[0] = |L^-1 B|_F^2  (B lower triangular, D x D: tr(Sigma_old^-1 Sigma_new) with B = L_new),
+//   out[1] = |L^-1 v|^2    ((mu_old - mu_new)^T Sigma_old^-1 (mu_old - mu_new)).
+// CTA c owns the 64 columns c of B (CTA T: v as column 0 of a zero block) and walks down the block rows k:
+//   Y_kc = L_kk^-1 (B_kc - sum_{j<k} L_kj Y_jc);
+// the products run on the fp64 tensor cores (tile_mma wants the second operand as [column][contraction], so Y is
+// kept TRANSPOSED in the workspace: Z_c[cc][i] = Y[i][64 c + cc]), the 64 x 64 substitution is warp-local (a warp
+// owns 8 columns, 4 lanes per column split the dot product).  B lower triangular => Y_kc = 0 for k < c.
+// Operand tiles of product j + 1 are in flight (cp.async) while product j multiplies.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t kTrsmSmem = (size_t)(6 * NB * PITCH + NB) * sizeof(double);
+
+__global__ void __launch_bounds__(kDenseThreads, 1)
+trsm_sumsq_kernel(const double* __restrict__ Lp, int64_t Dp, int T, const double* __restrict__ B,
+                  const double* __restrict__ v, int64_t D, double* __restrict__ Z, double* __restrict__ out) {
+  extern __shared__ double smem[];
+  double* Ab[2] = {smem, smem + 2 * NB * PITCH};
+  double* Bb[2] = {smem + NB * PITCH, smem + 3 * NB * PITCH};
+  double* Ts = smem + 4 * NB * PITCH;
+  double* Ls = smem + 5 * NB * PITCH;
+  double* invd = smem + 6 * NB * PITCH;
+  __shared__ double red[32];
+  const int c = blockIdx.x;
+  const bool vec = c == T;
+  if (vec ? v == nullptr : B == nullptr) return;
+  double* Zc = Z + (int64_t)c * NB * Dp;
+  const int k_first = vec ? 0 : c;
+  const int tid = threadIdx.x, lane = tid & 31;
+  double ss = 0.0;
+  for (int k = k_first; k < T; ++k) {
+    // right-hand side tile and the diagonal tile of L
+    const int rows = (int)min((int64_t)NB, D - (int64_t)k * NB);
+    if (!vec) {
+      load_tile<true>(Ts, B + ((int64_t)k * NB) * D + (int64_t)c * NB, D, rows, (int)min((int64_t)NB, D - (int64_t)c * NB));
+    } else {
+      for (int e = tid; e < NB * NB; e += kDenseThreads) {
+        const int r = e >> 6, cc = e & 63;
+        Ts[r * PITCH + cc] = (cc == 0 && r < rows) ? v[(int64_t)k * NB + r] : 0.0;
+      }
+    }
+    load_tile<false>(Ls, Lp + ((int64_t)k * NB) * Dp + (int64_t)k * NB, Dp);
+    TileAcc acc;
+    acc.zero();
+    if (k > k_first) {
+      load_tile_async(Ab[0], Lp + ((int64_t)k * NB) * Dp + (int64_t)k_first * NB, Dp);
+      load_tile_async(Bb[0], Zc + (int64_t)k_first * NB, Dp);
+      async_commit();
+      for (int j = k_first; j < k; ++j) {
+        const int cur = (j - k_first) & 1;
+        if (j + 1 < k) {
+          load_tile_async(Ab[cur ^ 1], Lp + ((int64_t)k * NB) * Dp + (int64_t)(j + 1) * NB, Dp);
+          load_tile_async(Bb[cur ^ 1], Zc + (int64_t)(j + 1) * NB, Dp);
+          async_commit();
+          async_wait<1>();
+        } else {
+          async_wait<0>();
+        }
+        __syncthreads();
+        tile_mma(Ab[cur], Bb[cur], acc);
+        __syncthreads();
+      }
+    } else {
+      __syncthreads();
+    }
+    tile_sub(Ts, acc);
+    if (tid < NB) invd[tid] = 1.0 / Ls[tid * PITCH + tid];
+    __syncthreads();
+    // warp-local substitution: column cc = tid / 4, lane part q = tid % 4 sums over j = q, q + 4, ...
+    {
+      const int cc = tid >> 2, q = tid & 3;
+      for (int i = 0; i < NB; ++i) {
+        double sacc = 0.0;
+        for (int j = q; j < i; j += 4) sacc = fma(Ls[i * PITCH + j], Ts[j * PITCH + cc], sacc);
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
+        if (q == 0) {
+          const double y = (Ts[i * PITCH + cc] - sacc) * invd[i];
+          Ts[i * PITCH + cc] = y;
+          ss = fma(y, y, ss);
+        }
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    // Z_c[cc][64 k + i] = Y_kc[i][cc]
+    for (int e = tid; e < NB * NB; e += kDenseThreads) {
+      const int cc = e >> 6, i = e & 63;
+      Zc[(int64_t)cc * Dp + (int64_t)k * NB + i] = Ts[i * PITCH + cc];
+    }
+    __syncthreads();
+  }
+  ss = block_sum(ss, red);
+  if (tid == 0) atomicAdd(out + (vec ? 1 : 0), ss);
+  (void)lane;
+}
+
 constexpr size_t kTileSmem = 2 * NB * PITCH * sizeof(double);   // 69 632 B: opt-in above 48 KB
 constexpr size_t kStepSmem = (size_t)(4 * NB * PITCH + 16 * kLtBlock + 256 + 4 * 16 * WP16 + 8 * 8 * WP16) * sizeof(double);
 
@@ -680,6 +777,7 @@ static int set_dense_attrs() {
   PPI_CUDA_TRY(cudaFuncSetAttribute(chol_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStepSmem));
   PPI_CUDA_TRY(cudaFuncSetAttribute(dgemm_nt_kernel<MODE_LG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileSmem));
   PPI_CUDA_TRY(cudaFuncSetAttribute(dgemm_nt_kernel<MODE_LLT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileSmem));
+  PPI_CUDA_TRY(cudaFuncSetAttribute(trsm_sumsq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTrsmSmem));
   done = true;
   return 0;
 }
@@ -782,6 +880,26 @@ extern "C" int ppi_tri_matvec(const double* l, int64_t D, const double* v, const
   PPI_REQUIRE(l && v && y32 && D > 0, PPI_ERR_INVALID, "ppi_tri_matvec: bad arguments");
   tri_matvec_kernel<<<(unsigned)ceil_div(D * 32, 256), 256, 0, (cudaStream_t)stream>>>(l, D, v, x0, y32, nullptr);
   return check_launch("tri_matvec_kernel");
+}
+
+// tr(Sigma_old^-1 Sigma_new) and the Mahalanobis term of the KL from the two Cholesky factors:
+// out[0] = |l^-1 b_lower|_F^2, out[1] = |l^-1 v|^2 (either operand may be NULL: its output is 0).
+// workspace: ppi_dense_workspace_bytes(D) (padded copy of l + the transposed solution).
+extern "C" int ppi_tri_solve_sumsq(const double* l, int64_t D, const double* b_lower, const double* v, double* out,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
+  PPI_REQUIRE(l && D > 0 && out && workspace && (b_lower || v), PPI_ERR_INVALID, "ppi_tri_solve_sumsq: bad arguments");
+  PPI_REQUIRE(workspace_bytes >= dense_ws_bytes(D), PPI_ERR_WORKSPACE, "ppi_tri_solve_sumsq: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int rc = set_dense_attrs()) return rc;
+  const DenseWs ws = dense_ws(workspace, D);
+  const int64_t Dp = pad64(D);
+  const int T = (int)(Dp / NB);
+  ProfileScope prof(PPI_PROF_DENSE_TAIL, st);
+  PPI_CUDA_TRY(cudaMemsetAsync(out, 0, 2 * sizeof(double), st));
+  pad_lower_kernel<<<(unsigned)min((int64_t)kNumSMs * 8, ceil_div(Dp * Dp, 256)), 256, 0, st>>>(l, D, Dp, ws.work);
+  // Z = (T + 1) x 64 x Dp doubles: ws.g and the head of ws.gt (contiguous)
+  trsm_sumsq_kernel<<<T + 1, kDenseThreads, kTrsmSmem, st>>>(ws.work, Dp, T, b_lower, v, D, ws.g, out);
+  return check_launch("pad_lower_kernel / trsm_sumsq_kernel", 2);
 }
 
 // debug: the phase clocks of the last factorisation (64 steps x 2 CTAs x 8 slots), see g_chol_trace

@@ -549,6 +549,11 @@ __device__ __forceinline__ void warp_transpose_reduce64(float (&t)[64]) {
 // cost terms + their reduction over the tile's columns) stays inside the two accumulator chunks the MMA issuer
 // can run ahead.  The CTA's registers are re-divided with setmaxnreg (WG0 40, drain warps 104 per thread).
 constexpr int kSampleThreads = 640;
+// setmaxnreg re-divides the CTA's OWN allocation (registers per thread at launch x threads; ptxas gives a
+// 640-thread CTA at most 96), not the SM's 64 K: a request beyond it blocks in setmaxnreg.inc for ever.
+constexpr int kSampleRegsLaunch = 96, kSampleRegsIssue = 40, kSampleRegsDrain = 104;
+static_assert(4 * 32 * kSampleRegsIssue + 16 * 32 * kSampleRegsDrain <= kSampleRegsLaunch * kSampleThreads,
+              "setmaxnreg budget of sample_gemm_kernel exceeds the CTA's register allocation");
 template <bool FP16, bool ZPAIR>
 __global__ void __launch_bounds__(kSampleThreads, 1)
 sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_constant__ CUtensorMap map_l2,
@@ -574,7 +579,7 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
   auto stages_of = [&](int tj) { return min(p.num_st, ((tj + 1) * BM + KS - 1) / KS); };  // L lower triangular
 
   if (warp < 4) {
-  reg_dec<40>();
+  reg_dec<kSampleRegsIssue>();
   if (warp == 0) {
     if (lane == 0) {
       // ================= TMA producer =================
@@ -656,7 +661,7 @@ sample_gemm_kernel(const __grid_constant__ CUtensorMap map_l, const __grid_const
   }
   } else {
     // setmaxnreg moves registers inside the CTA's own allocation (96 x 640 at launch): 40 x 128 + 104 x 512 fits
-    reg_inc<104>();
+    reg_inc<kSampleRegsDrain>();
     // ================= epilogue: TMEM -> registers -> global, 128 B per warp store =================
     const int e = warp - 4;
     const int q = warp & 3;   // TMEM lane quarter

@@ -86,6 +86,7 @@ SIGNATURES = {
     "ppi_white_finish": (_i, [_p, _p, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _sz, _p]),
     "ppi_tri_gram": (_i, [_p, _i64, _p, _p, _p]),
     "ppi_tri_matvec": (_i, [_p, _i64, _p, _p, _p, _p]),
+    "ppi_tri_solve_sumsq": (_i, [_p, _i64, _p, _p, _p, _p, _sz, _p]),
     "ppi_launch_count": (_i64, []),
     "ppi_profile_enable": (_i, [_i]),
     "ppi_profile_read": (_i, [_i, C.POINTER(_i64), C.POINTER(_d)]),

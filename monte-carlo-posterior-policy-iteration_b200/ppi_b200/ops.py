@@ -553,6 +553,18 @@ def tri_gram(l64, want32=False):
     return (out64, out32) if want32 else out64
 
 
+def tri_solve_sumsq(l64, b_lower64=None, v64=None):
+    """(|L^-1 B|_F^2, |L^-1 v|^2) as a 2-element fp64 device tensor (ppi_tri_solve_sumsq): the solve-dependent
+    terms of the Gaussian KL from Cholesky factors, without forming any inverse."""
+    dev = require_cuda()
+    D = l64.shape[0]
+    out = torch.empty(2, dtype=torch.float64, device=dev)
+    nbytes = _lib.query("ppi_dense_workspace_bytes", D)
+    ws = workspace("dense64", nbytes)
+    _lib.call("ppi_tri_solve_sumsq", ptr(l64), D, ptr(b_lower64), ptr(v64), ptr(out), ptr(ws), nbytes, stream_ptr())
+    return out
+
+
 def tri_matvec(l64, v64, x0_32):
     """x0 + L v (fp32 result) for a lower-triangular fp64 L: the mean step of the whitened update alone."""
     dev = require_cuda()

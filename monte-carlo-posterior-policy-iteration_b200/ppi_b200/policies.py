@@ -602,9 +602,9 @@ class GaussianPolicy(object):
             sigma_old.diagonal().add_(SIGMA_MIN)
             self._sigma64_dev = sigma_old
             self._factor()
-            # tr(sigma_old^-1 (sigma_old + eps I)) = D + eps |L_old^-1|_F^2  (rare branch: torch's triangular solve)
+            # tr(sigma_old^-1 (sigma_old + eps I)) = D + eps |L_old^-1|_F^2
             eye = torch.eye(d, dtype=torch.float64, device=l_old.device)
-            tr = d + SIGMA_MIN * float(torch.linalg.solve_triangular(l_old, eye, upper=False).square().sum().item())
+            tr = d + SIGMA_MIN * float(ops.tri_solve_sumsq(l_old, eye, None)[0].item())
             kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(self._logdet) + tr + msq - d)
             # (mu' - mu)^T sigma^-1 (mu' - mu) = |m|^2
         self._version += 1
@@ -667,9 +667,8 @@ class GaussianPolicy(object):
         # KL(new || old), ppi/policies.py:146-158,269, from the two Cholesky factors:
         # tr(S_old^-1 S_new) = |L_old^-1 L_new|_F^2 ; diff^T S_old^-1 diff = |L_old^-1 diff|^2
         l_new, logdet_new = self._chol64_dev, self._logdet
-        rhs = torch.cat([l_new, (mu_old_dev - mu_new_dev).double()[:, None]], dim=1)
-        sol = torch.linalg.solve_triangular(old_chol64, rhs, upper=False)
-        tr_quad = float((sol * sol).sum().item())
+        diff = (mu_old_dev - mu_new_dev).double().contiguous()
+        tr_quad = float(ops.tri_solve_sumsq(old_chol64, l_new.contiguous(), diff).sum().item())
         kl = 0.5 * (_clamped_logdet(old_logdet) - _clamped_logdet(logdet_new) + tr_quad - d)
         self._version += 1
         return float(w.stats.ess), kl

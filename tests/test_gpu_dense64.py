@@ -108,3 +108,34 @@ def test_white_finish_against_numpy(ops, record, D):
     _, _, _, scal2 = ops.white_finish(torch.as_tensor(S2, device="cuda"), ops.f64(m), ops.f64(L),
                                       torch.as_tensor(mu, device="cuda"))
     assert scal2[0].item() > 0 and abs(scal2[3].item() - m @ m) < 1e-12 * (m @ m)
+
+
+@pytest.mark.parametrize("D", [1, 63, 64, 65, 130, 200, 840, 1000, 2048])
+def test_tri_solve_sumsq_against_scipy(ops, record, D):
+    """The solve-dependent KL terms (ppi/policies.py:146-158) from two Cholesky factors: |L^-1 B|_F^2 and
+    |L^-1 v|^2 against SciPy's triangular solve in fp64; either operand alone as well."""
+    import scipy.linalg
+    import torch
+
+    rng = np.random.default_rng(7 * D + 1)
+    l = np.linalg.cholesky(_spd(D, rng))
+    b = np.linalg.cholesky(_spd(D, rng, 0.5))
+    v = rng.standard_normal(D)
+    ref_b = float(np.sum(scipy.linalg.solve_triangular(l, b, lower=True) ** 2))
+    ref_v = float(np.sum(scipy.linalg.solve_triangular(l, v, lower=True) ** 2))
+    dev = torch.device("cuda")
+    l_d, b_d, v_d = (torch.as_tensor(x, device=dev).contiguous() for x in (l, b, v))
+    out = ops.tri_solve_sumsq(l_d, b_d, v_d).cpu().numpy()
+    e_b, e_v = abs(out[0] - ref_b) / ref_b, abs(out[1] - ref_v) / ref_v
+    record(f"tri_solve_sumsq[{D}]", matrix=e_b, vector=e_v)
+    assert e_b < 1e-11 and e_v < 1e-11
+    only_b = ops.tri_solve_sumsq(l_d, b_d, None).cpu().numpy()
+    only_v = ops.tri_solve_sumsq(l_d, None, v_d).cpu().numpy()
+    # (per-CTA partial sums meet in an fp64 atomic: equal up to summation order)
+    assert abs(only_b[0] - out[0]) <= 1e-13 * out[0] and only_b[1] == 0.0
+    assert abs(only_v[1] - out[1]) <= 1e-13 * out[1] and only_v[0] == 0.0
+    # identity right-hand side: |L^-1|_F^2 (the regularisation branch of the whitened update)
+    eye = torch.eye(D, dtype=torch.float64, device=dev)
+    inv = float(ops.tri_solve_sumsq(l_d, eye, None)[0].item())
+    ref_inv = float(np.sum(scipy.linalg.solve_triangular(l, np.eye(D), lower=True) ** 2))
+    assert abs(inv - ref_inv) / ref_inv < 1e-11
