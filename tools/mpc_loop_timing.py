@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--iters", type=int, default=2)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--profile", action="store_true", help="cProfile the device loop and skip the NumPy legs")
     a = ap.parse_args()
     from oracle import ppi_oracle as O
     from ppi_b200 import algorithms as alg, functions as fn, policies as pol, samplers as smp
@@ -61,6 +62,22 @@ def main():
         act = control_step(i)
     torch.cuda.synchronize()
     ms_dev = (time.perf_counter() - t_start) / a.steps * 1e3
+    if a.profile:
+        import cProfile
+        import io
+        import pstats
+
+        pr = cProfile.Profile()
+        pr.enable()
+        for i in range(6 + a.steps, 6 + 2 * a.steps):
+            control_step(i)
+        torch.cuda.synchronize()
+        pr.disable()
+        s = io.StringIO()
+        pstats.Stats(pr, stream=s).sort_stats("cumulative").print_stats(60)
+        print(f"control step {ms_dev:.3f} ms (K = {K}, iters = {a.iters})")
+        print(s.getvalue()[:12000])
+        return
 
     # the same control step in NumPy (oracle restatement of the reference), fresh standard normals
     rng = np.random.default_rng(0)
