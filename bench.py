@@ -535,8 +535,14 @@ def run_b200(args, wl):
     policy = res["policy"]
     if wl["kind"] == "gaussian":
         D = wl["D"]
+        # a DENSE, well-conditioned host covariance (spectrum in [0.5, 1.5]): a diagonal one would hand the
+        # tensor cores operands full of zeros, which run cooler and faster on a power-capped board than the
+        # dense factors the resident leg sees after its warm-up
+        gen = torch.Generator().manual_seed(20261105)
+        a = torch.randn((D, D), dtype=torch.float64, generator=gen)
         pin = {"mu": torch.ones(D, dtype=torch.float64).pin_memory(),
-               "sigma": (0.5 * torch.eye(D, dtype=torch.float64)).pin_memory()}
+               "sigma": (0.5 * torch.eye(D, dtype=torch.float64) + (a @ a.T) * (0.25 / D)).pin_memory()}
+        del a
         host = {k: v.numpy() for k, v in pin.items()}
         sink = {}
 

@@ -21,8 +21,11 @@ host = {k: v.numpy() for k, v in pin.items()}
 sink = {}
 
 
+K = int(sys.argv[1]) if len(sys.argv) > 1 else wl["K"] // 8      # the per-rank share at N = 8
+
+
 def step():
-    pol_, sol_, cost_, K = bench.build_workload(wl, 1, pinned=host)
+    pol_, sol_, cost_ = bench.build_workload(wl, K, pinned=host)
     bench.one_step(pol_, sol_, cost_, K)
     sink["mu"], sink["sigma"] = pol_.mu, pol_.sigma
 
@@ -30,10 +33,17 @@ def step():
 for _ in range(3):
     step()
 torch.cuda.synchronize()
+import time
+
+t0 = time.perf_counter()
+for _ in range(10):
+    step()
+torch.cuda.synchronize()
+print(f"e2e step at K = {K}: {(time.perf_counter() - t0) * 100:.3f} ms wall per step")
 pr = cProfile.Profile()
 pr.enable()
 for _ in range(5):
     step()
 torch.cuda.synchronize()
 pr.disable()
-pstats.Stats(pr).sort_stats("cumulative").print_stats(35)
+pstats.Stats(pr).sort_stats("cumulative").print_stats(45)
