@@ -1014,46 +1014,55 @@ split_rows_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int
 // Samples >= rows_valid and columns >= D are written as zeros (finite operands for the padded tiles).
 __global__ void __launch_bounds__(256, 8)
 philox_store_kernel(uint16_t* __restrict__ zt, int64_t store_rows, int64_t n_blocks, int64_t rows_valid,
-                    int64_t D, uint64_t seed, uint64_t draw, uint64_t row_offset) {
+                    int64_t D, uint64_t seed, uint64_t draw, uint64_t row_offset, int rows_log2) {
+  // work item = (sample block of 2048, group of 2^rows_log2 store rows), dealt round-robin to the CTAs.  Inside
+  // an item a thread keeps its 8 samples (two row quads) and walks down the rows: the row quads and the
+  // alignment / ragged-end decision are loop invariants, the inner loop is branch-free with a 32-bit row
+  // counter and one pointer increment -- the per-item bookkeeping of the flat version cost 46 of 212
+  // instructions per 16-byte store (ncu).
   const PhiloxKeys keys = philox_keys(seed ^ kPhiloxColTag);
   const bool aligned = (row_offset & 3) == 0;
-  // items (sample block, column) are dealt round-robin to the CTAs (equal shares); the pair is advanced
-  // incrementally -- a 64-bit division per item cost a quarter of the instructions of the first version
-  // (28 per normal in the ncu capture)
-  const uint32_t rows32 = (uint32_t)store_rows;
-  const uint32_t d_blk = gridDim.x / rows32, d_i = gridDim.x % rows32;
-  uint32_t blk32 = blockIdx.x / rows32, i32 = blockIdx.x % rows32;
-  for (; blk32 < (uint32_t)n_blocks; blk32 += d_blk, i32 += d_i) {
-    if (i32 >= rows32) { i32 -= rows32; ++blk32; if (blk32 >= (uint32_t)n_blocks) break; }
-    const int64_t blk = blk32, i = i32;
-    const int64_t k = blk * kZBlock + (int64_t)threadIdx.x * 8;       // first local sample of this thread
-    uint4 o = make_uint4(0u, 0u, 0u, 0u);
-    if (i < D && k < rows_valid) {
-      if (aligned && k + 8 <= rows_valid) {
+  const uint32_t groups = (uint32_t)(store_rows >> rows_log2);
+  const uint32_t n_items = (uint32_t)n_blocks * groups;
+  const uint32_t rows_item = 1u << rows_log2;
+  for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const uint32_t blk = item / groups, i0 = (item - blk * groups) << rows_log2;
+    const int64_t k = (int64_t)blk * kZBlock + (int64_t)threadIdx.x * 8;       // first local sample of this thread
+    uint16_t* dst = zt + ((int64_t)blk * store_rows + i0) * kZBlock + (int64_t)threadIdx.x * 8;
+    const uint32_t i_end = (uint32_t)max((int64_t)i0, min((int64_t)(i0 + rows_item), D));  // rows >= D: zeros
+    if (aligned && k + 8 <= rows_valid) {
+      const uint64_t q = (row_offset + (uint64_t)k) >> 2;
+#pragma unroll 2
+      for (uint32_t i = i0; i < i_end; ++i, dst += kZBlock) {
         __half2 a0, a1, b0, b1;
-        const uint64_t q = (row_offset + (uint64_t)k) >> 2;
-        philox_cq_normal4_h2(keys, draw, (uint32_t)i, q, a0, a1);
-        philox_cq_normal4_h2(keys, draw, (uint32_t)i, q + 1, b0, b1);
+        philox_cq_normal4_h2(keys, draw, i, q, a0, a1);
+        philox_cq_normal4_h2(keys, draw, i, q + 1, b0, b1);
+        uint4 o;
         o.x = *reinterpret_cast<const uint32_t*>(&a0);
         o.y = *reinterpret_cast<const uint32_t*>(&a1);
         o.z = *reinterpret_cast<const uint32_t*>(&b0);
         o.w = *reinterpret_cast<const uint32_t*>(&b1);
-      } else {   // unaligned shard offset or the ragged end: element by element
+        *reinterpret_cast<uint4*>(dst) = o;
+      }
+    } else {   // unaligned shard offset, the ragged end of the draw, or samples beyond it (zeros)
+      for (uint32_t i = i0; i < i_end; ++i, dst += kZBlock) {
         uint16_t h[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
-          const float v = (k + u < rows_valid) ? philox_cq_normal1(seed, draw, row_offset + (uint64_t)(k + u), (uint32_t)i)
-                                                : 0.f;
+          const float v = (k + u < rows_valid) ? philox_cq_normal1(seed, draw, row_offset + (uint64_t)(k + u), i) : 0.f;
           const __half hv = __float2half_rn(v);
           h[u] = *reinterpret_cast<const uint16_t*>(&hv);
         }
+        uint4 o;
         o.x = (uint32_t)h[0] | ((uint32_t)h[1] << 16);
         o.y = (uint32_t)h[2] | ((uint32_t)h[3] << 16);
         o.z = (uint32_t)h[4] | ((uint32_t)h[5] << 16);
         o.w = (uint32_t)h[6] | ((uint32_t)h[7] << 16);
+        *reinterpret_cast<uint4*>(dst) = o;
       }
     }
-    *reinterpret_cast<uint4*>(zt + (blk * store_rows + i) * kZBlock + (int64_t)threadIdx.x * 8) = o;
+    for (uint32_t i = i_end; i < i0 + rows_item; ++i, dst += kZBlock)
+      *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
   }
 }
 
@@ -1965,8 +1974,13 @@ static int generate_store(uint16_t* zt, int64_t n_blocks, int64_t rows_valid, in
   static const cudaError_t carve = cudaFuncSetAttribute(
       philox_store_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
   (void)carve;
-  philox_store_kernel<<<grid_cap(n_blocks * store_rows, blocks_per_sm), 256, 0, st>>>(
-      zt, store_rows, n_blocks, rows_valid, D, seed, draw_id, row_offset);
+  // rows per work item: as many as keeps >= 6 items per resident CTA (balance) -- 128 at K = 2^20, 16 at 2^17
+  const int64_t ctas = (int64_t)kNumSMs * blocks_per_sm;
+  int rows_log2 = 7;
+  while (rows_log2 > 3 && n_blocks * (store_rows >> rows_log2) < 6 * ctas) --rows_log2;
+  const int64_t n_items = n_blocks * (store_rows >> rows_log2);
+  philox_store_kernel<<<(unsigned)(n_items < ctas ? n_items : ctas), 256, 0, st>>>(
+      zt, store_rows, n_blocks, rows_valid, D, seed, draw_id, row_offset, rows_log2);
   return check_launch("philox_store_kernel");
 }
 

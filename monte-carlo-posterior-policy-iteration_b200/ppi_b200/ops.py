@@ -10,7 +10,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .device import f32, f32_cached, f64, ptr, read_stats, require_cuda, stream_ptr, workspace
+from .device import f32, f32_cached, f64, ptr, read_stats, require_cuda, stream_ptr, sync_current_stream, workspace
 
 _u64 = lambda v: C.c_uint64(int(v) & 0xFFFFFFFFFFFFFFFF)  # noqa: E731
 
@@ -129,7 +129,7 @@ def kernel_shift(kind, sigma, ls, period, t_old, t_new, prior, prior_inv, cov_in
               ip[5] if has_lim else None, ip[6] if has_lim else None, float(anneal), float(jitter),
               op[0], op[1], op[2], op[3], ptr(st["ws"]), stream_ptr())
     st["h_out"].copy_(st["d_out"], non_blocking=True)
-    torch.cuda.current_stream().synchronize()
+    sync_current_stream()
     host = st["np_out"]
     a, b, c = st["cut"]
     return (host[:a].reshape(n_new, d).copy(), host[a:b].reshape(n_new, n_new).copy(),
@@ -481,7 +481,7 @@ def matnorm_update(x, nw, shift1, inv_cov_out, jitter=0.0, map_index=-1, stats=N
               nbytes, stream_ptr())
     stage = _pinned(8 * n)[: 8 * n].view(torch.float64)
     stage.copy_(packed, non_blocking=True)
-    torch.cuda.current_stream().synchronize()
+    sync_current_stream()
     host = stage.numpy().copy()
     if on_dev:
         stats.fill(host[n - n_stats:].tobytes())
