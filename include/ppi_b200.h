@@ -273,6 +273,24 @@ size_t ppi_solve_temperature_workspace_bytes(int64_t K);
 int ppi_solve_temperature(const float* costs, int64_t K, int mode, double hyper, float* nw,
                           float* log_w, ppi_weight_stats* stats, void* workspace,
                           size_t workspace_bytes, void* stream);
+/* ppi_solve_temperature without a workspace argument and without any allocation.  No counterpart in the
+ * reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, results and error
+ * behaviour as ppi_solve_temperature; the solver's scratch (grid-barrier counter + per-block partial sums,
+ * 75 904 bytes) is a file-scope `static __device__` array inside the library, held by every GPU that loads it
+ * until the process exits.  Limits and rules:
+ *   - K <= PPI_SOLVE_STATIC_MAX_K costs, larger K is refused with PPI_ERR_UNSUPPORTED;
+ *   - calls no cudaMalloc / cudaFree / allocating routine and creates no CUDA events (it is not bracketed by
+ *     ppi_profile_enable); the FIRST call on each device resolves the array's device address
+ *     (cudaGetSymbolAddress, once per device, with the caller's current device) -- make one call per device
+ *     before capturing a graph; `stream` must belong to the current device;
+ *   - every call on a device shares the one array: calls that overlap on the GPU (different streams, or graph
+ *     branches without a dependency) race -- serialise them, or use ppi_solve_temperature with one workspace
+ *     per stream.  The array keeps the previous call's contents; what must start at zero (the barrier counter)
+ *     is cleared on `stream` at the start of every call. */
+#define PPI_SOLVE_STATIC_MAX_K (1 << 22)
+int ppi_solve_temperature_static(const float* costs, int64_t K, int mode, double hyper, float* nw,
+                                 float* log_w, ppi_weight_stats* stats, void* stream);
 
 /* user-supplied log-weights -> normalised weights (m_projection head)  ppi/policies.py:84-87,
  * argmax ppi/policies.py:811,1153.  costs may be NULL (then the cost_* fields are 0).       */

@@ -20,6 +20,9 @@
 // The reference's Brent solutions agree with those roots to ~1e-8.
 #include "common.cuh"
 
+#include <mutex>
+#include <optional>
+
 namespace ppi {
 
 constexpr int kSolveThreads = 256;
@@ -576,7 +579,7 @@ static int64_t next_pow2(int64_t v) {
 
 static int launch_solve(const float* in, int64_t K, int mode, double hyper, float* nw, float* log_w,
                         ppi_weight_stats* stats, void* workspace, size_t workspace_bytes,
-                        cudaStream_t st) {
+                        cudaStream_t st, bool bracket = true) {
   PPI_REQUIRE(workspace_bytes >= sizeof(SolveWorkspace), PPI_ERR_WORKSPACE,
               "solve workspace too small: %zu < %zu", workspace_bytes, sizeof(SolveWorkspace));
   SolveWorkspace* ws = (SolveWorkspace*)workspace;
@@ -589,7 +592,8 @@ static int launch_solve(const float* in, int64_t K, int mode, double hyper, floa
   }
   void* args[] = {(void*)&in, (void*)&K, (void*)&mode, (void*)&hyper, (void*)&nw, (void*)&log_w,
                   (void*)&stats, (void*)&ws};
-  ProfileScope prof(PPI_PROF_SOLVE, st);
+  std::optional<ProfileScope> prof;   // (bracket = false: the allocation-free entry point creates no events)
+  if (bracket) prof.emplace(PPI_PROF_SOLVE, st);
   if (K <= 65536) {
     // up to 16 CTAs of 4096 costs each as one cluster (non-portable size, supported on B200; the
     // per-element fp64 work binds one SM to ~0.1 us per 256 costs, so more CTAs beat larger slices):
@@ -648,6 +652,57 @@ extern "C" int ppi_solve_temperature(const float* costs, int64_t K, int mode, do
   if (mode == PPI_TEMP_REPS_KL) PPI_REQUIRE(hyper > 0.0, PPI_ERR_INVALID, "epsilon must be > 0");
   return launch_solve(costs, K, mode, hyper, nw, log_w, stats, workspace, workspace_bytes,
                       (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// ppi_solve_temperature for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc): the solver's scratch (grid-barrier counter + per-block partial sums, 74 KB) lives in
+// a file-scope device array that every GPU holding the library keeps until exit.  In host code the array's NAME
+// is a host-side stand-in, not a device address: its address is resolved once per device with
+// cudaGetSymbolAddress (that device current) and the resolved pointer is what the kernel gets.
+// ---------------------------------------------------------------------------------------------
+namespace ppi {
+static __device__ __align__(256) unsigned char g_solve_scratch[sizeof(SolveWorkspace)];
+constexpr int kMaxScratchDevices = 64;
+
+static int solve_scratch_address(void** out) {
+  static std::mutex mu;
+  static void* resolved[kMaxScratchDevices] = {};
+  int dev = -1;
+  PPI_CUDA_TRY(cudaGetDevice(&dev));
+  PPI_REQUIRE(dev >= 0 && dev < kMaxScratchDevices, PPI_ERR_UNSUPPORTED,
+              "ppi_solve_temperature_static: device ordinal %d outside [0, %d)", dev, kMaxScratchDevices);
+  std::lock_guard<std::mutex> lock(mu);
+  if (resolved[dev] == nullptr) {
+    void* p = nullptr;
+    PPI_CUDA_TRY(cudaGetSymbolAddress(&p, g_solve_scratch));
+    PPI_REQUIRE(p != nullptr, PPI_ERR_DRIVER, "ppi_solve_temperature_static: scratch symbol did not resolve");
+    resolved[dev] = p;
+  }
+  *out = resolved[dev];
+  return 0;
+}
+}  // namespace ppi
+
+extern "C" int ppi_solve_temperature_static(const float* costs, int64_t K, int mode, double hyper, float* nw,
+                                            float* log_w, ppi_weight_stats* stats, void* stream) {
+  PPI_REQUIRE(costs && nw && stats && K > 0, PPI_ERR_INVALID, "ppi_solve_temperature_static: bad arguments");
+  PPI_REQUIRE(K <= (int64_t)PPI_SOLVE_STATIC_MAX_K, PPI_ERR_UNSUPPORTED,
+              "ppi_solve_temperature_static: K = %lld exceeds the maximum of %lld costs of the allocation-free "
+              "variant; use ppi_solve_temperature with a caller-owned workspace",
+              (long long)K, (long long)PPI_SOLVE_STATIC_MAX_K);
+  PPI_REQUIRE(mode >= PPI_TEMP_FIXED_NORMALISED && mode <= PPI_TEMP_LOWER_BOUND, PPI_ERR_INVALID,
+              "unknown temperature mode %d", mode);
+  if (mode == PPI_TEMP_ESS_TARGET) PPI_REQUIRE(hyper > 0.0, PPI_ERR_INVALID, "n_elites must be > 0");
+  if (mode == PPI_TEMP_LOWER_BOUND)
+    PPI_REQUIRE(hyper > 0.0 && hyper < 1.0, PPI_ERR_INVALID, "delta must be in (0,1)");
+  if (mode == PPI_TEMP_REPS_KL) PPI_REQUIRE(hyper > 0.0, PPI_ERR_INVALID, "epsilon must be > 0");
+  void* scratch = nullptr;
+  if (int rc = solve_scratch_address(&scratch)) return rc;
+  // the barrier counter is cleared on the stream by launch_solve; the partial sums are written before they are
+  // read inside every evaluation, so the previous call's contents do not matter
+  return launch_solve(costs, K, mode, hyper, nw, log_w, stats, scratch, sizeof(SolveWorkspace),
+                      (cudaStream_t)stream, /*bracket=*/false);
 }
 
 extern "C" int ppi_normalise_log_weights(const float* log_w, int64_t K, float* nw,

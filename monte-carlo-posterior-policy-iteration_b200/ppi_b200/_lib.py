@@ -72,6 +72,7 @@ SIGNATURES = {
     "ppi_cost_tracking": (_i, [_p, _i64, _i, _i, _p, _i, _p, _p]),
     "ppi_solve_temperature_workspace_bytes": (_sz, [_i64]),
     "ppi_solve_temperature": (_i, [_p, _i64, _i, _d, _p, _p, _p, _p, _sz, _p]),
+    "ppi_solve_temperature_static": (_i, [_p, _i64, _i, _d, _p, _p, _p, _p]),
     "ppi_normalise_log_weights": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
     "ppi_cem_workspace_bytes": (_sz, [_i64]),
     "ppi_cem_weights": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _sz, _p]),
