@@ -1449,7 +1449,7 @@ white_operand_kernel(const uint16_t* __restrict__ zrows, const float* __restrict
   }
   if (s1 && threadIdx.x < 128 && it + threadIdx.x < D)
     atomicAdd(s1 + it + threadIdx.x, colsum * (double)(1.f / sa));
-  // diagonal of S (see white_mean_kernel): the tile holds the STORED normals, z = tile / scale_b
+  // diagonal of S (see white_mean_bulk_kernel): the tile holds the STORED normals, z = tile / scale_b
   if (s2 && threadIdx.x < 128 && it + threadIdx.x < D)
     atomicAdd(s2 + it + threadIdx.x, colsq * (double)(1.f / sa) * (double)unz);
 }
@@ -1461,7 +1461,7 @@ white_operand_kernel(const uint16_t* __restrict__ zrows, const float* __restrict
 // (128 columns x 64 samples, exact fp16) into the fp16 pair of scale_a nw_k z in shared memory
 // (two 32-sample pair tiles in the canonical K-major 128-byte-swizzle layout) while the previous
 // stage multiplies; the B box feeds the MMA as it lands.  m = sum_k nw_k z_k comes from
-// white_mean_kernel (one HBM pass over the 2-byte store).
+// white_mean_bulk_kernel (one HBM pass over the 2-byte store).
 // CTA = 4 warpgroups: WG0 = TMA producer + MMA issuer, WG1-2 = TMEM drain (fp32 register
 // accumulators, as syrk_gemm_kernel), WG3 = transform; register budget moved with setmaxnreg.
 // ---------------------------------------------------------------------------------------------
@@ -1482,31 +1482,56 @@ white_weights_kernel(const float* __restrict__ nw, int64_t K, int64_t kt, const 
 
 // s1[i] += sum_k nw_k zT[i][k]: block = 8 store rows x 16384 samples, weights loaded once per 8 rows.
 constexpr int kMeanRows = 8;
-__global__ void __launch_bounds__(256)
-white_mean_kernel(const uint16_t* __restrict__ zt, int64_t zt_rows, const float* __restrict__ nw, int64_t K,
-                  int64_t D, double* __restrict__ s1, double* __restrict__ s2, int chunk) {
-  // s2[i] += sum_k nw_k zT[i][k]^2: the DIAGONAL of S with round-to-nearest fp32 products and fp64 sums.  The
-  // tensor-core accumulation truncates (a bias of ~2e-6 on sums of positive terms), and tr C = sum of D such
-  // entries enters the KL as (tr C - D): the finish takes the diagonal from here (same pass over the store).
+// white_mean_bulk_kernel: s1[i] += sum_k nw_k zT[i][k] and s2[i] += sum_k nw_k zT[i][k]^2 -- the DIAGONAL of S with
+// round-to-nearest fp32 products and fp64 sums.  The tensor-core accumulation truncates (a bias of ~2e-6 on sums
+// of positive terms), and tr C = sum of D such entries enters the KL as (tr C - D): the finish takes the diagonal
+// from here (one HBM pass over the 2-byte store).
+// The store is streamed through shared memory by bulk copies (cp.async.bulk, the non-tensor TMA path): the 8 rows
+// of a group are adjacent in zT[block][row][2048], so one stage = one 32 KB copy.  Bytes in flight do not depend
+// on registers and occupancy (a first version that loaded into registers held 3 CTAs of 80 registers per SM,
+// 35 % occupancy, and spent its time in long-scoreboard stalls: ncu 5.0 TB/s, 0.95 ms; this one 6.6 TB/s, 0.65 ms).  CTA = (row group, range
+// of sample blocks), two stages, two CTAs per SM; one thread issues the copies, __syncthreads() hands a
+// consumed stage back.
+constexpr int kMeanStages = 2;
+constexpr uint32_t kMeanStageBytes = kMeanRows * (uint32_t)kZBlock * 2u;   // 32 KB
+constexpr size_t kMeanBulkSmem = kMeanStages * kMeanStageBytes + 1024;
+
+__global__ void __launch_bounds__(256, 2)
+white_mean_bulk_kernel(const uint16_t* __restrict__ zt, int64_t zt_rows, const float* __restrict__ nw, int64_t K,
+                       int64_t D, int n_blocks, int ranges, double* __restrict__ s1, double* __restrict__ s2) {
+  extern __shared__ uint8_t wm_raw[];
+  __shared__ __align__(8) uint64_t full[kMeanStages];
   __shared__ double red[kMeanRows][8];
   __shared__ double red2[kMeanRows][8];
+  const uint32_t raw = smem_u32(wm_raw);
+  const uint32_t base = (raw + 127u) & ~127u;
+  const uint8_t* tiles = wm_raw + (base - raw);
   const int64_t i0 = (int64_t)blockIdx.x * kMeanRows;
-  const int64_t kc0 = (int64_t)blockIdx.y * chunk;
+  const int b_begin = (int)((int64_t)blockIdx.y * n_blocks / ranges);
+  const int b_end = (int)(((int64_t)blockIdx.y + 1) * n_blocks / ranges);
+  const int nb = b_end - b_begin;
   const bool w_vec = (reinterpret_cast<uintptr_t>(nw) & 15) == 0;
+  auto issue = [&](int it) {     // thread 0: stage it % 2 <- rows i0 .. i0+7 of sample block b_begin + it
+    const int s = it % kMeanStages;
+    const uint32_t bar = smem_u32(&full[s]);
+    mbar_expect_tx(bar, kMeanStageBytes);
+    const uint16_t* src = zt + ((int64_t)(b_begin + it) * zt_rows + i0) * kZBlock;
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(base + (uint32_t)s * kMeanStageBytes), "l"(src), "r"(kMeanStageBytes), "r"(bar) : "memory");
+  };
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kMeanStages; ++s) mbar_init(smem_u32(&full[s]), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    for (int it = 0; it < kMeanStages && it < nb; ++it) issue(it);
+  }
+  __syncthreads();
   float acc[kMeanRows], acc2[kMeanRows];
-  double accd[kMeanRows], accd2[kMeanRows];     // fp32 partials are folded into fp64 every 8 iterations (64 terms)
+  double accd[kMeanRows], accd2[kMeanRows];     // fp32 partials are folded into fp64 every 8 stages (64 terms)
 #pragma unroll
   for (int r = 0; r < kMeanRows; ++r) { acc[r] = acc2[r] = 0.f; accd[r] = accd2[r] = 0.0; }
-  for (int it = 0; it < chunk / (256 * 8); ++it) {
-    const int64_t k = kc0 + ((int64_t)it * 256 + threadIdx.x) * 8;
-    if (k >= K) break;
-    if ((it & 7) == 7) {
-#pragma unroll
-      for (int r = 0; r < kMeanRows; ++r) {
-        accd[r] += (double)acc[r]; accd2[r] += (double)acc2[r];
-        acc[r] = acc2[r] = 0.f;
-      }
-    }
+  for (int it = 0; it < nb; ++it) {
+    const int s = it % kMeanStages;
+    const int64_t k = (int64_t)(b_begin + it) * kZBlock + (int64_t)threadIdx.x * 8;
     float w[8];
     if (k + 8 <= K && w_vec) {
       const float4 w0 = __ldg(reinterpret_cast<const float4*>(nw + k));
@@ -1516,14 +1541,19 @@ white_mean_kernel(const uint16_t* __restrict__ zt, int64_t zt_rows, const float*
 #pragma unroll
       for (int u = 0; u < 8; ++u) w[u] = (k + u < K) ? __ldg(nw + k + u) : 0.f;
     }
-    uint4 zr[kMeanRows];
+    if ((it & 7) == 7) {
 #pragma unroll
-    for (int r = 0; r < kMeanRows; ++r)
-      zr[r] = (i0 + r < D) ? __ldg(reinterpret_cast<const uint4*>(zt + zt_index(k, i0 + r, zt_rows)))
-                           : make_uint4(0, 0, 0, 0);
+      for (int r = 0; r < kMeanRows; ++r) {
+        accd[r] += (double)acc[r]; accd2[r] += (double)acc2[r];
+        acc[r] = acc2[r] = 0.f;
+      }
+    }
+    mbar_wait(smem_u32(&full[s]), (uint32_t)(it / kMeanStages) & 1u);
+    const uint8_t* tile = tiles + (size_t)s * kMeanStageBytes + (size_t)threadIdx.x * 16;
 #pragma unroll
     for (int r = 0; r < kMeanRows; ++r) {
-      const uint32_t zw[4] = {zr[r].x, zr[r].y, zr[r].z, zr[r].w};
+      const uint4 zr = *reinterpret_cast<const uint4*>(tile + (size_t)r * kZBlock * 2);
+      const uint32_t zw[4] = {zr.x, zr.y, zr.z, zr.w};
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const float2 zf = __half22float2(*reinterpret_cast<const __half2*>(&zw[u]));
@@ -1534,6 +1564,8 @@ white_mean_kernel(const uint16_t* __restrict__ zt, int64_t zt_rows, const float*
         acc2[r] = fmaf(wy, zf.y, acc2[r]);
       }
     }
+    __syncthreads();                                   // stage consumed by every thread
+    if (threadIdx.x == 0 && it + kMeanStages < nb) issue(it + kMeanStages);
   }
   const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
 #pragma unroll
@@ -1875,11 +1907,20 @@ static int wmoments_white_direct(const void* zstore, const float* nw, int64_t K,
     ProfileScope prof(PPI_PROF_WMOMENTS_DIAG, st);
     // samples per CTA: as long as the grid still holds ~8 CTAs per SM (a 16 384-sample CTA lives 6 us: launch and
     // reduction tails cost a quarter of the kernel, ncu: 57 % of the DRAM peak)
-    int64_t chunk = 131072;
-    while (chunk > 16384 && ceil_div(D, kMeanRows) * ceil_div(K, chunk) < (int64_t)kNumSMs * 8) chunk >>= 1;
-    dim3 mg((unsigned)ceil_div(D, kMeanRows), (unsigned)ceil_div(K, chunk));
-    white_mean_kernel<<<mg, 256, 0, st>>>(zt, pl.Dp, nw, K, D, s1, s2, (int)chunk);
-    if (int rc = check_launch("white_mean_kernel")) return rc;
+    static bool mean_attr = false;
+    if (!mean_attr) {
+      PPI_CUDA_TRY(cudaFuncSetAttribute(white_mean_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)kMeanBulkSmem));
+      mean_attr = true;
+    }
+    // CTA = (group of 8 store rows, range of 2048-sample blocks): ~7 waves of 2 CTAs per SM
+    const int64_t groups = pl.Dp / kMeanRows, n_blocks = kt / kZBlock;
+    int64_t ranges = ceil_div((int64_t)kNumSMs * 2 * 7, groups);
+    if (ranges > n_blocks) ranges = n_blocks;
+    if (ranges < 1) ranges = 1;
+    dim3 mg((unsigned)groups, (unsigned)ranges);
+    white_mean_bulk_kernel<<<mg, 256, kMeanBulkSmem, st>>>(zt, pl.Dp, nw, K, D, (int)n_blocks, (int)ranges, s1, s2);
+    if (int rc = check_launch("white_mean_bulk_kernel")) return rc;
   }
   CUtensorMap a, b;
   if (int rc = make_map(&a, zt, (kt / kZBlock) * pl.Dp, kZBlock, BM, OP_F16_SINGLE)) return rc;
