@@ -158,6 +158,17 @@ class DeviceWeights:
         return float(np.asarray(self).min())
 
 
+_side_streams = {}
+
+
+def _side_stream(dev):
+    """One side stream per device for the generator of a draw that runs beside other work."""
+    st = _side_streams.get(dev.index)
+    if st is None:
+        st = _side_streams[dev.index] = torch.cuda.Stream(device=dev)
+    return st
+
+
 def _weights(log_weights):
     """Anything the reference accepts as log_weights -> DeviceWeights."""
     if isinstance(log_weights, DeviceWeights):
@@ -413,6 +424,12 @@ class GaussianPolicy(object):
             begin, end = shard_rows(x.shape[0])
             handle = DeviceArray(f32(x[begin:end]), begin, x.shape[0])
             return handle, handle
+        if (self._chol_dev is None and self._pre is None and self.defer_draws and d > self.small_dim
+                and not self.diagonal and _lib.load().ppi_get_option(_lib.OPT_GEMM_SCHEME) == _lib.GEMM_FP16X2):
+            # sigma is still on the host (a fresh policy, or the caller replaced it): the base normals do not
+            # depend on it, so their generator starts on the side stream now and runs beside the 4 D^2-byte
+            # upload (copy engine) and the factorisation that _factor() enqueues below
+            self._prefetch_next(n_samples)
         z, seed, draw, begin, n_local, n_total = _draw(self.sampler, n_samples, d)
         if d > self.small_dim and not self.diagonal and _lib.load().ppi_get_option(_lib.OPT_GEMM_SCHEME) == _lib.GEMM_FP16X2:
             # keep the base normals in HBM: weighted_update on this very handle contracts z, not x
@@ -475,12 +492,12 @@ class GaussianPolicy(object):
         dev = require_cuda()
         st = self.__dict__.setdefault("_pre_state", {})
         if st.get("shape") != (n_local, d):
-            sbytes = _lib.query("ppi_zstore_bytes", n_local, d, 0)
-            st.update(shape=(n_local, d), stores=[ops._aligned_bytes(sbytes, dev) for _ in range(2)],
-                      side=torch.cuda.Stream(), slot=0)
+            st.update(shape=(n_local, d), stores=[None, None], side=_side_stream(dev), slot=0)
             self._pre_owner = [None, None]
             self._pre_pending = [None, None]
         slot = st["slot"] = 1 - st["slot"]
+        if st["stores"][slot] is None:      # allocated on first use: a policy that prefetches once holds one store
+            st["stores"][slot] = ops._aligned_bytes(_lib.query("ppi_zstore_bytes", n_local, d, 0), dev)
         owner = self._pre_owner[slot]
         if owner is not None:
             owner.valid = False     # a handle that still holds this store falls back to the x-space update
