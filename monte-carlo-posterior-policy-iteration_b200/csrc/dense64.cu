@@ -230,62 +230,6 @@ __device__ __forceinline__ bool tile_cholesky(const double* __restrict__ Ds, dou
   return *fail_s == 0;
 }
 
-// X = T L^-T for the 64 x 64 tile in Ts (pitch PITCH) and the factor held in Lt / dinv: blocked forward
-// substitution over the 16 block columns; on return thread (ty, tx) holds block (ty, tx) of X in r.
-// pn: 2 x 256 doubles of scratch (the solved block column, double-buffered: one barrier per step).
-__device__ __forceinline__ void tile_solve(const double* __restrict__ Ts, const double* __restrict__ Lt,
-                                           const double* __restrict__ dinv, double* __restrict__ pn,
-                                           double (&r)[4][4]) {
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int c = 0; c < 4; ++c) r[a][c] = Ts[(4 * ty + a) * PITCH + 4 * tx + c];
-  // block column kb is solved (X = R W_kb^T) and published by the threads that own it right after THEIR part of
-  // the rank-4 update of step kb - 1, while the other columns are still being updated: one barrier per step
-  auto solve_column = [&](int kb) {
-    double* px = pn + (kb & 1) * kLtBlock;
-    const double* w = dinv + kb * 16;
-    double x[4][4];
-#pragma unroll
-    for (int a = 0; a < 4; ++a)
-#pragma unroll
-      for (int b2 = 0; b2 < 4; ++b2) {
-        double acc = 0.0;
-#pragma unroll
-        for (int c = 0; c <= b2; ++c) acc = fma(r[a][c], w[b2 * 4 + c], acc);
-        x[a][b2] = acc;
-      }
-#pragma unroll
-    for (int a = 0; a < 4; ++a)
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        r[a][c] = x[a][c];
-        px[(a * 4 + c) * 16 + ty] = x[a][c];
-      }
-  };
-  if (tx == 0) solve_column(0);
-  for (int kb = 0; kb < 15; ++kb) {
-    __syncthreads();                          // X(:, kb) published (buffer kb & 1)
-    if (tx > kb) {
-      // r -= X(ty, kb) L(tx, kb)^T
-      const double* px = pn + (kb & 1) * kLtBlock;
-      const double* pl = Lt + kb * kLtBlock;
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        double pa[4], pb[4];
-#pragma unroll
-        for (int a = 0; a < 4; ++a) { pa[a] = px[(a * 4 + c) * 16 + ty]; pb[a] = pl[(a * 4 + c) * 16 + tx]; }
-#pragma unroll
-        for (int a = 0; a < 4; ++a)
-#pragma unroll
-          for (int b2 = 0; b2 < 4; ++b2) r[a][b2] = fma(-pa[a], pb[b2], r[a][b2]);
-      }
-      if (tx == kb + 1) solve_column(kb + 1);  // writes buffer (kb + 1) & 1: nobody reads it before the barrier
-    }
-  }
-}
-
 // ---- panel solve on fp64 tensor cores ------------------------------------------------------------------------
 // X = T L^-T row by row is independent across rows, so every warp solves ITS 8 rows of the tile alone (no block
 // barrier): four 16-column blocks,  R_b = T_b - sum_{p<b} X_p L_bp^T  (m8n8k4 chain of 4 b k-steps),

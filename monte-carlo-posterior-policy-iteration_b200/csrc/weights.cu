@@ -235,6 +235,7 @@ struct SolverState {
   double lo, flo, hi, fhi, x, x_prev;
   int last_side;  // -1 lo replaced, +1 hi replaced
   double hi_cap;
+  double guess;   // where a Gaussian cost distribution would put the root (NaN: none)
   int status;
 };
 
@@ -345,8 +346,44 @@ solve_temperature_kernel(const float* __restrict__ in, int64_t K, int mode, doub
     st.hi_cap = (mode == PPI_TEMP_REPS_KL) ? kAlphaUpper : 1.0737418240e9;  // 2^30
     st.x = user ? 1.0 : (fixed ? hyper : st.lo);
     st.x_prev = -1.0;
+    st.guess = nan("");
     s_alpha = st.x;
     s_done = fixed ? 1 : 0;
+    if (!fixed) {
+      // First trial point from the statistics phase A already holds.  If the normalised costs were Gaussian
+      // with standard deviation sd, the weights exp(-alpha c) would give ESS = n exp(-(alpha sd)^2),
+      // KL(nw || uniform) = (alpha sd)^2 / 2, and the lower bound's derivative would vanish where
+      // u exp(u^2 / 2) = sd sqrt(n) / lambda, u = alpha sd.  Real costs are not Gaussian; the point only has to
+      // land within a small factor of the root, from there every evaluation is a Newton step.  (Starting at 1
+      // and following tangents cost 9 - 28 objective evaluations, tools/solve_iterations.py.)
+      const double mean_c = gsum / n_valid;
+      const double sd = sqrt(fmax(0.0, gsumsq / n_valid - mean_c * mean_c)) * view.scale;
+      if (sd > 0.0 && isfinite(sd)) {
+        if (mode == PPI_TEMP_ESS_TARGET) {
+          if (hyper < n_valid) st.guess = sqrt(log(n_valid / hyper)) / sd;
+        } else if (mode == PPI_TEMP_REPS_KL) {
+          st.guess = sqrt(2.0 * hyper) / sd;
+        } else {
+          const double lr = log(sd) + 0.5 * log(n_valid) - 0.5 * log((1.0 - hyper) / hyper);  // log of the right side
+          double u = lr > 0.5 ? sqrt(2.0 * lr) : exp(fmin(lr, 0.5));
+          for (int it = 0; it < 8; ++it) u = fmax(1e-6, u - (log(u) + 0.5 * u * u - lr) / (1.0 / u + u));
+          st.guess = u / sd;
+        }
+        if (!(st.guess > st.lo && st.guess < st.hi_cap)) st.guess = nan("");
+      }
+      // the value at alpha = 0 is known without a pass over the costs: ESS(0) = n, and the bound's derivative
+      // at 0 is minus the variance of the normalised costs
+      if (mode == PPI_TEMP_ESS_TARGET || mode == PPI_TEMP_LOWER_BOUND) {
+        st.flo = (mode == PPI_TEMP_ESS_TARGET) ? log(hyper) - log(n_valid) : -(sd * sd);
+        if (!(st.flo < 0.0)) {   // already at / beyond the root at the lower end
+          st.x = st.lo; st.phase = 3; st.status = 1; s_done = 1;
+        } else {
+          if (isfinite(st.guess)) st.hi = st.guess;
+          st.phase = 1; st.x = st.hi;
+        }
+        s_alpha = st.x;
+      }
+    }
   }
   __syncthreads();
   // sign convention: work with r(alpha) * dir so that the function is negative at lo
@@ -366,7 +403,8 @@ solve_temperature_kernel(const float* __restrict__ in, int64_t K, int mode, doub
           st.x = st.lo; st.phase = 3; st.status = 1;
         } else {
           // first upper point: the tangent's root when there is one (kept within [1e-3, 4]), else 1
-          if (newton > st.lo && isfinite(newton)) st.hi = fmin(fmin(fmax(newton, 1e-3), 4.0), st.hi_cap);
+          if (isfinite(st.guess)) st.hi = st.guess;
+          else if (newton > st.lo && isfinite(newton)) st.hi = fmin(fmin(fmax(newton, 1e-3), 4.0), st.hi_cap);
           st.phase = 1; st.x = st.hi;
         }
       } else if (st.phase == 1) {
