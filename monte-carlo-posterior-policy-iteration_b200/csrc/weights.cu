@@ -30,6 +30,12 @@ constexpr int kMaxSolveBlocks = 4 * kNumSMs;  // cooperative grid: up to 4 co-re
 constexpr int NP = 8;               // doubles per block partial
 constexpr int kModeUserLogW = 100;  // internal: input holds log-weights, not costs
 constexpr double kAlphaLower = 1e-5, kAlphaUpper = 5e2;  // ppi/algorithms.py:36-37 (REPS only)
+// A proposal that moves the iterate by less than this (relative) ends the solve.  The objective is evaluated with
+// fp32 exponentials, so the residual carries noise of ~1e-9 and the root is defined to ~1e-10 relative: a 1e-11
+// criterion is never met and the solver dithers for 3 - 8 further evaluations before the bracket-width test stops
+// it (CPU emulation of this state machine, round 2).  The step that meets 1e-8 is a Newton / secant step: the
+// iterate it produces is accurate to ~1e-9, four orders inside the 1e-5 parity bound on alpha.
+constexpr double kStepTol = 1e-8;
 
 struct SolveWorkspace {
   unsigned int barrier;
@@ -421,7 +427,7 @@ solve_temperature_kernel(const float* __restrict__ in, int64_t K, int mode, doub
             // there is no slope); a tangent step that no longer moves the iterate is the root
             double nxt = st.hi * 2.0;
             if (newton > st.hi && isfinite(newton)) {
-              if (newton - st.hi <= 1e-11 * st.hi) { st.x = newton; st.phase = 3; }
+              if (newton - st.hi <= kStepTol * st.hi) { st.x = newton; st.phase = 3; }
               nxt = fmin(newton, st.hi * 64.0);
             }
             if (st.phase != 3) { st.hi = fmin(nxt, st.hi_cap); st.x = st.hi; }
@@ -450,7 +456,7 @@ solve_temperature_kernel(const float* __restrict__ in, int64_t K, int mode, doub
           if (!(x > st.lo && x < st.hi)) x = 0.5 * (st.lo + st.hi);
           if (newton > st.lo && newton < st.hi) x = newton;   // tangent from the point just evaluated
           // the iterate has stopped moving: the secant point is the root to fp64 noise level
-          if (fabs(x - st.x_prev) <= 1e-11 * fabs(x)) st.phase = 3;
+          if (fabs(x - st.x_prev) <= kStepTol * fabs(x)) st.phase = 3;
           st.x_prev = x;
           st.x = x;
         }
