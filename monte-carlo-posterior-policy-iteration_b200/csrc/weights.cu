@@ -242,6 +242,7 @@ struct SolverState {
   int last_side;  // -1 lo replaced, +1 hi replaced
   double hi_cap;
   double guess;   // where a Gaussian cost distribution would put the root (NaN: none)
+  int left_steps; // consecutive trial points left of the root while expanding
   int status;
 };
 
@@ -353,6 +354,7 @@ solve_temperature_kernel(const float* __restrict__ in, int64_t K, int mode, doub
     st.x = user ? 1.0 : (fixed ? hyper : st.lo);
     st.x_prev = -1.0;
     st.guess = nan("");
+    st.left_steps = 0;
     s_alpha = st.x;
     s_done = fixed ? 1 : 0;
     if (!fixed) {
@@ -426,9 +428,15 @@ solve_temperature_kernel(const float* __restrict__ in, int64_t K, int mode, doub
             // still left of the root: follow the tangent (at most 64x, at least the old doubling when
             // there is no slope); a tangent step that no longer moves the iterate is the root
             double nxt = st.hi * 2.0;
+            ++st.left_steps;
             if (newton > st.hi && isfinite(newton)) {
               if (newton - st.hi <= kStepTol * st.hi) { st.x = newton; st.phase = 3; }
-              nxt = fmin(newton, st.hi * 64.0);
+              // the bound's derivative approaches its root like -C / alpha^2 when the costs have mass at their
+              // minimum: tangent steps then only multiply alpha by 1.5.  From the second consecutive miss on the
+              // step is doubled each time, until a point right of the root closes the bracket.
+              double step = newton - st.hi;
+              if (mode == PPI_TEMP_LOWER_BOUND && st.left_steps >= 2) step = ldexp(step, min(st.left_steps - 1, 6));
+              nxt = fmin(st.hi + step, st.hi * 64.0);
             }
             if (st.phase != 3) { st.hi = fmin(nxt, st.hi_cap); st.x = st.hi; }
           }

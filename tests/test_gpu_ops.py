@@ -545,3 +545,33 @@ def test_finalize_gaussian(ops):
     assert nerr(host(sigma), 0.5 * (cov + cov.T)) < 1e-6
     _, sigma = ops.finalize_gaussian(cov=covd, diagonal_only=True, want_mu=False)
     assert nerr(host(sigma), np.diag(np.diag(cov))) < 1e-7
+
+
+@pytest.mark.parametrize("K", [1024, 4096, 65536, 1 << 20])
+def test_temperature_solver_evaluation_count(ops, record, K):
+    """The 1-D solve is the latency of the small-matrix workloads (one objective evaluation = one pass over the
+    costs + a grid-wide reduction): with the first trial point taken from the cost statistics and a stopping step
+    matched to the fp32-exp noise floor it needs a handful of evaluations (it was 9 - 28), on bell-shaped and on
+    skewed cost distributions alike, and still lands on the oracle's root."""
+    from ppi_b200 import _lib
+
+    rng = np.random.default_rng(K)
+    shapes = {"normal": rng.normal(2.0e4, 135.0, K), "gamma": rng.gamma(2.0, 5.0, K),
+              "uniform": rng.random(K), "lognormal": np.exp(rng.normal(0.0, 1.0, K))}
+    worst = {}
+    for name, c in shapes.items():
+        c = np.asarray(c, np.float32).astype(np.float64)
+        for mode, hyper, tag in ((_lib.TEMP_ESS_TARGET, max(K // 64, 4), "ess"), (_lib.TEMP_LOWER_BOUND, 0.9, "lbps"),
+                                 (_lib.TEMP_REPS_KL, 0.5, "reps")):
+            nw, lw, st = ops.solve_temperature(c, mode, hyper)
+            assert st.status == 0, (name, tag, st.status)
+            worst[f"{tag}_{name}"] = st.iterations
+            # bell-shaped costs (sums over many dimensions / time steps: every configured workload) start next to
+            # the root; distributions with mass AT the minimum put the root at ~n^(1/3) instead of ~sqrt(log n) and
+            # are reached by tangent steps from the left (13 evaluations at worst here, 28 before)
+            assert st.iterations <= (8 if name == "normal" else 16), (name, tag, st.iterations)
+            if tag == "ess":
+                assert abs(st.ess - hyper) < TOL * hyper
+                _, alpha = O.essps_log_w(c, hyper)
+                assert abs(st.alpha - alpha) < TOL * alpha
+    record(f"solver_evaluations[{K}]", **worst)
